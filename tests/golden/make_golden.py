@@ -1,0 +1,391 @@
+"""Generate golden fixtures by running the REFERENCE itself (``/root/reference``).
+
+Run in the build container only (the GPU box has no ``/root/reference``):
+
+    python tests/golden/make_golden.py
+
+The reference hard-imports ``gymnasium``, ``h5py``, ``pettingzoo`` and ``jsonargparse``,
+none of which does arithmetic on the hot path and none of which is installed here; they
+are replaced by attribute-only stub modules.  Everything written below is
+an OUTPUT of reference code: ``BasePolicy.compute_episodic_return``,
+``BasePolicy.compute_nstep_return``, ``ReplayBuffer`` / ``VectorReplayBuffer`` /
+``ReplayBufferManager`` ``prev/next/unfinished_index/sample_indices``, ``SegmentTree`` and
+``PrioritizedVectorReplayBuffer``.  Versions are recorded in ``versions.json``.
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+import types
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF = os.environ.get("TS_REFERENCE", "/root/reference")
+
+
+def import_reference():
+    class _Any:
+        def __init__(self, *a, **k):
+            pass
+
+        def __getattr__(self, k):
+            return _Any()
+
+        def __call__(self, *a, **k):
+            return _Any()
+
+    def stub(name, **attrs):
+        m = types.ModuleType(name)
+        m.__dict__.update(attrs)
+
+        def _getattr(k):
+            if k == "__version__":
+                return "99.0.0"
+            if k.startswith("__"):
+                raise AttributeError(k)
+            return type(k, (_Any,), {})
+
+        m.__getattr__ = _getattr  # type: ignore
+        sys.modules[name] = m
+        return m
+
+    for name in [
+        "gymnasium", "gymnasium.spaces", "h5py", "pettingzoo", "pettingzoo.utils",
+        "pettingzoo.utils.env", "pettingzoo.utils.wrappers", "jsonargparse",
+    ]:
+        if name not in sys.modules:
+            stub(name)
+    sys.modules["gymnasium"].spaces = sys.modules["gymnasium.spaces"]
+    sys.path.insert(0, REF)
+    import torch  # noqa: F401  (before the stubs are consulted by anything else)
+    import tianshou  # noqa
+
+    return tianshou
+
+
+def fill_vecbuf(buf, Batch, rng, steps, n_env, p_term, p_trunc, ragged=False):
+    """Drive ``buf.add`` like the Collector does (collector.py:324)."""
+    for _ in range(steps):
+        ids = np.arange(n_env)
+        if ragged:
+            ids = ids[rng.random(n_env) < 0.7]
+            if ids.size == 0:
+                continue
+        m = ids.size
+        term = rng.random(m) < p_term
+        trunc = (rng.random(m) < p_trunc) & ~term
+        batch = Batch(
+            obs=rng.standard_normal((m, 3)).astype(np.float32),
+            act=rng.integers(0, 4, m),
+            rew=rng.standard_normal(m),
+            terminated=term,
+            truncated=trunc,
+            obs_next=rng.standard_normal((m, 3)).astype(np.float32),
+            info={},
+        )
+        buf.add(batch, buffer_ids=ids)
+
+
+def gen_gae(ts, out):
+    from tianshou.data import Batch, VectorReplayBuffer
+    from tianshou.policy import BasePolicy
+
+    cases = {}
+    specs = [
+        # name, n_env, steps, capacity_per_env, gamma, lam, p_term, p_trunc, ragged
+        ("small", 4, 37, 64, 0.99, 0.95, 0.1, 0.05, False),
+        ("wrap", 3, 150, 100, 0.99, 0.95, 0.05, 0.02, False),  # ring wrapped around
+        ("ragged", 5, 60, 80, 0.9, 0.8, 0.1, 0.05, True),
+        ("long4096", 2, 4096, 4096, 0.99, 0.95, 1 / 500, 1 / 2000, False),
+        ("mc4096", 2, 4096, 4096, 1.0, 1.0, 1 / 1000, 0.0, False),  # gamma=lambda=1 stress
+        ("noend", 2, 512, 512, 0.99, 0.95, 0.0, 0.0, False),
+    ]
+    for i, (name, n_env, steps, cap, gamma, lam, pt, ptr, ragged) in enumerate(specs):
+        rng = np.random.default_rng(100 + i)
+        buf = VectorReplayBuffer(cap * n_env, n_env)
+        fill_vecbuf(buf, Batch, rng, steps, n_env, pt, ptr, ragged)
+        batch, indices = buf.sample(0)
+        n = len(indices)
+        v_s = rng.standard_normal(n).astype(np.float32)
+        v_s_ = rng.standard_normal(n).astype(np.float32)
+        ret, adv = BasePolicy.compute_episodic_return(
+            batch, buf, indices, v_s_=v_s_.copy(), v_s=v_s.copy(), gamma=gamma, gae_lambda=lam
+        )
+        cases[name] = dict(
+            n_env=n_env, cap=cap, gamma=gamma, lam=lam,
+            buf_rew=buf.rew.copy(), buf_terminated=buf.terminated.copy(),
+            buf_truncated=buf.truncated.copy(), buf_done=buf.done.copy(),
+            last_index=buf.last_index.copy(), lengths=buf._lengths.copy(),
+            ring_index=np.array([b._index for b in buf.buffers]),
+            indices=indices, unfinished=buf.unfinished_index(),
+            v_s=v_s, v_s_=v_s_, returns=ret, adv=adv,
+        )
+        # v_s=None -> np.roll branch (policy/base.py:377); only for one small case
+        if name == "small":
+            ret2, adv2 = BasePolicy.compute_episodic_return(
+                batch, buf, indices, v_s_=v_s_.copy(), v_s=None, gamma=gamma, gae_lambda=lam
+            )
+            cases[name].update(returns_roll=ret2, adv_roll=adv2)
+            # v_s_=None requires lambda == 1 (:371-373), as PGPolicy does (pg.py:108-112)
+            ret3, adv3 = BasePolicy.compute_episodic_return(
+                batch, buf, indices, v_s_=None, v_s=None, gamma=gamma, gae_lambda=1.0
+            )
+            cases[name].update(returns_mc=ret3, adv_mc=adv3)
+    flat = {f"{c}/{k}": np.asarray(v) for c, d in cases.items() for k, v in d.items()}
+    np.savez_compressed(os.path.join(out, "gae.npz"), **flat)
+
+
+def gen_index(ts, out):
+    from tianshou.data import Batch, ReplayBuffer, ReplayBufferManager, VectorReplayBuffer
+
+    flat = {}
+    # equal sub-buffers, several fill levels incl. wrap-around and empty sub-buffers
+    specs = [("v_partial", 4, 20, 11, True), ("v_wrap", 4, 20, 57, False),
+             ("v_big", 16, 1024, 700, True), ("v_one", 1, 16, 40, False)]
+    for i, (name, n_env, total, steps, ragged) in enumerate(specs):
+        rng = np.random.default_rng(200 + i)
+        buf = VectorReplayBuffer(total, n_env)
+        fill_vecbuf(buf, Batch, rng, steps, n_env, 0.15, 0.05, ragged)
+        q = np.concatenate([np.arange(-3, buf.maxsize + 3), rng.integers(0, buf.maxsize, 64)])
+        flat.update({
+            f"{name}/offset": buf._extend_offset, f"{name}/done": buf.done,
+            f"{name}/last_index": buf.last_index, f"{name}/lengths": buf._lengths,
+            f"{name}/query": q, f"{name}/prev": buf.prev(q), f"{name}/next": buf.next(q),
+            f"{name}/unfinished": buf.unfinished_index(),
+            f"{name}/all_indices": buf.sample_indices(0),
+            f"{name}/ring_index": np.array([b._index for b in buf.buffers]),
+        })
+    # unequal sub-buffers (plain ReplayBufferManager)
+    rng = np.random.default_rng(250)
+    buf = ReplayBufferManager([ReplayBuffer(5), ReplayBuffer(9), ReplayBuffer(3), ReplayBuffer(16)])
+    fill_vecbuf(buf, Batch, rng, 12, 4, 0.2, 0.1, True)
+    q = np.arange(-2, buf.maxsize + 2)
+    flat.update({
+        "m_unequal/offset": buf._extend_offset, "m_unequal/done": buf.done,
+        "m_unequal/last_index": buf.last_index, "m_unequal/lengths": buf._lengths,
+        "m_unequal/query": q, "m_unequal/prev": buf.prev(q), "m_unequal/next": buf.next(q),
+        "m_unequal/unfinished": buf.unfinished_index(),
+        "m_unequal/all_indices": buf.sample_indices(0),
+        "m_unequal/ring_index": np.array([b._index for b in buf.buffers]),
+    })
+    # single ring, partially filled then wrapped
+    for name, size, steps in [("s_partial", 16, 9), ("s_wrap", 16, 41)]:
+        rng = np.random.default_rng(260 + steps)
+        buf = ReplayBuffer(size)
+        for _ in range(steps):
+            term = rng.random() < 0.2
+            buf.add(Batch(obs=np.zeros(2), act=0, rew=rng.standard_normal(), terminated=term,
+                          truncated=(not term) and rng.random() < 0.1, obs_next=np.zeros(2),
+                          info={}))
+        q = np.arange(len(buf))
+        flat.update({
+            f"{name}/done": buf.done, f"{name}/last_index": buf.last_index,
+            f"{name}/size": np.array(len(buf)), f"{name}/ring_index": np.array(buf._index),
+            f"{name}/query": q, f"{name}/prev": buf.prev(q), f"{name}/next": buf.next(q),
+            f"{name}/unfinished": buf.unfinished_index(),
+            f"{name}/all_indices": buf.sample_indices(0),
+        })
+    np.savez_compressed(os.path.join(out, "index.npz"), **flat)
+
+
+def gen_nstep(ts, out):
+    import torch
+    from tianshou.data import Batch, VectorReplayBuffer
+    from tianshou.policy import BasePolicy
+
+    flat = {}
+    specs = [("n1", 4, 64, 40, 1, 1), ("n3", 4, 64, 100, 3, 1), ("n3_d51", 4, 64, 100, 3, 51),
+             ("n10", 8, 256, 300, 10, 1), ("n5_partial", 6, 600, 37, 5, 3)]
+    for i, (name, n_env, total, steps, n_step, D) in enumerate(specs):
+        rng = np.random.default_rng(300 + i)
+        buf = VectorReplayBuffer(total, n_env)
+        fill_vecbuf(buf, Batch, rng, steps, n_env, 0.1, 0.05, name == "n5_partial")
+        table = rng.standard_normal((buf.maxsize, D)).astype(np.float32)
+
+        def target_q_fn(buffer, indices, table=table, D=D):
+            t = torch.from_numpy(table[indices])
+            return t if D > 1 else t.flatten()
+
+        indice = buf.sample_indices(0)
+        indice = np.concatenate([indice, rng.choice(indice, 50)])
+        batch = Batch()
+        out_b = BasePolicy.compute_nstep_return(batch, buf, indice, target_q_fn, gamma=0.97,
+                                                n_step=n_step)
+        flat.update({
+            f"{name}/n_env": np.array(n_env), f"{name}/n_step": np.array(n_step),
+            f"{name}/gamma": np.array(0.97), f"{name}/table": table,
+            f"{name}/rew": buf.rew, f"{name}/done": buf.done,
+            f"{name}/terminated": buf.terminated, f"{name}/truncated": buf.truncated,
+            f"{name}/offset": buf._extend_offset, f"{name}/last_index": buf.last_index,
+            f"{name}/lengths": buf._lengths, f"{name}/unfinished": buf.unfinished_index(),
+            f"{name}/ring_index": np.array([b._index for b in buf.buffers]),
+            f"{name}/indice": indice, f"{name}/returns": out_b.returns.numpy(),
+        })
+    np.savez_compressed(os.path.join(out, "nstep.npz"), **flat)
+
+
+def gen_segtree(ts, out):
+    from tianshou.data import SegmentTree
+
+    flat = {}
+    for name, size, rounds, bsz in [("t8", 8, 30, 4), ("t100", 100, 40, 16),
+                                    ("t16384", 16384, 20, 256), ("t5000", 5000, 10, 1024)]:
+        rng = np.random.default_rng(400 + size)
+        tree = SegmentTree(size)
+        idx_log, val_log = [], []
+        for r in range(rounds):
+            idx = rng.integers(0, size, bsz)
+            if r % 3 == 0:  # force duplicates: last occurrence must win
+                idx[bsz // 2:] = idx[: bsz - bsz // 2]
+            val = rng.random(bsz) if r % 2 == 0 else rng.random(bsz).astype(np.float32)
+            tree[idx] = val
+            idx_log.append(idx)
+            val_log.append(val.astype(np.float64))
+        total = tree.reduce()
+        u = rng.random(512)
+        scalar = u * total
+        pidx = tree.get_prefix_sum_idx(scalar.copy())
+        scalar32 = (u * total * 0.999).astype(np.float32)
+        mutated32 = scalar32.copy()
+        pidx32 = tree.get_prefix_sum_idx(mutated32)
+        mutated = scalar.copy()
+        tree.get_prefix_sum_idx(mutated)
+        se = np.sort(rng.integers(0, size + 1, (64, 2)), axis=1)
+        se = se[se[:, 0] < se[:, 1]]
+        red = np.array([tree.reduce(int(s), int(e)) for s, e in se])
+        flat.update({
+            f"{name}/size": np.array(size), f"{name}/idx_log": np.stack(idx_log),
+            f"{name}/val_log": np.stack(val_log), f"{name}/tree": tree._value.copy(),
+            f"{name}/scalar": scalar, f"{name}/prefix_idx": pidx, f"{name}/scalar_after": mutated,
+            f"{name}/scalar32": scalar32, f"{name}/prefix_idx32": pidx32,
+            f"{name}/scalar32_after": mutated32,
+            f"{name}/reduce_se": se, f"{name}/reduce": red,
+            f"{name}/reduce_neg_end": np.array(tree.reduce(1, -1)),
+        })
+    np.savez_compressed(os.path.join(out, "segtree.npz"), **flat)
+
+
+def gen_per(ts, out):
+    from tianshou.data import Batch, PrioritizedReplayBuffer, PrioritizedVectorReplayBuffer
+
+    flat = {}
+    for name, n_env, total, steps, bsz, wn in [("pv", 4, 256, 90, 32, True),
+                                                ("pv_nonorm", 8, 4096, 600, 256, False)]:
+        rng = np.random.default_rng(500 + n_env)
+        buf = PrioritizedVectorReplayBuffer(total, n_env, alpha=0.6, beta=0.4, weight_norm=wn)
+        fill_vecbuf(buf, Batch, rng, steps, n_env, 0.1, 0.05, False)
+        flat[f"{name}/tree_after_add"] = buf.weight._value.copy()
+        trees, idxs, weights, tds, us, mx, mn = [], [], [], [], [], [], []
+        for it in range(6):
+            np.random.seed(1000 + it)
+            u = np.random.rand(bsz)
+            np.random.seed(1000 + it)
+            idx = buf.sample_indices(bsz)
+            w = buf[idx].weight
+            td = rng.standard_normal(bsz).astype(np.float32)
+            if it % 2 == 0:
+                idx[-4:] = idx[:4]  # duplicates inside update_weight
+            buf.update_weight(idx, td)
+            us.append(u); idxs.append(idx.copy()); weights.append(np.asarray(w)); tds.append(td)
+            trees.append(buf.weight._value.copy())
+            mx.append(float(buf._max_prio)); mn.append(float(buf._min_prio))
+        flat.update({
+            f"{name}/size": np.array(buf.maxsize), f"{name}/n_env": np.array(n_env),
+            f"{name}/u": np.stack(us), f"{name}/idx": np.stack(idxs),
+            f"{name}/weight": np.stack(weights), f"{name}/td": np.stack(tds),
+            f"{name}/tree": np.stack(trees), f"{name}/max_prio": np.array(mx),
+            f"{name}/min_prio": np.array(mn), f"{name}/lengths": buf._lengths,
+        })
+    # single prioritized ring: test_priortized_replaybuffer-style (test_buffer.py:256-302)
+    rng = np.random.default_rng(550)
+    buf = PrioritizedReplayBuffer(50, 0.5, 0.5)
+    for i in range(70):
+        buf.add(Batch(obs=np.zeros(2), act=0, rew=1.0, terminated=i % 7 == 6, truncated=False,
+                      obs_next=np.zeros(2), info={}))
+    idx = rng.integers(0, 50, 20)
+    td = rng.standard_normal(20)
+    buf.update_weight(idx, td)
+    flat.update({"single/idx": idx, "single/td": td, "single/tree": buf.weight._value.copy(),
+                 "single/max_prio": np.array(buf._max_prio),
+                 "single/min_prio": np.array(buf._min_prio),
+                 "single/weight_all": buf.get_weight(np.arange(50))})
+    np.savez_compressed(os.path.join(out, "per.npz"), **flat)
+
+
+def gen_ppo(ts, out):
+    """Loss values and gradients of the reference expressions at ppo.py:109-144 evaluated
+    by torch autograd in f64 on CPU (the reference pins no loss value in its tests)."""
+    import torch
+
+    flat = {}
+    rng = np.random.default_rng(600)
+    n = 1000
+    base = dict(
+        logp_old=rng.normal(-8, 0.3, n), adv=rng.standard_normal(n) * 3 + 0.5,
+        returns=rng.standard_normal(n) * 2, v_s=rng.standard_normal(n),
+    )
+    base["logp"] = base["logp_old"] + rng.normal(0, 0.25, n)
+    base["value"] = base["v_s"] + rng.normal(0, 0.3, n)
+    for k, v in base.items():
+        flat[f"in/{k}"] = v.astype(np.float32)
+    variants = [("plain", False, False, None), ("norm", True, False, None),
+                ("vclip", False, True, None), ("norm_vclip", True, True, None),
+                ("dual", True, True, 5.0), ("dual_nonorm", False, False, 1.5)]
+    eps_clip, eps = 0.2, 1e-8
+    for name, norm_adv, value_clip, dual_clip in variants:
+        t = {k: torch.tensor(v.astype(np.float32).astype(np.float64)) for k, v in base.items()}
+        logp = t["logp"].clone().requires_grad_(True)
+        value = t["value"].clone().requires_grad_(True)
+        adv = t["adv"]
+        if norm_adv:
+            mean, std = adv.mean(), adv.std()
+            adv = (adv - mean) / (std + eps)
+        ratio = (logp - t["logp_old"]).exp()
+        surr1 = ratio * adv
+        surr2 = ratio.clamp(1.0 - eps_clip, 1.0 + eps_clip) * adv
+        if dual_clip:
+            clip1 = torch.min(surr1, surr2)
+            clip2 = torch.max(clip1, dual_clip * adv)
+            clip_loss = -torch.where(adv < 0, clip2, clip1).mean()
+        else:
+            clip_loss = -torch.min(surr1, surr2).mean()
+        if value_clip:
+            v_clip = t["v_s"] + (value - t["v_s"]).clamp(-eps_clip, eps_clip)
+            vf1 = (t["returns"] - value).pow(2)
+            vf2 = (t["returns"] - v_clip).pow(2)
+            vf_loss = torch.max(vf1, vf2).mean()
+        else:
+            vf_loss = (t["returns"] - value).pow(2).mean()
+        (clip_loss + 0.5 * vf_loss).backward()
+        flat.update({
+            f"{name}/cfg": np.array([float(norm_adv), float(value_clip), dual_clip or 0.0,
+                                     eps_clip, 0.5]),
+            f"{name}/clip_loss": clip_loss.detach().numpy(),
+            f"{name}/vf_loss": vf_loss.detach().numpy(),
+            f"{name}/dlogp": logp.grad.numpy(), f"{name}/dvalue": value.grad.numpy(),
+            f"{name}/adv_used": adv.numpy(),
+        })
+    np.savez_compressed(os.path.join(out, "ppo.npz"), **flat)
+
+
+def main():
+    ts = import_reference()
+    import numba
+
+    gen_gae(ts, HERE)
+    gen_index(ts, HERE)
+    gen_nstep(ts, HERE)
+    gen_segtree(ts, HERE)
+    gen_per(ts, HERE)
+    gen_ppo(ts, HERE)
+    with open(os.path.join(HERE, "versions.json"), "w") as f:
+        json.dump({"tianshou": ts.__version__, "numpy": np.__version__,
+                   "numba": numba.__version__, "reference": REF}, f, indent=1)
+    for fn in sorted(os.listdir(HERE)):
+        print(fn, os.path.getsize(os.path.join(HERE, fn)))
+
+
+if __name__ == "__main__":
+    main()
