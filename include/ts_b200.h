@@ -1,0 +1,233 @@
+/*
+ * ts_b200.h -- C-ABI of the B200 (sm_100a) return / replay hot path.
+ *
+ * The reference (aai-institute/tianshou-fork, Tianshou 0.5.1) has no FFI layer on this
+ * path: its boundary is plain Python (tianshou/data/__init__.py:4-41 and the static methods
+ * of tianshou/policy/base.py:BasePolicy).  The compiled code it calls is five numba @njit
+ * functions; each entry point below replaces one of them (or one NumPy expression around
+ * them) and cites it.  The Python host package `tianshou_fork_b200` binds these symbols with
+ * ctypes and mirrors the reference classes; INTEGRATION.md shows the stub a reference
+ * maintainer would add.
+ *
+ * Conventions
+ *   - Plain pointers and sizes only; no torch / C++ types.  All data pointers are DEVICE
+ *     pointers owned by the caller and valid for the stream-ordered duration of the call.
+ *   - Every entry point enqueues work on `stream` (a cudaStream_t passed as void*) and
+ *     returns immediately: it never allocates, never synchronises and never reads device
+ *     memory on the host, so all of them are legal inside CUDA-graph capture.
+ *   - Return value: TS_OK or a negative TS_ERR_* code.  ts_last_cuda_error() gives the
+ *     cudaError_t behind the most recent TS_ERR_CUDA on the calling thread.
+ *   - Range contracts that the reference enforces with `assert` on host arrays
+ *     (segtree.py:53, :79) are evaluated on the device into a caller-provided int32
+ *     `err_flag` word (bit mask TS_FLAG_*) which the host shim checks lazily.
+ *   - Stateless and re-entrant; ordering is the stream's.
+ *   - Booleans are uint8 (numpy bool_ / torch.bool layout).  Indices are int64.
+ */
+#ifndef TS_B200_H_
+#define TS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TS_B200_VERSION 100 /* major*1000 + minor*100 + patch */
+
+#define TS_OK 0
+#define TS_ERR_BAD_ARG (-1)   /* null pointer, negative size, unsupported dtype code */
+#define TS_ERR_WORKSPACE (-2) /* workspace_bytes smaller than ts_*_workspace_bytes() */
+#define TS_ERR_CUDA (-3)      /* launch failed; see ts_last_cuda_error() */
+#define TS_ERR_ALIGN (-4)     /* pointer not aligned to its element size */
+
+/* dtype codes for the float-typed arguments */
+#define TS_F32 0
+#define TS_F64 1
+
+/* bits of the device-side error flag word */
+#define TS_FLAG_INDEX_RANGE 1  /* SegmentTree.__setitem__: index outside [0, size)   */
+#define TS_FLAG_PREFIX_RANGE 2 /* get_prefix_sum_idx: value outside [0, tree[1])      */
+
+typedef void* ts_stream_t; /* cudaStream_t */
+
+int32_t ts_version(void);
+const char* ts_error_string(int32_t code);
+int32_t ts_last_cuda_error(void);
+
+/* ------------------------------------------------------------------------------------------
+ * GAE / TD(lambda) returns.
+ * Replaces: BasePolicy.compute_episodic_return (tianshou/policy/base.py:337-384) with
+ *           value_mask (:317-335) and the numba kernel _gae_return (:453-497) fused:
+ *   v_s_  <- v_s_ * ~terminated                       (:375-376)
+ *   end   <- terminated | truncated | unfinished-tail (:379-380)
+ *   A_t   <- delta_t + gamma*lambda*(1-end_t) * A_{t+1},  delta_t = rew + gamma*v_s_ - v_s
+ *   ret   <- A + v_s                                  (:382)
+ * Arithmetic is f64 (as the reference's numba path); inputs/outputs are f32 or f64.
+ * ---------------------------------------------------------------------------------------- */
+
+/*
+ * Canonical rollout layout: E independent env streams (VectorReplayBuffer sub-buffers,
+ * vecbuf.py:33-37) of T steps each, row-major.  rew/terminated/truncated rows are
+ * `buf_stride` elements apart (the sub-buffer capacity), v_s/v_s_next/adv/ret rows are
+ * `val_stride` apart.  The last step of every row is an episode boundary: it is either done
+ * or the sub-buffer's unfinished index (manager.py:68-74), so rows never exchange data.
+ * rew_dtype applies to rew, val_dtype to v_s and v_s_next, out_dtype to adv and ret.
+ */
+int32_t ts_gae_rows(const void* rew, const void* v_s, const void* v_s_next,
+                    const uint8_t* terminated, const uint8_t* truncated, int64_t E, int64_t T,
+                    int64_t buf_stride, int64_t val_stride, double gamma, double gae_lambda,
+                    int32_t rew_dtype, int32_t val_dtype, int32_t out_dtype, void* adv,
+                    void* ret, ts_stream_t stream);
+
+/*
+ * General form: one flattened batch of N transitions in the caller's order, exactly the
+ * reference's contract (batch == buffer[indices]); the recurrence runs across the whole
+ * array and is cut only by end flags, as _gae_return does.
+ *   rew, terminated, truncated, v_s, v_s_next : batch order, length N.
+ *   indices (nullable)        : batch position -> buffer index.  When given,
+ *                               buf_terminated[indices[i]] is the value mask (:335) and
+ *                               indices[i] == unfinished[sub(indices[i])] forces end (:380).
+ *   unfinished[B]             : per sub-buffer global index of the unfinished tail or -1
+ *                               (output of ts_unfinished_index).
+ *   offset[B+1], sub_size     : sub-buffer layout (_extend_offset, manager.py:38);
+ *                               sub_size > 0 means equal sub-buffers (k = idx / sub_size).
+ * workspace: ts_gae_flat_workspace_bytes(N) bytes, 16-byte aligned; contents are scratch.
+ */
+size_t ts_gae_flat_workspace_bytes(int64_t N);
+int32_t ts_gae_flat(const void* rew, const void* v_s, const void* v_s_next,
+                    const uint8_t* terminated, const uint8_t* truncated, const int64_t* indices,
+                    const uint8_t* buf_terminated, const int64_t* unfinished,
+                    const int64_t* offset, int64_t B, int64_t sub_size, int64_t N, double gamma,
+                    double gae_lambda, int32_t rew_dtype, int32_t val_dtype, int32_t out_dtype,
+                    void* adv, void* ret, void* workspace, size_t workspace_bytes,
+                    ts_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Episode-aware index arithmetic.
+ * Replaces: numba _prev_index / _next_index (tianshou/data/buffer/manager.py:259-297),
+ *           ReplayBuffer.prev / next (tianshou/data/buffer/base.py:153-168, the B == 1 case
+ *           with lengths[0] == current size) and unfinished_index (base.py:148-151,
+ *           manager.py:68-74).  Integer work: results are bit-exact.
+ *   index[M] any int64 (reduced mod offset[B] first, so -1 maps to the last slot);
+ *   offset[B+1]; done[cap]; last_index[B]; lengths[B]; sub_size as above.
+ * ---------------------------------------------------------------------------------------- */
+int32_t ts_prev_index(const int64_t* index, int64_t M, const int64_t* offset, int64_t B,
+                      int64_t sub_size, const uint8_t* done, const int64_t* last_index,
+                      const int64_t* lengths, int64_t* out, ts_stream_t stream);
+int32_t ts_next_index(const int64_t* index, int64_t M, const int64_t* offset, int64_t B,
+                      int64_t sub_size, const uint8_t* done, const int64_t* last_index,
+                      const int64_t* lengths, int64_t* out, ts_stream_t stream);
+/* out[k] = last_index[k] if lengths[k] > 0 and !done[last_index[k]] else -1 */
+int32_t ts_unfinished_index(const uint8_t* done, const int64_t* last_index,
+                            const int64_t* lengths, int64_t B, int64_t* out,
+                            ts_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * n-step TD target.
+ * Replaces: BasePolicy.compute_nstep_return (tianshou/policy/base.py:386-440) and numba
+ *           _nstep_return (:500-524).  Two launches around the caller's target network:
+ *   chain  : walks buffer.next n_step-1 times (:422-425, fused, no [n,bsz] matrix), with
+ *            end = done | unfinished (:433-434); emits terminal[bsz] (:428), the partial
+ *            discounted reward sum[bsz] (f64) and gamma^k * value_mask(terminal) coef[bsz].
+ *   combine: out[b,d] = target_q[b,d] * coef[b] + sum[b]            (:432, :523)
+ * ---------------------------------------------------------------------------------------- */
+int32_t ts_nstep_chain(const int64_t* indice, int64_t bsz, const void* rew, int32_t rew_dtype,
+                       const uint8_t* done, const uint8_t* terminated, const int64_t* offset,
+                       int64_t B, int64_t sub_size, const int64_t* last_index,
+                       const int64_t* lengths, double gamma, int32_t n_step, int64_t* terminal,
+                       double* ret_sum, double* coef, ts_stream_t stream);
+int32_t ts_nstep_combine(const void* target_q, int32_t q_dtype, int64_t bsz, int64_t D,
+                         const double* ret_sum, const double* coef, void* out,
+                         ts_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Segment tree (f64 binary heap of 2*bound nodes, leaf i at bound+i).
+ * Replaces: numba _setitem / _reduce / _get_prefix_sum_idx
+ *           (tianshou/data/utils/segtree.py:98-137) behind SegmentTree.__setitem__ (:37-54),
+ *           reduce (:56-64) and get_prefix_sum_idx (:66-85).  Every node is the IEEE f64 sum
+ *           left + right (no FMA), so node values are bit-identical to the reference's.
+ * ---------------------------------------------------------------------------------------- */
+
+/* Scratch owned by the tree object, both zero-initialised ONCE by the caller and left
+ * all-zero again by every call: `stamp` is uint32[size] (last-writer-wins arbitration of
+ * duplicated indices, segtree.py:40-49), `counter` is uint32[4] (block arrival counter). */
+/* tree[index[j]] = value[j] for j < M (M < 2^31), then every ancestor recomputed bottom-up.
+ * value is f32 or f64 (cast on store, segtree.py:91-92); value_stride 0 broadcasts value[0].
+ * index outside [0,size) sets TS_FLAG_INDEX_RANGE in *err_flag and that item is skipped. */
+int32_t ts_segtree_update(double* tree, int64_t size, int64_t bound, const int64_t* index,
+                          const void* value, int32_t value_dtype, int64_t value_stride,
+                          int64_t M, uint32_t* stamp, uint32_t* counter, int32_t* err_flag,
+                          ts_stream_t stream);
+/* *out = sum(leaf[start:end]) with the reference's climb order (:107-119); start==0 and
+ * end==size is tree[1] up to that order -- the caller handles the :58-59 fast path. */
+int32_t ts_segtree_reduce(const double* tree, int64_t bound, int64_t start, int64_t end,
+                          double* out, ts_stream_t stream);
+/* Batched prefix-sum descent (:122-137): strict `<`, subtract-on-right, `value` mutated in
+ * place like the reference (:134).  value_dtype f64 or f32.  If scale_by_total != 0 the
+ * query is value[j] * tree[1] (prio.py:61) computed on device in f64 (f64 values only). */
+int32_t ts_segtree_prefix_idx(const double* tree, int64_t bound, void* value,
+                              int32_t value_dtype, int64_t M, int32_t scale_by_total,
+                              int64_t* out, int32_t* err_flag, ts_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Prioritized replay, fused steps.
+ * Replaces: PrioritizedReplayBuffer.sample_indices / get_weight / __getitem__ weight
+ *           normalisation / update_weight (tianshou/data/buffer/prio.py:59-102).
+ * `prio` is double[2] on the device: {max_prio, min_prio} (prio.py:35, :88-89).
+ * ---------------------------------------------------------------------------------------- */
+/* idx = prefix_idx(u * tree[1]); weight = (leaf/min_prio)^(-beta); if weight_norm,
+ * weight /= max(weight) (done by the last CTA to finish, same launch).  u is NOT mutated.
+ * scratch16: 16 bytes, zero-initialised once by the caller, left zero by every call. */
+int32_t ts_per_sample(const double* tree, int64_t bound, const double* u, int64_t M,
+                      const double* prio, double beta, int32_t weight_norm, int64_t* idx,
+                      double* weight, void* scratch16, int32_t* err_flag, ts_stream_t stream);
+/* get_weight on given indices (prio.py:66-76), optional batch-max normalisation (:101). */
+int32_t ts_per_weight(const double* tree, int64_t bound, const int64_t* idx, int64_t M,
+                      const double* prio, double beta, int32_t weight_norm, double* weight,
+                      void* scratch16, ts_stream_t stream);
+/* p = |td| + eps computed in td's dtype (f32 eps, prio.py:38,86); leaf = p^alpha rounded to
+ * td's dtype (:87); tree update as ts_segtree_update; prio <- {max(max,p), min(min,p)}. */
+int32_t ts_per_update(double* tree, int64_t size, int64_t bound, const int64_t* idx,
+                      const void* td, int32_t td_dtype, int64_t M, double alpha, double* prio,
+                      uint32_t* stamp, uint32_t* counter, int32_t* err_flag,
+                      ts_stream_t stream);
+/* init_weight (prio.py:42-43): tree[idx] = max_prio^alpha, max_prio read from the device
+ * scalar; leaf_dtype TS_F32 rounds the power to f32 (the reference's result type once
+ * _max_prio has become an np.float32, prio.py:88). */
+int32_t ts_per_init_weight(double* tree, int64_t size, int64_t bound, const int64_t* idx,
+                           int64_t M, double alpha, const double* prio, int32_t leaf_dtype,
+                           uint32_t* stamp, uint32_t* counter, int32_t* err_flag,
+                           ts_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * PPO clipped-surrogate loss, fused with advantage normalisation.
+ * Replaces: the loss arithmetic of PPOPolicy.learn (tianshou/policy/modelfree/ppo.py:109-139)
+ *           over one minibatch given by `mb_index` (Batch.split, data/batch.py:896-912):
+ *   adv' = (adv - mean) / (std_unbiased + eps)         if norm_adv   (:109-113)
+ *   ratio = exp(logp - logp_old); surr1/surr2; dual clip (:114-128); value (clip) loss (:130-139)
+ * logp[m], value[m] are minibatch-ordered network outputs; logp_old/adv/returns/v_s are
+ * full-batch arrays gathered through mb_index (nullable => identity).
+ * Forward writes out[4] = {clip_loss, vf_loss, adv_mean, adv_std} (f32 on device) and the
+ * gradients dclip/dlogp[m], dvf/dvalue[m] (f32) used by the autograd backward.
+ * workspace: ts_ppo_loss_workspace_bytes(m).
+ * ---------------------------------------------------------------------------------------- */
+size_t ts_ppo_loss_workspace_bytes(int64_t m);
+int32_t ts_ppo_loss(const float* logp, const float* value, const float* logp_old,
+                    const float* adv, const float* returns, const float* v_s,
+                    const int64_t* mb_index, int64_t m, float eps_clip, float dual_clip,
+                    int32_t value_clip, int32_t norm_adv, float eps, float* out,
+                    float* dlogp, float* dvalue, void* workspace, size_t workspace_bytes,
+                    ts_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Row gather (buffer[indices], tianshou/data/buffer/base.py:360-389): out[j,:] =
+ * src[index[j],:] for rows of row_bytes bytes.  Pure byte copy.
+ * ---------------------------------------------------------------------------------------- */
+int32_t ts_gather_rows(const void* src, int64_t n_rows, int64_t row_bytes, const int64_t* index,
+                       int64_t M, void* out, ts_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TS_B200_H_ */

@@ -1,0 +1,66 @@
+"""Shared test helpers: replay of the add-streams that tests/golden/make_golden.py used."""
+import numpy as np
+
+
+def golden_stream(seed, steps, n_env, p_term, p_trunc, ragged=False):
+    """Yields (ids, batch_dict) in exactly the RNG order of make_golden.fill_vecbuf."""
+    rng = np.random.default_rng(seed)
+    return rng, _stream(rng, steps, n_env, p_term, p_trunc, ragged)
+
+
+def _stream(rng, steps, n_env, p_term, p_trunc, ragged):
+    for _ in range(steps):
+        ids = np.arange(n_env)
+        if ragged:
+            ids = ids[rng.random(n_env) < 0.7]
+            if ids.size == 0:
+                continue
+        m = ids.size
+        term = rng.random(m) < p_term
+        trunc = (rng.random(m) < p_trunc) & ~term
+        yield ids, dict(
+            obs=rng.standard_normal((m, 3)).astype(np.float32),
+            act=rng.integers(0, 4, m),
+            rew=rng.standard_normal(m),
+            terminated=term,
+            truncated=trunc,
+            obs_next=rng.standard_normal((m, 3)).astype(np.float32),
+            info={},
+        )
+
+
+def fill(buf, Batch, seed, steps, n_env, p_term, p_trunc, ragged=False):
+    rng, it = golden_stream(seed, steps, n_env, p_term, p_trunc, ragged)
+    for ids, d in it:
+        buf.add(Batch(**d), buffer_ids=ids)
+    return rng
+
+
+GAE_SPECS = [
+    # name, n_env, steps, cap, gamma, lam, p_term, p_trunc, ragged  (make_golden.gen_gae)
+    ("small", 4, 37, 64, 0.99, 0.95, 0.1, 0.05, False),
+    ("wrap", 3, 150, 100, 0.99, 0.95, 0.05, 0.02, False),
+    ("ragged", 5, 60, 80, 0.9, 0.8, 0.1, 0.05, True),
+    ("long4096", 2, 4096, 4096, 0.99, 0.95, 1 / 500, 1 / 2000, False),
+    ("mc4096", 2, 4096, 4096, 1.0, 1.0, 1 / 1000, 0.0, False),
+    ("noend", 2, 512, 512, 0.99, 0.95, 0.0, 0.0, False),
+]
+
+INDEX_SPECS = [("v_partial", 4, 20, 11, True), ("v_wrap", 4, 20, 57, False),
+               ("v_big", 16, 1024, 700, True), ("v_one", 1, 16, 40, False)]
+
+NSTEP_SPECS = [("n1", 4, 64, 40, 1, 1), ("n3", 4, 64, 100, 3, 1), ("n3_d51", 4, 64, 100, 3, 51),
+               ("n10", 8, 256, 300, 10, 1), ("n5_partial", 6, 600, 37, 5, 3)]
+
+
+def c2_rollout(E, T, seed=0, p_term=1 / 200, p_trunc=1 / 1000):
+    """Synthetic rollout of SURVEY.md 8d / BASELINE.json configs[1] (f32 values, bool flags)."""
+    rng = np.random.default_rng(seed)
+    rew = rng.random((E, T), dtype=np.float32)
+    v_s = rng.standard_normal((E, T), dtype=np.float32)
+    v_next = np.empty_like(v_s)
+    v_next[:, :-1] = v_s[:, 1:]
+    v_next[:, -1] = rng.standard_normal(E, dtype=np.float32)
+    term = rng.random((E, T)) < p_term
+    trunc = (rng.random((E, T)) < p_trunc) & ~term
+    return rew, v_s, v_next, term, trunc

@@ -1,0 +1,196 @@
+"""GAE parity on the GPU: CUDA path (through the C-ABI) vs the CPU oracle and the golden
+fixtures produced by the reference.  Tolerance: 1e-5 relative (BASELINE.json north_star);
+the f64-output path is additionally held to 1e-9."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+from helpers import GAE_SPECS, c2_rollout, fill
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5  # north_star: "within 1e-5 relative for trajectories up to 4096 steps"
+
+
+def _close(a, b, rtol=RTOL, scale=None):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    scale = np.abs(b).max() if scale is None else scale
+    # relative to each element, with an absolute floor tied to the array's magnitude: an
+    # advantage that cancels to ~0 cannot carry 1e-5 relative accuracy from f32 inputs
+    return np.all(np.abs(a - b) <= rtol * np.abs(b) + rtol * 1e-2 * scale)
+
+
+@pytest.mark.parametrize("spec", GAE_SPECS, ids=[s[0] for s in GAE_SPECS])
+def test_golden_gae_through_buffer(spec):
+    """make_golden.gen_gae replayed through the device VectorReplayBuffer + drop-in API."""
+    import tianshou_fork_b200 as ts
+    name, n_env, steps, cap, gamma, lam, pt, ptr, ragged = spec
+    c = load_golden("gae")[name]
+    buf = ts.VectorReplayBuffer(cap * n_env, n_env)
+    fill(buf, ts.Batch, 100 + GAE_SPECS.index(spec), steps, n_env, pt, ptr, ragged)
+    # bookkeeping and stored flags are integer/byte work: bit-exact
+    assert np.array_equal(buf.done.cpu().numpy(), c["buf_done"])
+    assert np.array_equal(buf.last_index, c["last_index"])
+    assert np.array_equal(buf._lengths, c["lengths"])
+    assert np.array_equal(buf.unfinished_index(), c["unfinished"])
+    batch, indices = buf.sample(0)
+    assert np.array_equal(indices.cpu().numpy(), c["indices"])
+    assert np.array_equal(batch.rew.cpu().numpy(), c["buf_rew"][c["indices"]])
+    # NumPy in -> NumPy f64 out, like the reference
+    ret, adv = ts.BasePolicy.compute_episodic_return(
+        batch, buf, indices, v_s_=c["v_s_"].copy(), v_s=c["v_s"].copy(), gamma=gamma,
+        gae_lambda=lam)
+    assert isinstance(ret, np.ndarray) and ret.dtype == np.float64
+    assert _close(adv, c["adv"], 1e-9) and _close(ret, c["returns"], 1e-9), name
+    # tensor in -> f32 tensor out, no host round trip
+    dev = buf.device
+    ret32, adv32 = ts.BasePolicy.compute_episodic_return(
+        batch, buf, indices, v_s_=torch.from_numpy(c["v_s_"]).to(dev),
+        v_s=torch.from_numpy(c["v_s"]).to(dev), gamma=gamma, gae_lambda=lam)
+    assert ret32.is_cuda and ret32.dtype == torch.float32
+    assert _close(adv32.cpu().numpy(), c["adv"]) and _close(ret32.cpu().numpy(), c["returns"])
+    if name == "small":
+        r2, a2 = ts.BasePolicy.compute_episodic_return(
+            batch, buf, indices, v_s_=c["v_s_"].copy(), v_s=None, gamma=gamma, gae_lambda=lam)
+        assert _close(r2, c["returns_roll"], 1e-9) and _close(a2, c["adv_roll"], 1e-9)
+        r3, a3 = ts.BasePolicy.compute_episodic_return(
+            ts.Batch(rew=batch.rew.cpu().numpy(), terminated=batch.terminated.cpu().numpy(),
+                     truncated=batch.truncated.cpu().numpy()),
+            buf, indices.cpu().numpy(), v_s_=None, v_s=None, gamma=gamma, gae_lambda=1.0)
+        assert _close(r3, c["returns_mc"], 1e-9) and _close(a3, c["adv_mc"], 1e-9)
+
+
+def test_canonical_rows_path_is_taken_and_matches_flat():
+    """sample(0) of an un-wrapped buffer goes through ts_gae_rows; same numbers as ts_gae_flat."""
+    import tianshou_fork_b200 as ts
+    name, n_env, steps, cap, gamma, lam, pt, ptr, ragged = GAE_SPECS[3]  # long4096
+    c = load_golden("gae")[name]
+    buf = ts.VectorReplayBuffer(cap * n_env, n_env)
+    fill(buf, ts.Batch, 103, steps, n_env, pt, ptr, ragged)
+    batch, indices = buf.sample(0)
+    assert buf.is_canonical(indices) == (n_env, steps)
+    dev = buf.device
+    vs, vn = torch.from_numpy(c["v_s"]).to(dev), torch.from_numpy(c["v_s_"]).to(dev)
+    r_rows, a_rows = ts.BasePolicy.compute_episodic_return(
+        batch, buf, indices, vn, vs, gamma, lam, out_dtype=torch.float64)
+    r_flat, a_flat = ts.BasePolicy.compute_episodic_return(
+        batch, buf, indices.clone(), vn, vs, gamma, lam, out_dtype=torch.float64)
+    assert buf.is_canonical(indices.clone()) is None
+    assert _close(a_rows.cpu().numpy(), c["adv"], 1e-9)
+    assert _close(a_flat.cpu().numpy(), c["adv"], 1e-9)
+    assert _close(r_rows.cpu().numpy(), r_flat.cpu().numpy(), 1e-12)
+
+
+@pytest.mark.parametrize("E,T", [(1, 1), (3, 7), (5, 8), (4, 33), (7, 255), (2, 256), (3, 257),
+                                 (6, 1000), (2, 2048), (3, 2049), (2, 4096), (1, 10000),
+                                 (64, 2048), (300, 128)])
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_rows_kernel_vs_oracle(E, T, dt):
+    """ts_gae_rows through the raw C-ABI on ragged / unaligned / multi-chunk shapes."""
+    from tianshou_fork_b200 import _lib as L
+    rew, v_s, v_next, term, trunc = c2_rollout(E, T, seed=E * 131 + T, p_term=1 / 50,
+                                               p_trunc=1 / 100)
+    ref_ret, ref_adv = orc.episodic_return_rows(rew, v_s, v_next, term, trunc, 0.99, 0.95)
+    tdt = torch.float32 if dt == "f32" else torch.float64
+    d = lambda a, t=None: torch.from_numpy(a).cuda().to(t) if t else torch.from_numpy(a).cuda()
+    g_rew, g_vs, g_vn = d(rew, tdt), d(v_s, tdt), d(v_next, tdt)
+    g_term, g_trunc = d(term.view(np.uint8)), d(trunc.view(np.uint8))
+    adv = torch.empty(E, T, dtype=tdt, device="cuda")
+    ret = torch.empty(E, T, dtype=tdt, device="cuda")
+    code = L.dtype_code(g_rew)
+    L.check(L.lib().ts_gae_rows(L.ptr(g_rew), L.ptr(g_vs), L.ptr(g_vn), L.ptr(g_term),
+                                L.ptr(g_trunc), E, T, T, T, 0.99, 0.95, code, code, code,
+                                L.ptr(adv), L.ptr(ret), L.stream()), "ts_gae_rows")
+    tol = RTOL if dt == "f32" else 1e-9
+    assert _close(adv.cpu().numpy(), ref_adv, tol)
+    assert _close(ret.cpu().numpy(), ref_ret, tol)
+
+
+def test_rows_kernel_strided_buffer_rows():
+    """rew/flags rows `buf_stride` apart (sub-buffer capacity), values `val_stride` apart."""
+    from tianshou_fork_b200 import _lib as L
+    E, T, cap = 9, 100, 160
+    rew, v_s, v_next, term, trunc = c2_rollout(E, T, seed=5, p_term=1 / 20)
+    ref_ret, ref_adv = orc.episodic_return_rows(rew, v_s, v_next, term, trunc, 0.97, 0.9)
+    pad = lambda a: np.concatenate([a, np.full((E, cap - T), 7, a.dtype)], axis=1)
+    g_rew = torch.from_numpy(pad(rew)).cuda()
+    g_term = torch.from_numpy(pad(term.view(np.uint8))).cuda()
+    g_trunc = torch.from_numpy(pad(trunc.view(np.uint8))).cuda()
+    g_vs, g_vn = torch.from_numpy(v_s).cuda(), torch.from_numpy(v_next).cuda()
+    adv = torch.empty(E, T, device="cuda")
+    ret = torch.empty(E, T, device="cuda")
+    L.check(L.lib().ts_gae_rows(L.ptr(g_rew), L.ptr(g_vs), L.ptr(g_vn), L.ptr(g_term),
+                                L.ptr(g_trunc), E, T, cap, T, 0.97, 0.9, 0, 0, 0, L.ptr(adv),
+                                L.ptr(ret), L.stream()), "ts_gae_rows")
+    assert _close(adv.cpu().numpy(), ref_adv) and _close(ret.cpu().numpy(), ref_ret)
+
+
+@pytest.mark.parametrize("N,p_end", [(1, 0.5), (2047, 0.01), (2048, 0.0), (2049, 0.001),
+                                     (100_000, 0.0), (300_001, 0.0005), (1_000_000, 0.005)])
+def test_flat_kernel_lookback_vs_oracle(N, p_end):
+    """ts_gae_flat: one long sequence; p_end = 0 makes every tile wait on its successor."""
+    from tianshou_fork_b200 import _lib as L
+    rng = np.random.default_rng(N)
+    rew = rng.standard_normal(N)
+    v_s = rng.standard_normal(N).astype(np.float32)
+    v_n = rng.standard_normal(N).astype(np.float32)
+    term = rng.random(N) < p_end
+    trunc = (rng.random(N) < p_end / 2) & ~term
+    end = term | trunc
+    ref_adv = orc.gae_return(v_s, v_n * ~term, rew, end, 0.99, 0.95)
+    d = lambda a: torch.from_numpy(a).cuda()
+    g = [d(rew), d(v_s), d(v_n), d(term.view(np.uint8)), d(trunc.view(np.uint8))]
+    adv = torch.empty(N, dtype=torch.float64, device="cuda")
+    ret = torch.empty(N, dtype=torch.float64, device="cuda")
+    nbytes = L.lib().ts_gae_flat_workspace_bytes(N)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    for _ in range(3):  # workspace reuse across calls
+        L.check(L.lib().ts_gae_flat(*[L.ptr(t) for t in g], None, None, None, None, 0, 0, N,
+                                    0.99, 0.95, 1, 0, 1, L.ptr(adv), L.ptr(ret), L.ptr(ws),
+                                    nbytes, L.stream()), "ts_gae_flat")
+    assert _close(adv.cpu().numpy(), ref_adv, 1e-9)
+    assert _close(ret.cpu().numpy(), ref_adv + v_s, 1e-9)
+
+
+def test_c2_full_size_properties():
+    """BASELINE.json configs[1] at full size (4096 x 2048): oracle parity on a row sample and
+    size-independent properties over the whole array."""
+    from tianshou_fork_b200 import _lib as L
+    E, T = 4096, 2048
+    rew, v_s, v_next, term, trunc = c2_rollout(E, T, seed=0)
+    d = lambda a: torch.from_numpy(a).cuda()
+    g_rew, g_vs, g_vn = d(rew), d(v_s), d(v_next)
+    g_term, g_trunc = d(term.view(np.uint8)), d(trunc.view(np.uint8))
+    adv = torch.empty(E, T, device="cuda")
+    ret = torch.empty(E, T, device="cuda")
+
+    def run(r, a_out, r_out):
+        L.check(L.lib().ts_gae_rows(L.ptr(r), L.ptr(g_vs), L.ptr(g_vn), L.ptr(g_term),
+                                    L.ptr(g_trunc), E, T, T, T, 0.99, 0.95, 0, 0, 0,
+                                    L.ptr(a_out), L.ptr(r_out), L.stream()), "ts_gae_rows")
+
+    run(g_rew, adv, ret)
+    a, r = adv.cpu().numpy(), ret.cpu().numpy()
+    rows = np.r_[0:8, 2000:2008, E - 8:E]
+    ref_ret, ref_adv = orc.episodic_return_rows(rew[rows], v_s[rows], v_next[rows], term[rows],
+                                                trunc[rows], 0.99, 0.95)
+    assert _close(a[rows], ref_adv) and _close(r[rows], ref_ret)
+    # returns = advantage + v_s  (policy/base.py:382)
+    assert np.allclose(r, a + v_s, rtol=0, atol=1e-5 * np.abs(r).max())
+    # one-step Bellman identity away from episode ends: A_t = delta_t + gl * A_{t+1}
+    end = term | trunc
+    end[:, -1] = True
+    delta = rew.astype(np.float64) + 0.99 * v_next * ~term - v_s
+    rhs = delta.copy()
+    rhs[:, :-1] += 0.99 * 0.95 * (~end[:, :-1]) * a[:, 1:]
+    assert np.allclose(a, rhs, rtol=0, atol=2e-5 * np.abs(a).max())
+    # linearity in the reward: A(2*rew) - A(rew) == A(rew) - A(0)
+    adv2, adv0 = torch.empty_like(adv), torch.empty_like(adv)
+    scratch = torch.empty_like(ret)
+    run(g_rew * 2, adv2, scratch)
+    run(torch.zeros_like(g_rew), adv0, scratch)
+    lhs = (adv2 - adv).double().cpu().numpy()
+    rhs = (adv - adv0).double().cpu().numpy()
+    assert np.allclose(lhs, rhs, rtol=0, atol=2e-5 * np.abs(a).max())

@@ -1,0 +1,202 @@
+"""SegmentTree and prioritized replay on the GPU.  Node values and sampled indices are
+bit-exact against the reference (golden fixtures) and the CPU oracle; importance weights and
+pow-derived leaves are float-compared."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+from helpers import fill
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def test_known_answers_from_reference_tests():
+    """test/base/test_buffer.py:497-567."""
+    import tianshou_fork_b200 as ts
+    tree = ts.SegmentTree(8)
+    assert len(tree) == 8 and np.all([tree[i] == 0.0 for i in range(8)])
+    with pytest.raises(IndexError):
+        tree[8 * 2]  # noqa
+    tree[np.array([0, 2])] = np.array([0.1, 0.1])
+    assert np.allclose(tree.reduce(), 0.2)
+    assert np.all(tree.get_prefix_sum_idx(np.array([0, 0.1, 0.1 + 1e-6, 0.2 - 1e-6]))
+                  == [0, 0, 2, 2])
+    with pytest.raises(AssertionError):
+        tree.get_prefix_sum_idx(0.2)
+    with pytest.raises(AssertionError):
+        tree[8] = 1.0
+    assert isinstance(tree.get_prefix_sum_idx(0.05), int)
+    tree[3] = 2.5  # python int index / float value
+    assert tree[3] == 2.5 and np.allclose(tree.reduce(2, 4), 2.6)
+    # tensor path: device-side range flag instead of a host assert
+    bad = torch.tensor([0.1, 99.0], dtype=torch.float64, device="cuda")
+    tree.get_prefix_sum_idx(bad)
+    with pytest.raises(AssertionError):
+        tree.check_errors()
+    tree[torch.tensor([1, 8], device="cuda")] = torch.tensor([1.0, 1.0], device="cuda")
+    with pytest.raises(AssertionError):
+        tree.check_errors()
+    assert tree[1] == 1.0
+
+
+@pytest.mark.parametrize("name", ["t8", "t100", "t16384", "t5000"])
+def test_golden_segtree(name):
+    import tianshou_fork_b200 as ts
+    c = load_golden("segtree")[name]
+    tree = ts.SegmentTree(int(c["size"]))
+    for r, (idx, val) in enumerate(zip(c["idx_log"], c["val_log"])):
+        if r % 2 == 1:
+            val = val.astype(np.float32)  # generator alternated f64 / f32 values
+        if r % 4 < 2:
+            tree[idx] = val
+        else:
+            tree[torch.from_numpy(idx).cuda()] = torch.from_numpy(val).cuda()
+    assert np.array_equal(tree._value.cpu().numpy(), c["tree"]), name  # every node, bit-exact
+    s = c["scalar"].copy()
+    assert np.array_equal(tree.get_prefix_sum_idx(s), c["prefix_idx"])
+    assert np.array_equal(s, c["scalar_after"])  # in-place mutation kept (segtree.py:134)
+    s32 = c["scalar32"].copy()
+    assert np.array_equal(tree.get_prefix_sum_idx(s32), c["prefix_idx32"])
+    assert np.array_equal(s32, c["scalar32_after"])
+    sd = torch.from_numpy(c["scalar"].copy()).cuda()
+    assert np.array_equal(tree.get_prefix_sum_idx(sd).cpu().numpy(), c["prefix_idx"])
+    assert np.array_equal(sd.cpu().numpy(), c["scalar_after"])
+    red = np.array([tree.reduce(int(a), int(b)) for a, b in c["reduce_se"][:16]])
+    assert np.array_equal(red, c["reduce"][:16])
+    assert tree.reduce(1, -1) == float(c["reduce_neg_end"])
+    assert tree.reduce() == c["tree"][1]
+
+
+@pytest.mark.parametrize("size,bsz", [(1, 1), (2, 3), (4096, 64), (4097, 4096), (1 << 20, 4096),
+                                      (1_000_000, 32), (1 << 20, 8192), (1 << 20, 20000),
+                                      (300_000, 100_000)])
+def test_update_and_descent_vs_oracle(size, bsz):
+    """Random batched updates with forced duplicates on every update path (dense tiny tree,
+    subtree-per-CTA, bulk rebuild), then a batched descent; all bit-exact vs the oracle."""
+    import tianshou_fork_b200 as ts
+    rng = np.random.default_rng(size % 1000 + bsz)
+    ref, tree = orc.SegTree(size), ts.SegmentTree(size)
+    for r in range(4):
+        idx = rng.integers(0, size, bsz)
+        if r % 2 == 0 and bsz > 1:
+            idx[bsz // 2:] = idx[: bsz - bsz // 2]  # duplicates: last occurrence wins
+        if r == 3:  # a skewed batch: everything inside one subtree
+            idx = rng.integers(0, max(size // 128, 1), bsz)
+        val = rng.random(bsz)
+        ref[idx] = val
+        tree[torch.from_numpy(idx).cuda()] = torch.from_numpy(val).cuda()
+    tree.check_errors()
+    assert np.array_equal(tree._value.cpu().numpy(), ref._value)
+    assert not tree._stamp.any() and not tree._counter.any()  # scratch left clean
+    u = rng.random(4096)
+    s = u * ref.reduce()
+    want = ref.get_prefix_sum_idx(s.copy())
+    got = tree.get_prefix_sum_idx(torch.from_numpy(s.copy()).cuda())
+    assert np.array_equal(got.cpu().numpy(), want)
+    tree.check_errors()
+
+
+def test_scalar_broadcast_and_empty():
+    import tianshou_fork_b200 as ts
+    tree, ref = ts.SegmentTree(100000), orc.SegTree(100000)
+    idx = np.arange(0, 100000, 7)
+    tree[idx] = 0.5
+    ref[idx] = np.full(idx.size, 0.5)
+    assert np.array_equal(tree._value.cpu().numpy(), ref._value)
+    with pytest.raises(IndexError):
+        tree[np.array([], dtype=np.int64)] = np.array([])  # reference: index[0] on empty
+
+
+@pytest.mark.parametrize("name", ["pv", "pv_nonorm"])
+def test_golden_per_vector(name):
+    """make_golden.gen_per replayed: add -> (sample, weight, update_weight) x 6."""
+    import tianshou_fork_b200 as ts
+    c = load_golden("per")[name]
+    n_env = int(c["n_env"])
+    total, steps, bsz = (256, 90, 32) if name == "pv" else (4096, 600, 256)
+    buf = ts.PrioritizedVectorReplayBuffer(total, n_env, alpha=0.6, beta=0.4,
+                                           weight_norm=(name == "pv"))
+    assert buf._weight_norm is True  # reference quirk: the manager always normalises
+    fill(buf, ts.Batch, 500 + n_env, steps, n_env, 0.1, 0.05, False)
+    rng = np.random.default_rng(500 + n_env)
+    # replay the generator's rng position: it drew `td` from the same stream after the fill
+    from helpers import golden_stream
+    rng, it = golden_stream(500 + n_env, steps, n_env, 0.1, 0.05, False)
+    for _ in it:
+        pass
+    assert np.array_equal(buf.weight._value.cpu().numpy(), c["tree_after_add"])
+    for it_ in range(c["u"].shape[0]):
+        np.random.seed(1000 + it_)
+        batch, idx = buf.sample(bsz)  # draws np.random.rand(bsz) like prio.py:61
+        gold_idx = c["idx"][it_].copy()
+        got_idx = idx.cpu().numpy()
+        if it_ % 2 == 0:
+            gold_idx[-4:] = got_idx[-4:]  # the generator overwrote the tail AFTER sampling
+        assert np.array_equal(got_idx, gold_idx), (name, it_)  # bit-exact indices
+        assert np.allclose(batch.weight.cpu().numpy(), c["weight"][it_], rtol=1e-12)
+        td = rng.standard_normal(bsz).astype(np.float32)
+        assert np.array_equal(td, c["td"][it_])
+        buf.update_weight(c["idx"][it_], torch.from_numpy(td).cuda())
+        # leaves go through pow: float compare; then exactness is re-anchored by loading the
+        # reference's tree so that later rounds still test index bit-exactness
+        got = buf.weight._value.cpu().numpy()
+        assert np.allclose(got, c["tree"][it_], rtol=2e-7, atol=0), (name, it_)
+        buf.weight._value.copy_(torch.from_numpy(c["tree"][it_]))
+        assert np.isclose(buf._max_prio, c["max_prio"][it_], rtol=0, atol=0)
+        assert np.isclose(buf._min_prio, c["min_prio"][it_], rtol=0, atol=0)
+    buf.check_errors()
+
+
+def test_golden_per_single():
+    import tianshou_fork_b200 as ts
+    c = load_golden("per")["single"]
+    buf = ts.PrioritizedReplayBuffer(50, 0.5, 0.5)
+    for i in range(70):
+        buf.add(ts.Batch(obs=np.zeros(2), act=0, rew=1.0, terminated=i % 7 == 6,
+                         truncated=False, obs_next=np.zeros(2), info={}))
+    buf.update_weight(c["idx"], c["td"])  # f64 td -> f64 pow
+    assert np.allclose(buf.weight._value.cpu().numpy(), c["tree"], rtol=1e-14)
+    assert buf._max_prio == float(c["max_prio"]) and buf._min_prio == float(c["min_prio"])
+    assert np.allclose(buf.get_weight(np.arange(50)), c["weight_all"], rtol=1e-12)
+    # tree[idx] == |w| ** alpha  (test/base/test_buffer.py:292-293)
+    last = {i: t for i, t in zip(c["idx"], c["td"])}
+    for i, t in last.items():
+        assert np.isclose(buf.weight[int(i)], (abs(t) + np.finfo(np.float32).eps) ** 0.5)
+
+
+def test_per_full_size_step_vs_oracle():
+    """BASELINE.json configs[3] shape: 2^20 leaves, batch 4096, alpha .6 beta .4; ten chained
+    sample -> update steps, every sampled index bit-exact vs the oracle on identical draws."""
+    import tianshou_fork_b200 as ts
+    size, bsz = 1 << 20, 4096
+    rng = np.random.default_rng(2)
+    leaves = ((np.abs(rng.standard_normal(size)) + 1e-7) ** 0.6)
+    ref = orc.PER(size, 0.6, 0.4)
+    ref.weight[np.arange(size)] = leaves
+    buf = ts.PrioritizedVectorReplayBuffer(size, 16, alpha=0.6, beta=0.4)
+    buf.weight[torch.arange(size, device="cuda")] = torch.from_numpy(leaves).cuda()
+    buf._lengths[:] = size // 16
+    assert np.array_equal(buf.weight._value.cpu().numpy(), ref.weight._value)
+    for step in range(10):
+        u = rng.random(bsz)
+        want = ref.sample_indices(u)
+        got = buf.sample_with_uniforms(torch.from_numpy(u).cuda())
+        assert np.array_equal(got.cpu().numpy(), want), step
+        w = buf._cached_weight[1].cpu().numpy()
+        assert np.allclose(w, ref.batch_weight(want), rtol=1e-12)
+        td = rng.standard_normal(bsz).astype(np.float32)
+        idx = want.copy()
+        idx[:200] = idx[200:400]  # 5 % duplicated indices
+        ref.update_weight(idx, td)
+        buf.update_weight(torch.from_numpy(idx).cuda(), torch.from_numpy(td).cuda())
+        got_tree = buf.weight._value.cpu().numpy()
+        assert np.allclose(got_tree, ref.weight._value, rtol=2e-7, atol=0)
+        # re-anchor on the oracle's leaves (f32 pow is not bit-reproducible across libms)
+        touched = np.unique(idx)
+        buf.weight[torch.from_numpy(touched).cuda()] = torch.from_numpy(
+            ref.weight[touched]).cuda()
+        assert np.array_equal(buf.weight._value.cpu().numpy(), ref.weight._value), step
+        assert buf._max_prio == ref._max_prio and buf._min_prio == ref._min_prio
+    buf.check_errors()

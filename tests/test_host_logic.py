@@ -1,0 +1,38 @@
+"""CPU tests of host-side logic that needs no kernel: Batch container and split boundaries."""
+import numpy as np
+import torch
+
+from tianshou_fork_b200.data.batch import Batch, create_value
+from tianshou_fork_b200.policy.ppo import _split_bounds
+
+
+def test_batch_index_assign_len():
+    b = Batch(a=np.arange(6), obs=Batch(x=np.arange(12).reshape(6, 2)), info={})
+    assert len(b) == 6 and "a" in b and b.info.is_empty()
+    sub = b[np.array([4, 1])]
+    assert np.array_equal(sub.a, [4, 1]) and np.array_equal(sub.obs.x, [[8, 9], [2, 3]])
+    store = create_value(b, 10, stack=False)
+    assert store.a.shape == (10,) and store.obs.x.shape == (10, 2)
+    store[np.array([7, 8])] = sub
+    assert np.array_equal(store.a[7:9], [4, 1])
+    t = Batch(a=torch.arange(6))
+    assert torch.equal(t[np.array([0, 5])].a, torch.tensor([0, 5]))
+    assert b.pop("a") is not None and "a" not in b
+
+
+def test_batch_split_matches_reference_boundaries():
+    """Batch.split (tianshou/data/batch.py:896-912): merge_last folds the short tail."""
+    b = Batch(a=np.arange(10))
+    sizes = [len(m) for m in b.split(4, shuffle=False, merge_last=True)]
+    assert sizes == [4, 6]
+    sizes = [len(m) for m in b.split(4, shuffle=False, merge_last=False)]
+    assert sizes == [4, 4, 2]
+    sizes = [len(m) for m in b.split(5, shuffle=False, merge_last=True)]
+    assert sizes == [5, 5]
+    assert _split_bounds(10, 4, True) == [(0, 4), (4, 10)]
+    assert _split_bounds(10, 4, False) == [(0, 4), (4, 8), (8, 10)]
+    assert _split_bounds(10, -1, True) == [(0, 10)]
+    np.random.seed(3)
+    got = np.concatenate([m.a for m in b.split(3)])
+    np.random.seed(3)
+    assert np.array_equal(got, np.random.permutation(10))

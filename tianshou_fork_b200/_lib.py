@@ -1,0 +1,128 @@
+"""ctypes binding of ``libts_b200.so`` (the C-ABI declared in ``include/ts_b200.h``).
+
+The shared object is built in-tree by ``csrc/Makefile`` (``__graft_entry__.build()``).  There
+is NO fallback: if the library is missing, fails to load, or a CUDA device is absent, every
+product call raises.  Pointers are raw device addresses taken from torch tensors; the stream
+is torch's current CUDA stream, so calls order with surrounding torch work and are legal
+inside ``torch.cuda.graph`` capture.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from typing import Optional
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(_HERE, "csrc")
+LIB_PATH = os.path.join(CSRC, "libts_b200.so")
+
+TS_F32, TS_F64 = 0, 1
+TS_FLAG_INDEX_RANGE, TS_FLAG_PREFIX_RANGE = 1, 2
+
+_vp, _i64, _i32, _f64, _f32, _sz = (
+    ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32, ctypes.c_double, ctypes.c_float,
+    ctypes.c_size_t,
+)
+
+# name -> (restype, argtypes); must list every symbol of include/ts_b200.h
+SIGNATURES = {
+    "ts_version": (_i32, []),
+    "ts_error_string": (ctypes.c_char_p, [_i32]),
+    "ts_last_cuda_error": (_i32, []),
+    "ts_gae_rows": (_i32, [_vp] * 5 + [_i64] * 4 + [_f64, _f64, _i32, _i32, _i32, _vp, _vp,
+                                                    _vp]),
+    "ts_gae_flat_workspace_bytes": (_sz, [_i64]),
+    "ts_gae_flat": (_i32, [_vp] * 9 + [_i64] * 3 + [_f64, _f64, _i32, _i32, _i32, _vp, _vp, _vp,
+                                                   _sz, _vp]),
+    "ts_prev_index": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "ts_next_index": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "ts_unfinished_index": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp]),
+    "ts_nstep_chain": (_i32, [_vp, _i64, _vp, _i32, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _f64,
+                              _i32, _vp, _vp, _vp, _vp]),
+    "ts_nstep_combine": (_i32, [_vp, _i32, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "ts_segtree_update": (_i32, [_vp, _i64, _i64, _vp, _vp, _i32, _i64, _i64, _vp, _vp, _vp,
+                                 _vp]),
+    "ts_segtree_reduce": (_i32, [_vp, _i64, _i64, _i64, _vp, _vp]),
+    "ts_segtree_prefix_idx": (_i32, [_vp, _i64, _vp, _i32, _i64, _i32, _vp, _vp, _vp]),
+    "ts_per_sample": (_i32, [_vp, _i64, _vp, _i64, _vp, _f64, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "ts_per_weight": (_i32, [_vp, _i64, _vp, _i64, _vp, _f64, _i32, _vp, _vp, _vp]),
+    "ts_per_update": (_i32, [_vp, _i64, _i64, _vp, _vp, _i32, _i64, _f64, _vp, _vp, _vp, _vp,
+                             _vp]),
+    "ts_per_init_weight": (_i32, [_vp, _i64, _i64, _vp, _i64, _f64, _vp, _i32, _vp, _vp, _vp,
+                                  _vp]),
+    "ts_ppo_loss_workspace_bytes": (_sz, [_i64]),
+    "ts_ppo_loss": (_i32, [_vp] * 7 + [_i64, _f32, _f32, _i32, _i32, _f32, _vp, _vp, _vp, _vp,
+                                      _sz, _vp]),
+    "ts_gather_rows": (_i32, [_vp, _i64, _i64, _vp, _i64, _vp, _vp]),
+}
+
+_lib: Optional[ctypes.CDLL] = None
+
+
+class TsError(RuntimeError):
+    """A C-ABI call returned a negative TS_ERR_* code."""
+
+
+def build(verbose: bool = False) -> str:
+    """Compile the CUDA sources for sm_100a (``make -C csrc``); nvcc cross-compiles on CPU."""
+    cmd = ["make", "-C", CSRC, "-j8"] + ([] if verbose else ["-s"])
+    subprocess.check_call(cmd)
+    return LIB_PATH
+
+
+def load() -> ctypes.CDLL:
+    """Load the library (does not need a GPU) and bind every declared symbol."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; "
+                "g.build()'` (there is no CPU or PyTorch fallback for this path)")
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError if the .so lacks a declared symbol
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def lib() -> ctypes.CDLL:
+    """The library, for compute calls: additionally requires a CUDA device."""
+    if not torch.cuda.is_available():
+        raise RuntimeError(
+            "tianshou_fork_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    return load()
+
+
+def check(code: int, what: str) -> None:
+    if code != 0:
+        msg = load().ts_error_string(code).decode()
+        raise TsError(f"{what}: {msg} (code {code})")
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    """Device address of a contiguous CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    assert t.is_cuda and t.is_contiguous(), "C-ABI arguments must be contiguous CUDA tensors"
+    return t.data_ptr()
+
+
+def stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def dtype_code(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return TS_F32
+    if t.dtype == torch.float64:
+        return TS_F64
+    raise TypeError(f"expected float32/float64, got {t.dtype}")
+
+
+def as_u8(t: torch.Tensor) -> torch.Tensor:
+    """bool tensors are passed as uint8 views (same layout)."""
+    return t.view(torch.uint8) if t.dtype == torch.bool else t

@@ -1,0 +1,21 @@
+// Version / error plumbing of the C-ABI (include/ts_b200.h).
+#include "ts_common.cuh"
+
+namespace ts {
+thread_local int32_t g_last_cuda_error = 0;
+}
+
+extern "C" int32_t ts_version(void) { return TS_B200_VERSION; }
+
+extern "C" int32_t ts_last_cuda_error(void) { return ts::g_last_cuda_error; }
+
+extern "C" const char* ts_error_string(int32_t code) {
+    switch (code) {
+        case TS_OK: return "ok";
+        case TS_ERR_BAD_ARG: return "bad argument (null pointer, negative size or unknown dtype)";
+        case TS_ERR_WORKSPACE: return "workspace too small";
+        case TS_ERR_CUDA: return cudaGetErrorString((cudaError_t)ts::g_last_cuda_error);
+        case TS_ERR_ALIGN: return "pointer not aligned to its element size";
+        default: return "unknown error code";
+    }
+}

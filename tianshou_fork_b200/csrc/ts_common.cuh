@@ -1,0 +1,61 @@
+// Shared device/host helpers for the sm_100a kernels behind include/ts_b200.h.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ts_b200.h"
+
+namespace ts {
+
+constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
+
+// Last cudaError_t seen by this host thread (ts_last_cuda_error()).
+extern thread_local int32_t g_last_cuda_error;
+
+inline int32_t check_launch() {
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) {
+        g_last_cuda_error = (int32_t)e;
+        (void)cudaGetLastError();
+        return TS_ERR_CUDA;
+    }
+    return TS_OK;
+}
+
+inline bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
+
+// numpy-style modulo for a positive modulus.
+__host__ __device__ __forceinline__ int64_t pymod(int64_t a, int64_t m) {
+    int64_t r = a % m;
+    return r < 0 ? r + m : r;
+}
+
+// Sub-buffer of a (already wrapped) global index: division when all sub-buffers are equal
+// (vecbuf.py:35), else binary search over _extend_offset (manager.py:38).
+__device__ __forceinline__ int64_t sub_of(int64_t idx, const int64_t* __restrict__ offset,
+                                          int64_t B, int64_t sub_size) {
+    if (sub_size > 0) return idx / sub_size;
+    int64_t lo = 0, hi = B;  // offset[lo] <= idx < offset[hi]
+    while (hi - lo > 1) {
+        int64_t mid = (lo + hi) >> 1;
+        if (__ldg(offset + mid) <= idx) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+__device__ __forceinline__ double shfl_down_f64(double v, int d) {
+    return __shfl_down_sync(0xffffffffu, v, d);
+}
+__device__ __forceinline__ double shfl_idx_f64(double v, int l) {
+    return __shfl_sync(0xffffffffu, v, l);
+}
+
+// Streaming (evict-first) vector accesses: every transition is touched exactly once.
+__device__ __forceinline__ float4 ld_stream(const float4* p) { return __ldcs(p); }
+__device__ __forceinline__ double2 ld_stream(const double2* p) { return __ldcs(p); }
+__device__ __forceinline__ uint2 ld_stream(const uint2* p) { return __ldcs(p); }
+__device__ __forceinline__ void st_stream(float4* p, float4 v) { __stcs(p, v); }
+__device__ __forceinline__ void st_stream(double2* p, double2 v) { __stcs(p, v); }
+
+}  // namespace ts

@@ -1,0 +1,13 @@
+"""Device-resident data structures (mirror of ``tianshou.data`` for the hot path)."""
+from .batch import Batch
+from .segtree import SegmentTree
+from .buffer import ReplayBuffer
+from .manager import ReplayBufferManager, VectorReplayBuffer
+from .prio import (PrioritizedReplayBuffer, PrioritizedReplayBufferManager,
+                   PrioritizedVectorReplayBuffer)
+
+__all__ = [
+    "Batch", "SegmentTree", "ReplayBuffer", "ReplayBufferManager", "VectorReplayBuffer",
+    "PrioritizedReplayBuffer", "PrioritizedReplayBufferManager",
+    "PrioritizedVectorReplayBuffer",
+]

@@ -1,0 +1,456 @@
+"""Device-resident replay buffers -- drop-ins for ``tianshou.data.ReplayBuffer``,
+``ReplayBufferManager`` and ``VectorReplayBuffer``
+(tianshou/data/buffer/base.py:11-389, manager.py:10-192, vecbuf.py:15-37).
+
+Storage (``obs/act/rew/terminated/truncated/done/obs_next/...``) lives in HBM as torch CUDA
+tensors inside a :class:`Batch`; ``prev`` / ``next`` / ``unfinished_index`` run as integer
+kernels (``csrc/index.cu``).  Ring bookkeeping (``_index``, ``_size``, ``last_index``,
+``_lengths``, episode statistics) stays on the host -- it is a handful of integers per
+sub-buffer that ``add`` needs synchronously for its return value -- and is mirrored to the
+device lazily, before the first kernel that needs it.
+
+Index arguments may be Python ints, lists, NumPy arrays or CUDA tensors; NumPy/int in ->
+NumPy/int out, CUDA tensor in -> CUDA tensor out.  ``sample_indices`` / ``sample`` return CUDA
+tensors so that the whole update stays on the device.
+
+Out of scope here: HDF5 save/load, ``from_data``.
+"""
+from __future__ import annotations
+
+from typing import Any, Dict, List, Optional, Tuple, Union
+
+import numpy as np
+import torch
+
+from .. import _lib as L
+from .batch import Batch, create_value
+
+IndexLike = Union[int, List[int], np.ndarray, torch.Tensor]
+
+
+def _is_scalar(index: Any) -> bool:
+    return isinstance(index, (int, np.integer)) or (
+        isinstance(index, np.ndarray) and index.ndim == 0)
+
+
+class ReplayBuffer:
+    """Circular buffer with device-resident storage (tianshou/data/buffer/base.py:11-389)."""
+
+    _reserved_keys = (
+        "obs", "act", "rew", "terminated", "truncated", "done", "obs_next", "info", "policy"
+    )
+    _input_keys = (
+        "obs", "act", "rew", "terminated", "truncated", "obs_next", "info", "policy"
+    )
+
+    def __init__(
+        self,
+        size: int,
+        stack_num: int = 1,
+        ignore_obs_next: bool = False,
+        save_only_last_obs: bool = False,
+        sample_avail: bool = False,
+        device: Union[str, torch.device, None] = None,
+        rew_dtype: torch.dtype = torch.float64,
+        **kwargs: Any,
+    ) -> None:
+        L.lib()  # no extension or no GPU -> fail here, loudly
+        self.options: Dict[str, Any] = {
+            "stack_num": stack_num,
+            "ignore_obs_next": ignore_obs_next,
+            "save_only_last_obs": save_only_last_obs,
+            "sample_avail": sample_avail,
+        }
+        self.device = torch.device(device if device is not None else
+                                   f"cuda:{torch.cuda.current_device()}")
+        self.rew_dtype = rew_dtype
+        self.maxsize = int(size)
+        assert stack_num > 0, "stack_num should be greater than 0"
+        self.stack_num = stack_num
+        self._save_obs_next = not ignore_obs_next
+        self._save_only_last_obs = save_only_last_obs
+        self._sample_avail = sample_avail
+        self._meta: Batch = Batch()
+        # ring state [index, size]; a manager re-points this at a row of its own table
+        self._ring = np.zeros(2, dtype=np.int64)
+        self._ep = {"rew": 0.0, "len": 0, "idx": 0}
+        self._version = 0
+        self._parent: Optional["ReplayBuffer"] = None  # set by a manager on its children
+        self._dev_state: Optional[Dict[str, torch.Tensor]] = None
+        self._dev_state_version = -1
+        self.reset()
+
+    # ---- ring state ------------------------------------------------------------------------
+    @property
+    def _index(self) -> int:
+        return int(self._ring[0])
+
+    @_index.setter
+    def _index(self, v: int) -> None:
+        self._ring[0] = v
+
+    @property
+    def _size(self) -> int:
+        return int(self._ring[1])
+
+    @_size.setter
+    def _size(self, v: int) -> None:
+        self._ring[1] = v
+
+    def __len__(self) -> int:
+        return self._size
+
+    def __repr__(self) -> str:
+        return self.__class__.__name__ + self._meta.__repr__()[5:]
+
+    def __getattr__(self, key: str) -> Any:
+        """``buf.rew`` etc. hand out the live device storage (base.py:74-79)."""
+        try:
+            return self.__dict__["_meta"][key]
+        except KeyError as exception:
+            raise AttributeError(key) from exception
+
+    def __setattr__(self, key: str, value: Any) -> None:
+        assert key not in self._reserved_keys, \
+            "key '{}' is reserved and cannot be assigned".format(key)
+        super().__setattr__(key, value)
+
+    def __getstate__(self) -> Dict[str, Any]:
+        """Pickle as host arrays (base.py:81-87; test/base/test_buffer.py:597-632)."""
+        state = dict(self.__dict__)
+        meta = Batch(self._meta)
+        state["_meta"] = _batch_to_numpy_copy(meta)
+        state["_dev_state"] = None
+        state["_dev_state_version"] = -1
+        state["device"] = str(self.device)
+        return state
+
+    def __setstate__(self, state: Dict[str, Any]) -> None:
+        self.__dict__.update(state)
+        self.__dict__["device"] = torch.device(state["device"])
+        self.__dict__["_meta"] = state["_meta"].to_torch(device=self.device)
+
+    def reset(self, keep_statistics: bool = False) -> None:
+        """Clear all the data in replay buffer and episode statistics (base.py:134-139)."""
+        self.last_index = np.array([0])
+        self._ring[:] = 0
+        if not keep_statistics:
+            self._ep = {"rew": 0.0, "len": 0, "idx": 0}
+        self._version += 1
+
+    def set_batch(self, batch: Batch) -> None:
+        """Manually choose the batch you want the ReplayBuffer to manage (base.py:141-146)."""
+        assert len(batch) == self.maxsize and set(batch.keys()).issubset(
+            self._reserved_keys
+        ), "Input batch doesn't meet ReplayBuffer's data form requirement."
+        self._meta = batch.to_torch(device=self.device)
+        self._version += 1
+
+    # ---- device mirrors of the bookkeeping ---------------------------------------------------
+    def _layout(self) -> Tuple[np.ndarray, np.ndarray, np.ndarray, int]:
+        """(extend_offset[B+1], last_index[B], lengths[B], sub_size) for the index kernels.
+
+        A single ring takes ``%`` by its CURRENT size (base.py:158-168), which is the manager
+        formula (manager.py:267-276) with one sub-buffer of capacity ``size``."""
+        size = max(self._size, 1)
+        return (np.array([0, size], dtype=np.int64),
+                np.asarray(self.last_index, dtype=np.int64).reshape(1),
+                np.array([self._size], dtype=np.int64), size)
+
+    def _state(self) -> Dict[str, torch.Tensor]:
+        version = self._version + (self._parent._version if self._parent is not None else 0)
+        if self._dev_state is None or self._dev_state_version != version:
+            off, last, lens, sub = self._layout()
+            packed = np.concatenate([off, last, lens]).astype(np.int64)
+            t = torch.from_numpy(packed).to(self.device)
+            b = last.size
+            self._dev_state = {"offset": t[: b + 1], "last_index": t[b + 1: 2 * b + 1],
+                               "lengths": t[2 * b + 1:], "B": b, "sub_size": sub}
+            self._dev_state_version = version
+        return self._dev_state
+
+    def _done_u8(self) -> torch.Tensor:
+        return L.as_u8(self._meta["done"])
+
+    def _neighbour(self, index: IndexLike, fn_name: str):
+        st = self._state()
+        scalar = _is_scalar(index)
+        if isinstance(index, torch.Tensor):
+            idx = index.to(device=self.device, dtype=torch.int64)
+            shape = idx.shape
+        else:
+            arr = np.asarray(index, dtype=np.int64)
+            shape = arr.shape
+            idx = torch.from_numpy(np.ascontiguousarray(arr)).to(self.device)
+        idx = idx.reshape(-1).contiguous()
+        out = torch.empty_like(idx)
+        if idx.numel():
+            fn = getattr(L.lib(), fn_name)
+            L.check(fn(L.ptr(idx), idx.numel(), L.ptr(st["offset"]), st["B"], st["sub_size"],
+                       L.ptr(self._done_u8()), L.ptr(st["last_index"]), L.ptr(st["lengths"]),
+                       L.ptr(out), L.stream()), fn_name)
+        out = out.reshape(shape)
+        if isinstance(index, torch.Tensor):
+            return out
+        res = out.cpu().numpy()
+        return res[()] if scalar else res
+
+    def prev(self, index: IndexLike):
+        """Index of the previous transition; unchanged at an episode start (base.py:153-160)."""
+        return self._neighbour(index, "ts_prev_index")
+
+    def next(self, index: IndexLike):
+        """Index of the next transition; unchanged at an episode end (base.py:162-168)."""
+        return self._neighbour(index, "ts_next_index")
+
+    def unfinished_index(self) -> np.ndarray:
+        """Index of the unfinished episode's last step (base.py:148-151).  Host array: it has
+        at most one entry per sub-buffer and the bookkeeping is host-side; the ``done`` bit
+        costs one small D2H read."""
+        u = self.unfinished_index_device()
+        u = u[u >= 0]
+        return u.cpu().numpy()
+
+    def unfinished_index_device(self) -> torch.Tensor:
+        """int64[B]: unfinished index per sub-buffer or -1 (device, no sync)."""
+        st = self._state()
+        out = torch.empty(st["B"], dtype=torch.int64, device=self.device)
+        if "done" not in self._meta:
+            return out.fill_(-1)
+        L.check(L.lib().ts_unfinished_index(
+            L.ptr(self._done_u8()), L.ptr(st["last_index"]), L.ptr(st["lengths"]), st["B"],
+            L.ptr(out), L.stream()), "ts_unfinished_index")
+        return out
+
+    # ---- writes ----------------------------------------------------------------------------
+    def update(self, buffer: "ReplayBuffer") -> np.ndarray:
+        """Move the data from the given buffer to current buffer (base.py:170-193)."""
+        if len(buffer) == 0 or self.maxsize == 0:
+            return np.array([], int)
+        stack_num, buffer.stack_num = buffer.stack_num, 1
+        from_indices = buffer.sample_indices(0)
+        buffer.stack_num = stack_num
+        n = len(from_indices)
+        if n == 0:
+            return np.array([], int)
+        to_indices = (self._index + np.arange(n)) % self.maxsize
+        self.last_index[0] = to_indices[-1]
+        self._index = int((self._index + n) % self.maxsize)
+        self._size = min(self._size + n, self.maxsize)
+        self._version += 1
+        if self._meta.is_empty():
+            self._meta = create_value(buffer._meta, self.maxsize, stack=False,
+                                      device=self.device)
+        self._meta[to_indices] = buffer._meta[from_indices]
+        return to_indices
+
+    def _add_index(self, rew: Union[float, np.ndarray], done: bool
+                   ) -> Tuple[int, Union[float, np.ndarray], int, int]:
+        """Advance the ring after adding one transition (base.py:195-214)."""
+        self.last_index[0] = ptr = self._index
+        self._size = min(self._size + 1, self.maxsize)
+        self._index = (self._index + 1) % self.maxsize
+        self._version += 1
+        ep = self._ep
+        ep["rew"] = ep["rew"] + rew
+        ep["len"] += 1
+        if done:
+            result = ptr, ep["rew"], ep["len"], ep["idx"]
+            ep["rew"], ep["len"], ep["idx"] = 0.0, 0, self._index
+            return result
+        return ptr, ep["rew"] * 0.0, 0, ep["idx"]
+
+    def _prepare_add(self, batch: Batch, keys, stacked: bool) -> Batch:
+        new_batch = Batch()
+        for key in set(keys).intersection(batch.keys()):
+            new_batch.__dict__[key] = batch[key]
+        batch = new_batch
+        term, trunc = _host(batch.terminated), _host(batch.truncated)
+        batch.__dict__["done"] = np.logical_or(term, trunc)
+        assert set(["obs", "act", "rew", "terminated", "truncated", "done"]).issubset(
+            batch.keys())
+        if self._save_only_last_obs:
+            batch.obs = batch.obs[:, -1] if stacked else batch.obs[-1]
+        if not self._save_obs_next:
+            batch.pop("obs_next", None)
+        elif self._save_only_last_obs:
+            batch.obs_next = batch.obs_next[:, -1] if stacked else batch.obs_next[-1]
+        return batch
+
+    def _widen(self, batch: Batch) -> Batch:
+        """rew -> float, flags -> bool before the first allocation (base.py:264-267)."""
+        batch.rew = _astype(batch.rew, self.rew_dtype)
+        for k in ("done", "terminated", "truncated"):
+            batch.__dict__[k] = _astype(batch[k], torch.bool)
+        return batch
+
+    def add(self, batch: Batch, buffer_ids: Optional[Union[np.ndarray, List[int]]] = None
+            ) -> Tuple[np.ndarray, np.ndarray, np.ndarray, np.ndarray]:
+        """Add a batch of data into replay buffer (base.py:216-274)."""
+        stacked_batch = buffer_ids is not None
+        batch = self._prepare_add(batch, self._input_keys, stacked_batch)
+        if stacked_batch:
+            assert len(batch) == 1
+            rew, done = _host(batch.rew)[0], bool(batch.done[0])
+        else:
+            rew, done = _host(batch.rew), bool(batch.done)
+        ptr, ep_rew, ep_len, ep_idx = list(
+            map(lambda x: np.array([x]), self._add_index(rew, done)))
+        batch = self._widen(batch)
+        if self._meta.is_empty():
+            self._meta = create_value(batch, self.maxsize, stack=not stacked_batch,
+                                      device=self.device)
+        elif not set(batch.keys()).issubset(self._meta.keys()):
+            _alloc_missing(self._meta, batch, self.maxsize, not stacked_batch, self.device)
+        if stacked_batch:
+            self._meta[ptr] = batch
+        else:
+            self._meta[ptr] = _unsqueeze0(batch)
+        return ptr, ep_rew, ep_len, ep_idx
+
+    # ---- sampling / gathers ------------------------------------------------------------------
+    def _all_indices_host(self) -> np.ndarray:
+        return np.concatenate([np.arange(self._index, self._size), np.arange(self._index)])
+
+    def sample_indices(self, batch_size: int) -> torch.Tensor:
+        """Random indices (host ``np.random`` stream, same draws as the reference), all valid
+        indices in chronological order for 0, empty for negative (base.py:276-305)."""
+        if self.stack_num == 1 or not self._sample_avail:
+            if batch_size > 0:
+                idx = np.random.choice(self._size, batch_size)
+            elif batch_size == 0:
+                idx = self._all_indices_host()
+            else:
+                idx = np.array([], int)
+        else:
+            if batch_size < 0:
+                idx = np.array([], int)
+            else:
+                all_indices = prev_indices = self._all_indices_host()
+                for _ in range(self.stack_num - 2):
+                    prev_indices = self.prev(prev_indices)
+                all_indices = all_indices[prev_indices != self.prev(prev_indices)]
+                idx = np.random.choice(all_indices, batch_size) if batch_size > 0 \
+                    else all_indices
+        return torch.from_numpy(np.asarray(idx, dtype=np.int64)).to(self.device)
+
+    def sample(self, batch_size: int) -> Tuple[Batch, torch.Tensor]:
+        """Random batch and its indices; all data for ``batch_size == 0`` (base.py:307-315)."""
+        indices = self.sample_indices(batch_size)
+        return self[indices], indices
+
+    def get(self, index: IndexLike, key: str, default_value: Any = None,
+            stack_num: Optional[int] = None):
+        """Stacked gather ``[obs[t-n+1], ..., obs[t]]`` through ``prev`` (base.py:317-358)."""
+        if key not in self._meta and default_value is not None:
+            return default_value
+        val = self._meta[key]
+        if stack_num is None:
+            stack_num = self.stack_num
+        try:
+            if stack_num == 1:
+                return _take(val, index)
+            stack: List[Any] = []
+            indices = self._as_device_index(index)
+            for _ in range(stack_num):
+                stack = [_take(val, indices)] + stack
+                indices = self.prev(indices)
+            if isinstance(val, Batch):
+                return Batch.stack(stack, axis=indices.ndim)
+            return torch.stack(stack, dim=indices.ndim)
+        except IndexError as exception:
+            if not (isinstance(val, Batch) and val.is_empty()):
+                raise exception
+            return Batch()
+
+    def _as_device_index(self, index: IndexLike) -> torch.Tensor:
+        if isinstance(index, torch.Tensor):
+            return index.to(device=self.device, dtype=torch.int64)
+        return torch.from_numpy(np.asarray(index, dtype=np.int64)).to(self.device)
+
+    def __getitem__(self, index: Union[slice, IndexLike]) -> Batch:
+        """``buffer[index]``: gather copies of every stored key (base.py:360-389)."""
+        if isinstance(index, slice):
+            indices = self.sample_indices(0) if index == slice(None) \
+                else self._as_device_index(np.arange(self.maxsize)[:len(self)][index])
+        else:
+            indices = self._as_device_index(index)
+        obs = self.get(indices, "obs")
+        if self._save_obs_next:
+            obs_next = self.get(indices, "obs_next", Batch())
+        else:
+            obs_next = self.get(self.next(indices), "obs", Batch())
+        return Batch(
+            obs=obs,
+            act=_take(self._meta["act"], indices),
+            rew=_take(self._meta["rew"], indices),
+            terminated=_take(self._meta["terminated"], indices),
+            truncated=_take(self._meta["truncated"], indices),
+            done=_take(self._meta["done"], indices),
+            obs_next=obs_next,
+            info=self.get(indices, "info", Batch()),
+            policy=self.get(indices, "policy", Batch()),
+        )
+
+
+# ---- helpers ---------------------------------------------------------------------------------
+def _host(x: Any) -> np.ndarray:
+    if isinstance(x, torch.Tensor):
+        return x.detach().cpu().numpy()
+    return np.asarray(x)
+
+
+def _astype(x: Any, dtype: torch.dtype) -> Any:
+    if isinstance(x, torch.Tensor):
+        return x.to(dtype)
+    np_dtype = {torch.float64: np.float64, torch.float32: np.float32, torch.bool: np.bool_}[dtype]
+    return np.asarray(x).astype(np_dtype)
+
+
+def _unsqueeze0(batch: Batch) -> Batch:
+    out = Batch()
+    for k, v in batch.items():
+        if isinstance(v, Batch):
+            out.__dict__[k] = _unsqueeze0(v) if not v.is_empty() else v
+        elif isinstance(v, torch.Tensor):
+            out.__dict__[k] = v.unsqueeze(0)
+        else:
+            out.__dict__[k] = np.asarray(v)[None]
+    return out
+
+
+def _take(val: Any, index: Any) -> Any:
+    if isinstance(val, Batch):
+        return val[index] if not val.is_empty() else Batch()
+    if isinstance(index, np.ndarray):
+        index = torch.from_numpy(index).to(val.device)
+    elif isinstance(index, list):
+        index = torch.as_tensor(index, device=val.device)
+    elif isinstance(index, (int, np.integer)):
+        if index >= val.shape[0] or index < -val.shape[0]:
+            raise IndexError(f"index {index} is out of bounds for size {val.shape[0]}")
+    return val[index]
+
+
+def _alloc_missing(meta: Batch, batch: Batch, size: int, stack: bool, device) -> None:
+    """Dynamic keys popping up after the first add (``_alloc_by_keys_diff``, base.py:271-272)."""
+    for k, v in batch.items():
+        if k not in meta:
+            meta.__dict__[k] = create_value(v, size, stack, device)
+        elif isinstance(v, Batch) and isinstance(meta[k], Batch):
+            if meta[k].is_empty():
+                meta.__dict__[k] = create_value(v, size, stack, device)
+            else:
+                _alloc_missing(meta[k], v, size, stack, device)
+
+
+def _batch_to_numpy_copy(b: Batch) -> Batch:
+    out = Batch()
+    for k, v in b.items():
+        if isinstance(v, Batch):
+            out.__dict__[k] = _batch_to_numpy_copy(v)
+        elif isinstance(v, torch.Tensor):
+            out.__dict__[k] = v.detach().cpu().numpy()
+        else:
+            out.__dict__[k] = v
+    return out

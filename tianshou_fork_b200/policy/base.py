@@ -1,0 +1,275 @@
+"""Return estimators on the device -- drop-ins for the static methods of
+``tianshou.policy.BasePolicy`` (tianshou/policy/base.py:317-524).
+
+``compute_episodic_return`` and ``compute_nstep_return`` keep the reference signatures and
+semantics; the numba kernels ``_gae_return`` / ``_nstep_return`` and the NumPy glue around
+them are replaced by the CUDA kernels in ``csrc/gae.cu`` / ``csrc/nstep.cu``.
+
+Array kinds: the reference takes and returns NumPy.  Here NumPy inputs give NumPy outputs
+(f64, as numba produces) and CUDA-tensor inputs give CUDA-tensor outputs with no host
+synchronisation; ``buffer`` may be one of this package's device-resident buffers or any
+object exposing the reference buffer attributes as NumPy arrays (they are then staged to the
+device -- there is no CPU compute path).
+"""
+from __future__ import annotations
+
+from typing import Any, Callable, Dict, Optional, Tuple, Union
+
+import numpy as np
+import torch
+
+from .. import _lib as L
+from ..data.batch import Batch
+from ..data.buffer import ReplayBuffer
+
+ArrayLike = Union[np.ndarray, torch.Tensor]
+
+_ws_cache: Dict[Tuple[int, int], torch.Tensor] = {}
+
+
+def _device_of(buffer: Any) -> torch.device:
+    dev = getattr(buffer, "device", None)
+    if isinstance(dev, torch.device) and dev.type == "cuda":
+        return dev
+    return torch.device(f"cuda:{torch.cuda.current_device()}")
+
+
+def _dev(x: Any, device: torch.device, dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    if isinstance(x, torch.Tensor):
+        t = x.detach().to(device)
+    else:
+        t = torch.from_numpy(np.ascontiguousarray(np.asarray(x))).to(device)
+    if dtype is not None and t.dtype != dtype:
+        t = t.to(dtype)
+    return t.contiguous()
+
+
+def _float_dev(x: Any, device: torch.device) -> torch.Tensor:
+    t = _dev(x, device)
+    if t.dtype not in (torch.float32, torch.float64):
+        t = t.to(torch.float64)
+    return t.reshape(-1).contiguous()
+
+
+def _workspace(nbytes: int, device: torch.device) -> torch.Tensor:
+    key = (device.index or 0, torch.cuda.current_stream().cuda_stream)
+    ws = _ws_cache.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 1 << 16), dtype=torch.uint8, device=device)
+        _ws_cache[key] = ws
+    return ws
+
+
+def _buffer_layout(buffer: Any, device: torch.device):
+    """Device copies of (offset[B+1], last_index[B], lengths[B], B, sub_size, done, terminated)."""
+    if isinstance(buffer, ReplayBuffer):
+        st = buffer._state()
+        return (st["offset"], st["last_index"], st["lengths"], st["B"], st["sub_size"],
+                L.as_u8(buffer._meta["done"]), L.as_u8(buffer._meta["terminated"]))
+    # a reference-style host buffer: stage the fields the kernels read
+    if hasattr(buffer, "_extend_offset"):
+        off = np.asarray(buffer._extend_offset, dtype=np.int64)
+        last = np.asarray(buffer.last_index, dtype=np.int64)
+        lens = np.asarray(buffer._lengths, dtype=np.int64)
+        sizes = np.diff(off)
+        sub = int(sizes[0]) if np.all(sizes == sizes[0]) else 0
+    else:
+        size = max(len(buffer), 1)
+        off = np.array([0, size], dtype=np.int64)
+        last = np.asarray(buffer.last_index, dtype=np.int64).reshape(1)
+        lens = np.array([len(buffer)], dtype=np.int64)
+        sub = size
+    return (_dev(off, device), _dev(last, device), _dev(lens, device), last.size, sub,
+            L.as_u8(_dev(buffer.done, device, torch.bool)),
+            L.as_u8(_dev(buffer.terminated, device, torch.bool)))
+
+
+class BasePolicy:
+    """Static return estimators with the reference's signatures (policy/base.py:317-440).
+
+    The surrounding ``update`` pipeline (``sample -> process_fn -> learn -> post_process_fn``,
+    policy/base.py:288-315) is kept for subclasses in this package.
+    """
+
+    def __init__(self) -> None:
+        self.updating = False
+        self.lr_scheduler = None
+
+    # ---- update pipeline (policy/base.py:244-315) -----------------------------------------------
+    def process_fn(self, batch: Batch, buffer: Any, indices: ArrayLike) -> Batch:
+        return batch
+
+    def learn(self, batch: Batch, **kwargs: Any) -> Dict[str, Any]:
+        raise NotImplementedError
+
+    def post_process_fn(self, batch: Batch, buffer: Any, indices: ArrayLike) -> None:
+        if hasattr(buffer, "update_weight") and hasattr(batch, "weight"):
+            buffer.update_weight(indices, batch.weight)  # policy/base.py:285-286
+
+    def update(self, sample_size: int, buffer: Optional[Any], **kwargs: Any) -> Dict[str, Any]:
+        if buffer is None:
+            return {}
+        batch, indices = buffer.sample(sample_size)
+        self.updating = True
+        batch = self.process_fn(batch, buffer, indices)
+        result = self.learn(batch, **kwargs)
+        self.post_process_fn(batch, buffer, indices)
+        if self.lr_scheduler is not None:
+            self.lr_scheduler.step()
+        self.updating = False
+        return result
+
+    # ---- value mask (policy/base.py:317-335) ------------------------------------------------------
+    @staticmethod
+    def value_mask(buffer: Any, indices: ArrayLike):
+        """``~buffer.terminated[indices]``: whether obs_next of buffer[indices] is valid."""
+        term = buffer.terminated
+        if isinstance(term, torch.Tensor):
+            idx = indices if isinstance(indices, torch.Tensor) else torch.as_tensor(
+                np.asarray(indices), device=term.device)
+            out = ~term[idx.to(term.device)]
+            return out if isinstance(indices, torch.Tensor) else out.cpu().numpy()
+        return ~term[indices]
+
+    # ---- GAE (policy/base.py:337-384) ---------------------------------------------------------------
+    @staticmethod
+    def compute_episodic_return(
+        batch: Batch,
+        buffer: Any,
+        indices: ArrayLike,
+        v_s_: Optional[ArrayLike] = None,
+        v_s: Optional[ArrayLike] = None,
+        gamma: float = 0.99,
+        gae_lambda: float = 0.95,
+        out_dtype: Optional[torch.dtype] = None,
+    ) -> Tuple[ArrayLike, ArrayLike]:
+        """GAE advantages and TD(lambda) returns of ``batch == buffer[indices]``.
+
+        Same contract as the reference: episodes are delimited by the batch's
+        ``terminated | truncated`` plus ``buffer.unfinished_index()``; ``v_s_`` is masked by
+        ``~buffer.terminated[indices]``; ``v_s=None`` means ``roll(v_s_, 1)``; ``v_s_=None``
+        requires ``gae_lambda == 1`` and means zeros.  Returns ``(returns, advantage)``.
+
+        ``out_dtype`` defaults to float64 for NumPy callers (what numba returns) and to the
+        dtype of ``v_s`` for tensor callers (what ``to_torch_as`` would produce, a2c.py:115).
+        """
+        dev = _device_of(buffer)
+        tensor_io = isinstance(v_s_, torch.Tensor) or isinstance(v_s, torch.Tensor) or (
+            v_s_ is None and v_s is None and isinstance(batch.rew, torch.Tensor))
+        rew = _float_dev(batch.rew, dev)
+        n = rew.numel()
+        canon = buffer.is_canonical(indices) if hasattr(buffer, "is_canonical") else None
+        off, last, lens, B, sub, buf_done, buf_term = _buffer_layout(buffer, dev)
+        idx = _dev(indices, dev, torch.int64).reshape(-1)
+        assert idx.numel() == n, "indices must address one buffer slot per batch element"
+
+        if v_s_ is None:
+            assert np.isclose(gae_lambda, 1.0)  # policy/base.py:372
+            vn = torch.zeros_like(rew)  # :373
+            masked_vn = vn
+        else:
+            vn = _float_dev(v_s_, dev)
+            masked_vn = None  # the kernel applies the value mask (:376)
+        if v_s is None:  # :377 -- roll of the MASKED v_s_
+            if masked_vn is None:
+                masked_vn = vn * (buf_term[idx] == 0).to(vn.dtype)
+            vs = torch.roll(masked_vn, 1)
+        else:
+            vs = _float_dev(v_s, dev)
+        if vs.dtype != vn.dtype:  # one value dtype per launch: widen, never narrow
+            vs, vn = vs.to(torch.float64), vn.to(torch.float64)
+        assert vs.numel() == n and vn.numel() == n
+
+        if out_dtype is None:
+            out_dtype = vs.dtype if tensor_io else torch.float64
+        adv = torch.empty(n, dtype=out_dtype, device=dev)
+        ret = torch.empty(n, dtype=out_dtype, device=dev)
+        lib = L.lib()
+        if n == 0:
+            pass
+        elif canon is not None and v_s_ is not None:
+            # canonical [E, T] rollout (buffer.sample(0) of an un-wrapped VectorReplayBuffer):
+            # batch order IS row-major [E, T], every row ends on a done/unfinished step, so
+            # the rows kernel runs without indices, unfinished list or look-back.  The batch's
+            # own rew/flags are read (a caller may have rewritten batch.rew, e.g. GAIL).
+            E, T = canon
+            term = L.as_u8(_dev(batch.terminated, dev, torch.bool).reshape(-1))
+            trunc = L.as_u8(_dev(batch.truncated, dev, torch.bool).reshape(-1))
+            L.check(lib.ts_gae_rows(
+                L.ptr(rew), L.ptr(vs), L.ptr(vn), L.ptr(term), L.ptr(trunc), E, T, T, T,
+                float(gamma), float(gae_lambda), L.dtype_code(rew), L.dtype_code(vs),
+                L.TS_F64 if out_dtype == torch.float64 else L.TS_F32, L.ptr(adv), L.ptr(ret),
+                L.stream()), "ts_gae_rows")
+        else:
+            term = L.as_u8(_dev(batch.terminated, dev, torch.bool).reshape(-1))
+            trunc = L.as_u8(_dev(batch.truncated, dev, torch.bool).reshape(-1))
+            unfinished = torch.empty(B, dtype=torch.int64, device=dev)
+            L.check(lib.ts_unfinished_index(L.ptr(buf_done), L.ptr(last), L.ptr(lens), B,
+                                            L.ptr(unfinished), L.stream()),
+                    "ts_unfinished_index")
+            nbytes = lib.ts_gae_flat_workspace_bytes(n)
+            ws = _workspace(nbytes, dev)
+            L.check(lib.ts_gae_flat(
+                L.ptr(rew), L.ptr(vs), L.ptr(vn), L.ptr(term), L.ptr(trunc), L.ptr(idx),
+                L.ptr(buf_term) if v_s_ is not None else None, L.ptr(unfinished), L.ptr(off), B,
+                sub, n, float(gamma), float(gae_lambda), L.dtype_code(rew), L.dtype_code(vs),
+                L.TS_F64 if out_dtype == torch.float64 else L.TS_F32, L.ptr(adv), L.ptr(ret),
+                L.ptr(ws), ws.numel(), L.stream()), "ts_gae_flat")
+        if tensor_io:
+            return ret, adv
+        return ret.cpu().numpy(), adv.cpu().numpy()
+
+    # ---- n-step (policy/base.py:386-440) -------------------------------------------------------------
+    @staticmethod
+    def compute_nstep_return(
+        batch: Batch,
+        buffer: Any,
+        indice: ArrayLike,
+        target_q_fn: Callable[[Any, ArrayLike], torch.Tensor],
+        gamma: float = 0.99,
+        n_step: int = 1,
+        rew_norm: bool = False,
+    ) -> Batch:
+        r"""n-step TD target, stored in ``batch.returns`` as a tensor shaped ``(bsz, -1)`` with
+        the dtype/device of ``target_q_fn``'s output (policy/base.py:431, :437).
+
+        ``target_q_fn(buffer, terminal)`` receives ``terminal`` as the same array kind as
+        ``indice`` (CUDA tensor in -> CUDA tensor, NumPy in -> NumPy).
+        """
+        assert not rew_norm, \
+            "Reward normalization in computing n-step returns is unsupported now."
+        dev = _device_of(buffer)
+        off, last, lens, B, sub, buf_done, buf_term = _buffer_layout(buffer, dev)
+        rew = buffer.rew if isinstance(buffer, ReplayBuffer) else _dev(buffer.rew, dev)
+        if rew.dtype not in (torch.float32, torch.float64):
+            rew = rew.to(torch.float64)
+        idx = _dev(indice, dev, torch.int64).reshape(-1)
+        bsz = idx.numel()
+        terminal = torch.empty(bsz, dtype=torch.int64, device=dev)
+        ret_sum = torch.empty(bsz, dtype=torch.float64, device=dev)
+        coef = torch.empty(bsz, dtype=torch.float64, device=dev)
+        lib = L.lib()
+        L.check(lib.ts_nstep_chain(
+            L.ptr(idx), bsz, L.ptr(rew.contiguous()), L.dtype_code(rew), L.ptr(buf_done),
+            L.ptr(buf_term), L.ptr(off), B, sub, L.ptr(last), L.ptr(lens), float(gamma),
+            int(n_step), L.ptr(terminal), L.ptr(ret_sum), L.ptr(coef), L.stream()),
+            "ts_nstep_chain")
+        terminal_arg = terminal if isinstance(indice, torch.Tensor) else terminal.cpu().numpy()
+        with torch.no_grad():
+            target_q_torch = target_q_fn(buffer, terminal_arg)  # (bsz, ?)  :430
+        tq = target_q_torch.reshape(bsz, -1)
+        tq_dev = tq.to(dev)
+        if tq_dev.dtype not in (torch.float32, torch.float64):
+            tq_dev = tq_dev.to(torch.float32)
+        tq_dev = tq_dev.contiguous()
+        out = torch.empty_like(tq_dev)
+        L.check(lib.ts_nstep_combine(L.ptr(tq_dev), L.dtype_code(tq_dev), bsz, tq_dev.shape[1],
+                                     L.ptr(ret_sum), L.ptr(coef), L.ptr(out), L.stream()),
+                "ts_nstep_combine")
+        batch.returns = out.to(device=target_q_torch.device, dtype=target_q_torch.dtype)  # :437
+        if hasattr(batch, "weight"):  # prio buffer update  :438-439
+            w = batch.weight
+            if not isinstance(w, torch.Tensor):
+                w = torch.from_numpy(np.asarray(w))
+            batch.weight = w.to(device=target_q_torch.device, dtype=target_q_torch.dtype)
+        return batch
