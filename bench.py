@@ -1,0 +1,444 @@
+#!/usr/bin/env python
+"""Benchmark of the return / replay hot path on B200 (contract: see the task statement).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+Headline metric (BASELINE.json): GAE transitions/s on configs[1], the synthetic GAE sweep
+4096 env streams x 2048 steps per GPU, gamma 0.99, lambda 0.95 (weak scaling: every rank owns
+its own 4096 streams, as VectorReplayBuffer sub-buffers shard with no communication).
+A "step" is one pass of ``ts_gae_rows`` (C-ABI) over the rank's rollout, resident in HBM.
+The same JSON line also carries: ``e2e`` (host pinned buffers in/out through the package's
+host pipeline, PCIe copies inside the timed region), ``roofline`` (algorithmic 21 B/transition
+over the CUDA-event kernel time vs MEASURED_PEAKS.json), ``cpu_baseline`` (the oracle port on
+the box's host cores, bounded sample), ``per`` (PER samples/s on configs[3]: 2^20 leaves, batch
+4096, sample + importance weights + update_weight per step, CUDA-graph replay) and ``clocks``.
+
+``--impl reference`` times the CPU restatement of the reference (oracle/, the numba kernels
+re-stated in C) on all host threads; it is the one place besides ``cpu_baseline`` where
+bench.py executes oracle/ code, and only as the thing being compared against.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+E_PER_GPU, T_STEPS = 4096, 2048
+GAMMA, LAMBDA = 0.99, 0.95
+ALG_BYTES_PER_TRANSITION = 21  # rew 4 + v_s 4 + v_s_ 4 + end flag 1 + adv 4 + ret 4
+MOVED_BYTES_PER_TRANSITION = 22  # terminated and truncated are two separate bytes
+PER_LEAVES, PER_BATCH, PER_ALPHA, PER_BETA = 1 << 20, 4096, 0.6, 0.4
+PER_ALG_BYTES_PER_SAMPLE = 664
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=2000)
+    p.add_argument("--warmup", type=int, default=20)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--streams", type=int, default=E_PER_GPU, help="env streams per GPU")
+    p.add_argument("--horizon", type=int, default=T_STEPS)
+    p.add_argument("--skip-per", action="store_true")
+    p.add_argument("--skip-e2e", action="store_true")
+    p.add_argument("--skip-cpu", action="store_true")
+    return p.parse_args()
+
+
+def rollout(E, T, seed):
+    """SURVEY.md 8d C2 generator (same as tests/helpers.c2_rollout)."""
+    rng = np.random.default_rng(seed)
+    rew = rng.random((E, T), dtype=np.float32)
+    v_s = rng.standard_normal((E, T), dtype=np.float32)
+    v_next = np.empty_like(v_s)
+    v_next[:, :-1] = v_s[:, 1:]
+    v_next[:, -1] = rng.standard_normal(E, dtype=np.float32)
+    term = rng.random((E, T)) < 1 / 200
+    trunc = (rng.random((E, T)) < 1 / 1000) & ~term
+    return rew, v_s, v_next, term.view(np.uint8), trunc.view(np.uint8)
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons through NVML while a timed region runs."""
+
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown",
+               0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown"}
+
+    def __init__(self, index: int) -> None:
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:  # NVML unavailable: clocks stay unknown
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._stop.clear()
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        if self._thread is not None:
+            self._stop.set()
+            self._thread.join()
+            self._thread = None
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+    def bad(self):
+        return bool(self.reasons & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"})
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU side: the oracle port of the reference (C restatement of the numba kernels)
+# ---------------------------------------------------------------------------------------------
+def cpu_gae(threads: int, seconds: float, rows: int, T: int):
+    """Times orc_episodic_return_rows on a bounded sample (rows x T); returns transitions/s."""
+    from oracle import oracle as orc
+    rew, v_s, v_next, term, trunc = rollout(rows, T, seed=1234)
+    orc.episodic_return_rows(rew, v_s, v_next, term, trunc, GAMMA, LAMBDA, threads)  # warm
+    n, t0 = 0, time.perf_counter()
+    times = []
+    while time.perf_counter() - t0 < seconds or n < 3:
+        a = time.perf_counter()
+        orc.episodic_return_rows(rew, v_s, v_next, term, trunc, GAMMA, LAMBDA, threads)
+        times.append(time.perf_counter() - a)
+        n += 1
+    med = float(np.median(times))
+    return rows * T / med, med, n
+
+
+def cpu_per(seconds: float):
+    """Times one PER step (sample + weights + update) of the oracle port; samples/s."""
+    from oracle import oracle as orc
+    rng = np.random.default_rng(2)
+    tree = orc.SegTree(PER_LEAVES)
+    tree[np.arange(PER_LEAVES)] = (np.abs(rng.standard_normal(PER_LEAVES)) + 1e-7) ** PER_ALPHA
+    mx = mn = 1.0
+    times, t0 = [], time.perf_counter()
+    while time.perf_counter() - t0 < seconds or len(times) < 5:
+        u = rng.random(PER_BATCH)
+        td = rng.standard_normal(PER_BATCH).astype(np.float32)
+        a = time.perf_counter()
+        _, _, mx, mn = orc.per_step_c(tree, u, td, PER_ALPHA, PER_BETA, True, mx, mn)
+        times.append(time.perf_counter() - a)
+    med = float(np.median(times))
+    return PER_BATCH / med, med, len(times)
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm on the host cores (rank 0 only)."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    from oracle import oracle as orc
+    threads = orc.max_threads()
+    rows = min(args.streams, 1024)
+    # each "step" is one pass over a bounded sample of the workload: rows x T transitions
+    rew, v_s, v_next, term, trunc = rollout(rows, args.horizon, seed=1234)
+    f = lambda th: orc.episodic_return_rows(rew, v_s, v_next, term, trunc, GAMMA, LAMBDA, th)
+    for _ in range(max(args.warmup, 1)):
+        f(threads)
+    steps = max(1, min(args.steps, 200))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        f(threads)
+    dt = time.perf_counter() - t0
+    value = rows * args.horizon * steps / dt
+    one, _, _ = cpu_gae(1, 2.0, min(rows, 256), args.horizon)
+    per, per_med, _ = cpu_per(3.0)
+    line = {
+        "impl": "reference", "metric": "GAE transitions/s", "value": value,
+        "unit": "transitions/s", "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
+        "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "GAE sweep 4096 streams x 2048 steps per GPU, gamma 0.99 "
+                               "lambda 0.95 (BASELINE.json configs[1])",
+                   "streams_per_gpu": args.streams, "horizon": args.horizon},
+        "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": threads,
+                         "kind": "port",
+                         "sample": f"{rows} streams x {args.horizon} steps per pass, OpenMP over "
+                                   f"streams ({threads} threads); 1 thread: {one:.3e}"},
+        "e2e": {"value": value, "unit": "transitions/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "per": {"metric": "PER samples/s", "value": per, "unit": "samples/s", "cores": 1,
+                "us_per_step": per_med * 1e6,
+                "workload": "2^20 leaves, batch 4096, sample + weights + update_weight"},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU side
+# ---------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    from tianshou_fork_b200 import _lib as L
+    from tianshou_fork_b200.pipeline import GaeHostPipeline
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device(f"cuda:{local}")
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = L.lib()  # raises if the CUDA extension is missing: there is no fallback
+    E, T = args.streams, args.horizon
+    K, W = args.steps, max(args.warmup, 3)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- inputs: pinned host copies (for e2e) and HBM-resident copies (for value) -------------
+    host = [torch.from_numpy(a).pin_memory() for a in rollout(E, T, seed=rank)]
+    d_rew, d_vs, d_vn, d_term, d_trunc = [h.to(dev) for h in host]
+    adv = torch.empty(E, T, dtype=torch.float32, device=dev)
+    ret = torch.empty(E, T, dtype=torch.float32, device=dev)
+    stream = torch.cuda.current_stream()
+    launches = 0
+
+    def gae_step():
+        L.check(lib.ts_gae_rows(
+            d_rew.data_ptr(), d_vs.data_ptr(), d_vn.data_ptr(), d_term.data_ptr(),
+            d_trunc.data_ptr(), E, T, T, T, GAMMA, LAMBDA, L.TS_F32, L.TS_F32, L.TS_F32,
+            adv.data_ptr(), ret.data_ptr(), stream.cuda_stream), "ts_gae_rows")
+
+    sampler = ClockSampler(local)
+
+    def timed_gae():
+        for _ in range(W):
+            gae_step()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with sampler:
+            e0.record(stream)
+            for _ in range(K):
+                gae_step()
+            e1.record(stream)
+            barrier()
+        return e0.elapsed_time(e1)  # ms on the launching stream
+
+    ms = timed_gae()
+    if sampler.bad():  # thermal / hw slowdown seen: re-measure once
+        sampler.samples.clear()
+        sampler.reasons.clear()
+        ms = timed_gae()
+    launches += K
+    ms = max_over_ranks(ms)
+    n_trans = E * T
+    value = n_trans * world * K / (ms * 1e-3)
+    kernel_s = ms * 1e-3 / K
+    peak, peak_src = measured_peaks()
+    achieved = n_trans * ALG_BYTES_PER_TRANSITION / kernel_s / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "kernel": "gae_rows_kernel<float,float,float,256>",
+                "alg_bytes_per_launch": n_trans * ALG_BYTES_PER_TRANSITION,
+                "moved_bytes_per_launch": n_trans * MOVED_BYTES_PER_TRANSITION,
+                "us_per_launch": kernel_s * 1e6}
+
+    # ---- e2e: pinned host buffers in and out through the package's host pipeline --------------
+    e2e = None
+    if not args.skip_e2e:
+        pipe = GaeHostPipeline(E, T, chunks=16, device=dev)
+        h_adv = torch.empty(E, T, dtype=torch.float32).pin_memory()
+        h_ret = torch.empty(E, T, dtype=torch.float32).pin_memory()
+        Ke = max(3, min(K, 100))
+        for _ in range(3):
+            pipe.run(*host, h_adv, h_ret, GAMMA, LAMBDA)
+        barrier()
+        pipe.launches = 0
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with sampler:
+            e0.record(stream)
+            for _ in range(Ke):
+                pipe.run(*host, h_adv, h_ret, GAMMA, LAMBDA)
+            e1.record(stream)
+            barrier()
+        ems = max_over_ranks(e0.elapsed_time(e1))
+        if rank == 0:  # the copied-back result is the real one
+            assert torch.allclose(h_adv, adv.cpu(), rtol=0, atol=0)
+        e2e = {"value": n_trans * world * Ke / (ems * 1e-3), "unit": "transitions/s",
+               "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
+               "ms_per_step": ems / Ke, "steps": Ke,
+               "api": "tianshou_fork_b200.pipeline.GaeHostPipeline.run (16 row chunks, 3 streams)",
+               "launches": pipe.launches}
+
+    # ---- PER: sample + importance weights + update_weight, CUDA-graph replay ------------------
+    per = None
+    if not args.skip_per:
+        per = run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks)
+
+    # ---- CPU baseline (rank 0, N == 1 only): oracle port on the box's host cores --------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.skip_cpu:
+        v1, med1, n1 = cpu_gae(1, 8.0, 512, T)
+        cpu = {"value": v1, "unit": "transitions/s", "cores": 1, "kind": "port",
+               "sample": f"512 streams x {T} steps per pass, {n1} passes, median "
+                         f"{med1 * 1e3:.2f} ms; oracle/ts_oracle.c (C restatement of numba "
+                         "_gae_return + value mask + end flags), f32 in / f64 out",
+               "host_cpus": os.cpu_count()}
+        if per is not None:
+            pv, pmed, pn = cpu_per(4.0)
+            per["cpu_baseline"] = {"value": pv, "unit": "samples/s", "cores": 1, "kind": "port",
+                                   "sample": f"{pn} steps, median {pmed * 1e6:.1f} us"}
+            per["speedup_vs_cpu_port"] = per["value"] / pv
+
+    if rank == 0:
+        line = {
+            "metric": "GAE transitions/s", "value": value, "unit": "transitions/s",
+            "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": "GAE sweep 4096 streams x 2048 steps per GPU, gamma 0.99 "
+                                   "lambda 0.95 (BASELINE.json configs[1])",
+                       "streams_per_gpu": E, "horizon": T, "storage": "f32 values, u8 flags",
+                       "l2": f"inputs+outputs {n_trans * 22 / 1e6:.0f} MB per step > 126 MB L2 "
+                             "(no flush needed)",
+                       "parallelism": f"env streams sharded over {world} GPU(s), no collective"},
+            "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": launches,
+            "roofline": roofline, "cpu_baseline": cpu, "per": per,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
+    """BASELINE.json configs[3]/[4] shape: one 2^20-leaf tree per GPU, batch 4096."""
+    rng = np.random.default_rng(100 + rank)
+    size = bound = PER_LEAVES
+    tree = torch.zeros(2 * bound, dtype=torch.float64, device=dev)
+    stamp = torch.zeros(size, dtype=torch.int32, device=dev)
+    counter = torch.zeros(4, dtype=torch.int32, device=dev)
+    err = torch.zeros(1, dtype=torch.int32, device=dev)
+    scratch = torch.zeros(4, dtype=torch.int32, device=dev)
+    prio = torch.ones(2, dtype=torch.float64, device=dev)
+    leaves = torch.from_numpy((np.abs(rng.standard_normal(size)) + 1e-7) ** PER_ALPHA).to(dev)
+    all_idx = torch.arange(size, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    L.check(lib.ts_segtree_update(tree.data_ptr(), size, bound, all_idx.data_ptr(),
+                                  leaves.data_ptr(), L.TS_F64, 1, size, stamp.data_ptr(),
+                                  counter.data_ptr(), err.data_ptr(), st), "ts_segtree_update")
+    R = 8  # distinct (uniforms, td) sets inside one graph
+    u = torch.from_numpy(rng.random((R, PER_BATCH))).to(dev)
+    td = torch.from_numpy(rng.standard_normal((R, PER_BATCH)).astype(np.float32)).to(dev)
+    idx = torch.empty(R, PER_BATCH, dtype=torch.int64, device=dev)
+    w = torch.empty(R, PER_BATCH, dtype=torch.float64, device=dev)
+    roots = torch.zeros(world, 3, dtype=torch.float64, device=dev)
+    mine = torch.zeros(3, dtype=torch.float64, device=dev)
+
+    def step(r, s):
+        L.check(lib.ts_per_sample(tree.data_ptr(), bound, u[r].data_ptr(), PER_BATCH,
+                                  prio.data_ptr(), PER_BETA, 1, idx[r].data_ptr(),
+                                  w[r].data_ptr(), scratch.data_ptr(), err.data_ptr(), s),
+                "ts_per_sample")
+        L.check(lib.ts_per_update(tree.data_ptr(), size, bound, idx[r].data_ptr(),
+                                  td[r].data_ptr(), L.TS_F32, PER_BATCH, PER_ALPHA,
+                                  prio.data_ptr(), stamp.data_ptr(), counter.data_ptr(),
+                                  err.data_ptr(), s), "ts_per_update")
+
+    side = torch.cuda.Stream(dev)
+    with torch.cuda.stream(side):
+        for r in range(R):
+            step(r, side.cuda_stream)
+    side.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=side):
+        for r in range(R):
+            step(r, side.cuda_stream)
+    replays = 50
+    for _ in range(5):
+        graph.replay()
+    barrier()
+    stream = torch.cuda.current_stream()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(replays):
+        graph.replay()
+        if world > 1:  # shard roots + prio extrema to every rank
+            mine[0] = tree[1]
+            mine[1:] = prio
+            dist.all_gather_into_tensor(roots.view(-1), mine)
+    e1.record(stream)
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    assert int(err.item()) == 0, "PER range flag raised"
+    steps = replays * R
+    us = ms * 1e3 / steps
+    value = PER_BATCH * world * steps / (ms * 1e-3)
+    peak, _ = measured_peaks()
+    return {"metric": "PER samples/s", "value": value, "unit": "samples/s", "us_per_step": us,
+            "workload": "per GPU: 2^20-leaf f64 sum tree, batch 4096, alpha 0.6 beta 0.4; step = "
+                        "sample (descent + IS weights + batch-max norm) + update_weight "
+                        "(|td|+eps, pow, dedupe, bottom-up); 8 steps per CUDA graph"
+                        + ("; all_gather of shard roots per graph" if world > 1 else ""),
+            "gpu_launches_per_step": 2,
+            "roofline": {"bound": "hbm", "achieved": PER_BATCH * PER_ALG_BYTES_PER_SAMPLE / (us * 1e-6) / 1e9,
+                         "peak": peak, "unit": "GB/s",
+                         "frac": PER_BATCH * PER_ALG_BYTES_PER_SAMPLE / (us * 1e-6) / 1e9 / peak,
+                         "note": "latency-bound (>= 40 dependent L2 accesses); tree is L2-resident"}}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -167,10 +167,9 @@ def test_nstep_known_answers_from_reference_tests():
                          obs_next=0, info={}))
     indices = np.array([2, 3, 4, 5, 6, 7, 8, 9, 0, 1])
 
-    def target_q_fn(buffer, idx):  # test_returns.py:137-141: target_q = arange(10)
-        return torch.arange(10, dtype=torch.float32, device="cuda")[
-            torch.as_tensor(idx, device="cuda")].reshape(len(idx), 1) * 0 + \
-            torch.arange(len(idx), dtype=torch.float32, device="cuda").reshape(-1, 1)
+    def target_q_fn(buffer, idx):  # test_returns.py:137-140: minus the NEXT reward
+        nxt = buffer.next(idx)
+        return -buffer.rew[torch.as_tensor(nxt, device="cuda")].float()
 
     for n, expect in [(1, [2.6, 4, 4.4, 5.3, 6.2, 8, 8, 8.9, 9.8, 12]),
                       (2, [3.4, 4, 5.53, 6.62, 7.8, 8, 9.89, 10.98, 12.2, 12]),
