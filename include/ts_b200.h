@@ -54,6 +54,9 @@ typedef void* ts_stream_t; /* cudaStream_t */
 int32_t ts_version(void);
 const char* ts_error_string(int32_t code);
 int32_t ts_last_cuda_error(void);
+/* Kernel-selection knobs for benchmarking (process-wide, not part of the reference-facing
+ * surface).  Keys: "gae_rows_variant" (0 = automatic; see csrc/gae.cu:kRowsVariants). */
+int32_t ts_tune_set(const char* key, int64_t value);
 
 /* ------------------------------------------------------------------------------------------
  * GAE / TD(lambda) returns.

@@ -194,3 +194,72 @@ def test_c2_full_size_properties():
     lhs = (adv2 - adv).double().cpu().numpy()
     rhs = (adv - adv0).double().cpu().numpy()
     assert np.allclose(lhs, rhs, rtol=0, atol=2e-5 * np.abs(a).max())
+
+
+@pytest.fixture
+def rows_variant():
+    """Selects a gae_rows kernel variant for one test and restores the automatic choice."""
+    from tianshou_fork_b200 import _lib as L
+
+    def set_variant(v):
+        L.check(L.lib().ts_tune_set(b"gae_rows_variant", v), "ts_tune_set")
+
+    yield set_variant
+    set_variant(0)
+
+
+# (E, T, buf_stride): T and strides multiples of 16 => the bulk-copy pipelined kernel is legal.
+_TMA_SHAPES = [(1, 16, 16), (3, 48, 64), (5, 1024, 1024), (7, 1040, 2048), (2, 2048, 2048),
+               (3, 4096, 4096), (700, 2048, 2048), (1500, 272, 288), (2, 10000, 10000)]
+
+
+@pytest.mark.parametrize("variant", [2, 3, 4, 5, 6, 7, 8, 9])
+@pytest.mark.parametrize("dt", ["f32", "f64"])
+def test_rows_pipelined_variants_vs_oracle(variant, dt, rows_variant):
+    """Every cp.async.bulk-pipelined variant on whole / partial / multi-chunk rows, more rows
+    than persistent CTAs (several rows per CTA), padded buffer rows, f32 and f64 storage."""
+    from tianshou_fork_b200 import _lib as L
+    rows_variant(variant)
+    tdt = torch.float32 if dt == "f32" else torch.float64
+    for E, T, cap in _TMA_SHAPES:
+        rew, v_s, v_next, term, trunc = c2_rollout(E, T, seed=E + T, p_term=1 / 50,
+                                                   p_trunc=1 / 100)
+        ref_ret, ref_adv = orc.episodic_return_rows(rew, v_s, v_next, term, trunc, 0.99, 0.95)
+        pad = lambda a: np.concatenate([a, np.full((E, cap - T), 3, a.dtype)], axis=1)
+        g_rew = torch.from_numpy(pad(rew)).cuda().to(tdt)
+        g_term = torch.from_numpy(pad(term.view(np.uint8))).cuda()
+        g_trunc = torch.from_numpy(pad(trunc.view(np.uint8))).cuda()
+        g_vs = torch.from_numpy(v_s).cuda().to(tdt)
+        g_vn = torch.from_numpy(v_next).cuda().to(tdt)
+        adv = torch.full((E, T), float("nan"), dtype=tdt, device="cuda")
+        ret = torch.full((E, T), float("nan"), dtype=tdt, device="cuda")
+        code = L.dtype_code(g_rew)
+        for _ in range(2):
+            L.check(L.lib().ts_gae_rows(L.ptr(g_rew), L.ptr(g_vs), L.ptr(g_vn), L.ptr(g_term),
+                                        L.ptr(g_trunc), E, T, cap, T, 0.99, 0.95, code, code,
+                                        code, L.ptr(adv), L.ptr(ret), L.stream()), "ts_gae_rows")
+        tol = RTOL if dt == "f32" else 1e-9
+        assert _close(adv.cpu().numpy(), ref_adv, tol), (E, T, cap)
+        assert _close(ret.cpu().numpy(), ref_ret, tol), (E, T, cap)
+        # the padding of the buffer rows is never written through
+        assert torch.all(g_rew[:, T:] == 3)
+
+
+def test_rows_pipelined_matches_register_kernel_f64(rows_variant):
+    """Two independent kernels (different composition order of the same affine maps) agree to
+    f64 rounding noise on a C2-shaped batch."""
+    from tianshou_fork_b200 import _lib as L
+    E, T = 600, 2048
+    rew, v_s, v_next, term, trunc = c2_rollout(E, T, seed=9)
+    d = lambda a: torch.from_numpy(a).cuda()
+    g = [d(rew), d(v_s), d(v_next), d(term.view(np.uint8)), d(trunc.view(np.uint8))]
+    outs = []
+    for variant in (1, 4):
+        rows_variant(variant)
+        adv = torch.empty(E, T, dtype=torch.float64, device="cuda")
+        ret = torch.empty(E, T, dtype=torch.float64, device="cuda")
+        L.check(L.lib().ts_gae_rows(*[L.ptr(t) for t in g], E, T, T, T, 0.99, 0.95, 0, 0, 1,
+                                    L.ptr(adv), L.ptr(ret), L.stream()), "ts_gae_rows")
+        outs.append((adv, ret))
+    for a, b in zip(outs[0], outs[1]):
+        assert float((a - b).abs().max()) <= 1e-12 * float(a.abs().max())

@@ -3,7 +3,10 @@
 
 namespace ts {
 thread_local int32_t g_last_cuda_error = 0;
+int g_tune_gae_rows_variant = 0;
 }
+
+#include <string.h>
 
 extern "C" int32_t ts_version(void) { return TS_B200_VERSION; }
 
@@ -18,4 +21,10 @@ extern "C" const char* ts_error_string(int32_t code) {
         case TS_ERR_ALIGN: return "pointer not aligned to its element size";
         default: return "unknown error code";
     }
+}
+
+extern "C" int32_t ts_tune_set(const char* key, int64_t value) {
+    if (!key) return TS_ERR_BAD_ARG;
+    if (strcmp(key, "gae_rows_variant") == 0) { ts::g_tune_gae_rows_variant = (int)value; return TS_OK; }
+    return TS_ERR_BAD_ARG;
 }

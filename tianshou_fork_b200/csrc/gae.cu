@@ -259,6 +259,219 @@ gae_rows_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
 }
 
 // ============================================================================================
+// Canonical [E, T] kernel, bulk-copy pipelined (the C2 fast path).
+// Persistent CTAs; each owns rows blockIdx.x, blockIdx.x + gridDim.x, ... and walks every row
+// in time tiles of NT*8 steps from the end.  One elected thread keeps STAGES tiles of the five
+// input arrays in flight with cp.async.bulk (completion on an mbarrier per stage), so HBM
+// reads never wait for the scan arithmetic; outputs are staged in shared memory and leave as
+// two bulk stores per tile (full-line writes).  Requires 16-byte aligned rows (T, strides
+// multiples of 16 elements); anything else takes gae_rows_kernel above.
+// ============================================================================================
+// The arithmetic below is written for instruction count (the first version of this kernel was
+// issue-bound at 610 warp instructions per 8-step strip, profiles/r01b): flag bytes are
+// tested in place with one LOP3->predicate each, the end-of-episode cuts are applied with
+// predicated DFMAs instead of selected coefficients, and the carry is added to all eight
+// local advantages independently through gl^1..gl^8.
+struct GlPow { double p[VEC + 1]; };  // p[j] = (gamma*lambda)^j, kernel parameter
+
+template <typename T>
+__device__ __forceinline__ void smem_ld8(const T* p, T (&v)[VEC]) {
+    if constexpr (sizeof(T) == 4) {
+        const float4 a = *reinterpret_cast<const float4*>(p);
+        const float4 b = *reinterpret_cast<const float4*>(p + 4);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+        v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < VEC / 2; ++k) {
+            const double2 a = *reinterpret_cast<const double2*>(p + 2 * k);
+            v[2 * k] = a.x; v[2 * k + 1] = a.y;
+        }
+    }
+}
+template <typename T>
+__device__ __forceinline__ void smem_st8(T* p, const double (&v)[VEC]) {
+    if constexpr (sizeof(T) == 4) {
+        *reinterpret_cast<float4*>(p) =
+            make_float4((float)v[0], (float)v[1], (float)v[2], (float)v[3]);
+        *reinterpret_cast<float4*>(p + 4) =
+            make_float4((float)v[4], (float)v[5], (float)v[6], (float)v[7]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < VEC / 2; ++k)
+            *reinterpret_cast<double2*>(p + 2 * k) = make_double2(v[2 * k], v[2 * k + 1]);
+    }
+}
+// byte k (0..7) of the 8 flag bytes held in w is non-zero
+__device__ __forceinline__ bool flag_byte(const uint2& w, int k) {
+    return k < 4 ? (w.x & (0xffu << (8 * k))) != 0u : (w.y & (0xffu << (8 * (k - 4)))) != 0u;
+}
+// no flag byte at positions k..7
+__device__ __forceinline__ bool no_flag_from(const uint2& w, int k) {
+    return k < 4 ? (w.y == 0u && (w.x >> (8 * k)) == 0u) : (w.y >> (8 * (k - 4))) == 0u;
+}
+
+template <typename RewT, typename InT, typename OutT, int NT>
+struct RowsTmaLayout {
+    static constexpr int TILE = NT * VEC;
+    static constexpr int OFF_VS = TILE * (int)sizeof(RewT);
+    static constexpr int OFF_VN = OFF_VS + TILE * (int)sizeof(InT);
+    static constexpr int OFF_TERM = OFF_VN + TILE * (int)sizeof(InT);
+    static constexpr int OFF_TRUNC = OFF_TERM + TILE;
+    static constexpr int IN_BYTES = OFF_TRUNC + TILE;          // one input stage
+    static constexpr int OUT_BYTES = 2 * TILE * (int)sizeof(OutT);  // adv | ret
+    static constexpr int IN_BYTES_PER_STEP = (int)sizeof(RewT) + 2 * (int)sizeof(InT) + 2;
+    static size_t smem_bytes(int stages) {
+        return (size_t)stages * IN_BYTES + OUT_BYTES + (size_t)stages * 8;
+    }
+};
+
+template <typename RewT, typename InT, typename OutT, int NT>
+__global__ void __launch_bounds__(NT)
+gae_rows_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
+                    const InT* __restrict__ v_next, const uint8_t* __restrict__ term,
+                    const uint8_t* __restrict__ trunc, int E, int64_t T, int64_t buf_stride,
+                    int64_t val_stride, double gamma, const GlPow glp, OutT* __restrict__ adv,
+                    OutT* __restrict__ ret, int stages) {
+    using L = RowsTmaLayout<RewT, InT, OutT, NT>;
+    constexpr int TILE = L::TILE;
+    constexpr int NW = NT / 32;
+    static_assert(NW > 1 && NW <= 8, "cross-warp step assumes 2..8 warps");
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ double sP[NW], sX[NW];
+    __shared__ double s_carry;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int e0 = tid * VEC;
+    unsigned char* out_base = smem + (size_t)stages * L::IN_BYTES;
+    const uint32_t bar0 = smem_u32(out_base + L::OUT_BYTES);
+    OutT* s_adv = reinterpret_cast<OutT*>(out_base);
+    OutT* s_ret = s_adv + TILE;
+
+    const int nchunks = (int)((T + TILE - 1) / TILE);
+    const int n_first = (int)(T - (int64_t)(nchunks - 1) * TILE);  // steps in a row's last tile
+    const int rows_mine = (int)blockIdx.x < E ? (E - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    const int ntiles = rows_mine * nchunks;  // E * nchunks < 2^31 checked by the host
+
+    // producer cursor (elected thread): tile p_it = (row p_row, chunk p_c)
+    int p_it = 0, p_row = blockIdx.x, p_c = nchunks - 1, p_stage = 0;
+    auto issue = [&]() {
+        const int n = p_c == nchunks - 1 ? n_first : TILE;
+        const int64_t t0 = (int64_t)p_c * TILE;
+        const uint32_t bar = bar0 + 8u * p_stage;
+        const uint32_t dst = smem_u32(smem + (size_t)p_stage * L::IN_BYTES);
+        mbar_expect_tx(bar, (uint32_t)n * L::IN_BYTES_PER_STEP);
+        const int64_t b = (int64_t)p_row * buf_stride + t0, v = (int64_t)p_row * val_stride + t0;
+        bulk_g2s(dst, rew + b, (uint32_t)n * sizeof(RewT), bar);
+        bulk_g2s(dst + L::OFF_VS, v_s + v, (uint32_t)n * sizeof(InT), bar);
+        bulk_g2s(dst + L::OFF_VN, v_next + v, (uint32_t)n * sizeof(InT), bar);
+        bulk_g2s(dst + L::OFF_TERM, term + b, (uint32_t)n, bar);
+        bulk_g2s(dst + L::OFF_TRUNC, trunc + b, (uint32_t)n, bar);
+        ++p_it;
+        if (--p_c < 0) { p_c = nchunks - 1; p_row += gridDim.x; }
+        if (++p_stage == stages) p_stage = 0;
+    };
+
+    if (tid == 0) {
+        for (int s = 0; s < stages; ++s) mbar_init(bar0 + 8u * s, 1u);
+        fence_mbar_init();
+    }
+    __syncthreads();
+    if (tid == 0)
+        while (p_it < stages && p_it < ntiles) issue();
+
+    // consumer cursor (all threads)
+    int row = blockIdx.x, c = nchunks - 1, stage = 0;
+    uint32_t parity = 0;
+    double carry = 0.0;
+    for (int it = 0; it < ntiles; ++it) {
+        const bool row_end = c == nchunks - 1;  // this tile holds the stream's last step
+        const int n = row_end ? n_first : TILE;
+        if (row_end) carry = 0.0;               // nothing beyond the end of the stream
+        mbar_wait(bar0 + 8u * stage, parity);
+
+        const unsigned char* in = smem + (size_t)stage * L::IN_BYTES;
+        const bool live = e0 < n;  // n is a multiple of 16: strips are whole or empty
+        RewT rw[VEC];
+        InT vs[VEC], vn[VEC];
+        smem_ld8(reinterpret_cast<const RewT*>(in) + e0, rw);
+        smem_ld8(reinterpret_cast<const InT*>(in + L::OFF_VS) + e0, vs);
+        smem_ld8(reinterpret_cast<const InT*>(in + L::OFF_VN) + e0, vn);
+        const uint2 wt = *reinterpret_cast<const uint2*>(in + L::OFF_TERM + e0);
+        uint2 wc = *reinterpret_cast<const uint2*>(in + L::OFF_TRUNC + e0);
+        wc.x |= wt.x;
+        wc.y |= wt.y;
+        // the stream's last step is done or the unfinished index (manager.py:68-74)
+        if (row_end && e0 + VEC == n) wc.y |= 0x01000000u;
+
+        // d[k] = delta_k = rew + gamma * v_s_ * ~terminated - v_s   (policy/base.py:376, 491)
+        double d[VEC];
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+            const InT v1 = flag_byte(wt, k) ? InT(0) : vn[k];
+            d[k] = fma((double)v1, gamma, (double)rw[k]) - (double)vs[k];
+        }
+        // local advantages (zero carry-in): d[k] += gl * d[k+1] unless step k ends an episode
+#pragma unroll
+        for (int k = VEC - 2; k >= 0; --k)
+            if (!flag_byte(wc, k)) d[k] = fma(glp.p[1], d[k + 1], d[k]);
+        // the strip as a map of its carry-in: c -> X + P * c
+        double P = (wc.x | wc.y) == 0u ? glp.p[VEC] : 0.0;
+        double X = d[0];
+        if (!live) { P = 1.0; X = 0.0; }
+
+        // ---- suffix scan over the warp: (P, X) <- this lane's strip .. lane 31's strip --------
+#pragma unroll
+        for (int dlt = 1; dlt < 32; dlt <<= 1) {
+            const double P2 = shfl_down_f64(P, dlt), X2 = shfl_down_f64(X, dlt);
+            if (lane + dlt < 32) {
+                X = fma(P, X2, X);
+                P *= P2;
+            }
+        }
+        // map of the lanes after this one
+        double eP = shfl_down_f64(P, 1), eX = shfl_down_f64(X, 1);
+        if (lane == 31) { eP = 1.0; eX = 0.0; }
+        if (lane == 0) { sP[warp] = P; sX[warp] = X; }
+        if (tid == 0) bulk_wait_read0();  // previous tile's stores have left the out buffer
+        __syncthreads();
+        // every thread holds its strip in registers: the stage can be refilled
+        if (tid == 0 && p_it < ntiles) issue();
+
+        // carry into this thread's strip: through the later warps, then the later lanes
+        double cin = carry;
+#pragma unroll
+        for (int w = NW - 1; w >= 1; --w)
+            if (w > warp) cin = fma(sP[w], cin, sX[w]);
+        cin = fma(eP, cin, eX);
+        // A_k = d[k] + gl^(8-k) * cin while no episode ends in k..7
+        double r_out[VEC];
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+            if (no_flag_from(wc, k)) d[k] = fma(glp.p[VEC - k], cin, d[k]);
+            r_out[k] = d[k] + (double)vs[k];  // returns = advantage + v_s (:382)
+        }
+        if (live) {
+            smem_st8(s_adv + e0, d);
+            smem_st8(s_ret + e0, r_out);
+        }
+        fence_proxy_async_smem();
+        if (tid == 0) s_carry = d[0];  // advantage at the tile's first step
+        __syncthreads();
+        if (tid == 0) {
+            const int64_t v = (int64_t)row * val_stride + (int64_t)c * TILE;
+            bulk_s2g(adv + v, smem_u32(s_adv), (uint32_t)n * sizeof(OutT));
+            bulk_s2g(ret + v, smem_u32(s_ret), (uint32_t)n * sizeof(OutT));
+            bulk_commit();
+        }
+        carry = s_carry;
+        if (--c < 0) { c = nchunks - 1; row += gridDim.x; }
+        if (++stage == stages) { stage = 0; parity ^= 1u; }
+    }
+    if (tid == 0) bulk_wait0();
+}
+
+// ============================================================================================
 // General flattened kernel: single pass over N with decoupled look-back between tiles.
 // Tiles are claimed through an atomic ticket so that a tile's successors in time (which it
 // depends on) always started before it: ticket 0 is the LAST tile of the sequence.
@@ -422,6 +635,51 @@ gae_flat_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     }
 }
 
+// Variants of the canonical kernel (ts_tune_set("gae_rows_variant", id)); 0 = automatic.
+struct RowsVariant { int nt, stages, ctas_per_sm; };  // nt == 0: register kernel
+constexpr RowsVariant kRowsVariants[] = {
+    {0, 0, 0},     // 0: automatic
+    {0, 0, 0},     // 1: gae_rows_kernel (LDG -> registers, one CTA per row)
+    {128, 3, 4},   // 2
+    {128, 4, 3},   // 3
+    {256, 3, 2},   // 4
+    {256, 2, 3},   // 5
+    {128, 2, 6},   // 6
+    {256, 4, 1},   // 7
+    {256, 6, 1},   // 8
+    {128, 6, 2},   // 9
+};
+constexpr int kNumRowsVariants = (int)(sizeof(kRowsVariants) / sizeof(kRowsVariants[0]));
+constexpr int kRowsAutoTma = 2;
+
+template <typename RewT, typename InT, typename OutT, int NT>
+int32_t launch_rows_tma(const void* rew, const void* v_s, const void* v_next,
+                        const uint8_t* term, const uint8_t* trunc, int64_t E, int64_t T,
+                        int64_t bs, int64_t vs, double gamma, double lam, void* adv, void* ret,
+                        int stages, int ctas_per_sm, cudaStream_t stream) {
+    using L = RowsTmaLayout<RewT, InT, OutT, NT>;
+    auto kern = gae_rows_tma_kernel<RewT, InT, OutT, NT>;
+    while (stages > 2 && L::smem_bytes(stages) > 227 * 1024) --stages;  // wide dtypes
+    const size_t smem = L::smem_bytes(stages);
+    if (smem > 227 * 1024) return TS_ERR_BAD_ARG;
+    static size_t attr_bytes = 0;  // per instantiation
+    if (smem > attr_bytes) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem);
+        if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
+        attr_bytes = smem;
+    }
+    const int64_t cap = (int64_t)kNumSMs * ctas_per_sm;
+    const unsigned grid = (unsigned)(E < cap ? E : cap);
+    GlPow glp;
+    glp.p[0] = 1.0;
+    for (int j = 1; j <= VEC; ++j) glp.p[j] = glp.p[j - 1] * (gamma * lam);
+    kern<<<grid, NT, smem, stream>>>((const RewT*)rew, (const InT*)v_s, (const InT*)v_next, term,
+                                     trunc, (int)E, T, bs, vs, gamma, glp, (OutT*)adv,
+                                     (OutT*)ret, stages);
+    return check_launch();
+}
+
 template <typename RewT, typename InT, typename OutT>
 int32_t launch_rows(const void* rew, const void* v_s, const void* v_next, const uint8_t* term,
                     const uint8_t* trunc, int64_t E, int64_t T, int64_t bs, int64_t vs,
@@ -429,6 +687,25 @@ int32_t launch_rows(const void* rew, const void* v_s, const void* v_next, const 
     const int vec_ok = aligned(rew, 16) && aligned(v_s, 16) && aligned(v_next, 16) &&
                        aligned(term, 8) && aligned(trunc, 8) && aligned(adv, 16) &&
                        aligned(ret, 16) && bs % VEC == 0 && vs % VEC == 0;
+    // bulk-copy path: every row segment starts and ends on a 16-byte boundary
+    const bool tma_ok = vec_ok && aligned(term, 16) && aligned(trunc, 16) && T % 16 == 0 &&
+                        bs % 16 == 0 && vs % 16 == 0 &&
+                        E * ((T + 1023) / 1024) < 0x7fffffffLL;  // 32-bit tile counters
+    int variant = g_tune_gae_rows_variant;
+    if (variant < 0 || variant >= kNumRowsVariants) return TS_ERR_BAD_ARG;
+    // automatic: the pipelined kernel pays off once there are enough rows to keep the
+    // persistent CTAs busy with several tiles each; short batches stay on the register kernel
+    if (variant == 0) variant = (tma_ok && E * T >= (1 << 20)) ? kRowsAutoTma : 1;
+    const RowsVariant rv = kRowsVariants[variant];
+    if (rv.nt != 0 && tma_ok) {
+        if (rv.nt == 128)
+            return launch_rows_tma<RewT, InT, OutT, 128>(rew, v_s, v_next, term, trunc, E, T, bs,
+                                                         vs, gamma, lam, adv, ret, rv.stages,
+                                                         rv.ctas_per_sm, stream);
+        return launch_rows_tma<RewT, InT, OutT, 256>(rew, v_s, v_next, term, trunc, E, T, bs, vs,
+                                                     gamma, lam, adv, ret, rv.stages,
+                                                     rv.ctas_per_sm, stream);
+    }
     const double gl = gamma * lam;
 #define TS_ROWS(NT)                                                                            \
     gae_rows_kernel<RewT, InT, OutT, NT><<<(unsigned)E, NT, 0, stream>>>(                      \
