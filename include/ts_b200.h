@@ -57,6 +57,9 @@ int32_t ts_last_cuda_error(void);
 /* Kernel-selection knobs for benchmarking (process-wide, not part of the reference-facing
  * surface).  Keys: "gae_rows_variant" (0 = automatic; see csrc/gae.cu:kRowsVariants). */
 int32_t ts_tune_set(const char* key, int64_t value);
+/* Debug: globaltimer ns at the six phase boundaries of the most recent tiered tree update
+ * (synchronises the device; host buffer of 6 uint64). */
+int32_t ts_debug_update_phases(uint64_t* out6);
 
 /* ------------------------------------------------------------------------------------------
  * GAE / TD(lambda) returns.
@@ -152,9 +155,13 @@ int32_t ts_nstep_combine(const void* target_q, int32_t q_dtype, int64_t bsz, int
  *           left + right (no FMA), so node values are bit-identical to the reference's.
  * ---------------------------------------------------------------------------------------- */
 
-/* Scratch owned by the tree object, both zero-initialised ONCE by the caller and left
- * all-zero again by every call: `stamp` is uint32[size] (last-writer-wins arbitration of
- * duplicated indices, segtree.py:40-49), `counter` is uint32[4] (block arrival counter). */
+/* Scratch owned by the tree object, both zero-initialised ONCE by the caller and opaque
+ * afterwards (one tree, one stream at a time): `stamp` is uint32[size], 16-byte aligned
+ * (last-writer-wins arbitration of duplicated indices, segtree.py:40-49; entries carry a
+ * per-call epoch so they never need resetting), `counter` is uint32[4] (grid-barrier
+ * arrivals, epoch).  Batches of up to 16383 indices on trees of more than 4096 leaves run as
+ * ONE cooperative launch (<= 148 CTAs that wait on each other: do not run two of them
+ * concurrently on one device from different streams). */
 /* tree[index[j]] = value[j] for j < M (M < 2^31), then every ancestor recomputed bottom-up.
  * value is f32 or f64 (cast on store, segtree.py:91-92); value_stride 0 broadcasts value[0].
  * index outside [0,size) sets TS_FLAG_INDEX_RANGE in *err_flag and that item is skipped. */
@@ -181,7 +188,8 @@ int32_t ts_segtree_prefix_idx(const double* tree, int64_t bound, void* value,
  * ---------------------------------------------------------------------------------------- */
 /* idx = prefix_idx(u * tree[1]); weight = (leaf/min_prio)^(-beta); if weight_norm,
  * weight /= max(weight) (done by the last CTA to finish, same launch).  u is NOT mutated.
- * scratch16: 16 bytes, zero-initialised once by the caller, left zero by every call. */
+ * The batch is handled by one 8-CTA thread-block cluster; the maximum is exchanged through
+ * distributed shared memory.  scratch16 is unused (kept for ABI stability; may be NULL). */
 int32_t ts_per_sample(const double* tree, int64_t bound, const double* u, int64_t M,
                       const double* prio, double beta, int32_t weight_norm, int64_t* idx,
                       double* weight, void* scratch16, int32_t* err_flag, ts_stream_t stream);

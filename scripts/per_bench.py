@@ -1,0 +1,106 @@
+#!/usr/bin/env python
+"""GPU-box microbenchmark of the PER kernels (BASELINE.json configs[3] shape): CUDA-graph replay
+of sample-only, update-only and sample+update steps, for both tier group sizes."""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from tianshou_fork_b200 import _lib as L  # noqa: E402
+
+
+def main():
+    lib = L.lib()
+    dev = torch.device("cuda:0")
+    lg = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+    B = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
+    size = bound = 1 << lg
+    rng = np.random.default_rng(0)
+    tree = torch.zeros(2 * bound, dtype=torch.float64, device=dev)
+    stamp = torch.zeros(size, dtype=torch.int32, device=dev)
+    counter = torch.zeros(4, dtype=torch.int32, device=dev)
+    err = torch.zeros(1, dtype=torch.int32, device=dev)
+    prio = torch.ones(2, dtype=torch.float64, device=dev)
+    leaves = torch.from_numpy((np.abs(rng.standard_normal(size)) + 1e-7) ** 0.6).to(dev)
+    all_idx = torch.arange(size, device=dev)
+    st0 = torch.cuda.current_stream().cuda_stream
+    L.check(lib.ts_segtree_update(tree.data_ptr(), size, bound, all_idx.data_ptr(),
+                                  leaves.data_ptr(), L.TS_F64, 1, size, stamp.data_ptr(),
+                                  counter.data_ptr(), err.data_ptr(), st0), "fill")
+    R = 8
+    u = torch.from_numpy(rng.random((R, B))).to(dev)
+    td = torch.from_numpy(rng.standard_normal((R, B)).astype(np.float32)).to(dev)
+    idx = torch.from_numpy(rng.integers(0, size, (R, B))).to(dev)
+    w = torch.empty(R, B, dtype=torch.float64, device=dev)
+
+    def sample(r, s):
+        L.check(lib.ts_per_sample(tree.data_ptr(), bound, u[r].data_ptr(), B, prio.data_ptr(),
+                                  0.4, 1, idx[r].data_ptr(), w[r].data_ptr(), None,
+                                  err.data_ptr(), s), "sample")
+
+    def update(r, s):
+        L.check(lib.ts_per_update(tree.data_ptr(), size, bound, idx[r].data_ptr(),
+                                  td[r].data_ptr(), L.TS_F32, B, 0.6, prio.data_ptr(),
+                                  stamp.data_ptr(), counter.data_ptr(), err.data_ptr(), s),
+                "update")
+
+    def prefix_on(buf, r, s):
+        L.check(lib.ts_segtree_prefix_idx(tree.data_ptr(), bound, buf[r].data_ptr(), L.TS_F64, B, 1,
+                                          idx[r].data_ptr(), err.data_ptr(), s), "prefix")
+
+    def timed(name, fn):
+        side = torch.cuda.Stream(dev)
+        with torch.cuda.stream(side):
+            for r in range(R):
+                fn(r, side.cuda_stream)
+        side.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            for r in range(R):
+                fn(r, side.cuda_stream)
+        for _ in range(5):
+            g.replay()
+        torch.cuda.synchronize()
+        best = 1e9
+        for _ in range(3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(50):
+                g.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1) * 1e3 / (50 * R))
+        print(json.dumps({"what": name, "lg": lg, "batch": B, "us_per_call": best}), flush=True)
+
+    import ctypes
+    for group in (128, 256):
+        L.check(lib.ts_tune_set(b"segtree_group", group), "tune")
+        timed(f"update(group={group})", update)
+        ph = (ctypes.c_uint64 * 6)()
+        torch.cuda.synchronize()
+        L.check(lib.ts_debug_update_phases(ph), "phases")
+        t = list(ph)
+        print(json.dumps({"phases_ns": dict(zip(
+            ["A+bar", "tier0", "bar->cta0", "top_load", "top_levels"],
+            [t[i + 1] - t[i] for i in range(5)]))}), flush=True)
+    L.check(lib.ts_tune_set(b"segtree_group", 128), "tune")
+    for cl in (8, 16):
+        L.check(lib.ts_tune_set(b"per_cluster", cl), "tune")
+        timed(f"sample(cluster={cl})", sample)
+    L.check(lib.ts_tune_set(b"per_cluster", 8), "tune")
+    for mc in (32, 64, 148):
+        L.check(lib.ts_tune_set(b"segtree_max_ctas", mc), "tune")
+        timed(f"update(max_ctas={mc})", update)
+    L.check(lib.ts_tune_set(b"segtree_max_ctas", 148), "tune")
+    timed("sample+update", lambda r, s: (sample(r, s), update(r, s)))
+    u2 = u.clone()
+    timed("copy+prefix_idx", lambda r, s: (u2[r].copy_(u[r]), prefix_on(u2, r, s)))
+    assert int(err.item()) == 0, int(err.item())
+
+
+if __name__ == "__main__":
+    main()

@@ -89,7 +89,7 @@ def test_update_and_descent_vs_oracle(size, bsz):
         tree[torch.from_numpy(idx).cuda()] = torch.from_numpy(val).cuda()
     tree.check_errors()
     assert np.array_equal(tree._value.cpu().numpy(), ref._value)
-    assert not tree._stamp.any() and not tree._counter.any()  # scratch left clean
+    assert int(tree._counter[0]) == 0  # grid-barrier arrivals are reset for the next call
     u = rng.random(4096)
     s = u * ref.reduce()
     want = ref.get_prefix_sum_idx(s.copy())
@@ -194,7 +194,16 @@ def test_per_full_size_step_vs_oracle():
         ref.update_weight(idx, td)
         buf.update_weight(torch.from_numpy(idx).cuda(), torch.from_numpy(td).cuda())
         got_tree = buf.weight._value.cpu().numpy()
-        assert np.allclose(got_tree, ref.weight._value, rtol=2e-7, atol=0)
+        # NumPy's f32 power (prio.py:87) is up to ~2.6 f32 ulp from the exact value (measured
+        # on the golden vectors); ours is the f64 power rounded once
+        assert np.allclose(got_tree, ref.weight._value, rtol=6e-7, atol=0)
+        # ... so the new leaves equal the correctly rounded f32 power, bit for bit
+        lastpos = {int(i): k for k, i in enumerate(idx)}
+        keys = np.fromiter(lastpos.keys(), np.int64)
+        tdl = td[np.fromiter(lastpos.values(), np.int64)]
+        p32 = np.abs(tdl) + np.finfo(np.float32).eps
+        exact = (p32.astype(np.float64) ** 0.6).astype(np.float32).astype(np.float64)
+        assert np.count_nonzero(got_tree[size + keys] != exact) <= 1
         # re-anchor on the oracle's leaves (f32 pow is not bit-reproducible across libms)
         touched = np.unique(idx)
         buf.weight[torch.from_numpy(touched).cuda()] = torch.from_numpy(

@@ -650,7 +650,7 @@ constexpr RowsVariant kRowsVariants[] = {
     {128, 6, 2},   // 9
 };
 constexpr int kNumRowsVariants = (int)(sizeof(kRowsVariants) / sizeof(kRowsVariants[0]));
-constexpr int kRowsAutoTma = 2;
+constexpr int kRowsAutoTma = 5;  // 256 threads x 2 stages x 3 CTAs/SM: best of the C2 sweep (profiles/)
 
 template <typename RewT, typename InT, typename OutT, int NT>
 int32_t launch_rows_tma(const void* rew, const void* v_s, const void* v_next,

@@ -53,14 +53,20 @@ __device__ __forceinline__ double per_priority(const ValueSrc& v, int64_t j) {
     return fabs(((const double*)v.ptr)[j]) + (double)kEpsF32;
 }
 
+// x^a for x >= 0 as exp2(a * log2(x)): relative error ~ |a log2 x| * 2^-52 (a few 1e-15), about
+// a third of the instructions of the correctly-rounded pow().  Used where the result is rounded
+// to f32 anyway (the reference's f32 power, prio.py:87) and for the importance weights
+// (parity tolerance 1e-12); f64 leaves keep pow().
+__device__ __forceinline__ double pow_fast(double x, double a) { return exp2(a * log2(x)); }
+
 __device__ __forceinline__ double leaf_value(const ValueSrc& v, int64_t j) {
     switch (v.mode) {
         case VM_F64: return ((const double*)v.ptr)[j * v.stride];
         case VM_F32: return (double)((const float*)v.ptr)[j * v.stride];
-        case VM_PER_F32: return (double)(float)pow(per_priority(v, j), v.alpha);
+        case VM_PER_F32: return (double)(float)pow_fast(per_priority(v, j), v.alpha);
         case VM_PER_F64: return pow(per_priority(v, j), v.alpha);
         case VM_INIT_F64: return pow(v.prio[0], v.alpha);
-        default: return (double)(float)pow(v.prio[0], v.alpha);
+        default: return (double)(float)pow_fast(v.prio[0], v.alpha);
     }
 }
 
@@ -76,126 +82,271 @@ __device__ __forceinline__ void atomic_min_pos(double* addr, double v) {
     atomicMin((unsigned long long*)addr, (unsigned long long)__double_as_longlong(v));
 }
 
-constexpr int UPD_NT = 128;
-constexpr int UPD_S = 128;             // subtrees = CTAs of the small-batch update
-constexpr int64_t kSmallM = 8192;      // item list of one CTA: M * 8 bytes of shared memory
+constexpr int64_t kSmallM = 16383;     // tiered path: batch position + 1 fits the stamp's 14 bits
 constexpr int64_t kDenseBound = 4096;  // trees up to this many leaves are rebuilt densely
+constexpr int kTagShift = 14;
+constexpr uint32_t kTagMax = (1u << (32 - kTagShift)) - 1u;
 
 // ============================================================================================
-// Small-batch update: one CTA per aligned subtree.
+// Tiered small-batch update (the replay-step case): ONE cooperative launch.
+//
+//   phase A   every item stamps its leaf: atomicMax(stamp[idx], tag << 14 | (j + 1)).  The tag
+//             is a per-call epoch kept on the device, so stale stamps of earlier calls are
+//             ignored and nothing has to be reset (CUDA-graph replays advance it themselves).
+//   barrier
+//   tier 0    one warp per item rebuilds the aligned group of G = 2^LG leaves that holds the
+//             item: loads the G leaves and their G stamps, replaces every stamped leaf by its
+//             new value (the stamp names the LAST batch position that wrote it,
+//             segtree.py:40-49), then forms the LG levels above with in-register adds and
+//             shuffles -- node = left + right in IEEE f64, the reference's order
+//             (segtree.py:104) -- and writes leaves and nodes back.  Items that share a group
+//             do identical work and write identical bits (benign).
+//   barrier   (+ further tiers of the same shape for trees deeper than LG + 13 levels)
+//   top       CTA 0 loads the remaining level (<= 8192 nodes) into shared memory and rebuilds
+//             every level above it densely; the other CTAs have already exited.
+//
+// Dependent memory round trips: index, stamp RED, group load, group store, top load -- about
+// five plus two grid barriers, against ~40 for a level-by-level climb.
 // ============================================================================================
-__global__ void __launch_bounds__(UPD_NT)
-segtree_update_small(double* __restrict__ tree, int64_t size, int64_t bound,
-                     const int64_t* __restrict__ index, ValueSrc vs, int64_t M,
-                     uint32_t* __restrict__ stamp, uint32_t* __restrict__ counter,
-                     int32_t* __restrict__ err_flag, int shift, int S) {
-    extern __shared__ uint2 items[];  // (heap node, batch position)
-    __shared__ int n_items;
-    __shared__ bool s_last;
-    __shared__ double s_top[2 * UPD_S];
-    __shared__ double s_red[2 * (UPD_NT / 32)];
+// Phase timestamps of the most recent tiered update (globaltimer ns, CTA 0 / thread 0):
+// start, after phase A barrier, after tier 0, after the last barrier, after top load, end.
+__device__ unsigned long long g_update_phase_ns[8];
+__device__ __forceinline__ void phase_mark(int slot) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_update_phase_ns[slot] = t;
+    }
+}
 
-    const int tid = threadIdx.x;
-    const int64_t sub = blockIdx.x;
-    if (tid == 0) n_items = 0;
-    __syncthreads();
+constexpr int TIER_NT = 1024;
+constexpr int kTopMax = 8192;  // nodes of the level handed to the top phase (128 KB heap)
 
-    // ---- scan the batch: claim items of this subtree, stamp their leaves ----------------------
-    double pmax = 0.0, pmin = INFINITY;
-    const bool reduce_prio = is_per(vs) && sub == 0;
-    for (int64_t j0 = 0; j0 < M; j0 += UPD_NT * 4) {
-        int64_t idx[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const int64_t j = j0 + q * UPD_NT + tid;
-            idx[q] = j < M ? index[j] : -1;
-        }
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const int64_t j = j0 + q * UPD_NT + tid;
-            if (j >= M) continue;
-            if (reduce_prio) {
-                const double p = per_priority(vs, j);
-                pmax = fmax(pmax, p);
-                pmin = fmin(pmin, p);
-            }
-            if (idx[q] < 0 || idx[q] >= size) {
-                if (sub == 0) atomicOr(err_flag, TS_FLAG_INDEX_RANGE);
-                continue;
-            }
-            if ((idx[q] >> shift) == sub) {
-                const int pos = atomicAdd(&n_items, 1);
-                items[pos] = make_uint2((uint32_t)(idx[q] + bound), (uint32_t)j);
-                atomicMax(stamp + idx[q], (uint32_t)j + 1u);
-            }
+struct GridBarrier {
+    unsigned int* count;  // monotonically increasing within one launch; reset by CTA 0 at exit
+    unsigned int ctas;
+    unsigned int phase = 0;
+    // every CTA arrives (its earlier writes become visible to whoever waits) ...
+    __device__ __forceinline__ void arrive() {
+        ++phase;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            atomicAdd(count, 1u);
         }
     }
-    __threadfence();
-    __syncthreads();
-    const int n = n_items;
-
-    // ---- leaves: only the last occurrence of an index writes ---------------------------------
-    for (int i = tid; i < n; i += UPD_NT) {
-        const uint2 it = items[i];
-        const int64_t leaf = (int64_t)it.x - bound;
-        if (__ldcg(stamp + leaf) == it.y + 1u) {
-            tree[it.x] = leaf_value(vs, it.y);
-            stamp[leaf] = 0u;  // losers compare against their own position: 0 never matches
-        }
-    }
-    __syncthreads();
-
-    // ---- climb the subtree ---------------------------------------------------------------------
-    for (int lvl = 0; lvl < shift; ++lvl) {
-        for (int i = tid; i < n; i += UPD_NT) {
-            const uint32_t node = items[i].x >> 1;
-            items[i].x = node;
-            tree[node] = __dadd_rn(__ldcg(tree + 2 * (size_t)node),
-                                   __ldcg(tree + 2 * (size_t)node + 1));  // segtree.py:104
+    // ... and the CTAs that go on to read other CTAs' writes wait for all arrivals
+    __device__ __forceinline__ void wait() {
+        if (threadIdx.x == 0) {
+            const unsigned int target = phase * ctas;
+            unsigned int seen;
+            do {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(count)
+                             : "memory");
+            } while (seen < target);
         }
         __syncthreads();
     }
+    __device__ __forceinline__ void arrive_and_wait(bool do_wait) {
+        arrive();
+        if (do_wait) wait(); else __syncthreads();
+    }
+};
 
-    // ---- priority extrema (prio.py:88-89), CTA 0 only -------------------------------------------
-    if (reduce_prio) {
+// One warp rebuilds the aligned group of G = 32 * K nodes that starts at heap index `first`,
+// LG = log2(G) levels up.  With STAMPED the group is a leaf group: stamped leaves are replaced.
+template <int K, bool STAMPED>
+__device__ __forceinline__ void rebuild_group(double* __restrict__ tree, int64_t first,
+                                              int64_t leaf0, int64_t size, const ValueSrc& vs,
+                                              const uint32_t* __restrict__ stamp, uint32_t tag,
+                                              int lane) {
+    static_assert(K == 4 || K == 8, "lane strip of 4 or 8 nodes");
+    double v[K];
+    const int64_t base = first + (int64_t)lane * K;
+#pragma unroll
+    for (int q = 0; q < K / 2; ++q) {
+        const double2 t = __ldcg(reinterpret_cast<const double2*>(tree + base) + q);
+        v[2 * q] = t.x; v[2 * q + 1] = t.y;
+    }
+    if (STAMPED) {
+        const int64_t p0 = leaf0 + (int64_t)lane * K;  // leaf number of v[0]
+        uint32_t st[K];
+        if (p0 + K <= size) {
+#pragma unroll
+            for (int q = 0; q < K / 4; ++q) {
+                const uint4 t = __ldcg(reinterpret_cast<const uint4*>(stamp + p0) + q);
+                st[4 * q] = t.x; st[4 * q + 1] = t.y; st[4 * q + 2] = t.z; st[4 * q + 3] = t.w;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < K; ++k) st[k] = p0 + k < size ? __ldcg(stamp + p0 + k) : 0u;
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if ((st[k] >> kTagShift) == tag) {  // written by this call; low bits = position + 1
+                v[k] = leaf_value(vs, (int64_t)(st[k] & ((1u << kTagShift) - 1u)) - 1);
+                tree[base + k] = v[k];
+            }
+        }
+    }
+    // levels inside the lane's strip
+    int64_t node = base;
+#pragma unroll
+    for (int w = K; w > 1; w >>= 1) {
+        node >>= 1;
+#pragma unroll
+        for (int k = 0; k < w / 2; ++k) v[k] = __dadd_rn(v[2 * k], v[2 * k + 1]);
+        if (w == 8) {
+            *reinterpret_cast<double2*>(tree + node) = make_double2(v[0], v[1]);
+            *reinterpret_cast<double2*>(tree + node + 2) = make_double2(v[2], v[3]);
+        } else if (w == 4) {
+            *reinterpret_cast<double2*>(tree + node) = make_double2(v[0], v[1]);
+        } else {
+            tree[node] = v[0];
+        }
+    }
+    // levels across lanes: lane l (multiple of 2d) holds left, lane l + d holds right
+    double x = v[0];
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const double r = __shfl_down_sync(0xffffffffu, x, d);
+        x = __dadd_rn(x, r);
+        node >>= 1;
+        if ((lane & (2 * d - 1)) == 0) tree[node] = x;
+    }
+}
+
+// One warp rebuilds everything above the level of n <= 128 nodes (heap indices [n, 2n)).
+__device__ __forceinline__ void warp_finish(double* __restrict__ tree, int n, int lane) {
+    const int c = n >= 32 ? n / 32 : 1;  // nodes per lane: 1, 2 or 4
+    double v[4] = {0.0, 0.0, 0.0, 0.0};
+    const bool mine = lane * c < n;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (k < c && mine) v[k] = __ldcg(tree + n + lane * c + k);
+    int node = n + lane * c;
+#pragma unroll
+    for (int w = 4; w > 1; w >>= 1) {
+        if (w > c) continue;
+        node >>= 1;
+#pragma unroll
+        for (int k = 0; k < w / 2; ++k) {
+            v[k] = __dadd_rn(v[2 * k], v[2 * k + 1]);
+            if (mine) tree[node + k] = v[k];
+        }
+    }
+    const int live = n < 32 ? n : 32;
+    double x = v[0];
+    for (int d = 1; d < live; d <<= 1) {
+        const double r = __shfl_down_sync(0xffffffffu, x, d);
+        x = __dadd_rn(x, r);
+        node >>= 1;
+        if ((lane & (2 * d - 1)) == 0 && lane < live) tree[node] = x;
+    }
+}
+
+template <int K>
+__global__ void __launch_bounds__(TIER_NT)
+segtree_update_tiered(double* __restrict__ tree, int64_t size, int64_t bound, int lg_bound,
+                      const int64_t* __restrict__ index, ValueSrc vs, int64_t M,
+                      uint32_t* __restrict__ stamp, uint32_t* __restrict__ counter,
+                      int32_t* __restrict__ err_flag) {
+    constexpr int G = 32 * K;
+    constexpr int LG = K == 4 ? 7 : 8;
+    __shared__ double s_red[2 * (TIER_NT / 32)];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int64_t gtid = blockIdx.x * (int64_t)TIER_NT + tid;
+    const int64_t gthreads = gridDim.x * (int64_t)TIER_NT;
+    GridBarrier bar{counter, gridDim.x};
+
+    phase_mark(0);
+    // counter[2] = epoch of the previous call, counter[3] = "stamps must be cleared first"
+    const uint32_t tag = __ldcg(counter + 2) + 1u;
+    if (__ldcg(counter + 3) != 0u) {  // epoch wrapped: forget every old stamp (rare)
+        for (int64_t i = gtid; i < size; i += gthreads) stamp[i] = 0u;
+        bar.arrive_and_wait(true);
+    }
+
+    // ---- phase A: stamps (+ priority extrema, prio.py:88-89) ----------------------------------
+    double pmax = 0.0, pmin = INFINITY;
+    for (int64_t j = gtid; j < M; j += gthreads) {
+        const int64_t idx = index[j];
+        if (is_per(vs)) {
+            const double p = per_priority(vs, j);
+            pmax = fmax(pmax, p);
+            pmin = fmin(pmin, p);
+        }
+        if (idx < 0 || idx >= size) { atomicOr(err_flag, TS_FLAG_INDEX_RANGE); continue; }
+        atomicMax(stamp + idx, (tag << kTagShift) | (uint32_t)(j + 1));
+    }
+    bar.arrive();
+    // priority extrema while the other CTAs arrive (nobody in this launch reads them)
+    if (is_per(vs) && blockIdx.x * (int64_t)TIER_NT < M) {
 #pragma unroll
         for (int d = 16; d >= 1; d >>= 1) {
             pmax = fmax(pmax, __shfl_xor_sync(0xffffffffu, pmax, d));
             pmin = fmin(pmin, __shfl_xor_sync(0xffffffffu, pmin, d));
         }
-        if ((tid & 31) == 0) { s_red[tid >> 5] = pmax; s_red[UPD_NT / 32 + (tid >> 5)] = pmin; }
+        if (lane == 0) { s_red[tid >> 5] = pmax; s_red[TIER_NT / 32 + (tid >> 5)] = pmin; }
         __syncthreads();
-        if (tid == 0) {
-            for (int w = 1; w < UPD_NT / 32; ++w) {
-                pmax = fmax(pmax, s_red[w]);
-                pmin = fmin(pmin, s_red[UPD_NT / 32 + w]);
+        if (tid < 32) {
+            pmax = s_red[tid];
+            pmin = s_red[TIER_NT / 32 + tid];
+#pragma unroll
+            for (int d = 16; d >= 1; d >>= 1) {
+                pmax = fmax(pmax, __shfl_xor_sync(0xffffffffu, pmax, d));
+                pmin = fmin(pmin, __shfl_xor_sync(0xffffffffu, pmin, d));
             }
-            vs.prio[0] = fmax(vs.prio[0], pmax);
-            vs.prio[1] = fmin(vs.prio[1], pmin);
+            if (tid == 0 && pmax > 0.0) {
+                atomic_max_pos(vs.prio, pmax);
+                atomic_min_pos(vs.prio + 1, pmin);
+            }
         }
     }
+    bar.wait();
+    phase_mark(1);
 
-    // ---- top log2(S) levels: last CTA to arrive ------------------------------------------------
-    if (S > 1) {
-        __threadfence();
-        __syncthreads();
-        if (tid == 0) s_last = (atomicAdd(counter, 1u) == (uint32_t)(S - 1));
-        __syncthreads();
-        if (s_last) {
-            __threadfence();
-            for (int i = tid; i < S; i += UPD_NT) s_top[S + i] = __ldcg(tree + S + i);
-            __syncthreads();
-            for (int w = S >> 1; w >= 1; w >>= 1) {
-                for (int i = tid; i < w; i += UPD_NT) {
-                    const int node = w + i;
-                    const double v = __dadd_rn(s_top[2 * node], s_top[2 * node + 1]);
-                    s_top[node] = v;
-                    tree[node] = v;
-                }
-                __syncthreads();
-            }
-            if (tid == 0) *counter = 0u;
+    // ---- tiers: warp per item, LG levels per tier ---------------------------------------------
+    const int64_t gwarp = gtid >> 5, gwarps = gthreads >> 5;
+    int lvl = lg_bound;  // depth of the level being consumed (leaves first)
+    bool first_tier = true;
+    while (true) {
+        const int shift = lg_bound - lvl;  // leaf number -> node number at this level
+        for (int64_t j = gwarp; j < M; j += gwarps) {
+            const int64_t idx = index[j];
+            if (idx < 0 || idx >= size) continue;
+            const int64_t grp = (idx >> shift) >> LG;        // group of G nodes at this level
+            const int64_t first = ((int64_t)1 << lvl) + (grp << LG);
+            if (first_tier) rebuild_group<K, true>(tree, first, grp << LG, size, vs, stamp, tag, lane);
+            else rebuild_group<K, false>(tree, first, 0, size, vs, stamp, tag, lane);
         }
+        lvl -= LG;
+        first_tier = false;
+        if (((int64_t)1 << lvl) <= kTopMax) break;
+        bar.arrive_and_wait(true);
+    }
+    // ---- top: CTA 0 rebuilds levels lvl-1 .. 0 from level lvl ---------------------------------
+    phase_mark(2);
+    bar.arrive_and_wait(blockIdx.x == 0);
+    if (blockIdx.x != 0) return;
+    phase_mark(3);
+    // 2^lvl <= 8192 nodes: groups of 256 per warp (8 levels, no CTA barrier inside), then one
+    // warp finishes the <= 128 nodes that remain.  Two dependent round trips to L2 in all.
+    if (lvl >= 8) {
+        const int groups = 1 << (lvl - 8);  // <= 32 = warps of this CTA
+        if ((tid >> 5) < groups)
+            rebuild_group<8, false>(tree, ((int64_t)1 << lvl) + ((int64_t)(tid >> 5) << 8), 0, size,
+                                    vs, stamp, tag, lane);
+        lvl -= 8;
+        __syncthreads();
+    }
+    phase_mark(4);
+    if (tid < 32) warp_finish(tree, 1 << lvl, lane);
+    phase_mark(5);
+    if (tid == 0) {
+        counter[0] = 0u;
+        if (tag >= kTagMax) { counter[2] = 0u; counter[3] = 1u; }
+        else { counter[2] = tag; counter[3] = 0u; }
     }
 }
 
@@ -268,6 +419,12 @@ segtree_rebuild_kernel(double* __restrict__ tree, int64_t level_base, int chunk)
     }
 }
 
+inline int ilog2(int64_t pow2) {
+    int lg = 0;
+    while ((1LL << lg) < pow2) ++lg;
+    return lg;
+}
+
 inline unsigned grid_for(int64_t n, int threads) {
     int64_t g = (n + threads - 1) / threads;
     const int64_t cap = (int64_t)kNumSMs * 16;
@@ -293,24 +450,34 @@ int32_t update_impl(double* tree, int64_t size, int64_t bound, const int64_t* in
     if (M == 0) return TS_OK;
     if (!tree || !index || !stamp || !counter || !err_flag) return TS_ERR_BAD_ARG;
 
+    if (!aligned(tree, 16) || !aligned(stamp, 16)) return TS_ERR_ALIGN;
     if (M <= kSmallM && bound > kDenseBound) {
-        int lg = 0;
-        while ((1LL << lg) < bound) ++lg;
-        int lgS = 0;
-        while ((1 << lgS) < UPD_S) ++lgS;
-        const int shift = lg - lgS;
-        static bool attr_set = false;
-        if (!attr_set) {
-            cudaFuncSetAttribute(segtree_update_small,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)(kSmallM * sizeof(uint2)));
-            attr_set = true;
-        }
-        segtree_update_small<<<UPD_S, UPD_NT, (size_t)M * sizeof(uint2), st>>>(
-            tree, size, bound, index, vs, M, stamp, counter, err_flag, shift, UPD_S);
+        const int lg = ilog2(bound);
+        // level handed to the top phase: strip LG levels per tier until <= kTopMax nodes
+        const int K = g_tune_segtree_group == 256 ? 8 : 4, LG = K == 8 ? 8 : 7;
+        auto kern = K == 8 ? segtree_update_tiered<8> : segtree_update_tiered<4>;
+        int64_t ctas = (M * 32 + TIER_NT - 1) / TIER_NT;  // one warp per item
+        if (ctas > g_tune_segtree_max_ctas) ctas = g_tune_segtree_max_ctas;  // co-resident
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)ctas);
+        cfg.blockDim = dim3(TIER_NT);
+        cfg.dynamicSmemBytes = 0;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeCooperative;  // the CTAs wait on each other
+        attr[0].val.cooperative = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tree, size, bound, lg, index, vs, M, stamp,
+                                           counter, err_flag);
+        if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; (void)cudaGetLastError(); return TS_ERR_CUDA; }
         return check_launch();
     }
-    // bulk or tiny-tree path
+    // bulk or tiny-tree path: plain stamps (position + 1), cleared before and after use
+    {
+        cudaError_t e = cudaMemsetAsync(stamp, 0, (size_t)size * sizeof(uint32_t), st);
+        if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
+    }
     segtree_stamp_kernel<<<grid_for(M, 256), 256, 0, st>>>(index, M, size, stamp, err_flag);
     segtree_leaf_kernel<<<grid_for(M, 256), 256, 0, st>>>(tree, size, bound, index, vs, M, stamp);
     if (bound == 1) {  // single leaf: heap node 1 is the leaf itself, node 0 unused
@@ -335,137 +502,189 @@ __global__ void segtree_reduce_kernel(const double* __restrict__ tree, int64_t s
 }
 
 // ============================================================================================
-// Prefix-sum descent (segtree.py:122-137).  One query per thread; the top ten levels
-// of the heap are staged in shared memory once per CTA (8 KB), the rest comes from L2 (a
-// 2^20-leaf tree is 16 MiB, resident in the 126 MB L2).
+// Prefix-sum descent (segtree.py:122-137).  One query per thread.  The top twelve levels of
+// the heap are staged in shared memory once per CTA (32 KB); below them the tree is read from
+// L2 (a 2^20-leaf tree is 16 MiB, resident in the 126 MB L2) THREE LEVELS PER ROUND TRIP: the
+// eight great-grandchildren of the current node are one aligned 64-byte run, and because
+// every node equals fl(left + right) the two levels above them are recomputed in registers
+// bit-exactly instead of being fetched -- 20 dependent loads become 11 shared + 3 global.
 // ============================================================================================
-constexpr int DESC_NT = 64;
-constexpr int kTopCached = 1024;  // heap indices [0, 1024) = levels 0..9, 8 KB per CTA
+constexpr int kTopCached = 4096;  // heap indices [0, 4096) = depths 0..11, 32 KB per CTA
 
+template <int NT>
 __device__ __forceinline__ int stage_top(const double* __restrict__ tree, int64_t bound,
                                          double* s_top, int tid) {
     const int cached = (int)(2 * bound < kTopCached ? 2 * bound : kTopCached);
-    for (int i = tid; i < cached; i += DESC_NT) s_top[i] = __ldcg(tree + i);
+    for (int i = tid * 2; i < cached; i += NT * 2) {
+        const double2 t = __ldcg(reinterpret_cast<const double2*>(tree + i));
+        s_top[i] = t.x;
+        s_top[i + 1] = t.y;
+    }
     __syncthreads();
     return cached;  // heap indices below this value are in shared memory
+}
+
+// one level: left son `lsons`, go right iff lsons < v (strict), subtracting it (:132-135)
+template <typename VT>
+__device__ __forceinline__ int step_down(double lsons, VT& v) {
+    const bool direct = lsons < (double)v;
+    if (direct) v = (VT)__dsub_rn((double)v, lsons);
+    return direct ? 1 : 0;
 }
 
 // Descent for one query; `v` is updated like the reference mutates `value` (:134).
 template <typename VT>
 __device__ __forceinline__ int64_t descend(const double* __restrict__ tree, int64_t bound,
-                                           const double* s_top, int cached, VT& v) {
+                                           int lg_bound, const double* s_top, int cached,
+                                           VT& v) {
     int64_t index = 1;
-    while (index < bound) {
-        index <<= 1;                                            // :131
-        const double lsons = index < cached ? s_top[index] : __ldg(tree + index);  // :132
-        const bool direct = lsons < (double)v;                  // :133 (strict)
-        if (direct) v = (VT)__dsub_rn((double)v, lsons);        // :134 (v - lsons*1; else v - 0)
-        index += direct;                                        // :135
+    int depth = 0;
+    while (depth < lg_bound && 2 * index < cached) {  // sons still in shared memory
+        index <<= 1;
+        index += step_down(s_top[index], v);
+        ++depth;
+    }
+    for (int r = (lg_bound - depth) % 3; r > 0; --r) {  // leave a multiple of three levels
+        index <<= 1;
+        index += step_down(__ldg(tree + index), v);
+        ++depth;
+    }
+    while (depth < lg_bound) {
+        const double2* q = reinterpret_cast<const double2*>(tree + (index << 3));
+        const double2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
+        const double n0 = __dadd_rn(a.x, a.y), n1 = __dadd_rn(b.x, b.y);  // tree[4i], tree[4i+1]
+        const double n2 = __dadd_rn(c.x, c.y);                            // tree[4i+2]
+        const double m0 = __dadd_rn(n0, n1);                              // tree[2i]
+        const int r1 = step_down(m0, v);
+        const int r2 = step_down(r1 ? n2 : n0, v);
+        const double l3 = r1 ? (r2 ? d.x : c.x) : (r2 ? b.x : a.x);
+        const int r3 = step_down(l3, v);
+        index = (index << 3) + 4 * r1 + 2 * r2 + r3;
+        depth += 3;
     }
     return index - bound;                                       // :136
 }
 
+constexpr int DESC_NT = 256;
+
 template <typename VT>
 __global__ void __launch_bounds__(DESC_NT)
-segtree_prefix_kernel(const double* __restrict__ tree, int64_t bound, VT* __restrict__ value,
-                      int64_t M, int scale_by_total, int64_t* __restrict__ out,
-                      int32_t* __restrict__ err_flag) {
+segtree_prefix_kernel(const double* __restrict__ tree, int64_t bound, int lg_bound,
+                      VT* __restrict__ value, int64_t M, int scale_by_total,
+                      int64_t* __restrict__ out, int32_t* __restrict__ err_flag) {
     __shared__ double s_top[kTopCached];
     const int tid = threadIdx.x;
-    const int cached = stage_top(tree, bound, s_top, tid);
+    const int cached = stage_top<DESC_NT>(tree, bound, s_top, tid);
     const double total = s_top[1];
     const int64_t j = blockIdx.x * (int64_t)DESC_NT + tid;
     if (j >= M) return;
     VT v = value[j];
     if (scale_by_total) v = (VT)__dmul_rn((double)v, total);     // prio.py:61
     if (!((double)v >= 0.0 && (double)v < total)) atomicOr(err_flag, TS_FLAG_PREFIX_RANGE);  // :79
-    out[j] = descend<VT>(tree, bound, s_top, cached, v);
+    out[j] = descend<VT>(tree, bound, lg_bound, s_top, cached, v);
     value[j] = v;
 }
 
 // ============================================================================================
 // Fused PER sample: scalar = u * total, descent, importance weight, batch-max normalisation.
 // prio.py:59-64 (sample_indices), :66-76 (get_weight), :101 (weight / max(weight)).
+//
+// The whole batch is handled by ONE thread-block cluster (8 CTAs x 512 threads = 4096 queries
+// per sweep): the batch maximum that normalises the weights is then a block reduction plus an
+// exchange through distributed shared memory behind the hardware cluster barrier -- no atomics,
+// no scratch in global memory, no serial tail by a "last" CTA.
 // ============================================================================================
-struct PerScratch {  // 16 bytes, all-zero between calls
-    unsigned long long wmax_bits;
-    unsigned int arrived;
-    unsigned int pad;
-};
+// cluster shape: 8 x 512 (portable) or 16 x 256 (opt-in size) -- ts_tune_set("per_cluster")
 
-__device__ __forceinline__ void finish_weights(double w, bool active, double* __restrict__ weight,
-                                               int64_t M, int weight_norm, PerScratch* sc) {
-    // CTA-level max -> one atomic per CTA -> last CTA normalises all M weights
-    __shared__ double s_w[DESC_NT / 32];
-    __shared__ bool s_last;
-    if (!weight_norm) return;
-    double m = active ? w : 0.0;
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;"
+                 ::: "memory");
+}
+// read a double at the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ double dsmem_ld_f64(const double* local, uint32_t rank) {
+    uint32_t addr = smem_u32(local), remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(addr), "r"(rank));
+    double v;
+    asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(v) : "r"(remote) : "memory");
+    return v;
+}
+
+// max over every thread of the cluster (all threads must call; result valid in all threads)
+template <int NT>
+__device__ __forceinline__ double cluster_max(double m, double* s_warp, double* s_cta) {
+    const int tid = threadIdx.x;
 #pragma unroll
     for (int d = 16; d >= 1; d >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, d));
-    const int tid = threadIdx.x;
-    if ((tid & 31) == 0) s_w[tid >> 5] = m;
+    if ((tid & 31) == 0) s_warp[tid >> 5] = m;
     __syncthreads();
-    if (tid == 0) {
-        for (int q = 1; q < DESC_NT / 32; ++q) m = fmax(m, s_w[q]);
-        atomicMax(&sc->wmax_bits, (unsigned long long)__double_as_longlong(m));
-        __threadfence();
-        s_last = (atomicAdd(&sc->arrived, 1u) == gridDim.x - 1);
+    if (tid < 32) {
+        m = tid < NT / 32 ? s_warp[tid] : 0.0;
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, d));
+        if (tid == 0) *s_cta = m;
     }
-    __syncthreads();
-    if (s_last) {
-        __threadfence();
-        const double wmax = __longlong_as_double((long long)__ldcg(&sc->wmax_bits));
-        for (int64_t j = tid; j < M; j += DESC_NT)
-            weight[j] = __ddiv_rn(__ldcg(weight + j), wmax);     // prio.py:101
-        __syncthreads();
-        if (tid == 0) { sc->wmax_bits = 0ull; sc->arrived = 0u; }
-    }
+    cluster_sync_all();  // every CTA's maximum is published
+    m = 0.0;
+    const uint32_t nrank = cluster_nctarank();
+    for (uint32_t r = 0; r < nrank; ++r) m = fmax(m, dsmem_ld_f64(s_cta, r));
+    cluster_sync_all();  // nobody leaves (or overwrites s_cta) while peers still read it
+    return m;
 }
 
 __device__ __forceinline__ double is_weight(double leaf, double min_prio, double beta) {
-    return pow(__ddiv_rn(leaf, min_prio), -beta);                // prio.py:76
+    return pow_fast(__ddiv_rn(leaf, min_prio), -beta);           // prio.py:76
 }
 
-__global__ void __launch_bounds__(DESC_NT)
-per_sample_kernel(const double* __restrict__ tree, int64_t bound, const double* __restrict__ u,
-                  int64_t M, const double* __restrict__ prio, double beta, int weight_norm,
-                  int64_t* __restrict__ idx, double* __restrict__ weight, PerScratch* sc,
-                  int32_t* __restrict__ err_flag) {
-    __shared__ double s_top[kTopCached];
+// SAMPLE: idx from the descent; otherwise idx is given (get_weight on known indices)
+template <bool SAMPLE, int NT>
+__global__ void __launch_bounds__(NT)
+per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg_bound,
+                          const double* __restrict__ u, int64_t M,
+                          const double* __restrict__ prio, double beta, int weight_norm,
+                          int64_t* __restrict__ idx, double* __restrict__ weight,
+                          int32_t* __restrict__ err_flag) {
+    __shared__ double s_top[SAMPLE ? kTopCached : 2];
+    __shared__ double s_warp[NT / 32];
+    __shared__ double s_cta;
     const int tid = threadIdx.x;
-    const int cached = stage_top(tree, bound, s_top, tid);
-    const double total = s_top[1];
-    const int64_t j = blockIdx.x * (int64_t)DESC_NT + tid;
-    const bool active = j < M;
-    double w = 0.0;
-    if (active) {
-        double v = __dmul_rn(u[j], total);                       // prio.py:61
-        if (!(v >= 0.0 && v < total)) atomicOr(err_flag, TS_FLAG_PREFIX_RANGE);
-        const int64_t leaf = descend<double>(tree, bound, s_top, cached, v);
-        idx[j] = leaf;
-        w = is_weight(__ldg(tree + bound + leaf), prio[1], beta);
-        weight[j] = w;
+    int cached = 0;
+    double total = 0.0;
+    if (SAMPLE) {
+        cached = stage_top<NT>(tree, bound, s_top, tid);
+        total = s_top[1];
     }
-    if (weight_norm) {
-        __threadfence();
-        finish_weights(w, active, weight, M, weight_norm, sc);
+    const double min_prio = __ldg(prio + 1);
+    const int64_t sweep = (int64_t)cluster_nctarank() * NT;
+    const int64_t j0 = (int64_t)cluster_ctarank() * NT + tid;
+    double wmax = 0.0, w_first = 0.0;
+    for (int64_t j = j0; j < M; j += sweep) {
+        int64_t leaf;
+        if (SAMPLE) {
+            double v = __dmul_rn(u[j], total);                   // prio.py:61
+            if (!(v >= 0.0 && v < total)) atomicOr(err_flag, TS_FLAG_PREFIX_RANGE);
+            leaf = descend<double>(tree, bound, lg_bound, s_top, cached, v);
+            idx[j] = leaf;
+        } else {
+            leaf = idx[j];
+        }
+        const double w = is_weight(__ldg(tree + bound + leaf), min_prio, beta);
+        if (j == j0) w_first = w; else weight[j] = w;  // later sweeps park the raw weight
+        wmax = fmax(wmax, w);
     }
-}
-
-__global__ void __launch_bounds__(DESC_NT)
-per_weight_kernel(const double* __restrict__ tree, int64_t bound, const int64_t* __restrict__ idx,
-                  int64_t M, const double* __restrict__ prio, double beta, int weight_norm,
-                  double* __restrict__ weight, PerScratch* sc) {
-    const int64_t j = blockIdx.x * (int64_t)DESC_NT + threadIdx.x;
-    const bool active = j < M;
-    double w = 0.0;
-    if (active) {
-        w = is_weight(__ldg(tree + bound + idx[j]), prio[1], beta);
-        weight[j] = w;
-    }
-    if (weight_norm) {
-        __threadfence();
-        finish_weights(w, active, weight, M, weight_norm, sc);
+    if (weight_norm) wmax = cluster_max<NT>(wmax, s_warp, &s_cta);
+    for (int64_t j = j0; j < M; j += sweep) {
+        const double w = j == j0 ? w_first : weight[j];
+        weight[j] = weight_norm ? __ddiv_rn(w, wmax) : w;        // prio.py:101
     }
 }
 
@@ -473,6 +692,37 @@ per_weight_kernel(const double* __restrict__ tree, int64_t bound, const int64_t*
 }  // namespace ts
 
 using namespace ts;
+
+// one cluster handles the whole batch
+template <bool SAMPLE>
+static int32_t launch_per_cluster(const double* tree, int64_t bound, int lg, const double* u,
+                                  int64_t M, const double* prio, double beta, int weight_norm,
+                                  int64_t* idx, double* weight, int32_t* err_flag,
+                                  cudaStream_t st) {
+    const bool wide = g_tune_per_cluster == 16;
+    auto kern = wide ? per_weight_cluster_kernel<SAMPLE, 256> : per_weight_cluster_kernel<SAMPLE, 512>;
+    static bool attr_set = false;
+    if (wide && !attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(wide ? 16 : 8);
+    cfg.blockDim = dim3(wide ? 256 : 512);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = wide ? 16 : 8;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tree, bound, lg, u, M, prio, beta, weight_norm,
+                                       idx, weight, err_flag);
+    if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; (void)cudaGetLastError(); return TS_ERR_CUDA; }
+    return check_launch();
+}
 
 extern "C" int32_t ts_segtree_update(double* tree, int64_t size, int64_t bound,
                                      const int64_t* index, const void* value,
@@ -501,14 +751,16 @@ extern "C" int32_t ts_segtree_prefix_idx(const double* tree, int64_t bound, void
     if (M < 0 || bound <= 0) return TS_ERR_BAD_ARG;
     if (M == 0) return TS_OK;
     if (!tree || !value || !out || !err_flag) return TS_ERR_BAD_ARG;
+    if ((bound & (bound - 1)) != 0) return TS_ERR_BAD_ARG;
+    if (!aligned(tree, 16)) return TS_ERR_ALIGN;
     const unsigned grid = (unsigned)((M + DESC_NT - 1) / DESC_NT);
     cudaStream_t st = (cudaStream_t)stream;
     if (value_dtype == TS_F64)
-        segtree_prefix_kernel<double><<<grid, DESC_NT, 0, st>>>(tree, bound, (double*)value, M,
-                                                               scale_by_total, out, err_flag);
+        segtree_prefix_kernel<double><<<grid, DESC_NT, 0, st>>>(
+            tree, bound, ilog2(bound), (double*)value, M, scale_by_total, out, err_flag);
     else if (value_dtype == TS_F32 && !scale_by_total)
-        segtree_prefix_kernel<float><<<grid, DESC_NT, 0, st>>>(tree, bound, (float*)value, M, 0,
-                                                              out, err_flag);
+        segtree_prefix_kernel<float><<<grid, DESC_NT, 0, st>>>(tree, bound, ilog2(bound),
+                                                              (float*)value, M, 0, out, err_flag);
     else
         return TS_ERR_BAD_ARG;
     return check_launch();
@@ -520,11 +772,12 @@ extern "C" int32_t ts_per_sample(const double* tree, int64_t bound, const double
                                  int32_t* err_flag, ts_stream_t stream) {
     if (M < 0 || bound <= 0) return TS_ERR_BAD_ARG;
     if (M == 0) return TS_OK;
-    if (!tree || !u || !prio || !idx || !weight || !scratch16 || !err_flag) return TS_ERR_BAD_ARG;
-    const unsigned grid = (unsigned)((M + DESC_NT - 1) / DESC_NT);
-    per_sample_kernel<<<grid, DESC_NT, 0, (cudaStream_t)stream>>>(
-        tree, bound, u, M, prio, beta, weight_norm, idx, weight, (PerScratch*)scratch16, err_flag);
-    return check_launch();
+    if (!tree || !u || !prio || !idx || !weight || !err_flag) return TS_ERR_BAD_ARG;
+    if ((bound & (bound - 1)) != 0) return TS_ERR_BAD_ARG;
+    if (!aligned(tree, 16)) return TS_ERR_ALIGN;
+    (void)scratch16;  // kept in the ABI; the cluster kernel needs no global scratch
+    return launch_per_cluster<true>(tree, bound, ilog2(bound), u, M, prio, beta, weight_norm, idx,
+                                    weight, err_flag, (cudaStream_t)stream);
 }
 
 extern "C" int32_t ts_per_weight(const double* tree, int64_t bound, const int64_t* idx, int64_t M,
@@ -532,11 +785,11 @@ extern "C" int32_t ts_per_weight(const double* tree, int64_t bound, const int64_
                                  double* weight, void* scratch16, ts_stream_t stream) {
     if (M < 0 || bound <= 0) return TS_ERR_BAD_ARG;
     if (M == 0) return TS_OK;
-    if (!tree || !idx || !prio || !weight || !scratch16) return TS_ERR_BAD_ARG;
-    const unsigned grid = (unsigned)((M + DESC_NT - 1) / DESC_NT);
-    per_weight_kernel<<<grid, DESC_NT, 0, (cudaStream_t)stream>>>(
-        tree, bound, idx, M, prio, beta, weight_norm, weight, (PerScratch*)scratch16);
-    return check_launch();
+    if (!tree || !idx || !prio || !weight) return TS_ERR_BAD_ARG;
+    (void)scratch16;
+    return launch_per_cluster<false>(tree, bound, 0, nullptr, M, prio, beta, weight_norm,
+                                     const_cast<int64_t*>(idx), weight, nullptr,
+                                     (cudaStream_t)stream);
 }
 
 extern "C" int32_t ts_per_update(double* tree, int64_t size, int64_t bound, const int64_t* idx,
@@ -559,4 +812,13 @@ extern "C" int32_t ts_per_init_weight(double* tree, int64_t size, int64_t bound,
                 leaf_dtype == TS_F32 ? VM_INIT_F32 : VM_INIT_F64};
     return update_impl(tree, size, bound, idx, vs, M, stamp, counter, err_flag,
                        (cudaStream_t)stream);
+}
+
+extern "C" int32_t ts_debug_update_phases(uint64_t* out6) {
+    if (!out6) return TS_ERR_BAD_ARG;
+    unsigned long long h[8];
+    cudaError_t e = cudaMemcpyFromSymbol(h, g_update_phase_ns, sizeof(h));
+    if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
+    for (int i = 0; i < 6; ++i) out6[i] = h[i];
+    return TS_OK;
 }
