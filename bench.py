@@ -284,7 +284,7 @@ def run_b200(args):
     achieved = n_trans * ALG_BYTES_PER_TRANSITION / kernel_s / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                "kernel": "gae_rows_kernel<float,float,float,256>",
+                "kernel": "gae_rows_tma_kernel<float,float,float,256> (persistent, cp.async.bulk pipelined)",
                 "alg_bytes_per_launch": n_trans * ALG_BYTES_PER_TRANSITION,
                 "moved_bytes_per_launch": n_trans * MOVED_BYTES_PER_TRANSITION,
                 "us_per_launch": kernel_s * 1e6}
@@ -423,13 +423,13 @@ def run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
     return {"metric": "PER samples/s", "value": value, "unit": "samples/s", "us_per_step": us,
             "workload": "per GPU: 2^20-leaf f64 sum tree, batch 4096, alpha 0.6 beta 0.4; step = "
                         "sample (descent + IS weights + batch-max norm) + update_weight "
-                        "(|td|+eps, pow, dedupe, bottom-up); 8 steps per CUDA graph"
+                        "(|td|+eps, pow, dedupe, tiered rebuild, one cooperative launch); 8 steps per CUDA graph"
                         + ("; all_gather of shard roots per graph" if world > 1 else ""),
             "gpu_launches_per_step": 2,
             "roofline": {"bound": "hbm", "achieved": PER_BATCH * PER_ALG_BYTES_PER_SAMPLE / (us * 1e-6) / 1e9,
                          "peak": peak, "unit": "GB/s",
                          "frac": PER_BATCH * PER_ALG_BYTES_PER_SAMPLE / (us * 1e-6) / 1e9 / peak,
-                         "note": "latency-bound (>= 40 dependent L2 accesses); tree is L2-resident"}}
+                         "note": "latency-bound: ~20 dependent L2 round trips of ~0.5 us per step, not bytes; tree is L2-resident"}}
 
 
 def main():

@@ -84,18 +84,13 @@ def main():
         torch.cuda.synchronize()
         L.check(lib.ts_debug_update_phases(ph), "phases")
         t = list(ph)
-        print(json.dumps({"phases_ns": dict(zip(
-            ["A+bar", "tier0", "bar->cta0", "top_load", "top_levels"],
-            [t[i + 1] - t[i] for i in range(5)]))}), flush=True)
+        print(json.dumps({"phases_ns": {"A+bar": t[1] - t[0], "tier0(cta0)": t[2] - t[1],
+                                        "rendezvous+top": t[5] - t[2]}}), flush=True)
     L.check(lib.ts_tune_set(b"segtree_group", 128), "tune")
     for cl in (8, 16):
         L.check(lib.ts_tune_set(b"per_cluster", cl), "tune")
         timed(f"sample(cluster={cl})", sample)
-    L.check(lib.ts_tune_set(b"per_cluster", 8), "tune")
-    for mc in (32, 64, 148):
-        L.check(lib.ts_tune_set(b"segtree_max_ctas", mc), "tune")
-        timed(f"update(max_ctas={mc})", update)
-    L.check(lib.ts_tune_set(b"segtree_max_ctas", 148), "tune")
+    L.check(lib.ts_tune_set(b"per_cluster", 0), "tune")
     timed("sample+update", lambda r, s: (sample(r, s), update(r, s)))
     u2 = u.clone()
     timed("copy+prefix_idx", lambda r, s: (u2[r].copy_(u[r]), prefix_on(u2, r, s)))

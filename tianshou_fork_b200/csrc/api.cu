@@ -5,7 +5,7 @@ namespace ts {
 thread_local int32_t g_last_cuda_error = 0;
 int g_tune_gae_rows_variant = 0;
 int g_tune_segtree_group = 128;
-int g_tune_per_cluster = 8;
+int g_tune_per_cluster = 0;
 int g_tune_segtree_max_ctas = 148;
 }
 
@@ -33,7 +33,7 @@ extern "C" int32_t ts_tune_set(const char* key, int64_t value) {
         ts::g_tune_segtree_max_ctas = (int)value;
         return TS_OK;
     }
-    if (strcmp(key, "per_cluster") == 0 && (value == 8 || value == 16)) {
+    if (strcmp(key, "per_cluster") == 0 && (value == 0 || value == 8 || value == 16)) {
         ts::g_tune_per_cluster = (int)value;
         return TS_OK;
     }

@@ -82,6 +82,30 @@ __device__ __forceinline__ void atomic_min_pos(double* addr, double v) {
     atomicMin((unsigned long long*)addr, (unsigned long long)__double_as_longlong(v));
 }
 
+// ---- thread-block cluster helpers ---------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;"
+                 ::: "memory");
+}
+// read a double at the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ double dsmem_ld_f64(const double* local, uint32_t rank) {
+    uint32_t addr = smem_u32(local), remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(addr), "r"(rank));
+    double v;
+    asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(v) : "r"(remote) : "memory");
+    return v;
+}
+
 constexpr int64_t kSmallM = 16383;     // tiered path: batch position + 1 fits the stamp's 14 bits
 constexpr int64_t kDenseBound = 4096;  // trees up to this many leaves are rebuilt densely
 constexpr int kTagShift = 14;
@@ -111,6 +135,7 @@ constexpr uint32_t kTagMax = (1u << (32 - kTagShift)) - 1u;
 // Phase timestamps of the most recent tiered update (globaltimer ns, CTA 0 / thread 0):
 // start, after phase A barrier, after tier 0, after the last barrier, after top load, end.
 __device__ unsigned long long g_update_phase_ns[8];
+
 __device__ __forceinline__ void phase_mark(int slot) {
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         unsigned long long t;
@@ -123,7 +148,7 @@ constexpr int TIER_NT = 1024;
 constexpr int kTopMax = 8192;  // nodes of the level handed to the top phase (128 KB heap)
 
 struct GridBarrier {
-    unsigned int* count;  // monotonically increasing within one launch; reset by CTA 0 at exit
+    unsigned int* count;  // monotonically increasing within one launch; reset by the last CTA
     unsigned int ctas;
     unsigned int phase = 0;
     // every CTA arrives (its earlier writes become visible to whoever waits) ...
@@ -147,19 +172,28 @@ struct GridBarrier {
         }
         __syncthreads();
     }
-    __device__ __forceinline__ void arrive_and_wait(bool do_wait) {
-        arrive();
-        if (do_wait) wait(); else __syncthreads();
+    // final rendezvous: nobody waits; returns true in the CTA that arrived last (CTA-uniform)
+    __device__ __forceinline__ bool arrive_last(bool* s_flag) {
+        ++phase;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            *s_flag = atomicAdd(count, 1u) == phase * ctas - 1u;
+            __threadfence();
+        }
+        __syncthreads();
+        return *s_flag;
     }
 };
 
 // One warp rebuilds the aligned group of G = 32 * K nodes that starts at heap index `first`,
-// LG = log2(G) levels up.  With STAMPED the group is a leaf group: stamped leaves are replaced.
+// LG = log2(G) levels up, and returns the group's root (valid in lane 0).  With STAMPED the
+// group is a leaf group: stamped leaves are replaced first.
 template <int K, bool STAMPED>
-__device__ __forceinline__ void rebuild_group(double* __restrict__ tree, int64_t first,
-                                              int64_t leaf0, int64_t size, const ValueSrc& vs,
-                                              const uint32_t* __restrict__ stamp, uint32_t tag,
-                                              int lane) {
+__device__ __forceinline__ double rebuild_group(double* __restrict__ tree, int64_t first,
+                                                int64_t leaf0, int64_t size, const ValueSrc& vs,
+                                                const uint32_t* __restrict__ stamp, uint32_t tag,
+                                                int lane) {
     static_assert(K == 4 || K == 8, "lane strip of 4 or 8 nodes");
     double v[K];
     const int64_t base = first + (int64_t)lane * K;
@@ -214,16 +248,25 @@ __device__ __forceinline__ void rebuild_group(double* __restrict__ tree, int64_t
         node >>= 1;
         if ((lane & (2 * d - 1)) == 0) tree[node] = x;
     }
+    return x;
 }
 
 // One warp rebuilds everything above the level of n <= 128 nodes (heap indices [n, 2n)).
-__device__ __forceinline__ void warp_finish(double* __restrict__ tree, int n, int lane) {
+// The level is read from shared memory when `s_level` is given (n <= 32), else from L2.
+__device__ __forceinline__ void warp_finish(double* __restrict__ tree, int n, int lane,
+                                            const double* s_level) {
     const int c = n >= 32 ? n / 32 : 1;  // nodes per lane: 1, 2 or 4
     double v[4] = {0.0, 0.0, 0.0, 0.0};
     const bool mine = lane * c < n;
+    if (s_level != nullptr) {
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
-        if (k < c && mine) v[k] = __ldcg(tree + n + lane * c + k);
+        for (int k = 0; k < 4; ++k)
+            if (k < c && mine) v[k] = s_level[lane * c + k];
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (k < c && mine) v[k] = __ldcg(tree + n + lane * c + k);
+    }
     int node = n + lane * c;
 #pragma unroll
     for (int w = 4; w > 1; w >>= 1) {
@@ -245,16 +288,19 @@ __device__ __forceinline__ void warp_finish(double* __restrict__ tree, int n, in
     }
 }
 
+constexpr int kIdxRounds = 8;  // rounds of 32 items per CTA whose indices stay in shared memory
+
 template <int K>
 __global__ void __launch_bounds__(TIER_NT)
 segtree_update_tiered(double* __restrict__ tree, int64_t size, int64_t bound, int lg_bound,
                       const int64_t* __restrict__ index, ValueSrc vs, int64_t M,
                       uint32_t* __restrict__ stamp, uint32_t* __restrict__ counter,
                       int32_t* __restrict__ err_flag) {
-    constexpr int G = 32 * K;
     constexpr int LG = K == 4 ? 7 : 8;
-    __shared__ double s_red[2 * (TIER_NT / 32)];
-    const int tid = threadIdx.x, lane = tid & 31;
+    __shared__ int64_t s_idx[kIdxRounds][32];
+    __shared__ double s_root[64];
+    __shared__ bool s_last;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t gtid = blockIdx.x * (int64_t)TIER_NT + tid;
     const int64_t gthreads = gridDim.x * (int64_t)TIER_NT;
     GridBarrier bar{counter, gridDim.x};
@@ -264,89 +310,104 @@ segtree_update_tiered(double* __restrict__ tree, int64_t size, int64_t bound, in
     const uint32_t tag = __ldcg(counter + 2) + 1u;
     if (__ldcg(counter + 3) != 0u) {  // epoch wrapped: forget every old stamp (rare)
         for (int64_t i = gtid; i < size; i += gthreads) stamp[i] = 0u;
-        bar.arrive_and_wait(true);
+        bar.arrive();
+        bar.wait();
     }
 
-    // ---- phase A: stamps (+ priority extrema, prio.py:88-89) ----------------------------------
-    double pmax = 0.0, pmin = INFINITY;
-    for (int64_t j = gtid; j < M; j += gthreads) {
-        const int64_t idx = index[j];
+    // Item j belongs to CTA (j / 32) % gridDim, round j / (32 * gridDim), slot j % 32: the
+    // CTA's first warp stamps slot = lane, and in the tiers warp `slot` rebuilds its group.
+    const int64_t per_round = 32 * (int64_t)gridDim.x;
+    const int64_t rounds = (M + per_round - 1) / per_round;
+
+    // ---- phase A: stamps (+ priority extrema, prio.py:88-89), one warp per CTA ----------------
+    if (warp == 0) {
+        double pmax = 0.0, pmin = INFINITY;
+        for (int64_t r = 0; r < rounds; ++r) {
+            const int64_t j = r * per_round + blockIdx.x * 32 + lane;
+            int64_t idx = -1;
+            if (j < M) {
+                idx = index[j];
+                if (is_per(vs)) {
+                    const double p = per_priority(vs, j);
+                    pmax = fmax(pmax, p);
+                    pmin = fmin(pmin, p);
+                }
+                if (idx < 0 || idx >= size) {
+                    atomicOr(err_flag, TS_FLAG_INDEX_RANGE);
+                    idx = -1;
+                } else {
+                    atomicMax(stamp + idx, (tag << kTagShift) | (uint32_t)(j + 1));
+                }
+            }
+            if (r < kIdxRounds) s_idx[r][lane] = idx;
+        }
         if (is_per(vs)) {
-            const double p = per_priority(vs, j);
-            pmax = fmax(pmax, p);
-            pmin = fmin(pmin, p);
-        }
-        if (idx < 0 || idx >= size) { atomicOr(err_flag, TS_FLAG_INDEX_RANGE); continue; }
-        atomicMax(stamp + idx, (tag << kTagShift) | (uint32_t)(j + 1));
-    }
-    bar.arrive();
-    // priority extrema while the other CTAs arrive (nobody in this launch reads them)
-    if (is_per(vs) && blockIdx.x * (int64_t)TIER_NT < M) {
-#pragma unroll
-        for (int d = 16; d >= 1; d >>= 1) {
-            pmax = fmax(pmax, __shfl_xor_sync(0xffffffffu, pmax, d));
-            pmin = fmin(pmin, __shfl_xor_sync(0xffffffffu, pmin, d));
-        }
-        if (lane == 0) { s_red[tid >> 5] = pmax; s_red[TIER_NT / 32 + (tid >> 5)] = pmin; }
-        __syncthreads();
-        if (tid < 32) {
-            pmax = s_red[tid];
-            pmin = s_red[TIER_NT / 32 + tid];
 #pragma unroll
             for (int d = 16; d >= 1; d >>= 1) {
                 pmax = fmax(pmax, __shfl_xor_sync(0xffffffffu, pmax, d));
                 pmin = fmin(pmin, __shfl_xor_sync(0xffffffffu, pmin, d));
             }
-            if (tid == 0 && pmax > 0.0) {
+            if (lane == 0 && pmax > 0.0) {
                 atomic_max_pos(vs.prio, pmax);
                 atomic_min_pos(vs.prio + 1, pmin);
             }
         }
     }
+    bar.arrive();
     bar.wait();
     phase_mark(1);
 
     // ---- tiers: warp per item, LG levels per tier ---------------------------------------------
-    const int64_t gwarp = gtid >> 5, gwarps = gthreads >> 5;
     int lvl = lg_bound;  // depth of the level being consumed (leaves first)
     bool first_tier = true;
     while (true) {
         const int shift = lg_bound - lvl;  // leaf number -> node number at this level
-        for (int64_t j = gwarp; j < M; j += gwarps) {
-            const int64_t idx = index[j];
-            if (idx < 0 || idx >= size) continue;
+        for (int64_t r = 0; r < rounds; ++r) {
+            int64_t idx;
+            if (r < kIdxRounds) {
+                idx = s_idx[r][warp];
+            } else {
+                const int64_t j = r * per_round + blockIdx.x * 32 + warp;
+                idx = j < M ? index[j] : -1;
+                if (idx >= size) idx = -1;
+            }
+            if (idx < 0) continue;  // warp-uniform
             const int64_t grp = (idx >> shift) >> LG;        // group of G nodes at this level
             const int64_t first = ((int64_t)1 << lvl) + (grp << LG);
-            if (first_tier) rebuild_group<K, true>(tree, first, grp << LG, size, vs, stamp, tag, lane);
-            else rebuild_group<K, false>(tree, first, 0, size, vs, stamp, tag, lane);
+            if (first_tier) (void)rebuild_group<K, true>(tree, first, grp << LG, size, vs, stamp, tag, lane);
+            else (void)rebuild_group<K, false>(tree, first, 0, size, vs, stamp, tag, lane);
         }
         lvl -= LG;
         first_tier = false;
         if (((int64_t)1 << lvl) <= kTopMax) break;
-        bar.arrive_and_wait(true);
+        bar.arrive();
+        bar.wait();
     }
-    // ---- top: CTA 0 rebuilds levels lvl-1 .. 0 from level lvl ---------------------------------
+    // ---- top: the CTA that arrives last rebuilds levels lvl-1 .. 0 from level lvl -------------
     phase_mark(2);
-    bar.arrive_and_wait(blockIdx.x == 0);
-    if (blockIdx.x != 0) return;
-    phase_mark(3);
-    // 2^lvl <= 8192 nodes: groups of 256 per warp (8 levels, no CTA barrier inside), then one
-    // warp finishes the <= 128 nodes that remain.  Two dependent round trips to L2 in all.
+    if (!bar.arrive_last(&s_last)) return;
+    // 2^lvl <= 8192 nodes: groups of 256 per warp (8 levels, no CTA barrier inside), whose roots
+    // go through shared memory to one warp that finishes the <= 128 nodes that remain.
+    const double* s_level = nullptr;
     if (lvl >= 8) {
-        const int groups = 1 << (lvl - 8);  // <= 32 = warps of this CTA
-        if ((tid >> 5) < groups)
-            rebuild_group<8, false>(tree, ((int64_t)1 << lvl) + ((int64_t)(tid >> 5) << 8), 0, size,
-                                    vs, stamp, tag, lane);
+        const int groups = 1 << (lvl - 8);  // <= 32 = warps of this CTA: a single pass
+        if (warp < groups) {
+            const double root = rebuild_group<8, false>(
+                tree, ((int64_t)1 << lvl) + ((int64_t)warp << 8), 0, size, vs, stamp, tag, lane);
+            if (lane == 0) s_root[warp] = root;
+        }
         lvl -= 8;
+        s_level = s_root;
         __syncthreads();
     }
-    phase_mark(4);
-    if (tid < 32) warp_finish(tree, 1 << lvl, lane);
-    phase_mark(5);
+    if (tid < 32) warp_finish(tree, 1 << lvl, lane, s_level);
     if (tid == 0) {
         counter[0] = 0u;
         if (tag >= kTagMax) { counter[2] = 0u; counter[3] = 1u; }
         else { counter[2] = tag; counter[3] = 0u; }
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_update_phase_ns[5] = t;
     }
 }
 
@@ -596,29 +657,6 @@ segtree_prefix_kernel(const double* __restrict__ tree, int64_t bound, int lg_bou
 // ============================================================================================
 // cluster shape: 8 x 512 (portable) or 16 x 256 (opt-in size) -- ts_tune_set("per_cluster")
 
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-    uint32_t r;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-    return r;
-}
-__device__ __forceinline__ uint32_t cluster_nctarank() {
-    uint32_t r;
-    asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
-    return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;"
-                 ::: "memory");
-}
-// read a double at the same shared-memory offset in CTA `rank` of the cluster
-__device__ __forceinline__ double dsmem_ld_f64(const double* local, uint32_t rank) {
-    uint32_t addr = smem_u32(local), remote;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(addr), "r"(rank));
-    double v;
-    asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(v) : "r"(remote) : "memory");
-    return v;
-}
-
 // max over every thread of the cluster (all threads must call; result valid in all threads)
 template <int NT>
 __device__ __forceinline__ double cluster_max(double m, double* s_warp, double* s_cta) {
@@ -699,14 +737,31 @@ static int32_t launch_per_cluster(const double* tree, int64_t bound, int lg, con
                                   int64_t M, const double* prio, double beta, int weight_norm,
                                   int64_t* idx, double* weight, int32_t* err_flag,
                                   cudaStream_t st) {
-    const bool wide = g_tune_per_cluster == 16;
-    auto kern = wide ? per_weight_cluster_kernel<SAMPLE, 256> : per_weight_cluster_kernel<SAMPLE, 512>;
-    static bool attr_set = false;
-    if (wide && !attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-        if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
-        attr_set = true;
+    // 16 CTAs x 256 threads spreads a large batch over twice the SMs (7.4 vs 8.7 us at 4096
+    // queries); it is an opt-in cluster size, so it is used only where the device can place it.
+    static int wide_ok = -1;  // per instantiation
+    auto kern16 = per_weight_cluster_kernel<SAMPLE, 256>;
+    if (wide_ok < 0) {
+        wide_ok = 0;
+        if (cudaFuncSetAttribute(kern16, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) ==
+            cudaSuccess) {
+            cudaLaunchConfig_t q = {};
+            q.gridDim = dim3(16);
+            q.blockDim = dim3(256);
+            cudaLaunchAttribute qa[1];
+            qa[0].id = cudaLaunchAttributeClusterDimension;
+            qa[0].val.clusterDim.x = 16;
+            qa[0].val.clusterDim.y = 1;
+            qa[0].val.clusterDim.z = 1;
+            q.attrs = qa;
+            q.numAttrs = 1;
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, kern16, &q) == cudaSuccess && n >= 1) wide_ok = 1;
+        }
+        (void)cudaGetLastError();
     }
+    const bool wide = wide_ok == 1 && (g_tune_per_cluster == 16 || (g_tune_per_cluster == 0 && M > 1024));
+    auto kern = wide ? kern16 : per_weight_cluster_kernel<SAMPLE, 512>;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(wide ? 16 : 8);
     cfg.blockDim = dim3(wide ? 256 : 512);

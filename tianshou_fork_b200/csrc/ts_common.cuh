@@ -117,7 +117,7 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
 // Tuning knobs (ts_tune_set): 0 = automatic choice.
 extern int g_tune_gae_rows_variant;
 extern int g_tune_segtree_max_ctas;  // CTAs of the cooperative tree update (<= 148)
-extern int g_tune_per_cluster;       // CTAs of the PER sampling cluster: 8 (x512 thr) or 16 (x256)
+extern int g_tune_per_cluster;       // PER sampling cluster: 0 auto, 8 (x512 threads) or 16 (x256)
 extern int g_tune_segtree_group;  // 128 (default) or 256 nodes per warp-rebuilt group
 
 }  // namespace ts
