@@ -193,12 +193,28 @@ int32_t ts_segtree_prefix_idx(const double* tree, int64_t bound, void* value,
 int32_t ts_per_sample(const double* tree, int64_t bound, const double* u, int64_t M,
                       const double* prio, double beta, int32_t weight_norm, int64_t* idx,
                       double* weight, void* scratch16, int32_t* err_flag, ts_stream_t stream);
-/* get_weight on given indices (prio.py:66-76), optional batch-max normalisation (:101). */
+/* Sharded form (one process per GPU): this GPU holds shard `rank` of G
+ * power-of-two-aligned subtrees of the reference's single global tree (manager.py:209-214).
+ * roots3 = double[G][3] = {shard root, max_prio, min_prio} of every rank (all-gathered by the
+ * caller after each update).  The log2(G) levels above the shard roots are rebuilt in the global
+ * tree's pairwise order, queries are routed down them, and those that land in this shard
+ * descend locally: idx[j] = LOCAL leaf, or -1 (weight 0) for queries owned by another rank.
+ * min_prio is the minimum over all ranks.  With weight_norm the kernel writes the maximum raw
+ * weight of this rank to *wmax_out; after a MAX all-reduce the caller applies ts_per_normalize. */
+int32_t ts_per_sample_sharded(const double* tree, int64_t bound, const double* u, int64_t M,
+                              const double* roots3, int32_t G, int32_t rank, const double* prio,
+                              double beta, int32_t weight_norm, int64_t* idx, double* weight,
+                              double* wmax_out, int32_t* err_flag, ts_stream_t stream);
+/* weight[j] /= *wmax  (prio.py:101) */
+int32_t ts_per_normalize(double* weight, int64_t M, const double* wmax, ts_stream_t stream);
+/* get_weight on given indices (prio.py:66-76), optional batch-max normalisation (:101);
+ * idx[j] == -1 gives weight 0. */
 int32_t ts_per_weight(const double* tree, int64_t bound, const int64_t* idx, int64_t M,
                       const double* prio, double beta, int32_t weight_norm, double* weight,
                       void* scratch16, ts_stream_t stream);
 /* p = |td| + eps computed in td's dtype (f32 eps, prio.py:38,86); leaf = p^alpha rounded to
- * td's dtype (:87); tree update as ts_segtree_update; prio <- {max(max,p), min(min,p)}. */
+ * td's dtype (:87); tree update as ts_segtree_update; prio <- {max(max,p), min(min,p)}.
+ * Entries with idx[j] == -1 are skipped silently (queries of another shard). */
 int32_t ts_per_update(double* tree, int64_t size, int64_t bound, const int64_t* idx,
                       const void* td, int32_t td_dtype, int64_t M, double alpha, double* prio,
                       uint32_t* stamp, uint32_t* counter, int32_t* err_flag,

@@ -467,3 +467,38 @@ def ppo_loss(logp, logp_old, adv, returns, v_s, value, eps_clip: float = 0.2,
         vf_loss = ((returns - value) ** 2).mean()  # :139
         dvalue = -2.0 * (returns - value) / n
     return clip_loss, vf_loss, dlogp, dvalue, adv
+
+
+# ---------------------------------------------------------------------------------------------
+# Sharded PER: G power-of-two-aligned shard trees == one global tree
+# ---------------------------------------------------------------------------------------------
+def global_tree_from_shards(shards) -> "SegTree":
+    """The reference's single global tree (manager.py:209-214) whose leaves are the shards'
+    leaves laid end to end; requires equal power-of-two shard bounds."""
+    G, b = len(shards), shards[0]._bound
+    assert G & (G - 1) == 0 and all(s._bound == b and s._size == b for s in shards)
+    g = SegTree(G * b)
+    g[np.arange(G * b)] = np.concatenate([s._value[b:] for s in shards])
+    return g
+
+
+def sharded_route(u, roots):
+    """Top of the global tree rebuilt from the shard roots in its pairwise order
+    (segtree.py:104), then ``_get_prefix_sum_idx`` (:122-137) over those log2(G) levels.
+    Returns (total, shard[M], residual value[M]) for ``scalar = u * total`` (prio.py:61)."""
+    roots = np.asarray(roots, dtype=np.float64)
+    G = roots.size
+    top = np.zeros(2 * G)
+    top[G:] = roots
+    for i in range(G - 1, 0, -1):
+        top[i] = top[2 * i] + top[2 * i + 1]
+    total = top[1] if G > 1 else roots[0]
+    v = np.asarray(u, dtype=np.float64) * total
+    node = np.ones(v.shape, dtype=np.int64)
+    while node[0] < G:
+        node = node * 2
+        lsons = top[node]
+        direct = lsons < v
+        v = v - lsons * direct
+        node = node + direct
+    return total, node - G, v

@@ -1,0 +1,139 @@
+"""Sharded PER on one GPU: the G ranks are emulated as G local trees on cuda:0 (the kernels of
+different ranks never wait on each other, so running them back to back is exact).  The union of
+the ranks' samples must equal the reference's samples from ONE global tree, bit for bit."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def _fill(tree_t, stamp, counter, err, leaves, L):
+    n = leaves.size
+    idx = torch.arange(n, device="cuda")
+    val = torch.from_numpy(leaves).cuda()
+    L.check(L.lib().ts_segtree_update(L.ptr(tree_t), n, n, L.ptr(idx), L.ptr(val), L.TS_F64, 1, n,
+                                      L.ptr(stamp), L.ptr(counter), L.ptr(err), L.stream()),
+            "fill")
+
+
+@pytest.mark.parametrize("G,cap,bsz", [(2, 1 << 13, 512), (4, 1 << 14, 4096), (8, 1 << 16, 4096),
+                                       (8, 1 << 20, 4096), (1, 1 << 14, 300)])
+def test_emulated_ranks_match_global_tree(G, cap, bsz):
+    from tianshou_fork_b200 import _lib as L
+    if G * cap > (1 << 21):
+        rng = np.random.default_rng(G)
+        steps = 2
+    else:
+        rng = np.random.default_rng(G + cap)
+        steps = 4
+    total = G * cap
+    leaves = (np.abs(rng.standard_normal(total)) + 1e-7) ** 0.6
+    glob = orc.PER(total, 0.6, 0.4)
+    glob.weight[np.arange(total)] = leaves
+    ranks = []
+    for r in range(G):
+        d = dict(tree=torch.zeros(2 * cap, dtype=torch.float64, device="cuda"),
+                 stamp=torch.zeros(cap, dtype=torch.int32, device="cuda"),
+                 counter=torch.zeros(4, dtype=torch.int32, device="cuda"),
+                 err=torch.zeros(1, dtype=torch.int32, device="cuda"),
+                 prio=torch.ones(2, dtype=torch.float64, device="cuda"),
+                 wmax=torch.zeros(1, dtype=torch.float64, device="cuda"))
+        _fill(d["tree"], d["stamp"], d["counter"], d["err"], leaves[r * cap:(r + 1) * cap], L)
+        ranks.append(d)
+    lib = L.lib()
+    for step in range(steps):
+        # ---- the exchange: {root, max_prio, min_prio} of every rank --------------------------
+        roots3 = torch.stack([torch.cat([d["tree"][1:2], d["prio"]]) for d in ranks]).contiguous()
+        gmax, gmin = roots3[:, 1].max(), roots3[:, 2].min()
+        for d in ranks:
+            d["prio"][0], d["prio"][1] = gmax, gmin
+        u = rng.random(bsz)
+        want = glob.sample_indices(u)
+        want_w = glob.batch_weight(want)  # (p/min)^-beta / max over the batch (prio.py:76,101)
+        ud = torch.from_numpy(u).cuda()
+        idxs, ws = [], []
+        for r, d in enumerate(ranks):
+            idx = torch.empty(bsz, dtype=torch.int64, device="cuda")
+            w = torch.empty(bsz, dtype=torch.float64, device="cuda")
+            L.check(lib.ts_per_sample_sharded(
+                L.ptr(d["tree"]), cap, L.ptr(ud), bsz, L.ptr(roots3), G, r, L.ptr(d["prio"]), 0.4,
+                1, L.ptr(idx), L.ptr(w), L.ptr(d["wmax"]), L.ptr(d["err"]), L.stream()), "sample")
+            idxs.append(idx)
+            ws.append(w)
+        own = torch.stack([i >= 0 for i in idxs])
+        assert bool((own.sum(0) == 1).all())  # every query owned by exactly one rank
+        got = sum(torch.where(i >= 0, i + r * cap, torch.zeros_like(i))
+                  for r, i in enumerate(idxs)).cpu().numpy()
+        assert np.array_equal(got, want), (G, step)  # bit-exact global indices
+        # MAX all-reduce of the per-rank maxima, then the normalisation kernel
+        wmax = torch.stack([d["wmax"] for d in ranks]).max().reshape(1)
+        for w in ws:
+            L.check(lib.ts_per_normalize(L.ptr(w), bsz, L.ptr(wmax), L.stream()), "norm")
+        got_w = sum(ws).cpu().numpy()  # foreign entries are 0
+        assert np.allclose(got_w, want_w, rtol=1e-12)
+        # ---- update: every rank gets the full batch with -1 for foreign samples ---------------
+        td = rng.standard_normal(bsz).astype(np.float32)
+        gidx = want.copy()
+        gidx[: bsz // 8] = gidx[bsz // 8: 2 * (bsz // 8)]  # duplicated indices
+        glob.update_weight(gidx, td)
+        tdd = torch.from_numpy(td).cuda()
+        for r, d in enumerate(ranks):
+            loc = np.where((gidx >= r * cap) & (gidx < (r + 1) * cap), gidx - r * cap, -1)
+            locd = torch.from_numpy(loc).cuda()
+            L.check(lib.ts_per_update(L.ptr(d["tree"]), cap, cap, L.ptr(locd), L.ptr(tdd), L.TS_F32,
+                                      bsz, 0.6, L.ptr(d["prio"]), L.ptr(d["stamp"]),
+                                      L.ptr(d["counter"]), L.ptr(d["err"]), L.stream()), "update")
+            assert int(d["err"].item()) == 0  # -1 is a sentinel, not a range error
+        # priority extrema: max / min over the ranks == the reference's single scalars
+        assert max(float(d["prio"][0]) for d in ranks) == glob._max_prio
+        assert min(float(d["prio"][1]) for d in ranks) == glob._min_prio
+        # leaves through pow: tolerance, then re-anchor on the oracle's leaves (as in the
+        # unsharded test) so the next round tests bit-exactness again
+        for r, d in enumerate(ranks):
+            got_l = d["tree"][cap:].cpu().numpy()
+            ref_l = glob.weight._value[total + r * cap: total + (r + 1) * cap]
+            assert np.allclose(got_l, ref_l, rtol=6e-7, atol=0)
+            ch = np.nonzero(got_l != ref_l)[0]
+            if ch.size:
+                ci = torch.from_numpy(ch).cuda()
+                cv = torch.from_numpy(ref_l[ch]).cuda()
+                L.check(lib.ts_segtree_update(L.ptr(d["tree"]), cap, cap, L.ptr(ci), L.ptr(cv),
+                                              L.TS_F64, 1, ch.size, L.ptr(d["stamp"]),
+                                              L.ptr(d["counter"]), L.ptr(d["err"]), L.stream()),
+                        "anchor")
+            # shard subtree == the global tree's subtree under node G + r, every level
+            node, width = G + r, 1
+            loc = d["tree"].cpu().numpy()
+            lnode = 1
+            while lnode < 2 * cap:
+                assert np.array_equal(loc[lnode:lnode + width],
+                                      glob.weight._value[node:node + width])
+                node, lnode, width = node * 2, lnode * 2, width * 2
+
+
+def test_world_size_one_class_equals_unsharded():
+    """No process group: the sharded class degenerates to PrioritizedVectorReplayBuffer."""
+    import tianshou_fork_b200 as ts
+    a = ts.ShardedPrioritizedVectorReplayBuffer(1 << 12, 8, alpha=0.6, beta=0.4)
+    b = ts.PrioritizedVectorReplayBuffer(1 << 12, 8, alpha=0.6, beta=0.4)
+    rng = np.random.default_rng(0)
+    for t in range(40):
+        batch = dict(obs=rng.standard_normal((8, 3)).astype(np.float32), act=rng.integers(0, 4, 8),
+                     rew=rng.standard_normal(8), terminated=rng.random(8) < 0.1,
+                     truncated=np.zeros(8, bool),
+                     obs_next=rng.standard_normal((8, 3)).astype(np.float32), info={})
+        a.add(ts.Batch(**batch))
+        b.add(ts.Batch(**batch))
+    for _ in range(3):
+        u = torch.from_numpy(rng.random(64)).cuda()
+        ia, ib = a.sample_with_uniforms(u), b.sample_with_uniforms(u)
+        assert torch.equal(ia, ib) and torch.equal(a._cached_weight[1], b._cached_weight[1])
+        td = torch.from_numpy(rng.standard_normal(64).astype(np.float32)).cuda()
+        a.update_weight(ia, td)
+        b.update_weight(ib, td)
+        assert torch.equal(a.weight._value, b.weight._value)
+        assert a._max_prio == b._max_prio and a._min_prio == b._min_prio
+    assert torch.equal(a.to_global(ia), ia)

@@ -15,7 +15,7 @@ All arithmetic runs in hand-written CUDA kernels (``csrc/*.cu``) behind the C-AB
 from . import _lib
 from .data import (Batch, PrioritizedReplayBuffer, PrioritizedReplayBufferManager,
                    PrioritizedVectorReplayBuffer, ReplayBuffer, ReplayBufferManager,
-                   SegmentTree, VectorReplayBuffer)
+                   SegmentTree, ShardedPrioritizedVectorReplayBuffer, VectorReplayBuffer)
 from .policy import BasePolicy, PPOPolicy, ppo_loss
 
 __version__ = "0.1.0"
@@ -23,5 +23,5 @@ __version__ = "0.1.0"
 __all__ = [
     "Batch", "ReplayBuffer", "ReplayBufferManager", "VectorReplayBuffer",
     "PrioritizedReplayBuffer", "PrioritizedReplayBufferManager",
-    "PrioritizedVectorReplayBuffer", "SegmentTree", "BasePolicy", "PPOPolicy", "ppo_loss",
+    "PrioritizedVectorReplayBuffer", "ShardedPrioritizedVectorReplayBuffer", "SegmentTree", "BasePolicy", "PPOPolicy", "ppo_loss",
 ]

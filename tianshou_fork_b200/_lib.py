@@ -50,6 +50,9 @@ SIGNATURES = {
     "ts_segtree_reduce": (_i32, [_vp, _i64, _i64, _i64, _vp, _vp]),
     "ts_segtree_prefix_idx": (_i32, [_vp, _i64, _vp, _i32, _i64, _i32, _vp, _vp, _vp]),
     "ts_per_sample": (_i32, [_vp, _i64, _vp, _i64, _vp, _f64, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "ts_per_sample_sharded": (_i32, [_vp, _i64, _vp, _i64, _vp, _i32, _i32, _vp, _f64, _i32, _vp,
+                                     _vp, _vp, _vp, _vp]),
+    "ts_per_normalize": (_i32, [_vp, _i64, _vp, _vp]),
     "ts_per_weight": (_i32, [_vp, _i64, _vp, _i64, _vp, _f64, _i32, _vp, _vp, _vp]),
     "ts_per_update": (_i32, [_vp, _i64, _i64, _vp, _vp, _i32, _i64, _f64, _vp, _vp, _vp, _vp,
                              _vp]),

@@ -109,6 +109,7 @@ __device__ __forceinline__ double dsmem_ld_f64(const double* local, uint32_t ran
 constexpr int64_t kSmallM = 16383;     // tiered path: batch position + 1 fits the stamp's 14 bits
 constexpr int64_t kDenseBound = 4096;  // trees up to this many leaves are rebuilt densely
 constexpr int kTagShift = 14;
+constexpr int64_t kSkipIndex = -1;  // batch entries to ignore silently (foreign shard)
 constexpr uint32_t kTagMax = (1u << (32 - kTagShift)) - 1u;
 
 // ============================================================================================
@@ -325,8 +326,8 @@ segtree_update_tiered(double* __restrict__ tree, int64_t size, int64_t bound, in
         for (int64_t r = 0; r < rounds; ++r) {
             const int64_t j = r * per_round + blockIdx.x * 32 + lane;
             int64_t idx = -1;
-            if (j < M) {
-                idx = index[j];
+            if (j < M) idx = index[j];
+            if (idx != kSkipIndex) {  // -1: "not in this shard" (ts_per_sample_sharded), no error
                 if (is_per(vs)) {
                     const double p = per_priority(vs, j);
                     pmax = fmax(pmax, p);
@@ -420,6 +421,7 @@ segtree_stamp_kernel(const int64_t* __restrict__ index, int64_t M, int64_t size,
     for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < M;
          j += (int64_t)gridDim.x * blockDim.x) {
         const int64_t idx = index[j];
+        if (idx == kSkipIndex) continue;
         if (idx < 0 || idx >= size) { atomicOr(err_flag, TS_FLAG_INDEX_RANGE); continue; }
         atomicMax(stamp + idx, (uint32_t)j + 1u);
     }
@@ -432,12 +434,13 @@ segtree_leaf_kernel(double* __restrict__ tree, int64_t size, int64_t bound,
     double pmax = 0.0, pmin = INFINITY;
     for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < M;
          j += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t idx = index[j];
+        if (idx == kSkipIndex) continue;
         if (is_per(vs)) {
             const double p = per_priority(vs, j);
             pmax = fmax(pmax, p);
             pmin = fmin(pmin, p);
         }
-        const int64_t idx = index[j];
         if (idx < 0 || idx >= size) continue;
         if (stamp[idx] == (uint32_t)j + 1u) {
             tree[bound + idx] = leaf_value(vs, j);
@@ -684,46 +687,91 @@ __device__ __forceinline__ double is_weight(double leaf, double min_prio, double
 }
 
 // SAMPLE: idx from the descent; otherwise idx is given (get_weight on known indices)
+// Sharded form: this GPU holds shard `rank` of G power-of-two-aligned subtrees of
+// the reference's single global tree (manager.py:209-214).  `roots3` = G x {root, max_prio,
+// min_prio} gathered from all ranks; the log2(G) levels above the shard roots are rebuilt here
+// in the global tree's own pairwise order, every query is routed down them with the same strict
+// compare / subtract, and only the queries that land in this shard descend locally -- the rest
+// get idx = -1, weight = 0.  Normalisation needs the maximum over ALL ranks, so with G > 1 the
+// kernel writes the local maximum to *wmax_out and leaves the weights raw.
+struct ShardInfo {
+    const double* roots3;  // nullptr: not sharded
+    int G, rank;
+    double* wmax_out;
+};
+constexpr int kMaxShards = 64;
+
 template <bool SAMPLE, int NT>
 __global__ void __launch_bounds__(NT)
 per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg_bound,
                           const double* __restrict__ u, int64_t M,
                           const double* __restrict__ prio, double beta, int weight_norm,
                           int64_t* __restrict__ idx, double* __restrict__ weight,
-                          int32_t* __restrict__ err_flag) {
+                          int32_t* __restrict__ err_flag, ShardInfo sh) {
     __shared__ double s_top[SAMPLE ? kTopCached : 2];
+    __shared__ double s_gtop[2 * kMaxShards];  // heap of the levels above the shard roots
     __shared__ double s_warp[NT / 32];
     __shared__ double s_cta;
     const int tid = threadIdx.x;
+    const bool sharded = sh.roots3 != nullptr;
+    const int G = sharded ? sh.G : 1;
     int cached = 0;
     double total = 0.0;
+    double min_prio = __ldg(prio + 1);
+    if (sharded) {
+        if (tid < G) s_gtop[G + tid] = __ldcg(sh.roots3 + 3 * tid);
+        __syncthreads();
+        for (int w = G >> 1; w >= 1; w >>= 1) {
+            if (tid < w) s_gtop[w + tid] = __dadd_rn(s_gtop[2 * (w + tid)], s_gtop[2 * (w + tid) + 1]);
+            __syncthreads();
+        }
+        for (int r = 0; r < G; ++r) min_prio = fmin(min_prio, __ldcg(sh.roots3 + 3 * r + 2));
+    }
     if (SAMPLE) {
         cached = stage_top<NT>(tree, bound, s_top, tid);
-        total = s_top[1];
+        total = sharded ? s_gtop[1] : s_top[1];
     }
-    const double min_prio = __ldg(prio + 1);
     const int64_t sweep = (int64_t)cluster_nctarank() * NT;
     const int64_t j0 = (int64_t)cluster_ctarank() * NT + tid;
     double wmax = 0.0, w_first = 0.0;
     for (int64_t j = j0; j < M; j += sweep) {
         int64_t leaf;
+        bool mine = true;
         if (SAMPLE) {
             double v = __dmul_rn(u[j], total);                   // prio.py:61
             if (!(v >= 0.0 && v < total)) atomicOr(err_flag, TS_FLAG_PREFIX_RANGE);
-            leaf = descend<double>(tree, bound, lg_bound, s_top, cached, v);
+            if (sharded) {
+                int node = 1;
+                while (node < G) {                               // the global tree's top levels
+                    node <<= 1;
+                    node += step_down(s_gtop[node], v);
+                }
+                mine = node - G == sh.rank;
+            }
+            leaf = mine ? descend<double>(tree, bound, lg_bound, s_top, cached, v) : -1;
             idx[j] = leaf;
         } else {
             leaf = idx[j];
+            mine = leaf >= 0;
         }
-        const double w = is_weight(__ldg(tree + bound + leaf), min_prio, beta);
+        const double w = mine ? is_weight(__ldg(tree + bound + leaf), min_prio, beta) : 0.0;
         if (j == j0) w_first = w; else weight[j] = w;  // later sweeps park the raw weight
         wmax = fmax(wmax, w);
     }
     if (weight_norm) wmax = cluster_max<NT>(wmax, s_warp, &s_cta);
+    const bool scale = weight_norm && !sharded;
+    if (sharded && weight_norm && j0 == 0) *sh.wmax_out = wmax;
     for (int64_t j = j0; j < M; j += sweep) {
         const double w = j == j0 ? w_first : weight[j];
-        weight[j] = weight_norm ? __ddiv_rn(w, wmax) : w;        // prio.py:101
+        weight[j] = scale ? __ddiv_rn(w, wmax) : w;              // prio.py:101
     }
+}
+
+// weight[j] /= *wmax (prio.py:101) once the maximum over all shards is known
+__global__ void __launch_bounds__(256)
+per_normalize_kernel(double* __restrict__ weight, int64_t M, const double* __restrict__ wmax) {
+    const int64_t j = blockIdx.x * (int64_t)256 + threadIdx.x;
+    if (j < M) weight[j] = __ddiv_rn(weight[j], __ldg(wmax));
 }
 
 }  // namespace
@@ -736,7 +784,7 @@ template <bool SAMPLE>
 static int32_t launch_per_cluster(const double* tree, int64_t bound, int lg, const double* u,
                                   int64_t M, const double* prio, double beta, int weight_norm,
                                   int64_t* idx, double* weight, int32_t* err_flag,
-                                  cudaStream_t st) {
+                                  ShardInfo sh, cudaStream_t st) {
     // 16 CTAs x 256 threads spreads a large batch over twice the SMs (7.4 vs 8.7 us at 4096
     // queries); it is an opt-in cluster size, so it is used only where the device can place it.
     static int wide_ok = -1;  // per instantiation
@@ -774,7 +822,7 @@ static int32_t launch_per_cluster(const double* tree, int64_t bound, int lg, con
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tree, bound, lg, u, M, prio, beta, weight_norm,
-                                       idx, weight, err_flag);
+                                       idx, weight, err_flag, sh);
     if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; (void)cudaGetLastError(); return TS_ERR_CUDA; }
     return check_launch();
 }
@@ -832,7 +880,8 @@ extern "C" int32_t ts_per_sample(const double* tree, int64_t bound, const double
     if (!aligned(tree, 16)) return TS_ERR_ALIGN;
     (void)scratch16;  // kept in the ABI; the cluster kernel needs no global scratch
     return launch_per_cluster<true>(tree, bound, ilog2(bound), u, M, prio, beta, weight_norm, idx,
-                                    weight, err_flag, (cudaStream_t)stream);
+                                    weight, err_flag, ShardInfo{nullptr, 1, 0, nullptr},
+                                    (cudaStream_t)stream);
 }
 
 extern "C" int32_t ts_per_weight(const double* tree, int64_t bound, const int64_t* idx, int64_t M,
@@ -844,7 +893,7 @@ extern "C" int32_t ts_per_weight(const double* tree, int64_t bound, const int64_
     (void)scratch16;
     return launch_per_cluster<false>(tree, bound, 0, nullptr, M, prio, beta, weight_norm,
                                      const_cast<int64_t*>(idx), weight, nullptr,
-                                     (cudaStream_t)stream);
+                                     ShardInfo{nullptr, 1, 0, nullptr}, (cudaStream_t)stream);
 }
 
 extern "C" int32_t ts_per_update(double* tree, int64_t size, int64_t bound, const int64_t* idx,
@@ -876,4 +925,33 @@ extern "C" int32_t ts_debug_update_phases(uint64_t* out6) {
     if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
     for (int i = 0; i < 6; ++i) out6[i] = h[i];
     return TS_OK;
+}
+
+extern "C" int32_t ts_per_sample_sharded(const double* tree, int64_t bound, const double* u,
+                                         int64_t M, const double* roots3, int32_t G,
+                                         int32_t rank, const double* prio, double beta,
+                                         int32_t weight_norm, int64_t* idx, double* weight,
+                                         double* wmax_out, int32_t* err_flag,
+                                         ts_stream_t stream) {
+    if (M < 0 || bound <= 0 || G < 1 || G > kMaxShards || (G & (G - 1)) != 0 || rank < 0 ||
+        rank >= G)
+        return TS_ERR_BAD_ARG;
+    if (M == 0) return TS_OK;
+    if (!tree || !u || !roots3 || !prio || !idx || !weight || !wmax_out || !err_flag)
+        return TS_ERR_BAD_ARG;
+    if ((bound & (bound - 1)) != 0) return TS_ERR_BAD_ARG;
+    if (!aligned(tree, 16)) return TS_ERR_ALIGN;
+    return launch_per_cluster<true>(tree, bound, ilog2(bound), u, M, prio, beta, weight_norm, idx,
+                                    weight, err_flag, ShardInfo{roots3, G, rank, wmax_out},
+                                    (cudaStream_t)stream);
+}
+
+extern "C" int32_t ts_per_normalize(double* weight, int64_t M, const double* wmax,
+                                    ts_stream_t stream) {
+    if (M < 0) return TS_ERR_BAD_ARG;
+    if (M == 0) return TS_OK;
+    if (!weight || !wmax) return TS_ERR_BAD_ARG;
+    per_normalize_kernel<<<(unsigned)((M + 255) / 256), 256, 0, (cudaStream_t)stream>>>(weight, M,
+                                                                                       wmax);
+    return check_launch();
 }

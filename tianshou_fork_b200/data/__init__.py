@@ -5,9 +5,10 @@ from .buffer import ReplayBuffer
 from .manager import ReplayBufferManager, VectorReplayBuffer
 from .prio import (PrioritizedReplayBuffer, PrioritizedReplayBufferManager,
                    PrioritizedVectorReplayBuffer)
+from .sharded import ShardedPrioritizedVectorReplayBuffer
 
 __all__ = [
     "Batch", "SegmentTree", "ReplayBuffer", "ReplayBufferManager", "VectorReplayBuffer",
     "PrioritizedReplayBuffer", "PrioritizedReplayBufferManager",
-    "PrioritizedVectorReplayBuffer",
+    "PrioritizedVectorReplayBuffer", "ShardedPrioritizedVectorReplayBuffer",
 ]
