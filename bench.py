@@ -357,14 +357,20 @@ def run_b200(args):
 
 
 def run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
-    """BASELINE.json configs[3]/[4] shape: one 2^20-leaf tree per GPU, batch 4096."""
+    """BASELINE.json configs[3] (1 GPU) / configs[4] (N GPUs): one 2^20-leaf shard per GPU.
+
+    N == 1: step = ts_per_sample + ts_per_update, 8 steps per CUDA graph.
+    N  > 1: the reference's ONE global tree of N * 2^20 leaves, sharded; a
+    step samples the GLOBAL batch of 4096 from identical uniforms on every rank
+    (ts_per_sample_sharded: each rank descends only the queries it owns), MAX-all-reduces the
+    weight maximum, normalises, updates its own leaves and all-gathers the 24-byte
+    {root, max, min} records.  The batch is global, so this leg is strong scaling."""
     rng = np.random.default_rng(100 + rank)
     size = bound = PER_LEAVES
     tree = torch.zeros(2 * bound, dtype=torch.float64, device=dev)
     stamp = torch.zeros(size, dtype=torch.int32, device=dev)
     counter = torch.zeros(4, dtype=torch.int32, device=dev)
     err = torch.zeros(1, dtype=torch.int32, device=dev)
-    scratch = torch.zeros(4, dtype=torch.int32, device=dev)
     prio = torch.ones(2, dtype=torch.float64, device=dev)
     leaves = torch.from_numpy((np.abs(rng.standard_normal(size)) + 1e-7) ** PER_ALPHA).to(dev)
     all_idx = torch.arange(size, device=dev)
@@ -372,64 +378,109 @@ def run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
     L.check(lib.ts_segtree_update(tree.data_ptr(), size, bound, all_idx.data_ptr(),
                                   leaves.data_ptr(), L.TS_F64, 1, size, stamp.data_ptr(),
                                   counter.data_ptr(), err.data_ptr(), st), "ts_segtree_update")
-    R = 8  # distinct (uniforms, td) sets inside one graph
-    u = torch.from_numpy(rng.random((R, PER_BATCH))).to(dev)
-    td = torch.from_numpy(rng.standard_normal((R, PER_BATCH)).astype(np.float32)).to(dev)
+    R = 8  # distinct (uniforms, td) sets
+    shared = np.random.default_rng(2)  # the same draws on every rank
+    u = torch.from_numpy(shared.random((R, PER_BATCH))).to(dev)
+    td = torch.from_numpy(shared.standard_normal((R, PER_BATCH)).astype(np.float32)).to(dev)
     idx = torch.empty(R, PER_BATCH, dtype=torch.int64, device=dev)
     w = torch.empty(R, PER_BATCH, dtype=torch.float64, device=dev)
-    roots = torch.zeros(world, 3, dtype=torch.float64, device=dev)
-    mine = torch.zeros(3, dtype=torch.float64, device=dev)
-
-    def step(r, s):
-        L.check(lib.ts_per_sample(tree.data_ptr(), bound, u[r].data_ptr(), PER_BATCH,
-                                  prio.data_ptr(), PER_BETA, 1, idx[r].data_ptr(),
-                                  w[r].data_ptr(), scratch.data_ptr(), err.data_ptr(), s),
-                "ts_per_sample")
-        L.check(lib.ts_per_update(tree.data_ptr(), size, bound, idx[r].data_ptr(),
-                                  td[r].data_ptr(), L.TS_F32, PER_BATCH, PER_ALPHA,
-                                  prio.data_ptr(), stamp.data_ptr(), counter.data_ptr(),
-                                  err.data_ptr(), s), "ts_per_update")
-
-    side = torch.cuda.Stream(dev)
-    with torch.cuda.stream(side):
-        for r in range(R):
-            step(r, side.cuda_stream)
-    side.synchronize()
-    graph = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(graph, stream=side):
-        for r in range(R):
-            step(r, side.cuda_stream)
-    replays = 50
-    for _ in range(5):
-        graph.replay()
-    barrier()
-    stream = torch.cuda.current_stream()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for _ in range(replays):
-        graph.replay()
-        if world > 1:  # shard roots + prio extrema to every rank
-            mine[0] = tree[1]
-            mine[1:] = prio
-            dist.all_gather_into_tensor(roots.view(-1), mine)
-    e1.record(stream)
-    barrier()
-    ms = max_over_ranks(e0.elapsed_time(e1))
-    assert int(err.item()) == 0, "PER range flag raised"
-    steps = replays * R
-    us = ms * 1e3 / steps
-    value = PER_BATCH * world * steps / (ms * 1e-3)
     peak, _ = measured_peaks()
+
+    if world == 1:
+        def step(r, s):
+            L.check(lib.ts_per_sample(tree.data_ptr(), bound, u[r].data_ptr(), PER_BATCH,
+                                      prio.data_ptr(), PER_BETA, 1, idx[r].data_ptr(),
+                                      w[r].data_ptr(), None, err.data_ptr(), s), "ts_per_sample")
+            L.check(lib.ts_per_update(tree.data_ptr(), size, bound, idx[r].data_ptr(),
+                                      td[r].data_ptr(), L.TS_F32, PER_BATCH, PER_ALPHA,
+                                      prio.data_ptr(), stamp.data_ptr(), counter.data_ptr(),
+                                      err.data_ptr(), s), "ts_per_update")
+
+        side = torch.cuda.Stream(dev)
+        with torch.cuda.stream(side):
+            for r in range(R):
+                step(r, side.cuda_stream)
+        side.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            for r in range(R):
+                step(r, side.cuda_stream)
+        replays = 50
+        for _ in range(5):
+            graph.replay()
+        barrier()
+        stream = torch.cuda.current_stream()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(replays):
+            graph.replay()
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        steps = replays * R
+        launches_per_step, scaling = 2, "n/a (1 GPU)"
+        how = "8 steps per CUDA graph"
+    else:
+        mine3 = torch.zeros(3, dtype=torch.float64, device=dev)
+        roots3 = torch.zeros(world, 3, dtype=torch.float64, device=dev)
+        wmax = torch.zeros(1, dtype=torch.float64, device=dev)
+
+        def sync_roots():
+            mine3[0:1].copy_(tree[1:2])
+            mine3[1:3].copy_(prio)
+            dist.all_gather_into_tensor(roots3.view(-1), mine3)
+            prio[0:1].copy_(roots3[:, 1].amax(0, keepdim=True))
+            prio[1:2].copy_(roots3[:, 2].amin(0, keepdim=True))
+
+        def step(r):
+            s = torch.cuda.current_stream().cuda_stream
+            L.check(lib.ts_per_sample_sharded(
+                tree.data_ptr(), bound, u[r].data_ptr(), PER_BATCH, roots3.data_ptr(), world,
+                rank, prio.data_ptr(), PER_BETA, 1, idx[r].data_ptr(), w[r].data_ptr(),
+                wmax.data_ptr(), err.data_ptr(), s), "ts_per_sample_sharded")
+            dist.all_reduce(wmax, op=dist.ReduceOp.MAX)
+            L.check(lib.ts_per_normalize(w[r].data_ptr(), PER_BATCH, wmax.data_ptr(), s),
+                    "ts_per_normalize")
+            L.check(lib.ts_per_update(tree.data_ptr(), size, bound, idx[r].data_ptr(),
+                                      td[r].data_ptr(), L.TS_F32, PER_BATCH, PER_ALPHA,
+                                      prio.data_ptr(), stamp.data_ptr(), counter.data_ptr(),
+                                      err.data_ptr(), s), "ts_per_update")
+            sync_roots()
+
+        sync_roots()
+        for i in range(16):
+            step(i % R)
+        barrier()
+        stream = torch.cuda.current_stream()
+        steps = 400
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(steps):
+            step(i % R)
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        owned = (idx >= 0).sum().to(torch.float64)
+        dist.all_reduce(owned)
+        assert int(owned.item()) == R * PER_BATCH, "every query must be owned by exactly one rank"
+        launches_per_step, scaling = 3, "strong (global batch 4096 over all shards)"
+        how = "eager launches; 2 NCCL collectives per step (MAX all-reduce 8 B, all-gather 24 B)"
+    ms = max_over_ranks(ms)
+    assert int(err.item()) == 0, "PER range flag raised"
+    us = ms * 1e3 / steps
+    value = PER_BATCH * steps / (ms * 1e-3)  # global samples/s (the batch is global for N > 1)
+    achieved = PER_BATCH * PER_ALG_BYTES_PER_SAMPLE / (us * 1e-6) / 1e9
     return {"metric": "PER samples/s", "value": value, "unit": "samples/s", "us_per_step": us,
-            "workload": "per GPU: 2^20-leaf f64 sum tree, batch 4096, alpha 0.6 beta 0.4; step = "
-                        "sample (descent + IS weights + batch-max norm) + update_weight "
-                        "(|td|+eps, pow, dedupe, tiered rebuild, one cooperative launch); 8 steps per CUDA graph"
-                        + ("; all_gather of shard roots per graph" if world > 1 else ""),
-            "gpu_launches_per_step": 2,
-            "roofline": {"bound": "hbm", "achieved": PER_BATCH * PER_ALG_BYTES_PER_SAMPLE / (us * 1e-6) / 1e9,
-                         "peak": peak, "unit": "GB/s",
-                         "frac": PER_BATCH * PER_ALG_BYTES_PER_SAMPLE / (us * 1e-6) / 1e9 / peak,
-                         "note": "latency-bound: ~20 dependent L2 round trips of ~0.5 us per step, not bytes; tree is L2-resident"}}
+            "scaling": scaling,
+            "workload": f"{world} shard(s) x 2^20-leaf f64 sum tree, global batch 4096, alpha 0.6 "
+                        "beta 0.4; step = sample (descent + IS weights + batch-max norm) + "
+                        "update_weight (|td|+eps, pow, dedupe, tiered rebuild, one cooperative "
+                        "launch); " + how,
+            "gpu_launches_per_step": launches_per_step,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak,
+                         "note": "latency-bound: ~20 dependent L2 round trips of ~0.5 us per "
+                                 "step, not bytes; tree is L2-resident"}}
 
 
 def main():

@@ -48,6 +48,7 @@ extern "C" {
 /* bits of the device-side error flag word */
 #define TS_FLAG_INDEX_RANGE 1  /* SegmentTree.__setitem__: index outside [0, size)   */
 #define TS_FLAG_PREFIX_RANGE 2 /* get_prefix_sum_idx: value outside [0, tree[1])      */
+#define TS_FLAG_PEER_TIMEOUT 4 /* sharded PER: a peer's record never arrived (bounded spin) */
 
 typedef void* ts_stream_t; /* cudaStream_t */
 
@@ -205,6 +206,24 @@ int32_t ts_per_sample_sharded(const double* tree, int64_t bound, const double* u
                               const double* roots3, int32_t G, int32_t rank, const double* prio,
                               double beta, int32_t weight_norm, int64_t* idx, double* weight,
                               double* wmax_out, int32_t* err_flag, ts_stream_t stream);
+/* The same step with the exchange INSIDE the kernels, over NVLink peer memory (no collective
+ * library call, CUDA-graph capturable).  Every rank owns `slots`, a zero-initialised buffer of
+ * 12 * G doubles that all peers can write (symmetric memory / cudaIpc); `peer_slots` is a DEVICE
+ * array of the G ranks' buffer addresses as mapped in this process; `state` is uint64[2] on the
+ * device, zero-initialised: {records published, samples drawn}.
+ *   ts_per_publish    after every tree change (fill, add, update_weight): stores this rank's
+ *                     {root, max_prio, min_prio, epoch} into every peer's buffer.
+ *   ts_per_sample_p2p waits (bounded; TS_FLAG_PEER_TIMEOUT) for the G records of the current
+ *                     epoch, routes and descends as ts_per_sample_sharded, exchanges the weight
+ *                     maximum the same way and writes NORMALISED weights; adopts the global
+ *                     priority extrema into `prio` (the reference has one pair, prio.py:35).
+ * All ranks issue the same sequence of calls (SPMD). */
+int32_t ts_per_publish(const double* tree, const double* prio, uint64_t* state,
+                       double* const* peer_slots, int32_t G, int32_t rank, ts_stream_t stream);
+int32_t ts_per_sample_p2p(const double* tree, int64_t bound, const double* u, int64_t M,
+                          double* slots, double* const* peer_slots, uint64_t* state, int32_t G,
+                          int32_t rank, double* prio, double beta, int32_t weight_norm,
+                          int64_t* idx, double* weight, int32_t* err_flag, ts_stream_t stream);
 /* weight[j] /= *wmax  (prio.py:101) */
 int32_t ts_per_normalize(double* weight, int64_t M, const double* wmax, ts_stream_t stream);
 /* get_weight on given indices (prio.py:66-76), optional batch-max normalisation (:101);

@@ -137,3 +137,77 @@ def test_world_size_one_class_equals_unsharded():
         assert torch.equal(a.weight._value, b.weight._value)
         assert a._max_prio == b._max_prio and a._min_prio == b._min_prio
     assert torch.equal(a.to_global(ia), ia)
+
+
+@pytest.mark.parametrize("G,cap,bsz", [(2, 1 << 13, 700), (8, 1 << 15, 4096)])
+def test_p2p_protocol_emulated_on_one_gpu(G, cap, bsz):
+    """The in-kernel exchange (ts_per_publish -> slot buffers -> ts_per_sample_p2p) with the G
+    ranks' slot buffers all on cuda:0.  Ranks run back to back, which is exact as long as no
+    kernel has to wait for a LATER one: the records are published before anyone samples, and the
+    weight-maximum exchange (which is mutual) is off here -- it is covered on real GPUs by
+    scripts/sharded_check.py."""
+    from tianshou_fork_b200 import _lib as L
+    lib = L.lib()
+    rng = np.random.default_rng(G * 31 + 1)
+    total = G * cap
+    leaves = (np.abs(rng.standard_normal(total)) + 1e-7) ** 0.6
+    glob = orc.PER(total, 0.6, 0.4)
+    glob.weight[np.arange(total)] = leaves
+    ranks = []
+    for r in range(G):
+        d = dict(tree=torch.zeros(2 * cap, dtype=torch.float64, device="cuda"),
+                 stamp=torch.zeros(cap, dtype=torch.int32, device="cuda"),
+                 counter=torch.zeros(4, dtype=torch.int32, device="cuda"),
+                 err=torch.zeros(1, dtype=torch.int32, device="cuda"),
+                 prio=torch.ones(2, dtype=torch.float64, device="cuda"),
+                 slots=torch.zeros(12 * G, dtype=torch.float64, device="cuda"),
+                 state=torch.zeros(2, dtype=torch.int64, device="cuda"))
+        _fill(d["tree"], d["stamp"], d["counter"], d["err"], leaves[r * cap:(r + 1) * cap], L)
+        ranks.append(d)
+    peers = torch.tensor([d["slots"].data_ptr() for d in ranks], dtype=torch.int64, device="cuda")
+
+    def publish_all():
+        for r, d in enumerate(ranks):
+            L.check(lib.ts_per_publish(L.ptr(d["tree"]), L.ptr(d["prio"]), L.ptr(d["state"]),
+                                       L.ptr(peers), G, r, L.stream()), "publish")
+
+    publish_all()
+    for step in range(4):
+        u = rng.random(bsz)
+        want = glob.sample_indices(u)
+        want_w = glob.get_weight(want)  # raw (p / min_prio) ** -beta, prio.py:76
+        ud = torch.from_numpy(u).cuda()
+        idxs, ws = [], []
+        for r, d in enumerate(ranks):
+            idx = torch.empty(bsz, dtype=torch.int64, device="cuda")
+            w = torch.empty(bsz, dtype=torch.float64, device="cuda")
+            L.check(lib.ts_per_sample_p2p(
+                L.ptr(d["tree"]), cap, L.ptr(ud), bsz, L.ptr(d["slots"]), L.ptr(peers),
+                L.ptr(d["state"]), G, r, L.ptr(d["prio"]), 0.4, 0, L.ptr(idx), L.ptr(w),
+                L.ptr(d["err"]), L.stream()), "sample_p2p")
+            idxs.append(idx)
+            ws.append(w)
+            assert int(d["err"].item()) == 0  # no peer timeout, no range error
+            assert d["state"].tolist() == [step + 1, step + 1]
+            # the global extrema were adopted into this rank's scalars
+            assert float(d["prio"][0]) == glob._max_prio and float(d["prio"][1]) == glob._min_prio
+        got = sum(torch.where(i >= 0, i + r * cap, torch.zeros_like(i))
+                  for r, i in enumerate(idxs)).cpu().numpy()
+        assert np.array_equal(got, want), (G, step)
+        assert np.allclose(sum(ws).cpu().numpy(), want_w, rtol=1e-12)
+        td = rng.standard_normal(bsz).astype(np.float32)
+        glob.update_weight(want, td)
+        tdd = torch.from_numpy(td).cuda()
+        for r, d in enumerate(ranks):
+            L.check(lib.ts_per_update(L.ptr(d["tree"]), cap, cap, L.ptr(idxs[r]), L.ptr(tdd),
+                                      L.TS_F32, bsz, 0.6, L.ptr(d["prio"]), L.ptr(d["stamp"]),
+                                      L.ptr(d["counter"]), L.ptr(d["err"]), L.stream()), "update")
+            # re-anchor the touched leaves on the oracle's f32 powers (see the unsharded test)
+            loc = idxs[r][idxs[r] >= 0].unique()
+            if loc.numel():
+                vals = torch.from_numpy(glob.weight[loc.cpu().numpy() + r * cap]).cuda()
+                L.check(lib.ts_segtree_update(L.ptr(d["tree"]), cap, cap, L.ptr(loc), L.ptr(vals),
+                                              L.TS_F64, 1, loc.numel(), L.ptr(d["stamp"]),
+                                              L.ptr(d["counter"]), L.ptr(d["err"]), L.stream()),
+                        "anchor")
+        publish_all()

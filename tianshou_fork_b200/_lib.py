@@ -20,7 +20,7 @@ CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libts_b200.so")
 
 TS_F32, TS_F64 = 0, 1
-TS_FLAG_INDEX_RANGE, TS_FLAG_PREFIX_RANGE = 1, 2
+TS_FLAG_INDEX_RANGE, TS_FLAG_PREFIX_RANGE, TS_FLAG_PEER_TIMEOUT = 1, 2, 4
 
 _vp, _i64, _i32, _f64, _f32, _sz = (
     ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32, ctypes.c_double, ctypes.c_float,
@@ -52,6 +52,9 @@ SIGNATURES = {
     "ts_per_sample": (_i32, [_vp, _i64, _vp, _i64, _vp, _f64, _i32, _vp, _vp, _vp, _vp, _vp]),
     "ts_per_sample_sharded": (_i32, [_vp, _i64, _vp, _i64, _vp, _i32, _i32, _vp, _f64, _i32, _vp,
                                      _vp, _vp, _vp, _vp]),
+    "ts_per_publish": (_i32, [_vp, _vp, _vp, _vp, _i32, _i32, _vp]),
+    "ts_per_sample_p2p": (_i32, [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i32, _i32, _vp, _f64, _i32,
+                                 _vp, _vp, _vp, _vp]),
     "ts_per_normalize": (_i32, [_vp, _i64, _vp, _vp]),
     "ts_per_weight": (_i32, [_vp, _i64, _vp, _i64, _vp, _f64, _i32, _vp, _vp, _vp]),
     "ts_per_update": (_i32, [_vp, _i64, _i64, _vp, _vp, _i32, _i64, _f64, _vp, _vp, _vp, _vp,

@@ -694,12 +694,57 @@ __device__ __forceinline__ double is_weight(double leaf, double min_prio, double
 // compare / subtract, and only the queries that land in this shard descend locally -- the rest
 // get idx = -1, weight = 0.  Normalisation needs the maximum over ALL ranks, so with G > 1 the
 // kernel writes the local maximum to *wmax_out and leaves the weights raw.
+//
+// Two exchange modes.  NCCL mode: the caller all-gathers the records into `roots3` and
+// MAX-all-reduces *wmax_out between this kernel and ts_per_normalize.  P2P mode (`slots` set):
+// the exchange is INSIDE the kernels, over NVLink peer memory -- every rank owns a slot buffer
+// that all peers can write (torch symmetric memory / cudaIpc); ts_per_publish stores
+// {root, max_prio, min_prio, epoch} straight into every peer's buffer after an update, this
+// kernel spins (bounded) until the G records of its epoch have landed, and the weight maximum
+// is exchanged the same way before the normalising division -- no collective library call,
+// no extra launch, capturable in a CUDA graph (epochs live on the device).
 struct ShardInfo {
-    const double* roots3;  // nullptr: not sharded
+    const double* roots3;  // NCCL mode: G x {root, max_prio, min_prio}; nullptr otherwise
     int G, rank;
-    double* wmax_out;
+    double* wmax_out;      // NCCL mode
+    double* slots;                       // P2P mode: this rank's slot buffer, 12 * G doubles
+    double* const* peer_slots;           // P2P mode: device array of the G ranks' slot buffers
+    unsigned long long* state;           // P2P mode: {records published, samples drawn} by this rank
 };
 constexpr int kMaxShards = 64;
+// slot buffer: records [2][G][4] = {root, max, min, epoch bits}; maxima [2][G][2] = {wmax, epoch}
+__host__ __device__ inline int slot_record(int G, unsigned long long e, int r) {
+    return ((int)(e & 1ull) * G + r) * 4;
+}
+__host__ __device__ inline int slot_wmax(int G, unsigned long long e, int r) {
+    return 8 * G + ((int)(e & 1ull) * G + r) * 2;
+}
+constexpr int kPeerSpin = 1 << 22;  // bounded wait (~ seconds), then TS_FLAG_PEER_TIMEOUT
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const void* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys_u64(void* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ double ld_relaxed_sys_f64(const double* p) {
+    double v;
+    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_sys_f64(double* p, double v) {
+    asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+// spin until the epoch word at `flag` equals `want`; false on timeout
+__device__ __forceinline__ bool wait_epoch(const double* flag, unsigned long long want) {
+    for (int it = 0; it < kPeerSpin; ++it) {
+        if (ld_acquire_sys_u64(flag) == want) return true;
+        __nanosleep(64);
+    }
+    return false;
+}
 
 template <bool SAMPLE, int NT>
 __global__ void __launch_bounds__(NT)
@@ -713,19 +758,38 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
     __shared__ double s_warp[NT / 32];
     __shared__ double s_cta;
     const int tid = threadIdx.x;
-    const bool sharded = sh.roots3 != nullptr;
+    __shared__ double s_gext[2 * kMaxShards];  // max_prio | min_prio of every rank
+    const bool p2p = sh.slots != nullptr;
+    const bool sharded = sh.roots3 != nullptr || p2p;
     const int G = sharded ? sh.G : 1;
     int cached = 0;
     double total = 0.0;
-    double min_prio = __ldg(prio + 1);
+    double min_prio = p2p ? INFINITY : __ldg(prio + 1);
+    unsigned long long epoch = 0, draw = 0;
     if (sharded) {
-        if (tid < G) s_gtop[G + tid] = __ldcg(sh.roots3 + 3 * tid);
+        if (p2p) {
+            epoch = __ldcg(sh.state);         // records this rank has published == everyone's
+            draw = __ldcg(sh.state + 1) + 1;  // this sample's number
+        }
+        if (tid < G) {
+            if (p2p) {
+                const double* rec = sh.slots + slot_record(G, epoch, tid);
+                if (!wait_epoch(rec + 3, epoch)) atomicOr(err_flag, TS_FLAG_PEER_TIMEOUT);
+                s_gtop[G + tid] = ld_relaxed_sys_f64(rec);
+                s_gext[tid] = ld_relaxed_sys_f64(rec + 1);
+                s_gext[G + tid] = ld_relaxed_sys_f64(rec + 2);
+            } else {
+                s_gtop[G + tid] = __ldcg(sh.roots3 + 3 * tid);
+                s_gext[tid] = __ldcg(sh.roots3 + 3 * tid + 1);
+                s_gext[G + tid] = __ldcg(sh.roots3 + 3 * tid + 2);
+            }
+        }
         __syncthreads();
         for (int w = G >> 1; w >= 1; w >>= 1) {
             if (tid < w) s_gtop[w + tid] = __dadd_rn(s_gtop[2 * (w + tid)], s_gtop[2 * (w + tid) + 1]);
             __syncthreads();
         }
-        for (int r = 0; r < G; ++r) min_prio = fmin(min_prio, __ldcg(sh.roots3 + 3 * r + 2));
+        for (int r = 0; r < G; ++r) min_prio = fmin(min_prio, s_gext[G + r]);
     }
     if (SAMPLE) {
         cached = stage_top<NT>(tree, bound, s_top, tid);
@@ -759,12 +823,62 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
         wmax = fmax(wmax, w);
     }
     if (weight_norm) wmax = cluster_max<NT>(wmax, s_warp, &s_cta);
-    const bool scale = weight_norm && !sharded;
-    if (sharded && weight_norm && j0 == 0) *sh.wmax_out = wmax;
+    bool scale = weight_norm && !sharded;
+    if (sharded && !p2p && weight_norm && j0 == 0) *sh.wmax_out = wmax;
+    if (p2p) {
+        const bool lead = cluster_ctarank() == 0;
+        if (weight_norm) {
+            // maximum over ALL ranks: store ours into every peer's buffer, wait for theirs
+            if (lead && tid < G) {
+                double* dst = sh.peer_slots[tid] + slot_wmax(G, draw, sh.rank);
+                st_relaxed_sys_f64(dst, wmax);
+                __threadfence_system();
+                st_release_sys_u64(dst + 1, draw);
+            }
+            if (tid < G) {
+                const double* src = sh.slots + slot_wmax(G, draw, tid);
+                if (!wait_epoch(src + 1, draw)) atomicOr(err_flag, TS_FLAG_PEER_TIMEOUT);
+                s_gtop[tid] = ld_relaxed_sys_f64(src);
+            }
+            __syncthreads();
+            wmax = 0.0;
+            for (int r = 0; r < G; ++r) wmax = fmax(wmax, s_gtop[r]);
+            scale = true;
+        }
+        if (!weight_norm) cluster_sync_all();  // every CTA has read `state` before it moves
+        if (lead && tid == 0) {
+            sh.state[1] = draw;
+            // the reference has ONE _max_prio / _min_prio (prio.py:35): adopt the global extrema
+            double gmax = 0.0;
+            for (int r = 0; r < G; ++r) gmax = fmax(gmax, s_gext[r]);
+            const_cast<double*>(prio)[0] = gmax;
+            const_cast<double*>(prio)[1] = min_prio;
+        }
+    }
     for (int64_t j = j0; j < M; j += sweep) {
         const double w = j == j0 ? w_first : weight[j];
         weight[j] = scale ? __ddiv_rn(w, wmax) : w;              // prio.py:101
     }
+}
+
+// After a tree change: this rank's {root, max_prio, min_prio} goes straight into every peer's
+// slot buffer over NVLink (G small stores), tagged with the new epoch.
+__global__ void __launch_bounds__(kMaxShards)
+per_publish_kernel(const double* __restrict__ tree, const double* __restrict__ prio,
+                   unsigned long long* __restrict__ state, double* const* __restrict__ peer_slots,
+                   int G, int rank) {
+    const int tid = threadIdx.x;
+    const unsigned long long e = __ldcg(state) + 1;
+    if (tid < G) {
+        double* dst = peer_slots[tid] + slot_record(G, e, rank);
+        st_relaxed_sys_f64(dst, __ldcg(tree + 1));
+        st_relaxed_sys_f64(dst + 1, __ldcg(prio));
+        st_relaxed_sys_f64(dst + 2, __ldcg(prio + 1));
+        __threadfence_system();
+        st_release_sys_u64(dst + 3, e);
+    }
+    __syncthreads();
+    if (tid == 0) state[0] = e;
 }
 
 // weight[j] /= *wmax (prio.py:101) once the maximum over all shards is known
@@ -880,7 +994,7 @@ extern "C" int32_t ts_per_sample(const double* tree, int64_t bound, const double
     if (!aligned(tree, 16)) return TS_ERR_ALIGN;
     (void)scratch16;  // kept in the ABI; the cluster kernel needs no global scratch
     return launch_per_cluster<true>(tree, bound, ilog2(bound), u, M, prio, beta, weight_norm, idx,
-                                    weight, err_flag, ShardInfo{nullptr, 1, 0, nullptr},
+                                    weight, err_flag, ShardInfo{nullptr, 1, 0, nullptr, nullptr, nullptr, nullptr},
                                     (cudaStream_t)stream);
 }
 
@@ -893,7 +1007,7 @@ extern "C" int32_t ts_per_weight(const double* tree, int64_t bound, const int64_
     (void)scratch16;
     return launch_per_cluster<false>(tree, bound, 0, nullptr, M, prio, beta, weight_norm,
                                      const_cast<int64_t*>(idx), weight, nullptr,
-                                     ShardInfo{nullptr, 1, 0, nullptr}, (cudaStream_t)stream);
+                                     ShardInfo{nullptr, 1, 0, nullptr, nullptr, nullptr, nullptr}, (cudaStream_t)stream);
 }
 
 extern "C" int32_t ts_per_update(double* tree, int64_t size, int64_t bound, const int64_t* idx,
@@ -942,7 +1056,7 @@ extern "C" int32_t ts_per_sample_sharded(const double* tree, int64_t bound, cons
     if ((bound & (bound - 1)) != 0) return TS_ERR_BAD_ARG;
     if (!aligned(tree, 16)) return TS_ERR_ALIGN;
     return launch_per_cluster<true>(tree, bound, ilog2(bound), u, M, prio, beta, weight_norm, idx,
-                                    weight, err_flag, ShardInfo{roots3, G, rank, wmax_out},
+                                    weight, err_flag, ShardInfo{roots3, G, rank, wmax_out, nullptr, nullptr, nullptr},
                                     (cudaStream_t)stream);
 }
 
@@ -953,5 +1067,35 @@ extern "C" int32_t ts_per_normalize(double* weight, int64_t M, const double* wma
     if (!weight || !wmax) return TS_ERR_BAD_ARG;
     per_normalize_kernel<<<(unsigned)((M + 255) / 256), 256, 0, (cudaStream_t)stream>>>(weight, M,
                                                                                        wmax);
+    return check_launch();
+}
+
+extern "C" int32_t ts_per_sample_p2p(const double* tree, int64_t bound, const double* u, int64_t M,
+                                     double* slots, double* const* peer_slots, uint64_t* state,
+                                     int32_t G, int32_t rank, double* prio, double beta,
+                                     int32_t weight_norm, int64_t* idx, double* weight,
+                                     int32_t* err_flag, ts_stream_t stream) {
+    if (M < 0 || bound <= 0 || G < 1 || G > kMaxShards || (G & (G - 1)) != 0 || rank < 0 ||
+        rank >= G)
+        return TS_ERR_BAD_ARG;
+    if (M == 0) return TS_OK;  // NOTE: every rank passes the same M, so all skip together
+    if (!tree || !u || !slots || !peer_slots || !state || !prio || !idx || !weight || !err_flag)
+        return TS_ERR_BAD_ARG;
+    if ((bound & (bound - 1)) != 0) return TS_ERR_BAD_ARG;
+    if (!aligned(tree, 16) || !aligned(slots, 8)) return TS_ERR_ALIGN;
+    return launch_per_cluster<true>(
+        tree, bound, ilog2(bound), u, M, prio, beta, weight_norm, idx, weight, err_flag,
+        ShardInfo{nullptr, G, rank, nullptr, slots, peer_slots, (unsigned long long*)state},
+        (cudaStream_t)stream);
+}
+
+extern "C" int32_t ts_per_publish(const double* tree, const double* prio, uint64_t* state,
+                                  double* const* peer_slots, int32_t G, int32_t rank,
+                                  ts_stream_t stream) {
+    if (!tree || !prio || !state || !peer_slots || G < 1 || G > kMaxShards || rank < 0 ||
+        rank >= G)
+        return TS_ERR_BAD_ARG;
+    per_publish_kernel<<<1, kMaxShards, 0, (cudaStream_t)stream>>>(
+        tree, prio, (unsigned long long*)state, peer_slots, G, rank);
     return check_launch();
 }

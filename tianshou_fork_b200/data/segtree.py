@@ -66,6 +66,8 @@ class SegmentTree:
             self._err.zero_()
             if flags & L.TS_FLAG_INDEX_RANGE:
                 raise AssertionError("SegmentTree index out of range [0, size)")  # :53
+            if flags & L.TS_FLAG_PEER_TIMEOUT:
+                raise RuntimeError("sharded PER: a peer's record did not arrive in time")
             if flags & L.TS_FLAG_PREFIX_RANGE:
                 raise AssertionError("prefix-sum value outside [0, tree.reduce())")  # :79
 

@@ -64,7 +64,7 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
 
     def __init__(self, total_size: int, buffer_num: int, rank: Optional[int] = None,
                  world_size: Optional[int] = None, group: Optional[dist.ProcessGroup] = None,
-                 **kwargs: Any) -> None:
+                 exchange: str = "auto", **kwargs: Any) -> None:
         if world_size is None:
             world_size = dist.get_world_size(group) if dist.is_initialized() else 1
         if rank is None:
@@ -78,13 +78,43 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
         self._mine3 = torch.zeros(3, dtype=torch.float64, device=self.device)
         self._roots3 = torch.zeros(world_size, 3, dtype=torch.float64, device=self.device)
         self._wmax = torch.zeros(1, dtype=torch.float64, device=self.device)
+        # exchange over NVLink peer memory inside the kernels ("p2p"), or NCCL collectives
+        # between them ("nccl"); "auto" tries p2p when there is more than one rank
+        assert exchange in ("auto", "p2p", "nccl")
+        self.exchange = "nccl"
+        if world_size > 1 and exchange in ("auto", "p2p"):
+            try:
+                self._setup_p2p()
+                self.exchange = "p2p"
+            except Exception:
+                if exchange == "p2p":
+                    raise
         self.sync_roots()
+
+    def _setup_p2p(self) -> None:
+        """Slot buffer every peer can write: torch symmetric memory (cudaIpc / fabric handles
+        exchanged through the process group's store), zeroed before anyone publishes."""
+        import torch.distributed._symmetric_memory as symm_mem
+        grp = self.group if self.group is not None else dist.group.WORLD
+        self._slots = symm_mem.empty(12 * self.world_size, dtype=torch.float64,
+                                     device=self.device)
+        self._slots.zero_()
+        self._symm = symm_mem.rendezvous(self._slots, grp)
+        self._peer_ptrs = int(self._symm.buffer_ptrs_dev)
+        self._state = torch.zeros(2, dtype=torch.int64, device=self.device)
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
 
     # ---- the one exchange step of the path ---------------------------------------------------
     def sync_roots(self) -> None:
         """Publish this shard's root and priority extrema, adopt the global extrema (the
         reference has ONE ``_max_prio`` / ``_min_prio``, prio.py:35, 88-89).  Stream-ordered
         device copies + one 24-byte all-gather; no host sync."""
+        if self.exchange == "p2p":
+            L.check(L.lib().ts_per_publish(
+                L.ptr(self.weight._value), L.ptr(self._prio), L.ptr(self._state),
+                self._peer_ptrs, self.world_size, self.rank, L.stream()), "ts_per_publish")
+            return  # the global extrema are adopted by the next sampling kernel
         self._mine3[0:1].copy_(self.weight._value[1:2])
         self._mine3[1:3].copy_(self._prio)
         self._roots3 = exchange_roots(self._mine3, self.world_size, self.group)
@@ -107,6 +137,14 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
         idx = torch.empty(m, dtype=torch.int64, device=self.device)
         w = torch.empty(m, dtype=torch.float64, device=self.device)
         t = self.weight
+        if self.exchange == "p2p":
+            L.check(L.lib().ts_per_sample_p2p(
+                L.ptr(t._value), t._bound, L.ptr(u), m, L.ptr(self._slots), self._peer_ptrs,
+                L.ptr(self._state), self.world_size, self.rank, L.ptr(self._prio),
+                float(self._beta), int(self._weight_norm), L.ptr(idx), L.ptr(w), L.ptr(t._err),
+                L.stream()), "ts_per_sample_p2p")
+            self._cached_weight = (idx, w)
+            return idx
         L.check(L.lib().ts_per_sample_sharded(
             L.ptr(t._value), t._bound, L.ptr(u), m, L.ptr(self._roots3), self.world_size,
             self.rank, L.ptr(self._prio), float(self._beta), int(self._weight_norm), L.ptr(idx),
