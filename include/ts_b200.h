@@ -220,6 +220,13 @@ int32_t ts_per_sample_sharded(const double* tree, int64_t bound, const double* u
  * All ranks issue the same sequence of calls (SPMD). */
 int32_t ts_per_publish(const double* tree, const double* prio, uint64_t* state,
                        double* const* peer_slots, int32_t G, int32_t rank, ts_stream_t stream);
+/* ts_per_update followed by ts_per_publish as ONE launch: the CTA that writes the new root also
+ * stores this rank's record into every peer's buffer (compute + exchange fused). */
+int32_t ts_per_update_publish(double* tree, int64_t size, int64_t bound, const int64_t* idx,
+                              const void* td, int32_t td_dtype, int64_t M, double alpha,
+                              double* prio, uint32_t* stamp, uint32_t* counter,
+                              int32_t* err_flag, uint64_t* state, double* const* peer_slots,
+                              int32_t G, int32_t rank, ts_stream_t stream);
 int32_t ts_per_sample_p2p(const double* tree, int64_t bound, const double* u, int64_t M,
                           double* slots, double* const* peer_slots, uint64_t* state, int32_t G,
                           int32_t rank, double* prio, double beta, int32_t weight_norm,

@@ -53,6 +53,8 @@ SIGNATURES = {
     "ts_per_sample_sharded": (_i32, [_vp, _i64, _vp, _i64, _vp, _i32, _i32, _vp, _f64, _i32, _vp,
                                      _vp, _vp, _vp, _vp]),
     "ts_per_publish": (_i32, [_vp, _vp, _vp, _vp, _i32, _i32, _vp]),
+    "ts_per_update_publish": (_i32, [_vp, _i64, _i64, _vp, _vp, _i32, _i64, _f64, _vp, _vp, _vp,
+                                     _vp, _vp, _vp, _i32, _i32, _vp]),
     "ts_per_sample_p2p": (_i32, [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i32, _i32, _vp, _f64, _i32,
                                  _vp, _vp, _vp, _vp]),
     "ts_per_normalize": (_i32, [_vp, _i64, _vp, _vp]),

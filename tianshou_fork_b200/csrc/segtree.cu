@@ -106,6 +106,65 @@ __device__ __forceinline__ double dsmem_ld_f64(const double* local, uint32_t ran
     return v;
 }
 
+// ---- sharded PER: peer-memory exchange helpers --------------------------------------------
+constexpr int kMaxShards = 64;
+// slot buffer: records [2][G][4] = {root, max, min, epoch bits}; maxima [2][G][2] = {wmax, epoch}
+__host__ __device__ inline int slot_record(int G, unsigned long long e, int r) {
+    return ((int)(e & 1ull) * G + r) * 4;
+}
+__host__ __device__ inline int slot_wmax(int G, unsigned long long e, int r) {
+    return 8 * G + ((int)(e & 1ull) * G + r) * 2;
+}
+constexpr int kPeerSpin = 1 << 22;  // bounded wait (~ seconds), then TS_FLAG_PEER_TIMEOUT
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const void* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys_u64(void* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ double ld_relaxed_sys_f64(const double* p) {
+    double v;
+    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_sys_f64(double* p, double v) {
+    asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+// spin until the epoch word at `flag` equals `want`; false on timeout
+__device__ __forceinline__ bool wait_epoch(const double* flag, unsigned long long want) {
+    for (int it = 0; it < kPeerSpin; ++it) {
+        if (ld_acquire_sys_u64(flag) == want) return true;
+        __nanosleep(64);
+    }
+    return false;
+}
+
+// Where the update kernel publishes this rank's record when it is the producer side of the
+// exchange (state == nullptr: nothing to publish).
+struct PublishInfo {
+    unsigned long long* state;
+    double* const* peer_slots;
+    int G, rank;
+};
+// G threads: store {root, max_prio, min_prio, epoch} into every peer's slot buffer
+__device__ __forceinline__ void publish_record(const double* tree, const double* prio,
+                                               const PublishInfo& pub, int tid) {
+    const unsigned long long e = __ldcg(pub.state) + 1;
+    if (tid < pub.G) {
+        double* dst = pub.peer_slots[tid] + slot_record(pub.G, e, pub.rank);
+        st_relaxed_sys_f64(dst, __ldcg(tree + 1));
+        st_relaxed_sys_f64(dst + 1, __ldcg(prio));
+        st_relaxed_sys_f64(dst + 2, __ldcg(prio + 1));
+        __threadfence_system();
+        st_release_sys_u64(dst + 3, e);
+    }
+    __syncthreads();
+    if (tid == 0) pub.state[0] = e;
+}
+
 constexpr int64_t kSmallM = 16383;     // tiered path: batch position + 1 fits the stamp's 14 bits
 constexpr int64_t kDenseBound = 4096;  // trees up to this many leaves are rebuilt densely
 constexpr int kTagShift = 14;
@@ -296,7 +355,7 @@ __global__ void __launch_bounds__(TIER_NT)
 segtree_update_tiered(double* __restrict__ tree, int64_t size, int64_t bound, int lg_bound,
                       const int64_t* __restrict__ index, ValueSrc vs, int64_t M,
                       uint32_t* __restrict__ stamp, uint32_t* __restrict__ counter,
-                      int32_t* __restrict__ err_flag) {
+                      int32_t* __restrict__ err_flag, PublishInfo pub, const double* prio) {
     constexpr int LG = K == 4 ? 7 : 8;
     __shared__ int64_t s_idx[kIdxRounds][32];
     __shared__ double s_root[64];
@@ -402,6 +461,12 @@ segtree_update_tiered(double* __restrict__ tree, int64_t size, int64_t bound, in
         __syncthreads();
     }
     if (tid < 32) warp_finish(tree, 1 << lvl, lane, s_level);
+    if (pub.state != nullptr) {
+        // fused producer side of the shard exchange: the CTA that just wrote the new root stores
+        // this rank's record into every peer's buffer over NVLink
+        __syncthreads();
+        publish_record(tree, prio, pub, tid);
+    }
     if (tid == 0) {
         counter[0] = 0u;
         if (tag >= kTagMax) { counter[2] = 0u; counter[3] = 1u; }
@@ -506,12 +571,16 @@ int32_t dense_rebuild(double* tree, int64_t bound, cudaStream_t st) {
     return check_launch();
 }
 
+int32_t publish_launch(const double* tree, const double* prio, const PublishInfo& pub,
+                       cudaStream_t st);
+
 int32_t update_impl(double* tree, int64_t size, int64_t bound, const int64_t* index,
                     ValueSrc vs, int64_t M, uint32_t* stamp, uint32_t* counter,
-                    int32_t* err_flag, cudaStream_t st) {
+                    int32_t* err_flag, cudaStream_t st,
+                    PublishInfo pub = PublishInfo{nullptr, nullptr, 1, 0}) {
     if (M < 0 || size <= 0 || bound < size || (bound & (bound - 1)) != 0) return TS_ERR_BAD_ARG;
     if (M >= 0x7fffffffLL || bound > (1LL << 30)) return TS_ERR_BAD_ARG;
-    if (M == 0) return TS_OK;
+    if (M == 0) return pub.state != nullptr && tree ? publish_launch(tree, vs.prio, pub, st) : TS_OK;
     if (!tree || !index || !stamp || !counter || !err_flag) return TS_ERR_BAD_ARG;
 
     if (!aligned(tree, 16) || !aligned(stamp, 16)) return TS_ERR_ALIGN;
@@ -532,8 +601,9 @@ int32_t update_impl(double* tree, int64_t size, int64_t bound, const int64_t* in
         attr[0].val.cooperative = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
+        const double* prio_c = vs.prio;
         cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tree, size, bound, lg, index, vs, M, stamp,
-                                           counter, err_flag);
+                                           counter, err_flag, pub, prio_c);
         if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; (void)cudaGetLastError(); return TS_ERR_CUDA; }
         return check_launch();
     }
@@ -544,10 +614,10 @@ int32_t update_impl(double* tree, int64_t size, int64_t bound, const int64_t* in
     }
     segtree_stamp_kernel<<<grid_for(M, 256), 256, 0, st>>>(index, M, size, stamp, err_flag);
     segtree_leaf_kernel<<<grid_for(M, 256), 256, 0, st>>>(tree, size, bound, index, vs, M, stamp);
-    if (bound == 1) {  // single leaf: heap node 1 is the leaf itself, node 0 unused
-        return check_launch();
-    }
-    return dense_rebuild(tree, bound, st);
+    // single leaf: heap node 1 is the leaf itself, node 0 unused
+    int32_t rc = bound == 1 ? check_launch() : dense_rebuild(tree, bound, st);
+    if (rc == TS_OK && pub.state != nullptr) rc = publish_launch(tree, vs.prio, pub, st);
+    return rc;
 }
 
 // ============================================================================================
@@ -711,41 +781,6 @@ struct ShardInfo {
     double* const* peer_slots;           // P2P mode: device array of the G ranks' slot buffers
     unsigned long long* state;           // P2P mode: {records published, samples drawn} by this rank
 };
-constexpr int kMaxShards = 64;
-// slot buffer: records [2][G][4] = {root, max, min, epoch bits}; maxima [2][G][2] = {wmax, epoch}
-__host__ __device__ inline int slot_record(int G, unsigned long long e, int r) {
-    return ((int)(e & 1ull) * G + r) * 4;
-}
-__host__ __device__ inline int slot_wmax(int G, unsigned long long e, int r) {
-    return 8 * G + ((int)(e & 1ull) * G + r) * 2;
-}
-constexpr int kPeerSpin = 1 << 22;  // bounded wait (~ seconds), then TS_FLAG_PEER_TIMEOUT
-
-__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const void* p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_sys_u64(void* p, unsigned long long v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ double ld_relaxed_sys_f64(const double* p) {
-    double v;
-    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_relaxed_sys_f64(double* p, double v) {
-    asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
-}
-// spin until the epoch word at `flag` equals `want`; false on timeout
-__device__ __forceinline__ bool wait_epoch(const double* flag, unsigned long long want) {
-    for (int it = 0; it < kPeerSpin; ++it) {
-        if (ld_acquire_sys_u64(flag) == want) return true;
-        __nanosleep(64);
-    }
-    return false;
-}
-
 template <bool SAMPLE, int NT>
 __global__ void __launch_bounds__(NT)
 per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg_bound,
@@ -867,18 +902,14 @@ __global__ void __launch_bounds__(kMaxShards)
 per_publish_kernel(const double* __restrict__ tree, const double* __restrict__ prio,
                    unsigned long long* __restrict__ state, double* const* __restrict__ peer_slots,
                    int G, int rank) {
-    const int tid = threadIdx.x;
-    const unsigned long long e = __ldcg(state) + 1;
-    if (tid < G) {
-        double* dst = peer_slots[tid] + slot_record(G, e, rank);
-        st_relaxed_sys_f64(dst, __ldcg(tree + 1));
-        st_relaxed_sys_f64(dst + 1, __ldcg(prio));
-        st_relaxed_sys_f64(dst + 2, __ldcg(prio + 1));
-        __threadfence_system();
-        st_release_sys_u64(dst + 3, e);
-    }
-    __syncthreads();
-    if (tid == 0) state[0] = e;
+    publish_record(tree, prio, PublishInfo{state, peer_slots, G, rank}, threadIdx.x);
+}
+
+int32_t publish_launch(const double* tree, const double* prio, const PublishInfo& pub,
+                       cudaStream_t st) {
+    per_publish_kernel<<<1, kMaxShards, 0, st>>>(tree, prio, pub.state, pub.peer_slots, pub.G,
+                                                 pub.rank);
+    return check_launch();
 }
 
 // weight[j] /= *wmax (prio.py:101) once the maximum over all shards is known
@@ -1095,7 +1126,21 @@ extern "C" int32_t ts_per_publish(const double* tree, const double* prio, uint64
     if (!tree || !prio || !state || !peer_slots || G < 1 || G > kMaxShards || rank < 0 ||
         rank >= G)
         return TS_ERR_BAD_ARG;
-    per_publish_kernel<<<1, kMaxShards, 0, (cudaStream_t)stream>>>(
-        tree, prio, (unsigned long long*)state, peer_slots, G, rank);
-    return check_launch();
+    return publish_launch(tree, prio, PublishInfo{(unsigned long long*)state, peer_slots, G, rank},
+                          (cudaStream_t)stream);
+}
+
+extern "C" int32_t ts_per_update_publish(double* tree, int64_t size, int64_t bound,
+                                         const int64_t* idx, const void* td, int32_t td_dtype,
+                                         int64_t M, double alpha, double* prio, uint32_t* stamp,
+                                         uint32_t* counter, int32_t* err_flag, uint64_t* state,
+                                         double* const* peer_slots, int32_t G, int32_t rank,
+                                         ts_stream_t stream) {
+    if (!td || !prio || !state || !peer_slots || G < 1 || G > kMaxShards || rank < 0 || rank >= G)
+        return TS_ERR_BAD_ARG;
+    if (td_dtype != TS_F32 && td_dtype != TS_F64) return TS_ERR_BAD_ARG;
+    ValueSrc vs{td, 1, alpha, prio, td_dtype == TS_F64 ? VM_PER_F64 : VM_PER_F32};
+    return update_impl(tree, size, bound, idx, vs, M, stamp, counter, err_flag,
+                       (cudaStream_t)stream,
+                       PublishInfo{(unsigned long long*)state, peer_slots, G, rank});
 }

@@ -159,5 +159,22 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
 
     def update_weight(self, index, new_weight) -> None:
         """``index`` local, ``-1`` entries (other ranks' samples) are skipped by the kernel."""
-        super().update_weight(index, new_weight)
-        self.sync_roots()
+        if self.exchange != "p2p":
+            super().update_weight(index, new_weight)
+            self.sync_roots()
+            return
+        idx = self.weight._dev_index(index)
+        td = new_weight.detach().to(self.device) if isinstance(new_weight, torch.Tensor) \
+            else torch.as_tensor(np.asarray(new_weight), device=self.device)
+        if td.dtype not in (torch.float32, torch.float64):
+            td = td.to(torch.float64)
+        td = td.reshape(-1).contiguous()
+        assert td.numel() == idx.numel()
+        t = self.weight
+        # update + publish in one launch (the record must go out even for an empty batch)
+        L.check(L.lib().ts_per_update_publish(
+            L.ptr(t._value), t._size, t._bound, L.ptr(idx), L.ptr(td), L.dtype_code(td),
+            idx.numel(), float(self._alpha), L.ptr(self._prio), L.ptr(t._stamp),
+            L.ptr(t._counter), L.ptr(t._err), L.ptr(self._state), self._peer_ptrs,
+            self.world_size, self.rank, L.stream()), "ts_per_update_publish")
+        self._prio_f32 = td.dtype == torch.float32
