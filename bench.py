@@ -36,6 +36,7 @@ E_PER_GPU, T_STEPS = 4096, 2048
 GAMMA, LAMBDA = 0.99, 0.95
 ALG_BYTES_PER_TRANSITION = 21  # rew 4 + v_s 4 + v_s_ 4 + end flag 1 + adv 4 + ret 4
 MOVED_BYTES_PER_TRANSITION = 22  # terminated and truncated are two separate bytes
+NCU_DRAM_BYTES_PER_LAUNCH = 117_464_576 + 26_511_360  # profiles/r01b_gae_ncu.md, shipped kernel
 PER_LEAVES, PER_BATCH, PER_ALPHA, PER_BETA = 1 << 20, 4096, 0.6, 0.4
 PER_ALG_BYTES_PER_SAMPLE = 664
 
@@ -284,7 +285,12 @@ def run_b200(args):
     peak, peak_src = measured_peaks()
     achieved = n_trans * ALG_BYTES_PER_TRANSITION / kernel_s / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": NCU_DRAM_BYTES_PER_LAUNCH if (E, T) == (
+                    E_PER_GPU, T_STEPS) else None,
+                "traffic_source": "ncu --set full, profiles/r01b_gae_ncu.md (gae_top): dram read "
+                                  "117.46 MB + write 26.51 MB; the rest of the 67.1 MB output is "
+                                  "still dirty in L2 at kernel end",
+                "peak_source": peak_src,
                 "kernel": "gae_rows_tma_kernel<float,float,float,256> (persistent, cp.async.bulk pipelined)",
                 "alg_bytes_per_launch": n_trans * ALG_BYTES_PER_TRANSITION,
                 "moved_bytes_per_launch": n_trans * MOVED_BYTES_PER_TRANSITION,
