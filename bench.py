@@ -36,6 +36,7 @@ E_PER_GPU, T_STEPS = 4096, 2048
 GAMMA, LAMBDA = 0.99, 0.95
 ALG_BYTES_PER_TRANSITION = 21  # rew 4 + v_s 4 + v_s_ 4 + end flag 1 + adv 4 + ret 4
 MOVED_BYTES_PER_TRANSITION = 22  # terminated and truncated are two separate bytes
+E2E_CHUNKS = int(os.environ.get("TS_E2E_CHUNKS", "4"))
 NCU_DRAM_BYTES_PER_LAUNCH = 117_464_576 + 26_511_360  # profiles/r01b_gae_ncu.md, shipped kernel
 PER_LEAVES, PER_BATCH, PER_ALPHA, PER_BETA = 1 << 20, 4096, 0.6, 0.4
 PER_ALG_BYTES_PER_SAMPLE = 664
@@ -299,7 +300,8 @@ def run_b200(args):
     # ---- e2e: pinned host buffers in and out through the package's host pipeline --------------
     e2e = None
     if not args.skip_e2e:
-        pipe = GaeHostPipeline(E, T, chunks=16, device=dev)
+        pipe = GaeHostPipeline(E, T, chunks=E2E_CHUNKS, device=dev)
+        pipe.zero_copy = os.environ.get("TS_E2E_ZERO_COPY", "0") == "1"
         h_adv = torch.empty(E, T, dtype=torch.float32).pin_memory()
         h_ret = torch.empty(E, T, dtype=torch.float32).pin_memory()
         Ke = max(3, min(K, 100))
@@ -317,10 +319,37 @@ def run_b200(args):
         ems = max_over_ranks(e0.elapsed_time(e1))
         if rank == 0:  # the copied-back result is the real one
             assert torch.allclose(h_adv, adv.cpu(), rtol=0, atol=0)
+        # what the link can do: one big pinned copy each way, then both at once (context for e2e)
+        def link_gbs(fn, nbytes):
+            best = 1e9
+            for _ in range(3):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize()
+                a.record(stream)
+                fn()
+                b.record(stream)
+                torch.cuda.synchronize()
+                best = min(best, a.elapsed_time(b))
+            return nbytes / (best * 1e-3) / 1e9
+        s2 = torch.cuda.Stream(dev)
+        nb_in, nb_out = host[0].numel() * 4, h_adv.numel() * 4
+
+        def both():
+            s2.wait_stream(stream)
+            with torch.cuda.stream(s2):
+                h_adv.copy_(adv, non_blocking=True)
+            d_rew.copy_(host[0], non_blocking=True)
+            stream.wait_stream(s2)
+        pcie = {"h2d_GBps": link_gbs(lambda: d_rew.copy_(host[0], non_blocking=True), nb_in),
+                "d2h_GBps": link_gbs(lambda: h_adv.copy_(adv, non_blocking=True), nb_out),
+                "duplex_GBps": link_gbs(both, nb_in + nb_out)}
+        pcie["floor_ms_per_step"] = max(pipe.h2d_bytes / pcie["h2d_GBps"],
+                                        pipe.d2h_bytes / pcie["d2h_GBps"]) / 1e6
         e2e = {"value": n_trans * world * Ke / (ems * 1e-3), "unit": "transitions/s",
+               "link": pcie,
                "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
                "ms_per_step": ems / Ke, "steps": Ke,
-               "api": "tianshou_fork_b200.pipeline.GaeHostPipeline.run (16 row chunks, 3 streams)",
+               "api": f"tianshou_fork_b200.pipeline.GaeHostPipeline.run ({E2E_CHUNKS} row chunks; H2D, compute and D2H streams)",
                "launches": pipe.launches}
 
     # ---- PER: sample + importance weights + update_weight, CUDA-graph replay ------------------
