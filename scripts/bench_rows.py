@@ -1,0 +1,256 @@
+#!/usr/bin/env python
+"""Per-row timings of the hot path on the GPU box, each beside the
+CPU oracle port on one host core.  Prints one JSON object per row; results are committed under
+profiles/.  GPU times are CUDA-event timings through the package's public API (host launch
+overhead included) unless the row says "graph".
+
+    python scripts/bench_rows.py > gpurun_out/rows.jsonl
+"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import tianshou_fork_b200 as ts  # noqa: E402
+from oracle import oracle as orc  # noqa: E402
+from tianshou_fork_b200 import _lib as L  # noqa: E402
+
+DEV = torch.device("cuda:0")
+PEAK = 6545.3
+try:
+    PEAK = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+except Exception:
+    pass
+
+
+def gpu_us(fn, iters=200, warm=10):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    best = 1e30
+    for _ in range(3):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        best = min(best, a.elapsed_time(b) * 1e3 / iters)
+    return best
+
+
+def graph_us(fn, calls=8, replays=50):
+    side = torch.cuda.Stream(DEV)
+    with torch.cuda.stream(side):
+        for _ in range(3):
+            fn(side.cuda_stream)
+    side.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=side):
+        for _ in range(calls):
+            fn(side.cuda_stream)
+    return gpu_us(g.replay, iters=replays, warm=5) / calls
+
+
+def cpu_us(fn, seconds=2.0):
+    fn()
+    t, n = [], 0
+    t0 = time.perf_counter()
+    while time.perf_counter() - t0 < seconds or n < 3:
+        a = time.perf_counter()
+        fn()
+        t.append(time.perf_counter() - a)
+        n += 1
+    return float(np.median(t)) * 1e6
+
+
+def emit(row, **kw):
+    print(json.dumps(dict(row=row, **kw)), flush=True)
+
+
+def fill_vec(buf, E, T, rng, p_term=1 / 1000, p_trunc=1 / 10000, rew3=True):
+    """Bulk-fill a device VectorReplayBuffer through its storage (rollouts are synthetic)."""
+    n = E * T
+    rew = rng.choice(np.array([-1.0, 0.0, 1.0]), n, p=[0.05, 0.9, 0.05]) if rew3 else rng.random(n)
+    term = rng.random(n) < p_term
+    trunc = (rng.random(n) < p_trunc) & ~term
+    for t in range(2):  # two real adds allocate the storage and initialise bookkeeping
+        buf.add(ts.Batch(obs=np.zeros((E, 1), np.float32), act=np.zeros(E, np.int64),
+                         rew=np.zeros(E), terminated=np.zeros(E, bool), truncated=np.zeros(E, bool),
+                         obs_next=np.zeros((E, 1), np.float32), info={}))
+    buf._meta.rew.copy_(torch.from_numpy(rew).to(buf._meta.rew.dtype))
+    buf._meta.terminated.copy_(torch.from_numpy(term))
+    buf._meta.truncated.copy_(torch.from_numpy(trunc))
+    buf._meta.done.copy_(torch.from_numpy(term | trunc))
+    buf._rings[:, 0] = 0
+    buf._rings[:, 1] = T
+    buf._lengths[:] = T
+    buf.last_index[:] = np.arange(E) * T + T - 1
+    buf._version += 1
+    for b in buf.buffers:
+        b._index, b._size = 0, T
+    return rew, term, trunc
+
+
+def row_gae_flat():
+    """a1, general form: arbitrary indices (a rotated buffer), decoupled look-back."""
+    for E, T in ((4096, 2048), (64, 2048)):
+        n = E * T
+        rng = np.random.default_rng(1)
+        rew = torch.from_numpy(rng.random(n, dtype=np.float32)).to(DEV)
+        vs = torch.from_numpy(rng.standard_normal(n, dtype=np.float32)).to(DEV)
+        vn = torch.from_numpy(rng.standard_normal(n, dtype=np.float32)).to(DEV)
+        term = torch.from_numpy((rng.random(n) < 1 / 200).view(np.uint8)).to(DEV)
+        trunc = torch.zeros(n, dtype=torch.uint8, device=DEV)
+        idx = torch.arange(n, device=DEV)
+        unf = torch.full((E,), -1, dtype=torch.int64, device=DEV)
+        off = torch.arange(E + 1, device=DEV) * T
+        adv, ret = torch.empty(n, device=DEV), torch.empty(n, device=DEV)
+        lib = L.lib()
+        nbytes = lib.ts_gae_flat_workspace_bytes(n)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
+
+        def go(with_idx):
+            L.check(lib.ts_gae_flat(L.ptr(rew), L.ptr(vs), L.ptr(vn), L.ptr(term), L.ptr(trunc),
+                                    L.ptr(idx) if with_idx else None,
+                                    L.ptr(term) if with_idx else None,
+                                    L.ptr(unf) if with_idx else None, L.ptr(off), E, T, n, 0.99,
+                                    0.95, 0, 0, 0, L.ptr(adv), L.ptr(ret), L.ptr(ws), nbytes,
+                                    L.stream()), "flat")
+        for with_idx, bpt in ((False, 21), (True, 30)):
+            us = gpu_us(lambda: go(with_idx), iters=100)
+            emit("a1 gae_flat", E=E, T=T, indices=with_idx, us=us, alg_bytes_per_transition=bpt,
+                 GBps=n * bpt / us / 1e3, frac_of_measured_peak=n * bpt / us / 1e3 / PEAK)
+
+
+def row_gae_flat_sweep():
+    """Pipelined-ranges kernel: CTAs per SM x ring stages, two sequence lengths, no indices."""
+    lib = L.lib()
+    for n in (4096 * 2048, 4000 * 2048, 4000 * 2048 + 7):
+        rng = np.random.default_rng(1)
+        rew = torch.from_numpy(rng.random(n, dtype=np.float32)).to(DEV)
+        vs = torch.from_numpy(rng.standard_normal(n, dtype=np.float32)).to(DEV)
+        vn = torch.from_numpy(rng.standard_normal(n, dtype=np.float32)).to(DEV)
+        term = torch.from_numpy((rng.random(n) < 1 / 200).view(np.uint8)).to(DEV)
+        trunc = torch.zeros(n, dtype=torch.uint8, device=DEV)
+        adv, ret = torch.empty(n, device=DEV), torch.empty(n, device=DEV)
+        nbytes = lib.ts_gae_flat_workspace_bytes(n)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
+
+        def go(stream=None):
+            L.check(lib.ts_gae_flat(L.ptr(rew), L.ptr(vs), L.ptr(vn), L.ptr(term), L.ptr(trunc),
+                                    None, None, None, None, 0, 0, n, 0.99, 0.95, 0, 0, 0,
+                                    L.ptr(adv), L.ptr(ret), L.ptr(ws), nbytes,
+                                    stream if stream is not None else L.stream()), "flat")
+        for ctas in (1, 2, 3):
+            for stages in (2, 3, 4, 6):
+                lib.ts_tune_set(b"gae_flat_ctas", ctas)
+                lib.ts_tune_set(b"gae_flat_stages", stages)
+                us = gpu_us(go, iters=100)
+                gus = graph_us(go)
+                emit("a1 gae_flat sweep", N=n, ctas_per_sm=ctas, stages=stages, us=us,
+                     graph_us=gus, frac_of_measured_peak=n * 21 / gus / 1e3 / PEAK)
+    lib.ts_tune_set(b"gae_flat_ctas", 0)
+    lib.ts_tune_set(b"gae_flat_stages", 0)
+
+
+def row_nstep_index():
+    """a2 n-step target and a3/a4 prev/next on the C4 buffer (2^20 transitions, 16 sub-buffers)."""
+    E, T = 16, 1 << 16
+    rng = np.random.default_rng(3)
+    buf = ts.VectorReplayBuffer(E * T, E)
+    rew, term, trunc = fill_vec(buf, E, T, rng)
+    st = orc.RingState(E * T, E)
+    st.rew, st.done, st.terminated = rew, term | trunc, term
+    st.last_index, st.lengths = buf.last_index.copy(), buf._lengths.copy()
+    for bsz in (32, 4096):
+        idx_np = rng.integers(0, E * T, bsz)
+        idx = torch.from_numpy(idx_np).to(DEV)
+        for D in (1, 51):
+            tq = torch.from_numpy(rng.standard_normal((bsz, D)).astype(np.float32)).to(DEV)
+            tq_np = tq.cpu().numpy()
+            batch = ts.Batch()
+            us = gpu_us(lambda: ts.BasePolicy.compute_nstep_return(
+                batch, buf, idx, lambda b, t: tq, 0.99, 3))
+            cus = cpu_us(lambda: orc.compute_nstep_return(st, idx_np, lambda t: tq_np, 0.99, 3))
+            emit("a2 nstep", bsz=bsz, D=D, n_step=3, gpu_us=us, cpu_port_us=cus, speedup=cus / us)
+        us_n = gpu_us(lambda: buf.next(idx))
+        us_p = gpu_us(lambda: buf.prev(idx))
+        cus = cpu_us(lambda: st.next(idx_np))
+        emit("a3/a4 next", M=bsz, B=E, gpu_us=us_n, prev_gpu_us=us_p, cpu_port_us=cus,
+             speedup=cus / us_n)
+    # many sub-buffers: the reference's njit loop is O(B * M)
+    E2, T2 = 4096, 256
+    buf2 = ts.VectorReplayBuffer(E2 * T2, E2)
+    rew, term, trunc = fill_vec(buf2, E2, T2, rng)
+    st2 = orc.RingState(E2 * T2, E2)
+    st2.rew, st2.done, st2.terminated = rew, term | trunc, term
+    st2.last_index, st2.lengths = buf2.last_index.copy(), buf2._lengths.copy()
+    idx_np = rng.integers(0, E2 * T2, 4096)
+    idx = torch.from_numpy(idx_np).to(DEV)
+    us = gpu_us(lambda: buf2.next(idx))
+    cus = cpu_us(lambda: st2.next(idx_np))
+    emit("a3/a4 next", M=4096, B=E2, gpu_us=us, cpu_port_us=cus, speedup=cus / us)
+
+
+def row_gather():
+    """a5: buffer[indices] for Atari-shaped rows (4 x 84 x 84 u8 = 28 224 B)."""
+    n_rows, row = 100_000, 4 * 84 * 84
+    src = torch.randint(0, 255, (n_rows, row), dtype=torch.uint8, device=DEV)
+    rng = np.random.default_rng(4)
+    for bsz in (32, 4096):
+        idx = torch.from_numpy(rng.integers(0, n_rows, bsz)).to(DEV)
+        out = torch.empty(bsz, row, dtype=torch.uint8, device=DEV)
+        lib = L.lib()
+        us = graph_us(lambda s: L.check(lib.ts_gather_rows(L.ptr(src), n_rows, row, L.ptr(idx), bsz,
+                                                           L.ptr(out), s), "gather"))
+        emit("a5 gather_rows (graph)", bsz=bsz, row_bytes=row, us=us,
+             GBps=2 * bsz * row / us / 1e3, frac_of_measured_peak=2 * bsz * row / us / 1e3 / PEAK)
+        assert torch.equal(out, src[idx])
+
+
+def row_ppo():
+    """a11: fused PPO loss forward + backward per minibatch (C3: N = 131 072)."""
+    N = 131072
+    rng = np.random.default_rng(5)
+    f = lambda a: torch.from_numpy(a.astype(np.float32)).to(DEV)
+    adv, ret, vs = f(rng.standard_normal(N)), f(rng.standard_normal(N)), f(rng.standard_normal(N))
+    lo = f(rng.normal(-8, 0.3, N))
+    for m in (64, 1024, N):
+        mb = torch.from_numpy(rng.permutation(N)[:m]).to(DEV)
+        lp = (lo[mb] + 0.1 * torch.randn(m, device=DEV)).requires_grad_(True)
+        val = (vs[mb] + 0.3 * torch.randn(m, device=DEV)).requires_grad_(True)
+
+        def fused():
+            cl, vl, _ = ts.ppo_loss(lp, val, lo, adv, ret, vs, mb, 0.2, None, True, True)
+            (cl + 0.5 * vl).backward()
+
+        def eager():  # the reference's expressions (ppo.py:109-144) in torch eager on the GPU
+            a = adv[mb]
+            a = (a - a.mean()) / (a.std() + 1e-8)
+            ratio = (lp - lo[mb]).exp().float()
+            s1, s2 = ratio * a, ratio.clamp(0.8, 1.2) * a
+            cl = -torch.min(s1, s2).mean()
+            vclip = vs[mb] + (val - vs[mb]).clamp(-0.2, 0.2)
+            vl = torch.max((ret[mb] - val).pow(2), (ret[mb] - vclip).pow(2)).mean()
+            (cl + 0.5 * vl).backward()
+
+        us, eus = gpu_us(fused, iters=100), gpu_us(eager, iters=100)
+        lpn, lon = lp.detach().cpu().numpy(), lo[mb].cpu().numpy()
+        an, rn = adv[mb].cpu().numpy(), ret[mb].cpu().numpy()
+        vn_, valn = vs[mb].cpu().numpy(), val.detach().cpu().numpy()
+        cus = cpu_us(lambda: orc.ppo_loss(lpn, lon, an, rn, vn_, valn, 0.2, None, True, True), 1.0)
+        emit("a11 ppo_loss fwd+bwd", m=m, fused_gpu_us=us, torch_eager_gpu_us=eus,
+             cpu_port_fwd_us=cus, speedup_vs_eager=eus / us)
+
+
+if __name__ == "__main__":
+    torch.cuda.set_device(0)
+    which = sys.argv[1:] or ["gae_flat", "nstep_index", "gather", "ppo"]
+    for w in which:
+        globals()["row_" + w]()

@@ -127,11 +127,16 @@ def test_rows_kernel_strided_buffer_rows():
     assert _close(adv.cpu().numpy(), ref_adv) and _close(ret.cpu().numpy(), ref_ret)
 
 
-@pytest.mark.parametrize("N,p_end", [(1, 0.5), (2047, 0.01), (2048, 0.0), (2049, 0.001),
-                                     (100_000, 0.0), (300_001, 0.0005), (1_000_000, 0.005)])
-def test_flat_kernel_lookback_vs_oracle(N, p_end):
-    """ts_gae_flat: one long sequence; p_end = 0 makes every tile wait on its successor."""
+@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("N,p_end", [(1, 0.5), (15, 0.2), (16, 0.0), (2047, 0.01), (2048, 0.0),
+                                     (2049, 0.001), (100_000, 0.0), (300_001, 0.0005),
+                                     (1_000_000, 0.005), (3_000_017, 0.0)])
+def test_flat_kernel_lookback_vs_oracle(N, p_end, variant):
+    """ts_gae_flat, both kernels (1: decoupled look-back per tile, 2: pipelined ranges with
+    read-ahead carry): one long sequence; p_end = 0 leaves no episode boundary, so the carry
+    has to come from the discount decay (gamma*lambda = 0.94) or from the neighbour chain."""
     from tianshou_fork_b200 import _lib as L
+    L.check(L.lib().ts_tune_set(b"gae_flat_variant", variant), "tune")
     rng = np.random.default_rng(N)
     rew = rng.standard_normal(N)
     v_s = rng.standard_normal(N).astype(np.float32)
@@ -150,8 +155,75 @@ def test_flat_kernel_lookback_vs_oracle(N, p_end):
         L.check(L.lib().ts_gae_flat(*[L.ptr(t) for t in g], None, None, None, None, 0, 0, N,
                                     0.99, 0.95, 1, 0, 1, L.ptr(adv), L.ptr(ret), L.ptr(ws),
                                     nbytes, L.stream()), "ts_gae_flat")
+    L.check(L.lib().ts_tune_set(b"gae_flat_variant", 0), "tune")
     assert _close(adv.cpu().numpy(), ref_adv, 1e-9)
     assert _close(ret.cpu().numpy(), ref_adv + v_s, 1e-9)
+
+
+@pytest.mark.parametrize("gl", [(1.0, 1.0), (0.999, 1.0)])
+def test_flat_kernel_neighbour_chain(gl):
+    """No episode end and (almost) no discount: read-ahead cannot resolve the carry, every
+    range takes its neighbour's published head value (the Monte-Carlo return of pg.py:108-112
+    over one 600 000-step sequence)."""
+    from tianshou_fork_b200 import _lib as L
+    gamma, lam = gl
+    N = 600_000
+    rng = np.random.default_rng(3)
+    rew = rng.standard_normal(N)
+    v_s = rng.standard_normal(N).astype(np.float32)
+    v_n = rng.standard_normal(N).astype(np.float32)
+    z = np.zeros(N, dtype=bool)
+    ref_adv = orc.gae_return(v_s, v_n, rew, z, gamma, lam)
+    d = lambda a: torch.from_numpy(a).cuda()
+    g = [d(rew), d(v_s), d(v_n), d(z.view(np.uint8)), d(z.view(np.uint8))]
+    adv = torch.empty(N, dtype=torch.float64, device="cuda")
+    ret = torch.empty(N, dtype=torch.float64, device="cuda")
+    nbytes = L.lib().ts_gae_flat_workspace_bytes(N)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    L.check(L.lib().ts_gae_flat(*[L.ptr(t) for t in g], None, None, None, None, 0, 0, N, gamma,
+                                lam, 1, 0, 1, L.ptr(adv), L.ptr(ret), L.ptr(ws), nbytes,
+                                L.stream()), "ts_gae_flat")
+    assert _close(adv.cpu().numpy(), ref_adv, 1e-9)
+
+
+@pytest.mark.parametrize("B,cap,rotate", [(37, 1000, True), (700, 5, False), (300, 13, False),
+                                          (300, 13, True)])
+@pytest.mark.parametrize("variant", [1, 2])
+def test_flat_kernel_with_indices_vs_oracle(variant, B, cap, rotate):
+    """Gathered form through the raw C-ABI: value mask from buffer.terminated[indices], end
+    flags from the unfinished index of each sub-buffer (policy/base.py:335, 379-380)."""
+    from tianshou_fork_b200 import _lib as L
+    L.check(L.lib().ts_tune_set(b"gae_flat_variant", variant), "tune")
+    rng = np.random.default_rng(11)
+    # a batch that visits every sub-buffer's slots in a rotated order (wrapped rings); without
+    # rotation 8-step strips are consecutive and straddle one or several short sub-buffers
+    rot = rng.integers(0, cap, B) if rotate else np.zeros(B, dtype=np.int64)
+    indices = np.concatenate([k * cap + (rot[k] + np.arange(cap)) % cap for k in range(B)])
+    N = indices.size
+    buf_term = rng.random(B * cap) < 1 / 80
+    buf_trunc = (rng.random(B * cap) < 1 / 300) & ~buf_term
+    unfinished = np.array([k * cap + (rot[k] - 1) % cap for k in range(B)])  # newest slot per ring
+    unfinished[::5] = -1
+    rew = rng.standard_normal(N)
+    v_s = rng.standard_normal(N).astype(np.float32)
+    v_n = rng.standard_normal(N).astype(np.float32)
+    term, trunc = buf_term[indices], buf_trunc[indices]
+    end = term | trunc | np.isin(indices, unfinished)
+    ref_adv = orc.gae_return(v_s, v_n * ~term, rew, end, 0.99, 0.95)
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    offset = d(np.arange(B + 1) * cap)
+    adv = torch.empty(N, dtype=torch.float32, device="cuda")
+    ret = torch.empty(N, dtype=torch.float32, device="cuda")
+    nbytes = L.lib().ts_gae_flat_workspace_bytes(N)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    g = [d(rew), d(v_s), d(v_n), d(term.view(np.uint8)), d(trunc.view(np.uint8)), d(indices),
+         d(buf_term.view(np.uint8)), d(unfinished), offset]
+    for sub in (cap, 0):  # equal sub-buffers by division, then by binary search over offset
+        L.check(L.lib().ts_gae_flat(*[L.ptr(t) for t in g], B, sub, N, 0.99, 0.95, 1, 0, 0,
+                                    L.ptr(adv), L.ptr(ret), L.ptr(ws), nbytes, L.stream()),
+                "ts_gae_flat")
+        assert _close(adv.cpu().numpy(), ref_adv) and _close(ret.cpu().numpy(), ref_adv + v_s)
+    L.check(L.lib().ts_tune_set(b"gae_flat_variant", 0), "tune")
 
 
 def test_c2_full_size_properties():

@@ -4,6 +4,9 @@
 namespace ts {
 thread_local int32_t g_last_cuda_error = 0;
 int g_tune_gae_rows_variant = 0;
+int g_tune_gae_flat_variant = 0;
+int g_tune_gae_flat_ctas = 0;
+int g_tune_gae_flat_stages = 0;
 int g_tune_segtree_group = 128;
 int g_tune_per_cluster = 0;
 int g_tune_segtree_max_ctas = 148;
@@ -29,6 +32,18 @@ extern "C" const char* ts_error_string(int32_t code) {
 extern "C" int32_t ts_tune_set(const char* key, int64_t value) {
     if (!key) return TS_ERR_BAD_ARG;
     if (strcmp(key, "gae_rows_variant") == 0) { ts::g_tune_gae_rows_variant = (int)value; return TS_OK; }
+    if (strcmp(key, "gae_flat_variant") == 0 && value >= 0 && value <= 2) {
+        ts::g_tune_gae_flat_variant = (int)value;
+        return TS_OK;
+    }
+    if (strcmp(key, "gae_flat_ctas") == 0 && value >= 0 && value <= 3) {
+        ts::g_tune_gae_flat_ctas = (int)value;
+        return TS_OK;
+    }
+    if (strcmp(key, "gae_flat_stages") == 0 && value >= 0 && value <= 6) {
+        ts::g_tune_gae_flat_stages = (int)value;
+        return TS_OK;
+    }
     if (strcmp(key, "segtree_max_ctas") == 0 && value >= 1 && value <= ts::kNumSMs) {
         ts::g_tune_segtree_max_ctas = (int)value;
         return TS_OK;

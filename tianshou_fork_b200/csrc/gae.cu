@@ -472,6 +472,436 @@ gae_rows_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
 }
 
 // ============================================================================================
+// General flattened form, bulk-copy pipelined: one sequence of N transitions in the caller's
+// order (batch == buffer[indices]), cut only by end flags, exactly _gae_return's contract.
+//
+// The 16-aligned part of the sequence is split into tiles of NT*8 steps; persistent CTA b owns
+// a CONTIGUOUS range of tiles and walks it from its end with the same stage ring, scan and
+// staged stores as gae_rows_tma_kernel, so the carry between tiles stays in registers.  What
+// a CTA needs from outside is ONE number: the advantage of the first step after its range.
+// It does not wait for the CTA that owns that step; one warp reads AHEAD from the range
+// boundary in windows of 256 steps and composes their maps until an episode boundary (P == 0)
+// or until the accumulated discount is below 1e-60 of the carry -- on real rollouts one or two
+// windows of redundant reads.  Only if neither happens within 4096 steps (no episode end AND
+// gamma*lambda ~ 1) does the CTA fall back to waiting for its neighbour's published head value;
+// the chain starts at the CTA that owns the end of the sequence, which never waits.
+// ============================================================================================
+struct FlatGather {               // how value mask and unfinished tails are found (nullable)
+    const int64_t* indices;       // batch position -> buffer index
+    const uint8_t* buf_term;      // buffer.terminated (value_mask, policy/base.py:335)
+    const int64_t* unfinished;    // per sub-buffer unfinished index or -1 (:380)
+    const int64_t* offset;
+    int64_t B, sub_size;
+};
+
+// mask / cut of one transition from its flags (and, with indices, from the buffer)
+__device__ __forceinline__ void flat_flags(const FlatGather& g, int64_t idx, uint32_t t,
+                                           uint32_t c, bool& masked, bool& cut) {
+    masked = t != 0u;
+    cut = (t | c) != 0u;
+    if (g.indices != nullptr) {
+        if (g.buf_term != nullptr) masked = __ldg(g.buf_term + idx) != 0;
+        if (g.unfinished != nullptr &&
+            __ldg(g.unfinished + sub_of(idx, g.offset, g.B, g.sub_size)) == idx)
+            cut = true;
+    }
+}
+
+// One warp: the map (P, X) of the 256 steps starting at i_first, read straight from global
+// memory.  Steps at or beyond N act as "episode over, value 0".  Split in two so that the caller
+// can put other work (the first bulk loads) between issuing the reads and needing them.
+template <typename T>
+__device__ __forceinline__ void gmem_ld8(const T* __restrict__ p, int nvalid, T (&v)[VEC]) {
+    if (nvalid == VEC) {
+        constexpr int PER = 16 / sizeof(T);
+        using V = typename std::conditional<sizeof(T) == 4, float4, double2>::type;
+#pragma unroll
+        for (int q = 0; q < VEC / PER; ++q) {
+            const V x = __ldcs(reinterpret_cast<const V*>(p) + q);
+            const T* e = reinterpret_cast<const T*>(&x);
+#pragma unroll
+            for (int j = 0; j < PER; ++j) v[q * PER + j] = e[j];
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) v[k] = k < nvalid ? __ldcs(p + k) : T(0);
+    }
+}
+__device__ __forceinline__ uint2 gmem_ld8_flags(const uint8_t* __restrict__ p, int nvalid) {
+    if (nvalid == VEC) return __ldcs(reinterpret_cast<const uint2*>(p));
+    uint2 w = make_uint2(0u, 0u);
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+        const uint32_t byte = k < nvalid ? (uint32_t)__ldcs(p + k) : 0u;
+        if (k < 4) w.x |= byte << (8 * k);
+        else w.y |= byte << (8 * (k - 4));
+    }
+    return w;
+}
+
+template <typename RewT, typename InT>
+struct FlatWindow {
+    RewT rw[VEC];
+    InT vs[VEC], vn[VEC];
+    uint2 wt, wc;
+    int64_t idx[VEC];
+    int nvalid;
+
+    // issue the reads of this lane's 8 steps (all arrays are 16-byte aligned, i_first % 8 == 0)
+    __device__ __forceinline__ void load(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
+                                         const InT* __restrict__ v_next,
+                                         const uint8_t* __restrict__ term,
+                                         const uint8_t* __restrict__ trunc, const FlatGather& g,
+                                         int64_t i_first, int64_t N, int lane) {
+        const int64_t i0 = i_first + lane * VEC;
+        const int64_t left = N - i0;
+        nvalid = left >= VEC ? VEC : (left > 0 ? (int)left : 0);
+        const int64_t at = nvalid > 0 ? i0 : 0;  // keep the address in range when nothing is read
+        gmem_ld8(rew + at, nvalid, rw);
+        gmem_ld8(v_s + at, nvalid, vs);
+        gmem_ld8(v_next + at, nvalid, vn);
+        wt = gmem_ld8_flags(term + at, nvalid);
+        wc = gmem_ld8_flags(trunc + at, nvalid);
+        if (g.indices != nullptr) {
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) idx[k] = k < nvalid ? __ldg(g.indices + at + k) : 0;
+        }
+    }
+    // the window's map, valid in every lane
+    __device__ __forceinline__ void reduce(const FlatGather& g, double gamma, const GlPow& glp,
+                                           int lane, double& Pw, double& Xw) {
+        wc.x |= wt.x;
+        wc.y |= wt.y;
+        if (g.indices != nullptr) {  // value mask / unfinished tails live in the buffer
+            uint2 bt = make_uint2(0u, 0u), un = make_uint2(0u, 0u);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) {
+                const uint32_t bit = 1u << (8 * (k & 3));
+                if (g.buf_term != nullptr && __ldg(g.buf_term + idx[k]) != 0)
+                    (k < 4 ? bt.x : bt.y) |= bit;
+                if (g.unfinished != nullptr &&
+                    __ldg(g.unfinished + sub_of(idx[k], g.offset, g.B, g.sub_size)) == idx[k])
+                    (k < 4 ? un.x : un.y) |= bit;
+            }
+            if (g.buf_term != nullptr) wt = bt;
+            wc.x |= un.x;
+            wc.y |= un.y;
+        }
+        double P = 1.0, X = 0.0;
+#pragma unroll
+        for (int k = VEC - 1; k >= 0; --k) {  // last step first
+            if (k >= nvalid) { P = 0.0; X = 0.0; continue; }
+            const double v1 = flag_byte(wt, k) ? 0.0 : (double)vn[k];
+            const double d = fma(v1, gamma, (double)rw[k]) - (double)vs[k];
+            const bool cut = flag_byte(wc, k);
+            X = cut ? d : fma(glp.p[1], X, d);
+            P = cut ? 0.0 : P * glp.p[1];
+        }
+#pragma unroll
+        for (int dlt = 1; dlt < 32; dlt <<= 1) {
+            const double P2 = shfl_down_f64(P, dlt), X2 = shfl_down_f64(X, dlt);
+            if (lane + dlt < 32) { X = fma(P, X2, X); P *= P2; }
+        }
+        Pw = shfl_idx_f64(P, 0);
+        Xw = shfl_idx_f64(X, 0);
+    }
+};
+constexpr double kCarryNegligible = 1e-60;  // accumulated discount below which the rest is 0
+
+template <typename RewT, typename InT, typename OutT, int NT, bool HAS_IDX>
+struct FlatTmaLayout {
+    using R = RowsTmaLayout<RewT, InT, OutT, NT>;
+    static constexpr int TILE = R::TILE;
+    static constexpr int OFF_IDX = R::IN_BYTES;  // int64 indices behind the five arrays
+    static constexpr int IN_BYTES = R::IN_BYTES + (HAS_IDX ? TILE * 8 : 0);
+    static constexpr int OUT_BYTES = R::OUT_BYTES;
+    static constexpr int IN_BYTES_PER_STEP = R::IN_BYTES_PER_STEP + (HAS_IDX ? 8 : 0);
+    static size_t smem_bytes(int stages) {
+        return (size_t)stages * IN_BYTES + OUT_BYTES + (size_t)stages * 8;
+    }
+};
+
+template <typename RewT, typename InT, typename OutT, int NT, bool HAS_IDX>
+__global__ void __launch_bounds__(NT, 768 / NT)  // 3 x 256 threads per SM: <= 80 registers
+gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
+                    const InT* __restrict__ v_next, const uint8_t* __restrict__ term,
+                    const uint8_t* __restrict__ trunc, const FlatGather g, int64_t N,
+                    double gamma, const GlPow glp, OutT* __restrict__ adv,
+                    OutT* __restrict__ ret, int stages, double* __restrict__ heads,
+                    unsigned int* __restrict__ head_flags) {
+    using L = FlatTmaLayout<RewT, InT, OutT, NT, HAS_IDX>;
+    using R = RowsTmaLayout<RewT, InT, OutT, NT>;
+    constexpr int TILE = L::TILE;
+    constexpr int NW = NT / 32;
+    static_assert(NW > 1 && NW <= 8, "cross-warp step assumes 2..8 warps");
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ double sP[NW], sX[NW];
+    __shared__ double s_carry;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int e0 = tid * VEC;
+    unsigned char* out_base = smem + (size_t)stages * L::IN_BYTES;
+    const uint32_t bar0 = smem_u32(out_base + L::OUT_BYTES);
+    OutT* s_adv = reinterpret_cast<OutT*>(out_base);
+    OutT* s_ret = s_adv + TILE;
+
+    const int64_t N16 = N & ~(int64_t)15;  // the bulk-copy part; [N16, N) is done by one thread
+    const int64_t ntiles_all = (N16 + TILE - 1) / TILE;
+    // balanced contiguous ranges; CTA 0 owns the END of the sequence (it never needs a neighbour)
+    const int64_t base = ntiles_all / gridDim.x, rem = ntiles_all % gridDim.x;
+    const int64_t b = blockIdx.x;
+    const int64_t before = b * base + (b < rem ? b : rem);  // tiles owned by CTAs 0..b-1
+    const int ntiles = (int)(base + (b < rem ? 1 : 0));
+    const int64_t k_hi = ntiles_all - before;
+    const int n_last = (int)(N16 - (ntiles_all - 1) * TILE);  // steps in the sequence's last tile
+
+    // producer cursor (elected thread): tile p_k, descending
+    int p_it = 0, p_stage = 0;
+    int64_t p_k = k_hi - 1;
+    auto issue = [&]() {
+        const int n = p_k == ntiles_all - 1 ? n_last : TILE;
+        const int64_t t0 = p_k * TILE;
+        const uint32_t bar = bar0 + 8u * p_stage;
+        const uint32_t dst = smem_u32(smem + (size_t)p_stage * L::IN_BYTES);
+        mbar_expect_tx(bar, (uint32_t)n * L::IN_BYTES_PER_STEP);
+        bulk_g2s(dst, rew + t0, (uint32_t)n * sizeof(RewT), bar);
+        bulk_g2s(dst + R::OFF_VS, v_s + t0, (uint32_t)n * sizeof(InT), bar);
+        bulk_g2s(dst + R::OFF_VN, v_next + t0, (uint32_t)n * sizeof(InT), bar);
+        bulk_g2s(dst + R::OFF_TERM, term + t0, (uint32_t)n, bar);
+        bulk_g2s(dst + R::OFF_TRUNC, trunc + t0, (uint32_t)n, bar);
+        if (HAS_IDX) bulk_g2s(dst + L::OFF_IDX, g.indices + t0, (uint32_t)n * 8u, bar);
+        ++p_it;
+        --p_k;
+        if (++p_stage == stages) p_stage = 0;
+    };
+
+    // ---- carry into the range: the advantage of step k_hi * TILE -----------------------------
+    // CTA 0: the ragged end [N16, N), at most 15 steps, one per lane, outputs included.
+    // Others: read ahead -- first 256 steps by one warp (resolves ~3 ranges in 4 on rollouts with
+    // an episode end every ~200 steps), then 2048 more by the whole CTA, then the neighbour.
+    // (Issuing the first window's reads ahead of the first bulk loads was tried: the registers it
+    // pins cost more than the queueing it avoids, 41.2 vs 38.7 us at 8.4 M steps.)
+    __shared__ int s_state;  // 0 unresolved, 1 resolved
+    double carry = 0.0;
+    const bool working = ntiles > 0 || blockIdx.x == 0;
+    const int64_t p_ahead = k_hi * TILE;
+    if (tid == 0) {
+        for (int s = 0; s < stages; ++s) mbar_init(bar0 + 8u * s, 1u);
+        fence_mbar_init();
+        while (p_it < stages && p_it < ntiles) issue();
+    }
+    __syncthreads();
+    FlatWindow<RewT, InT> W;
+    if (working) {
+        if (blockIdx.x == 0) {
+            if (warp == 0) {  // one step per lane: loads in parallel, the recurrence by shuffles
+                const int nr = (int)(N - N16);
+                const int64_t i = N16 + lane;
+                double dl = 0.0, vsl = 0.0, mine = 0.0;
+                bool cutl = true;
+                if (lane < nr) {
+                    const int64_t idx = g.indices != nullptr ? g.indices[i] : i;
+                    bool masked;
+                    flat_flags(g, idx, term[i], trunc[i], masked, cutl);
+                    const double v1 = masked ? 0.0 : (double)v_next[i];
+                    vsl = (double)v_s[i];
+                    dl = fma(v1, gamma, (double)rew[i]) - vsl;
+                }
+                double A = 0.0;
+                for (int j = nr - 1; j >= 0; --j) {
+                    const double dj = shfl_idx_f64(dl, j);
+                    const bool cj = __shfl_sync(0xffffffffu, (int)cutl, j) != 0;
+                    A = cj ? dj : fma(glp.p[1], A, dj);
+                    if (lane == j) mine = A;
+                }
+                if (lane < nr) {
+                    adv[i] = (OutT)mine;
+                    ret[i] = (OutT)(mine + vsl);
+                }
+                if (lane == 0) { s_carry = A; s_state = 1; }
+            }
+            __syncthreads();
+        } else {
+            double Pc = 1.0, Xc = 0.0;
+            if (warp == 0) {
+                W.load(rew, v_s, v_next, term, trunc, g, p_ahead, N, lane);
+                W.reduce(g, gamma, glp, lane, Pc, Xc);
+                if (lane == 0) {
+                    s_state = fabs(Pc) < kCarryNegligible ? 1 : 0;
+                    s_carry = Xc;
+                    sP[0] = Pc;
+                }
+            }
+            __syncthreads();
+            if (s_state == 0) {  // CTA-uniform: the next NW * 256 steps, one window per warp
+                double Pw, Xw;
+                W.load(rew, v_s, v_next, term, trunc, g, p_ahead + 256 + (int64_t)warp * 256, N,
+                       lane);
+                W.reduce(g, gamma, glp, lane, Pw, Xw);
+                __syncthreads();  // sP[0] has been read by nobody else yet; keep it in a register
+                Pc = sP[0];
+                Xc = s_carry;
+                __syncthreads();
+                if (lane == 0) { sP[warp] = Pw; sX[warp] = Xw; }
+                __syncthreads();
+                if (tid == 0) {
+                    for (int w = 0; w < NW && fabs(Pc) >= kCarryNegligible; ++w) {
+                        Xc = fma(Pc, sX[w], Xc);
+                        Pc *= sP[w];
+                    }
+                    if (fabs(Pc) >= kCarryNegligible) {
+                        // no boundary within reach: the neighbour's published head value
+                        unsigned int f;
+                        do {
+                            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];"
+                                         : "=r"(f) : "l"(head_flags + blockIdx.x - 1) : "memory");
+                        } while (f == 0u);
+                        Xc = __ldcg(heads + blockIdx.x - 1);
+                    }
+                    s_carry = Xc;
+                }
+                __syncthreads();
+            }
+        }
+        carry = s_carry;
+    }
+    __syncthreads();
+    if (ntiles == 0) {  // nothing but (for CTA 0) the ragged end: pass the value on
+        if (blockIdx.x == 0 && tid == 0) {
+            heads[0] = carry;
+            __threadfence();
+            *(volatile unsigned int*)head_flags = 1u;
+        }
+        return;
+    }
+
+    int stage = 0;
+    uint32_t parity = 0;
+    int64_t k = k_hi - 1;
+    for (int it = 0; it < ntiles; ++it, --k) {
+        const int n = k == ntiles_all - 1 ? n_last : TILE;
+        mbar_wait(bar0 + 8u * stage, parity);
+
+        const unsigned char* in = smem + (size_t)stage * L::IN_BYTES;
+        const bool live = e0 < n;
+        RewT rw[VEC];
+        InT vs[VEC], vn[VEC];
+        smem_ld8(reinterpret_cast<const RewT*>(in) + e0, rw);
+        smem_ld8(reinterpret_cast<const InT*>(in + R::OFF_VS) + e0, vs);
+        smem_ld8(reinterpret_cast<const InT*>(in + R::OFF_VN) + e0, vn);
+        uint2 wt = *reinterpret_cast<const uint2*>(in + R::OFF_TERM + e0);
+        uint2 wc = *reinterpret_cast<const uint2*>(in + R::OFF_TRUNC + e0);
+        wc.x |= wt.x;
+        wc.y |= wt.y;
+        if (HAS_IDX && live) {
+            // value mask and unfinished tails come from the buffer, through the indices
+            int64_t id[VEC];
+#pragma unroll
+            for (int q = 0; q < VEC / 2; ++q) {
+                const longlong2 a =
+                    *(reinterpret_cast<const longlong2*>(in + L::OFF_IDX) + (e0 / 2 + q));
+                id[2 * q] = a.x; id[2 * q + 1] = a.y;
+            }
+            if (g.buf_term != nullptr) {
+                uint32_t m_lo = 0, m_hi = 0;
+#pragma unroll
+                for (int q = 0; q < VEC; ++q) {
+                    const uint32_t bit = __ldg(g.buf_term + id[q]) != 0 ? 1u << (8 * (q & 3)) : 0u;
+                    if (q < 4) m_lo |= bit; else m_hi |= bit;
+                }
+                wt.x = m_lo; wt.y = m_hi;
+            }
+            if (g.unfinished != nullptr) {
+                // a strip of consecutive indices touches at most two sub-buffers of >= 8 steps:
+                // two sub-buffer look-ups instead of eight
+                bool consec = true;
+#pragma unroll
+                for (int q = 1; q < VEC; ++q) consec = consec && id[q] == id[0] + q;
+                const int64_t s0 = sub_of(id[0], g.offset, g.B, g.sub_size);
+                const int64_t s7 = sub_of(id[VEC - 1], g.offset, g.B, g.sub_size);
+                if (consec && s7 - s0 <= 1) {
+                    const int64_t u0 = __ldg(g.unfinished + s0) - id[0];
+                    const int64_t u7 = s7 != s0 ? __ldg(g.unfinished + s7) - id[0] : -1;
+                    if (u0 >= 0 && u0 < VEC) {
+                        const uint32_t bit = 1u << (8 * ((int)u0 & 3));
+                        if (u0 < 4) wc.x |= bit; else wc.y |= bit;
+                    }
+                    if (u7 >= 0 && u7 < VEC) {
+                        const uint32_t bit = 1u << (8 * ((int)u7 & 3));
+                        if (u7 < 4) wc.x |= bit; else wc.y |= bit;
+                    }
+                } else {
+#pragma unroll
+                    for (int q = 0; q < VEC; ++q) {
+                        if (__ldg(g.unfinished + sub_of(id[q], g.offset, g.B, g.sub_size)) == id[q]) {
+                            const uint32_t bit = 1u << (8 * (q & 3));
+                            if (q < 4) wc.x |= bit; else wc.y |= bit;
+                        }
+                    }
+                }
+            }
+        }
+
+        double d[VEC];
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) {
+            const InT v1 = flag_byte(wt, q) ? InT(0) : vn[q];
+            d[q] = fma((double)v1, gamma, (double)rw[q]) - (double)vs[q];
+        }
+#pragma unroll
+        for (int q = VEC - 2; q >= 0; --q)
+            if (!flag_byte(wc, q)) d[q] = fma(glp.p[1], d[q + 1], d[q]);
+        double P = (wc.x | wc.y) == 0u ? glp.p[VEC] : 0.0;
+        double X = d[0];
+        if (!live) { P = 1.0; X = 0.0; }
+#pragma unroll
+        for (int dlt = 1; dlt < 32; dlt <<= 1) {
+            const double P2 = shfl_down_f64(P, dlt), X2 = shfl_down_f64(X, dlt);
+            if (lane + dlt < 32) { X = fma(P, X2, X); P *= P2; }
+        }
+        double eP = shfl_down_f64(P, 1), eX = shfl_down_f64(X, 1);
+        if (lane == 31) { eP = 1.0; eX = 0.0; }
+        if (lane == 0) { sP[warp] = P; sX[warp] = X; }
+        if (tid == 0) bulk_wait_read0();
+        __syncthreads();
+        if (tid == 0 && p_it < ntiles) issue();
+
+        double cin = carry;
+#pragma unroll
+        for (int w = NW - 1; w >= 1; --w)
+            if (w > warp) cin = fma(sP[w], cin, sX[w]);
+        cin = fma(eP, cin, eX);
+        double r_out[VEC];
+#pragma unroll
+        for (int q = 0; q < VEC; ++q) {
+            if (no_flag_from(wc, q)) d[q] = fma(glp.p[VEC - q], cin, d[q]);
+            r_out[q] = d[q] + (double)vs[q];
+        }
+        if (live) {
+            smem_st8(s_adv + e0, d);
+            smem_st8(s_ret + e0, r_out);
+        }
+        fence_proxy_async_smem();
+        if (tid == 0) s_carry = d[0];
+        __syncthreads();
+        if (tid == 0) {
+            const int64_t t0 = k * TILE;
+            bulk_s2g(adv + t0, smem_u32(s_adv), (uint32_t)n * sizeof(OutT));
+            bulk_s2g(ret + t0, smem_u32(s_ret), (uint32_t)n * sizeof(OutT));
+            bulk_commit();
+        }
+        carry = s_carry;
+        if (++stage == stages) { stage = 0; parity ^= 1u; }
+    }
+    if (tid == 0) {
+        heads[blockIdx.x] = carry;  // advantage of this range's first step, for a waiting neighbour
+        __threadfence();
+        *(volatile unsigned int*)(head_flags + blockIdx.x) = 1u;
+        bulk_wait0();
+    }
+}
+
+// ============================================================================================
 // General flattened kernel: single pass over N with decoupled look-back between tiles.
 // Tiles are claimed through an atomic ticket so that a tile's successors in time (which it
 // depends on) always started before it: ticket 0 is the LAST tile of the sequence.
@@ -719,6 +1149,47 @@ int32_t launch_rows(const void* rew, const void* v_s, const void* v_next, const 
     return check_launch();
 }
 
+template <typename RewT, typename InT, typename OutT, bool HAS_IDX>
+int32_t launch_flat_tma(const void* rew, const void* v_s, const void* v_next, const uint8_t* term,
+                        const uint8_t* trunc, const FlatGather& g, int64_t N, double gamma,
+                        double lam, void* adv, void* ret, FlatWorkspace ws, cudaStream_t stream) {
+    constexpr int NT = 256;
+    using L = FlatTmaLayout<RewT, InT, OutT, NT, HAS_IDX>;
+    auto kern = gae_flat_tma_kernel<RewT, InT, OutT, NT, HAS_IDX>;
+    int want = g_tune_gae_flat_ctas > 0 ? g_tune_gae_flat_ctas : 3;
+    int stages = g_tune_gae_flat_stages > 0 ? g_tune_gae_flat_stages : 2;
+    if (stages < 2) stages = 2;
+    while (stages > 2 && L::smem_bytes(stages) > 227 * 1024) --stages;
+    const size_t smem = L::smem_bytes(stages);
+    if (smem > 227 * 1024) return TS_ERR_BAD_ARG;
+    // what actually fits (the CTAs of one launch may wait on each other: all must be resident)
+    static int fits[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // per instantiation, by stage count
+    static int attr_stages = 0;
+    if (attr_stages != stages) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem);
+        if (e == cudaSuccess && fits[stages] == 0)
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fits[stages], kern, NT, smem);
+        if (e != cudaSuccess || fits[stages] < 1) {
+            fits[stages] = 0;
+            g_last_cuda_error = (int32_t)e;
+            return TS_ERR_CUDA;
+        }
+        attr_stages = stages;
+    }
+    const int ctas_per_sm = fits[stages] < want ? fits[stages] : want;
+    const int64_t tiles = ((N & ~(int64_t)15) + L::TILE - 1) / L::TILE;
+    const int64_t cap = (int64_t)kNumSMs * ctas_per_sm;
+    const unsigned grid = (unsigned)(tiles < 1 ? 1 : (tiles < cap ? tiles : cap));
+    GlPow glp;
+    glp.p[0] = 1.0;
+    for (int j = 1; j <= VEC; ++j) glp.p[j] = glp.p[j - 1] * (gamma * lam);
+    kern<<<grid, NT, smem, stream>>>((const RewT*)rew, (const InT*)v_s, (const InT*)v_next, term,
+                                     trunc, g, N, gamma, glp, (OutT*)adv, (OutT*)ret, stages,
+                                     ws.aggP, ws.status);
+    return check_launch();
+}
+
 template <typename RewT, typename InT, typename OutT>
 int32_t launch_flat(const void* rew, const void* v_s, const void* v_next, const uint8_t* term,
                     const uint8_t* trunc, const int64_t* indices, const uint8_t* buf_term,
@@ -728,6 +1199,19 @@ int32_t launch_flat(const void* rew, const void* v_s, const void* v_next, const 
     const int vec_ok = aligned(rew, 16) && aligned(v_s, 16) && aligned(v_next, 16) &&
                        aligned(term, 8) && aligned(trunc, 8) && aligned(adv, 16) &&
                        aligned(ret, 16);
+    const bool tma_ok = vec_ok && aligned(term, 16) && aligned(trunc, 16) &&
+                        (indices == nullptr || aligned(indices, 16)) && N < (1LL << 40);
+    int variant = g_tune_gae_flat_variant;  // 0 auto, 1 decoupled look-back, 2 pipelined ranges
+    // short sequences have too few tiles per CTA to amortise the read-ahead: look-back kernel
+    if (variant == 0) variant = N >= (1 << 20) ? 2 : 1;
+    if (variant == 2 && tma_ok) {
+        const FlatGather g{indices, buf_term, unfinished, offset, B, sub_size};
+        if (indices != nullptr)
+            return launch_flat_tma<RewT, InT, OutT, true>(rew, v_s, v_next, term, trunc, g, N, gamma,
+                                                          lam, adv, ret, ws, stream);
+        return launch_flat_tma<RewT, InT, OutT, false>(rew, v_s, v_next, term, trunc, g, N, gamma,
+                                                       lam, adv, ret, ws, stream);
+    }
     gae_flat_kernel<RewT, InT, OutT><<<(unsigned)flat_tiles(N), FLAT_NT, 0, stream>>>(
         (const RewT*)rew, (const InT*)v_s, (const InT*)v_next, term, trunc, indices, buf_term,
         unfinished, offset, B, sub_size, N, gamma, gamma * lam, (OutT*)adv, (OutT*)ret, ws,

@@ -35,7 +35,11 @@ __host__ __device__ __forceinline__ int64_t pymod(int64_t a, int64_t m) {
 // (vecbuf.py:35), else binary search over _extend_offset (manager.py:38).
 __device__ __forceinline__ int64_t sub_of(int64_t idx, const int64_t* __restrict__ offset,
                                           int64_t B, int64_t sub_size) {
-    if (sub_size > 0) return idx / sub_size;
+    if (sub_size > 0) {
+        if ((((uint64_t)idx | (uint64_t)sub_size) >> 32) == 0)  // the usual case: 32-bit divide
+            return (int64_t)((uint32_t)idx / (uint32_t)sub_size);
+        return idx / sub_size;
+    }
     int64_t lo = 0, hi = B;  // offset[lo] <= idx < offset[hi]
     while (hi - lo > 1) {
         int64_t mid = (lo + hi) >> 1;
@@ -116,6 +120,9 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
 
 // Tuning knobs (ts_tune_set): 0 = automatic choice.
 extern int g_tune_gae_rows_variant;
+extern int g_tune_gae_flat_variant;  // 0 auto, 1 decoupled look-back, 2 pipelined ranges
+extern int g_tune_gae_flat_ctas;     // pipelined ranges: CTAs per SM (0 auto, 1..3)
+extern int g_tune_gae_flat_stages;   // pipelined ranges: stages of the ring (0 auto, 2..6)
 extern int g_tune_segtree_max_ctas;  // CTAs of the cooperative tree update (<= 148)
 extern int g_tune_per_cluster;       // PER sampling cluster: 0 auto, 8 (x512 threads) or 16 (x256)
 extern int g_tune_segtree_group;  // 128 (default) or 256 nodes per warp-rebuilt group
