@@ -207,7 +207,7 @@ def run_reference(args):
                 "workload": "2^20 leaves, batch 4096, sample + weights + update_weight"},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit_result(line)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -226,7 +226,6 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device(f"cuda:{local}")
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG", "WARN")  # keep NCCL's version banner off stdout
         dist.init_process_group("nccl", device_id=dev)
     lib = L.lib()  # raises if the CUDA extension is missing: there is no fallback
     E, T = args.streams, args.horizon
@@ -387,7 +386,7 @@ def run_b200(args):
             "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "cpu_baseline": cpu, "per": per,
         }
-        print(json.dumps(line), flush=True)
+        emit_result(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -574,8 +573,31 @@ def run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
                                  "step, not bytes; tree is L2-resident"}}
 
 
+_RESULT_FD = None
+
+
+def _keep_stdout_clean():
+    """The driver reads ONE JSON line from stdout.  Libraries (NCCL's version banner, torchrun
+    children) write to file descriptor 1 behind Python's back: point fd 1 at stderr for the
+    whole run and keep a private duplicate of the real stdout for the result line."""
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit_result(line: dict) -> None:
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
     args = parse_args()
+    _keep_stdout_clean()
     if args.impl == "reference":
         run_reference(args)
     else:
