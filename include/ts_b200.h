@@ -58,9 +58,13 @@ int32_t ts_last_cuda_error(void);
 /* Kernel-selection knobs for benchmarking (process-wide, not part of the reference-facing
  * surface).  Keys: "gae_rows_variant" (0 = automatic; see csrc/gae.cu:kRowsVariants). */
 int32_t ts_tune_set(const char* key, int64_t value);
-/* Debug: globaltimer ns at the six phase boundaries of the most recent tiered tree update
- * (synchronises the device; host buffer of 6 uint64). */
-int32_t ts_debug_update_phases(uint64_t* out6);
+/* Debug: globaltimer ns at the phase boundaries of the most recent small-batch tree update
+ * (synchronises the device; host buffer of 8 uint64: start, batch scanned, groups rebuilt,
+ * last-CTA ticket, -, end, table cleared, batch loads landed). */
+int32_t ts_debug_update_phases(uint64_t* out8);
+/* Debug: per-CTA globaltimer ns {start, batch scanned, groups rebuilt, ticket taken} of the most
+ * recent ranged tree update, 128 CTAs x 4 (synchronises the device). */
+int32_t ts_debug_update_ctas(uint64_t* out512);
 
 /* ------------------------------------------------------------------------------------------
  * GAE / TD(lambda) returns.

@@ -77,16 +77,28 @@ def main():
         print(json.dumps({"what": name, "lg": lg, "batch": B, "us_per_call": best}), flush=True)
 
     import ctypes
-    for group in (128, 256):
-        L.check(lib.ts_tune_set(b"segtree_group", group), "tune")
-        timed(f"update(group={group})", update)
-        ph = (ctypes.c_uint64 * 6)()
+    for group in (1, 0):
+        L.check(lib.ts_tune_set(b"segtree_ranged", group), "tune")
+        timed(f"update(ranged={group})", update)
+        ph = (ctypes.c_uint64 * 8)()
         torch.cuda.synchronize()
         L.check(lib.ts_debug_update_phases(ph), "phases")
         t = list(ph)
-        print(json.dumps({"phases_ns": {"A+bar": t[1] - t[0], "tier0(cta0)": t[2] - t[1],
-                                        "rendezvous+top": t[5] - t[2]}}), flush=True)
-    L.check(lib.ts_tune_set(b"segtree_group", 128), "tune")
+        print(json.dumps({"phases_ns": {"zero": t[6] - t[0], "compact": t[7] - t[6],
+                                        "pow+table": t[1] - t[7], "groups": t[2] - t[1],
+                                        "ticket(last)": t[3] - t[2], "top": t[5] - t[3],
+                                        "total": t[5] - t[0]}}), flush=True)
+        ct = (ctypes.c_uint64 * 512)()
+        L.check(lib.ts_debug_update_ctas(ct), "ctas")
+        c = np.array(list(ct), dtype=np.int64).reshape(128, 4)
+        t0 = c[:, 0].min()
+        q = lambda a: [int(np.percentile(a, p)) for p in (0, 50, 90, 100)]
+        print(json.dumps({"cta_ns(min,p50,p90,max)": {
+            "start": q(c[:, 0] - t0), "scan_done": q(c[:, 1] - t0), "groups_done": q(c[:, 2] - t0),
+            "ticket": q(c[:, 3] - t0), "scan_dur": q(c[:, 1] - c[:, 0]),
+            "groups_dur": q(c[:, 2] - c[:, 1]), "slowest_cta": int(np.argmax(c[:, 3]))}}),
+            flush=True)
+    L.check(lib.ts_tune_set(b"segtree_ranged", 1), "tune")
     for cl in (8, 16):
         L.check(lib.ts_tune_set(b"per_cluster", cl), "tune")
         timed(f"sample(cluster={cl})", sample)

@@ -69,10 +69,20 @@ def test_golden_segtree(name):
     assert tree.reduce() == c["tree"][1]
 
 
+@pytest.fixture(params=[1, 0], ids=["ranged", "tiered"])
+def update_kernel(request):
+    """Both small-batch update kernels: per-CTA leaf ranges (default) and the tiered one."""
+    from tianshou_fork_b200 import _lib as L
+    L.check(L.lib().ts_tune_set(b"segtree_ranged", request.param), "tune")
+    yield request.param
+    L.check(L.lib().ts_tune_set(b"segtree_ranged", 1), "tune")
+
+
 @pytest.mark.parametrize("size,bsz", [(1, 1), (2, 3), (4096, 64), (4097, 4096), (1 << 20, 4096),
                                       (1_000_000, 32), (1 << 20, 8192), (1 << 20, 20000),
-                                      (300_000, 100_000)])
-def test_update_and_descent_vs_oracle(size, bsz):
+                                      (300_000, 100_000), (10_000, 5000), (70_000, 16383),
+                                      (1 << 21, 4096)])
+def test_update_and_descent_vs_oracle(size, bsz, update_kernel):
     """Random batched updates with forced duplicates on every update path (dense tiny tree,
     subtree-per-CTA, bulk rebuild), then a batched descent; all bit-exact vs the oracle."""
     import tianshou_fork_b200 as ts
@@ -168,7 +178,7 @@ def test_golden_per_single():
         assert np.isclose(buf.weight[int(i)], (abs(t) + np.finfo(np.float32).eps) ** 0.5)
 
 
-def test_per_full_size_step_vs_oracle():
+def test_per_full_size_step_vs_oracle(update_kernel):
     """BASELINE.json configs[3] shape: 2^20 leaves, batch 4096, alpha .6 beta .4; ten chained
     sample -> update steps, every sampled index bit-exact vs the oracle on identical draws."""
     import tianshou_fork_b200 as ts

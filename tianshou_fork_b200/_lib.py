@@ -34,6 +34,7 @@ SIGNATURES = {
     "ts_last_cuda_error": (_i32, []),
     "ts_tune_set": (_i32, [ctypes.c_char_p, _i64]),
     "ts_debug_update_phases": (_i32, [_vp]),
+    "ts_debug_update_ctas": (_i32, [_vp]),
     "ts_gae_rows": (_i32, [_vp] * 5 + [_i64] * 4 + [_f64, _f64, _i32, _i32, _i32, _vp, _vp,
                                                     _vp]),
     "ts_gae_flat_workspace_bytes": (_sz, [_i64]),

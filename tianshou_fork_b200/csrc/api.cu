@@ -8,6 +8,7 @@ int g_tune_gae_flat_variant = 0;
 int g_tune_gae_flat_ctas = 0;
 int g_tune_gae_flat_stages = 0;
 int g_tune_segtree_group = 128;
+int g_tune_segtree_ranged = 1;
 int g_tune_per_cluster = 0;
 int g_tune_segtree_max_ctas = 148;
 }
@@ -50,6 +51,10 @@ extern "C" int32_t ts_tune_set(const char* key, int64_t value) {
     }
     if (strcmp(key, "per_cluster") == 0 && (value == 0 || value == 8 || value == 16)) {
         ts::g_tune_per_cluster = (int)value;
+        return TS_OK;
+    }
+    if (strcmp(key, "segtree_ranged") == 0 && (value == 0 || value == 1)) {
+        ts::g_tune_segtree_ranged = (int)value;
         return TS_OK;
     }
     if (strcmp(key, "segtree_group") == 0 && (value == 128 || value == 256)) {

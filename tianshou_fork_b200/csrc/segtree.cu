@@ -195,9 +195,20 @@ constexpr uint32_t kTagMax = (1u << (32 - kTagShift)) - 1u;
 // Phase timestamps of the most recent tiered update (globaltimer ns, CTA 0 / thread 0):
 // start, after phase A barrier, after tier 0, after the last barrier, after top load, end.
 __device__ unsigned long long g_update_phase_ns[8];
+// start / batch scanned / groups done / ticket taken, per CTA of the most recent ranged update
+__device__ unsigned long long g_update_cta_ns[128][4];
+
+__device__ __forceinline__ void cta_mark(int slot) {
+    if (threadIdx.x == 0 && blockIdx.x < 128) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_update_cta_ns[blockIdx.x][slot] = t;
+    }
+}
 
 __device__ __forceinline__ void phase_mark(int slot) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
+    // CTA 1 when there is one: CTA 0 carries the batch-wide extras and is not representative
+    if (blockIdx.x == (gridDim.x > 1 ? 1u : 0u) && threadIdx.x == 0) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         g_update_phase_ns[slot] = t;
@@ -246,6 +257,10 @@ struct GridBarrier {
     }
 };
 
+template <int K>
+__device__ __forceinline__ double group_levels(double* __restrict__ tree, int64_t base,
+                                               double (&v)[K], int lane);
+
 // One warp rebuilds the aligned group of G = 32 * K nodes that starts at heap index `first`,
 // LG = log2(G) levels up, and returns the group's root (valid in lane 0).  With STAMPED the
 // group is a leaf group: stamped leaves are replaced first.
@@ -283,6 +298,13 @@ __device__ __forceinline__ double rebuild_group(double* __restrict__ tree, int64
             }
         }
     }
+    return group_levels<K>(tree, base, v, lane);
+}
+
+// The LG levels above a group whose 32 * K nodes are already in registers (K per lane).
+template <int K>
+__device__ __forceinline__ double group_levels(double* __restrict__ tree, int64_t base,
+                                               double (&v)[K], int lane) {
     // levels inside the lane's strip
     int64_t node = base;
 #pragma unroll
@@ -346,6 +368,33 @@ __device__ __forceinline__ void warp_finish(double* __restrict__ tree, int n, in
         node >>= 1;
         if ((lane & (2 * d - 1)) == 0 && lane < live) tree[node] = x;
     }
+}
+
+// One CTA of 32 warps rebuilds levels lvl-1 .. 0 from level lvl (2^lvl <= 8192 nodes): groups of
+// 256 per warp (8 levels, no CTA barrier inside), whose roots go through shared memory to one
+// warp that finishes the <= 128 nodes that remain.
+__device__ __forceinline__ void rebuild_top(double* __restrict__ tree, int lvl, double* s_root,
+                                            int tid) {
+    const int lane = tid & 31, warp = tid >> 5;
+    const double* s_level = nullptr;
+    if (lvl >= 8) {
+        const int groups = 1 << (lvl - 8);  // <= 32 = warps of the CTA: a single pass
+        if (warp < groups) {
+            double v[8];
+            const int64_t base = ((int64_t)1 << lvl) + ((int64_t)warp << 8) + (int64_t)lane * 8;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const double2 t = __ldcg(reinterpret_cast<const double2*>(tree + base) + q);
+                v[2 * q] = t.x; v[2 * q + 1] = t.y;
+            }
+            const double root = group_levels<8>(tree, base, v, lane);
+            if (lane == 0) s_root[warp] = root;
+        }
+        lvl -= 8;
+        s_level = s_root;
+        __syncthreads();
+    }
+    if (tid < 32) warp_finish(tree, 1 << lvl, lane, s_level);
 }
 
 constexpr int kIdxRounds = 8;  // rounds of 32 items per CTA whose indices stay in shared memory
@@ -446,21 +495,7 @@ segtree_update_tiered(double* __restrict__ tree, int64_t size, int64_t bound, in
     // ---- top: the CTA that arrives last rebuilds levels lvl-1 .. 0 from level lvl -------------
     phase_mark(2);
     if (!bar.arrive_last(&s_last)) return;
-    // 2^lvl <= 8192 nodes: groups of 256 per warp (8 levels, no CTA barrier inside), whose roots
-    // go through shared memory to one warp that finishes the <= 128 nodes that remain.
-    const double* s_level = nullptr;
-    if (lvl >= 8) {
-        const int groups = 1 << (lvl - 8);  // <= 32 = warps of this CTA: a single pass
-        if (warp < groups) {
-            const double root = rebuild_group<8, false>(
-                tree, ((int64_t)1 << lvl) + ((int64_t)warp << 8), 0, size, vs, stamp, tag, lane);
-            if (lane == 0) s_root[warp] = root;
-        }
-        lvl -= 8;
-        s_level = s_root;
-        __syncthreads();
-    }
-    if (tid < 32) warp_finish(tree, 1 << lvl, lane, s_level);
+    rebuild_top(tree, lvl, s_root, tid);
     if (pub.state != nullptr) {
         // fused producer side of the shard exchange: the CTA that just wrote the new root stores
         // this rank's record into every peer's buffer over NVLink
@@ -471,6 +506,301 @@ segtree_update_tiered(double* __restrict__ tree, int64_t size, int64_t bound, in
         counter[0] = 0u;
         if (tag >= kTagMax) { counter[2] = 0u; counter[3] = 1u; }
         else { counter[2] = tag; counter[3] = 0u; }
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_update_phase_ns[5] = t;
+    }
+}
+
+// ============================================================================================
+// Ranged small-batch update (trees up to 2^20 leaves): ONE ordinary launch, no grid barrier,
+// no global stamps.
+//
+// CTA c owns the aligned range of L = bound / gridDim leaves (<= 8192).  Every CTA reads the
+// WHOLE batch (M indices, coalesced, 8 B each -- the same 32 KB for all CTAs, served by L2) and
+// keeps the items that fall in its range in a shared-memory table, one 64-bit word per leaf:
+// atomicMax((j + 1) << 32 | f32 bits of the new leaf).  The maximum is the LAST batch position
+// that wrote the leaf (segtree.py:40-49) and carries its value, so after one __syncthreads the
+// CTA knows every leaf it has to write without another trip to memory.  Then one warp per touched
+// group of 128 leaves: load the group, overlay the table, write leaves and the 7 levels above.
+// The CTA that finishes last rebuilds the 13 levels that remain (rebuild_top).
+//
+// Dependent memory round trips: batch read, group read, last-CTA ticket, top read -- four, and
+// the only inter-CTA dependency is "last one out", which needs no co-residency.
+// ============================================================================================
+constexpr int RANGE_NT = 1024;
+constexpr int kRangeLgMax = 13;       // 8192 leaves per CTA: 64 KB table
+constexpr int kRangeLgMin = 10;       // at least 8 groups per CTA
+constexpr int kRangeUnroll = 4;       // items per thread whose loads are in flight together
+constexpr int kRangeList = 2048;      // compacted in-range items per pass (more: handled in place)
+
+__device__ __forceinline__ bool carries_f32(int mode) {
+    return mode == VM_PER_F32 || mode == VM_F32 || mode == VM_INIT_F32;
+}
+
+// f32 bits of the new leaf of batch item j (modes whose leaves are f32 values)
+__device__ __forceinline__ uint32_t carried_bits(const ValueSrc& vs, int64_t j, float td) {
+    if (vs.mode == VM_PER_F32)
+        return __float_as_uint((float)pow_fast((double)(fabsf(td) + kEpsF32), vs.alpha));
+    return __float_as_uint((float)leaf_value(vs, j));
+}
+
+// one warp: store {root, max_prio, min_prio, epoch} into every peer's slot buffer
+__device__ __forceinline__ void publish_record_warp(const double* tree, const double* prio,
+                                                    const PublishInfo& pub, int lane) {
+    const unsigned long long e = __ldcg(pub.state) + 1;
+    for (int t = lane; t < pub.G; t += 32) {
+        double* dst = pub.peer_slots[t] + slot_record(pub.G, e, pub.rank);
+        st_relaxed_sys_f64(dst, __ldcg(tree + 1));
+        st_relaxed_sys_f64(dst + 1, __ldcg(prio));
+        st_relaxed_sys_f64(dst + 2, __ldcg(prio + 1));
+        __threadfence_system();
+        st_release_sys_u64(dst + 3, e);
+    }
+    __syncwarp();
+    if (lane == 0) pub.state[0] = e;
+}
+
+// Out-of-line copies for the paths that are rarely taken: the kernel's instruction footprint is
+// what its latency is made of (every phase runs once per launch, from a cold instruction cache).
+__device__ __noinline__ uint32_t carried_bits_cold(const ValueSrc& vs, int64_t j, float td) {
+    return carried_bits(vs, j, td);
+}
+__device__ __noinline__ double leaf_value_cold(const ValueSrc& vs, int64_t j) {
+    return leaf_value(vs, j);
+}
+__device__ __noinline__ double per_priority_cold(const ValueSrc& vs, int64_t j) {
+    return per_priority(vs, j);
+}
+
+// PERF32: vs.mode == VM_PER_F32, the replay step's update_weight (prio.py:78-89 on a f32 td_error);
+// every mode test folds away.  The other modes share the generic instantiation.
+template <bool PERF32>
+__global__ void __launch_bounds__(RANGE_NT)
+segtree_update_ranged(double* __restrict__ tree, int64_t size, int lg_bound, int lg_range,
+                      const int64_t* __restrict__ index, ValueSrc vs, int64_t M,
+                      uint32_t* __restrict__ counter, int32_t* __restrict__ err_flag,
+                      PublishInfo pub, const double* prio) {
+    extern __shared__ __align__(16) unsigned long long s_tab[];  // [L]: (j + 1) << 32 | f32 bits
+    __shared__ uint2 s_list[kRangeList];                         // {j + 1, leaf - lo}
+    __shared__ float s_list_td[kRangeList];
+    __shared__ unsigned int s_n[2];         // list length, alternating between passes
+    __shared__ unsigned int s_touched[64];  // per group of 128 leaves
+    __shared__ double s_root[64];
+    __shared__ double s_pmax[32], s_pmin[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int L = 1 << lg_range;
+    const int groups = L >> 7;  // 8 .. 64: one or two per warp
+    const bool audits = blockIdx.x == 0;  // batch-wide checks and extrema are CTA 0's job
+    const int64_t lo = (int64_t)blockIdx.x << lg_range;
+    const bool carry = PERF32 || carries_f32(vs.mode);
+    const bool tracks_prio = PERF32 || vs.mode == VM_PER_F64;
+    constexpr int64_t kPass = (int64_t)kRangeUnroll * RANGE_NT;
+
+    phase_mark(0);
+    cta_mark(0);
+    // warp 0: this range's group roots as they are now; the untouched ones are needed at the end
+    const int gper = groups > 32 ? 2 : 1;
+    const int64_t groot0 = ((int64_t)1 << (lg_bound - 7)) + (lo >> 7);
+    double old_root0 = 0.0, old_root1 = 0.0;
+    if (warp == 0 && lane * gper < groups) {
+        old_root0 = __ldcg(tree + groot0 + lane * gper);
+        if (gper == 2) old_root1 = __ldcg(tree + groot0 + lane * gper + 1);
+    }
+    for (int i = tid; i < L / 2; i += RANGE_NT)
+        reinterpret_cast<ulonglong2*>(s_tab)[i] = make_ulonglong2(0ull, 0ull);
+    if (tid < 64) s_touched[tid] = 0u;
+    if (tid < 2) s_n[tid] = 0u;
+    __syncthreads();
+    phase_mark(6);
+
+    // ---- the batch: every CTA scans all of it, keeps what falls in its range ---------------------
+    double pmax = 0.0, pmin = INFINITY;                 // VM_PER_F64
+    uint32_t fmax_bits = 0u, fmin_bits = 0x7f800000u;   // VM_PER_F32: positive floats order like bits
+    int pass = 0;
+    for (int64_t j0 = 0; j0 < M; j0 += kPass, pass ^= 1) {
+        int64_t id[kRangeUnroll];
+        float tdf[kRangeUnroll];
+#pragma unroll
+        for (int q = 0; q < kRangeUnroll; ++q) {
+            const int64_t j = j0 + (int64_t)q * RANGE_NT + tid;
+            id[q] = j < M ? __ldg(index + j) : kSkipIndex;
+            tdf[q] = PERF32 && j < M ? __ldg((const float*)vs.ptr + j) : 0.f;
+        }
+        if (audits) {
+#pragma unroll
+            for (int q = 0; q < kRangeUnroll; ++q) {
+                const int64_t idx = id[q];
+                if (idx == kSkipIndex) continue;  // "not in this shard" (ts_per_sample_sharded)
+                if (PERF32) {  // priority extrema over the batch (prio.py:88-89)
+                    const uint32_t pb = __float_as_uint(fabsf(tdf[q]) + kEpsF32);
+                    fmax_bits = max(fmax_bits, pb);
+                    fmin_bits = min(fmin_bits, pb);
+                } else if (tracks_prio) {
+                    const double p = per_priority_cold(vs, j0 + (int64_t)q * RANGE_NT + tid);
+                    pmax = fmax(pmax, p);
+                    pmin = fmin(pmin, p);
+                }
+                if (idx < 0 || idx >= size) atomicOr(err_flag, TS_FLAG_INDEX_RANGE);
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < kRangeUnroll; ++q) {
+            const int64_t j = j0 + (int64_t)q * RANGE_NT + tid;
+            const int64_t rel = id[q] - lo;
+            if (id[q] == kSkipIndex || rel < 0 || rel >= L || id[q] >= size) continue;
+            s_touched[rel >> 7] = 1u;
+            const unsigned int pos = atomicAdd(&s_n[pass], 1u);
+            if (pos < (unsigned)kRangeList) {
+                s_list[pos] = make_uint2((uint32_t)(j + 1), (uint32_t)rel);
+                s_list_td[pos] = tdf[q];
+            } else {  // a batch concentrated on this range: finish the item here
+                const uint32_t bits = carry ? carried_bits_cold(vs, j, tdf[q]) : 0u;
+                atomicMax(s_tab + rel, ((unsigned long long)(j + 1) << 32) | bits);
+            }
+        }
+        __syncthreads();
+        phase_mark(7);
+        // the kept items, densely: the exponent is a few hundred dependent f64 instructions
+        const unsigned int n = min(s_n[pass], (unsigned)kRangeList);
+        if (tid == 0) s_n[pass ^ 1] = 0u;  // the next pass's counter; nobody is using it now
+        for (unsigned int i = tid; i < n; i += RANGE_NT) {
+            const uint2 it = s_list[i];
+            uint32_t bits = 0u;
+            if (PERF32)
+                bits = __float_as_uint(
+                    (float)pow_fast((double)(fabsf(s_list_td[i]) + kEpsF32), vs.alpha));
+            else if (carry)
+                bits = carried_bits_cold(vs, (int64_t)it.x - 1, 0.f);
+            atomicMax(s_tab + it.y, ((unsigned long long)it.x << 32) | bits);
+        }
+        __syncthreads();
+    }
+    if (audits && tracks_prio) {
+        if (PERF32) {
+            fmax_bits = __reduce_max_sync(0xffffffffu, fmax_bits);
+            fmin_bits = __reduce_min_sync(0xffffffffu, fmin_bits);
+            pmax = fmax_bits != 0u ? (double)__uint_as_float(fmax_bits) : 0.0;
+            pmin = (double)__uint_as_float(fmin_bits);
+        } else {
+#pragma unroll
+            for (int d = 16; d >= 1; d >>= 1) {
+                pmax = fmax(pmax, __shfl_xor_sync(0xffffffffu, pmax, d));
+                pmin = fmin(pmin, __shfl_xor_sync(0xffffffffu, pmin, d));
+            }
+        }
+        if (lane == 0) { s_pmax[warp] = pmax; s_pmin[warp] = pmin; }
+    }
+    phase_mark(1);
+    cta_mark(1);
+
+    // ---- touched groups: warp per group of 128 leaves (its two groups fetched together) ---------
+    {
+        const int64_t leaves = ((int64_t)1 << lg_bound) + lo + lane * 4;
+        const int g0 = warp, g1 = warp + 32;
+        const bool t0 = g0 < groups && s_touched[g0] != 0u;  // warp-uniform
+        const bool t1 = g1 < groups && s_touched[g1] != 0u;
+        double v[2][4];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 0 ? t0 : t1) {
+                const int64_t base = leaves + ((int64_t)(h == 0 ? g0 : g1) << 7);
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const double2 t = __ldcg(reinterpret_cast<const double2*>(tree + base) + q);
+                    v[h][2 * q] = t.x; v[h][2 * q + 1] = t.y;
+                }
+            }
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 0 ? t0 : t1) {
+                const int gl = h == 0 ? g0 : g1;
+                const int64_t base = leaves + ((int64_t)gl << 7);
+                const ulonglong2* e2 =
+                    reinterpret_cast<const ulonglong2*>(s_tab + (gl << 7) + lane * 4);
+                const ulonglong2 ea = e2[0], eb = e2[1];
+                const unsigned long long e[4] = {ea.x, ea.y, eb.x, eb.y};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (e[k] != 0ull) {
+                        v[h][k] = carry ? (double)__uint_as_float((uint32_t)e[k])
+                                        : leaf_value_cold(vs, (int64_t)(e[k] >> 32) - 1);
+                        tree[base + k] = v[h][k];
+                    }
+                }
+                const double root = group_levels<4>(tree, base, v[h], lane);
+                if (lane == 0) s_root[gl] = root;
+            }
+        }
+    }
+    __syncthreads();
+    phase_mark(2);
+    cta_mark(2);
+    if (warp != 0) return;
+
+    if (audits && tracks_prio) {
+        pmax = s_pmax[lane];
+        pmin = s_pmin[lane];
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) {
+            pmax = fmax(pmax, __shfl_xor_sync(0xffffffffu, pmax, d));
+            pmin = fmin(pmin, __shfl_xor_sync(0xffffffffu, pmin, d));
+        }
+        if (lane == 0 && pmax > 0.0) {
+            atomic_max_pos(vs.prio, pmax);
+            atomic_min_pos(vs.prio + 1, pmin);
+        }
+    }
+    // ---- warp 0: this range's root from its group roots (untouched ones from the tree) ------------
+    {
+        const int g0 = lane * gper;
+        const bool in = g0 < groups;
+        const bool m0 = in && s_touched[g0] != 0u;
+        const bool m1 = in && gper == 2 && s_touched[g0 + 1] != 0u;
+        if (__any_sync(0xffffffffu, m0 || m1)) {  // else nothing in this range changed
+            double x = 0.0;
+            int64_t node = groot0 + g0;
+            if (in) x = m0 ? s_root[g0] : old_root0;
+            if (gper == 2) {
+                const double y = m1 ? s_root[g0 + 1] : old_root1;
+                x = __dadd_rn(x, y);
+                node >>= 1;
+                tree[node] = x;
+            }
+            const int live = groups / gper;  // 8 .. 32 lanes hold one node each
+            for (int d = 1; d < live; d <<= 1) {
+                const double r = __shfl_down_sync(0xffffffffu, x, d);
+                x = __dadd_rn(x, r);
+                node >>= 1;
+                if ((lane & (2 * d - 1)) == 0 && lane < live) tree[node] = x;
+            }
+        }
+        __syncwarp();
+    }
+
+    // ---- warp 0 of every CTA: the one that arrives last rebuilds the levels above the ranges -------
+    int last = 0;
+    if (lane == 0) {
+        __threadfence();
+        last = atomicAdd(counter, 1u) == gridDim.x - 1u;
+    }
+    cta_mark(3);
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (!last) return;
+    __threadfence();  // acquire side: the other CTAs' nodes
+    if (lane == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_update_phase_ns[3] = t;
+    }
+    if (gridDim.x > 1) warp_finish(tree, (int)gridDim.x, lane, nullptr);
+    if (pub.state != nullptr) {
+        __syncwarp();
+        publish_record_warp(tree, prio, pub, lane);
+    }
+    if (lane == 0) {
+        counter[0] = 0u;
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         g_update_phase_ns[5] = t;
@@ -584,6 +914,34 @@ int32_t update_impl(double* tree, int64_t size, int64_t bound, const int64_t* in
     if (!tree || !index || !stamp || !counter || !err_flag) return TS_ERR_BAD_ARG;
 
     if (!aligned(tree, 16) || !aligned(stamp, 16)) return TS_ERR_ALIGN;
+    if (M <= kSmallM && bound > kDenseBound && bound <= (1LL << (kRangeLgMax + 7)) &&
+        g_tune_segtree_ranged != 0) {
+        const int lg = ilog2(bound);
+        int lg_range = lg - 7;  // 128 CTAs when the range stays within [2^10, 2^13] leaves
+        if (lg_range > kRangeLgMax) lg_range = kRangeLgMax;
+        if (lg_range < kRangeLgMin) lg_range = kRangeLgMin;
+        const unsigned ctas = (unsigned)(bound >> lg_range);
+        const size_t smem = sizeof(unsigned long long) << lg_range;
+        static bool attr_done = false;
+        if (!attr_done) {
+            const int cap = (int)(sizeof(unsigned long long) << kRangeLgMax);
+            cudaError_t e = cudaFuncSetAttribute(segtree_update_ranged<true>,
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+            if (e == cudaSuccess)
+                e = cudaFuncSetAttribute(segtree_update_ranged<false>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+            if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
+            attr_done = true;
+        }
+        const double* prio_c = vs.prio;
+        if (vs.mode == VM_PER_F32)
+            segtree_update_ranged<true><<<ctas, RANGE_NT, smem, st>>>(
+                tree, size, lg, lg_range, index, vs, M, counter, err_flag, pub, prio_c);
+        else
+            segtree_update_ranged<false><<<ctas, RANGE_NT, smem, st>>>(
+                tree, size, lg, lg_range, index, vs, M, counter, err_flag, pub, prio_c);
+        return check_launch();
+    }
     if (M <= kSmallM && bound > kDenseBound) {
         const int lg = ilog2(bound);
         // level handed to the top phase: strip LG levels per tier until <= kTopMax nodes
@@ -667,12 +1025,15 @@ __device__ __forceinline__ int step_down(double lsons, VT& v) {
 }
 
 // Descent for one query; `v` is updated like the reference mutates `value` (:134).
+// `leaf_out` (optional) receives tree[bound + result]: the last round trip has already fetched it.
 template <typename VT>
 __device__ __forceinline__ int64_t descend(const double* __restrict__ tree, int64_t bound,
                                            int lg_bound, const double* s_top, int cached,
-                                           VT& v) {
+                                           VT& v, double* leaf_out = nullptr) {
     int64_t index = 1;
     int depth = 0;
+    double leaf = 0.0;
+    bool have_leaf = false;
     while (depth < lg_bound && 2 * index < cached) {  // sons still in shared memory
         index <<= 1;
         index += step_down(s_top[index], v);
@@ -695,7 +1056,13 @@ __device__ __forceinline__ int64_t descend(const double* __restrict__ tree, int6
         const int r3 = step_down(l3, v);
         index = (index << 3) + 4 * r1 + 2 * r2 + r3;
         depth += 3;
+        if (leaf_out != nullptr && depth == lg_bound) {  // the eight nodes were leaves
+            const double r_ = r1 ? (r2 ? d.y : c.y) : (r2 ? b.y : a.y);
+            leaf = r3 ? r_ : l3;
+            have_leaf = true;
+        }
     }
+    if (leaf_out != nullptr) *leaf_out = have_leaf ? leaf : __ldg(tree + index);
     return index - bound;                                       // :136
 }
 
@@ -826,18 +1193,21 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
         }
         for (int r = 0; r < G; ++r) min_prio = fmin(min_prio, s_gext[G + r]);
     }
+    const int64_t sweep = (int64_t)cluster_nctarank() * NT;
+    const int64_t j0 = (int64_t)cluster_ctarank() * NT + tid;
+    // the first query's draw is fetched while the top of the tree is being staged
+    const double u_first = SAMPLE && j0 < M ? __ldg(u + j0) : 0.0;
     if (SAMPLE) {
         cached = stage_top<NT>(tree, bound, s_top, tid);
         total = sharded ? s_gtop[1] : s_top[1];
     }
-    const int64_t sweep = (int64_t)cluster_nctarank() * NT;
-    const int64_t j0 = (int64_t)cluster_ctarank() * NT + tid;
     double wmax = 0.0, w_first = 0.0;
     for (int64_t j = j0; j < M; j += sweep) {
         int64_t leaf;
+        double leaf_val = 0.0;
         bool mine = true;
         if (SAMPLE) {
-            double v = __dmul_rn(u[j], total);                   // prio.py:61
+            double v = __dmul_rn(j == j0 ? u_first : u[j], total);  // prio.py:61
             if (!(v >= 0.0 && v < total)) atomicOr(err_flag, TS_FLAG_PREFIX_RANGE);
             if (sharded) {
                 int node = 1;
@@ -847,13 +1217,14 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
                 }
                 mine = node - G == sh.rank;
             }
-            leaf = mine ? descend<double>(tree, bound, lg_bound, s_top, cached, v) : -1;
+            leaf = mine ? descend<double>(tree, bound, lg_bound, s_top, cached, v, &leaf_val) : -1;
             idx[j] = leaf;
         } else {
             leaf = idx[j];
             mine = leaf >= 0;
+            if (mine) leaf_val = __ldg(tree + bound + leaf);
         }
-        const double w = mine ? is_weight(__ldg(tree + bound + leaf), min_prio, beta) : 0.0;
+        const double w = mine ? is_weight(leaf_val, min_prio, beta) : 0.0;
         if (j == j0) w_first = w; else weight[j] = w;  // later sweeps park the raw weight
         wmax = fmax(wmax, w);
     }
@@ -1063,12 +1434,20 @@ extern "C" int32_t ts_per_init_weight(double* tree, int64_t size, int64_t bound,
                        (cudaStream_t)stream);
 }
 
-extern "C" int32_t ts_debug_update_phases(uint64_t* out6) {
+extern "C" int32_t ts_debug_update_ctas(uint64_t* out512) {
+    if (!out512) return TS_ERR_BAD_ARG;
+    cudaError_t e = cudaMemcpyFromSymbol(out512, g_update_cta_ns, sizeof(unsigned long long) * 512);
+    if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
+    return TS_OK;
+}
+
+extern "C" int32_t ts_debug_update_phases(uint64_t* out8) {
+    uint64_t* out6 = out8;
     if (!out6) return TS_ERR_BAD_ARG;
     unsigned long long h[8];
     cudaError_t e = cudaMemcpyFromSymbol(h, g_update_phase_ns, sizeof(h));
     if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
-    for (int i = 0; i < 6; ++i) out6[i] = h[i];
+    for (int i = 0; i < 8; ++i) out6[i] = h[i];
     return TS_OK;
 }
 

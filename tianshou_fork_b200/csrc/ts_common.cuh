@@ -125,6 +125,7 @@ extern int g_tune_gae_flat_ctas;     // pipelined ranges: CTAs per SM (0 auto, 1
 extern int g_tune_gae_flat_stages;   // pipelined ranges: stages of the ring (0 auto, 2..6)
 extern int g_tune_segtree_max_ctas;  // CTAs of the cooperative tree update (<= 148)
 extern int g_tune_per_cluster;       // PER sampling cluster: 0 auto, 8 (x512 threads) or 16 (x256)
+extern int g_tune_segtree_ranged;  // 1 (default): per-CTA leaf ranges with a shared-memory table; 0: tiered
 extern int g_tune_segtree_group;  // 128 (default) or 256 nodes per warp-rebuilt group
 
 }  // namespace ts
