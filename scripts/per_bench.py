@@ -104,6 +104,11 @@ def main():
         timed(f"sample(cluster={cl})", sample)
     L.check(lib.ts_tune_set(b"per_cluster", 0), "tune")
     timed("sample+update", lambda r, s: (sample(r, s), update(r, s)))
+    for pdl in (0, 1):
+        L.check(lib.ts_tune_set(b"pdl", pdl), "tune")
+        timed(f"update(pdl={pdl})", update)
+        timed(f"sample(pdl={pdl})", sample)
+        timed(f"sample+update(pdl={pdl})", lambda r, s: (sample(r, s), update(r, s)))
     u2 = u.clone()
     timed("copy+prefix_idx", lambda r, s: (u2[r].copy_(u[r]), prefix_on(u2, r, s)))
     assert int(err.item()) == 0, int(err.item())

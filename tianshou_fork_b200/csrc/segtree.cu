@@ -597,6 +597,12 @@ segtree_update_ranged(double* __restrict__ tree, int64_t size, int lg_bound, int
     const bool tracks_prio = PERF32 || vs.mode == VM_PER_F64;
     constexpr int64_t kPass = (int64_t)kRangeUnroll * RANGE_NT;
 
+    pdl_launch_dependents();
+    for (int i = tid; i < L / 2; i += RANGE_NT)
+        reinterpret_cast<ulonglong2*>(s_tab)[i] = make_ulonglong2(0ull, 0ull);
+    if (tid < 64) s_touched[tid] = 0u;
+    if (tid < 2) s_n[tid] = 0u;
+    pdl_wait();  // nothing above touches global memory
     phase_mark(0);
     cta_mark(0);
     // warp 0: this range's group roots as they are now; the untouched ones are needed at the end
@@ -607,10 +613,6 @@ segtree_update_ranged(double* __restrict__ tree, int64_t size, int lg_bound, int
         old_root0 = __ldcg(tree + groot0 + lane * gper);
         if (gper == 2) old_root1 = __ldcg(tree + groot0 + lane * gper + 1);
     }
-    for (int i = tid; i < L / 2; i += RANGE_NT)
-        reinterpret_cast<ulonglong2*>(s_tab)[i] = make_ulonglong2(0ull, 0ull);
-    if (tid < 64) s_touched[tid] = 0u;
-    if (tid < 2) s_n[tid] = 0u;
     __syncthreads();
     phase_mark(6);
 
@@ -934,12 +936,20 @@ int32_t update_impl(double* tree, int64_t size, int64_t bound, const int64_t* in
             attr_done = true;
         }
         const double* prio_c = vs.prio;
-        if (vs.mode == VM_PER_F32)
-            segtree_update_ranged<true><<<ctas, RANGE_NT, smem, st>>>(
-                tree, size, lg, lg_range, index, vs, M, counter, err_flag, pub, prio_c);
-        else
-            segtree_update_ranged<false><<<ctas, RANGE_NT, smem, st>>>(
-                tree, size, lg, lg_range, index, vs, M, counter, err_flag, pub, prio_c);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(ctas);
+        cfg.blockDim = dim3(RANGE_NT);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = g_tune_pdl ? 1 : 0;
+        auto kern = vs.mode == VM_PER_F32 ? segtree_update_ranged<true> : segtree_update_ranged<false>;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tree, size, lg, lg_range, index, vs, M,
+                                           counter, err_flag, pub, prio_c);
+        if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; (void)cudaGetLastError(); return TS_ERR_CUDA; }
         return check_launch();
     }
     if (M <= kSmallM && bound > kDenseBound) {
@@ -1112,9 +1122,12 @@ __device__ __forceinline__ double cluster_max(double m, double* s_warp, double* 
         if (tid == 0) *s_cta = m;
     }
     cluster_sync_all();  // every CTA's maximum is published
-    m = 0.0;
+    // lane r reads CTA r's maximum (one remote read per lane, in parallel), then a warp reduction
     const uint32_t nrank = cluster_nctarank();
-    for (uint32_t r = 0; r < nrank; ++r) m = fmax(m, dsmem_ld_f64(s_cta, r));
+    const uint32_t lane = (uint32_t)tid & 31u;
+    m = lane < nrank ? dsmem_ld_f64(s_cta, lane) : 0.0;
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, d));
     cluster_sync_all();  // nobody leaves (or overwrites s_cta) while peers still read it
     return m;
 }
@@ -1148,7 +1161,8 @@ struct ShardInfo {
     double* const* peer_slots;           // P2P mode: device array of the G ranks' slot buffers
     unsigned long long* state;           // P2P mode: {records published, samples drawn} by this rank
 };
-template <bool SAMPLE, int NT>
+// SHARD: 0 = one GPU (no exchange code in the instantiation at all), 1 = NCCL mode, 2 = P2P mode
+template <bool SAMPLE, int NT, int SHARD>
 __global__ void __launch_bounds__(NT)
 per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg_bound,
                           const double* __restrict__ u, int64_t M,
@@ -1161,8 +1175,10 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
     __shared__ double s_cta;
     const int tid = threadIdx.x;
     __shared__ double s_gext[2 * kMaxShards];  // max_prio | min_prio of every rank
-    const bool p2p = sh.slots != nullptr;
-    const bool sharded = sh.roots3 != nullptr || p2p;
+    constexpr bool p2p = SHARD == 2;
+    constexpr bool sharded = SHARD != 0;
+    pdl_launch_dependents();
+    pdl_wait();  // the tree and the priorities come from the kernel before
     const int G = sharded ? sh.G : 1;
     int cached = 0;
     double total = 0.0;
@@ -1296,15 +1312,15 @@ per_normalize_kernel(double* __restrict__ weight, int64_t M, const double* __res
 using namespace ts;
 
 // one cluster handles the whole batch
-template <bool SAMPLE>
-static int32_t launch_per_cluster(const double* tree, int64_t bound, int lg, const double* u,
-                                  int64_t M, const double* prio, double beta, int weight_norm,
-                                  int64_t* idx, double* weight, int32_t* err_flag,
-                                  ShardInfo sh, cudaStream_t st) {
+template <bool SAMPLE, int SHARD>
+static int32_t launch_per_cluster_mode(const double* tree, int64_t bound, int lg, const double* u,
+                                       int64_t M, const double* prio, double beta,
+                                       int weight_norm, int64_t* idx, double* weight,
+                                       int32_t* err_flag, ShardInfo sh, cudaStream_t st) {
     // 16 CTAs x 256 threads spreads a large batch over twice the SMs (7.4 vs 8.7 us at 4096
     // queries); it is an opt-in cluster size, so it is used only where the device can place it.
     static int wide_ok = -1;  // per instantiation
-    auto kern16 = per_weight_cluster_kernel<SAMPLE, 256>;
+    auto kern16 = per_weight_cluster_kernel<SAMPLE, 256, SHARD>;
     if (wide_ok < 0) {
         wide_ok = 0;
         if (cudaFuncSetAttribute(kern16, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) ==
@@ -1325,22 +1341,39 @@ static int32_t launch_per_cluster(const double* tree, int64_t bound, int lg, con
         (void)cudaGetLastError();
     }
     const bool wide = wide_ok == 1 && (g_tune_per_cluster == 16 || (g_tune_per_cluster == 0 && M > 1024));
-    auto kern = wide ? kern16 : per_weight_cluster_kernel<SAMPLE, 512>;
+    auto kern = wide ? kern16 : per_weight_cluster_kernel<SAMPLE, 512, SHARD>;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(wide ? 16 : 8);
     cfg.blockDim = dim3(wide ? 256 : 512);
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = wide ? 16 : 8;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = g_tune_pdl ? 2 : 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tree, bound, lg, u, M, prio, beta, weight_norm,
                                        idx, weight, err_flag, sh);
     if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; (void)cudaGetLastError(); return TS_ERR_CUDA; }
     return check_launch();
+}
+
+template <bool SAMPLE>
+static int32_t launch_per_cluster(const double* tree, int64_t bound, int lg, const double* u,
+                                  int64_t M, const double* prio, double beta, int weight_norm,
+                                  int64_t* idx, double* weight, int32_t* err_flag,
+                                  ShardInfo sh, cudaStream_t st) {
+    if (sh.slots != nullptr)
+        return launch_per_cluster_mode<SAMPLE, 2>(tree, bound, lg, u, M, prio, beta, weight_norm,
+                                                  idx, weight, err_flag, sh, st);
+    if (sh.roots3 != nullptr)
+        return launch_per_cluster_mode<SAMPLE, 1>(tree, bound, lg, u, M, prio, beta, weight_norm,
+                                                  idx, weight, err_flag, sh, st);
+    return launch_per_cluster_mode<SAMPLE, 0>(tree, bound, lg, u, M, prio, beta, weight_norm, idx,
+                                              weight, err_flag, sh, st);
 }
 
 extern "C" int32_t ts_segtree_update(double* tree, int64_t size, int64_t bound,

@@ -62,6 +62,17 @@ __device__ __forceinline__ uint2 ld_stream(const uint2* p) { return __ldcs(p); }
 __device__ __forceinline__ void st_stream(float4* p, float4 v) { __stcs(p, v); }
 __device__ __forceinline__ void st_stream(double2* p, double2 v) { __stcs(p, v); }
 
+// ---- programmatic dependent launch (griddepcontrol) ---------------------------------------------
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start while its
+// predecessor in the stream is still running: launch latency and the prologue that touches no
+// global data overlap the predecessor's tail.  pdl_wait() returns once the predecessor grid has
+// completed and its writes are visible; every global read of data an earlier kernel may have
+// produced comes after it.  Both are no-ops under an ordinary launch.
+__device__ __forceinline__ void pdl_launch_dependents() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- sm_100a bulk-copy engine (TMA, 1-D form) + mbarrier -------------------------------------
 // cp.async.bulk moves a contiguous run of bytes global<->shared without touching registers;
 // loads complete on an mbarrier (transaction bytes), stores are tracked by bulk groups.
@@ -126,6 +137,7 @@ extern int g_tune_gae_flat_stages;   // pipelined ranges: stages of the ring (0 
 extern int g_tune_segtree_max_ctas;  // CTAs of the cooperative tree update (<= 148)
 extern int g_tune_per_cluster;       // PER sampling cluster: 0 auto, 8 (x512 threads) or 16 (x256)
 extern int g_tune_segtree_ranged;  // 1 (default): per-CTA leaf ranges with a shared-memory table; 0: tiered
+extern int g_tune_pdl;  // 1 (default): PER kernels are launched with programmatic stream serialization
 extern int g_tune_segtree_group;  // 128 (default) or 256 nodes per warp-rebuilt group
 
 }  // namespace ts
