@@ -55,8 +55,17 @@ typedef void* ts_stream_t; /* cudaStream_t */
 int32_t ts_version(void);
 const char* ts_error_string(int32_t code);
 int32_t ts_last_cuda_error(void);
-/* Kernel-selection knobs for benchmarking (process-wide, not part of the reference-facing
- * surface).  Keys: "gae_rows_variant" (0 = automatic; see csrc/gae.cu:kRowsVariants). */
+/* Kernel-selection knobs for benchmarking and for the tests that cover every kernel
+ * (process-wide, not part of the reference-facing surface).  Keys:
+ *   "gae_rows_variant"  0 = automatic, else an entry of csrc/gae.cu:kRowsVariants
+ *   "gae_flat_variant"  0 = automatic, 1 = decoupled look-back, 2 = pipelined ranges
+ *   "gae_flat_ctas"     pipelined ranges: CTAs per SM (0 = automatic = 3, 1..3)
+ *   "gae_flat_stages"   pipelined ranges: stages of the bulk-copy ring (0 = automatic = 2, 2..6)
+ *   "segtree_ranged"    1 (default) = ranged update kernel for trees <= 2^20 leaves, 0 = tiered
+ *   "segtree_group"     tiered kernel: 128 (default) or 256 nodes per warp-rebuilt group
+ *   "segtree_max_ctas"  tiered kernel: CTAs of the cooperative launch (<= 148)
+ *   "per_cluster"       PER sampling cluster: 0 = automatic, 8 (x512 threads) or 16 (x256)
+ *   "pdl"               1 (default) = PER kernels use programmatic dependent launch, 0 = off */
 int32_t ts_tune_set(const char* key, int64_t value);
 /* Debug: globaltimer ns at the phase boundaries of the most recent small-batch tree update
  * (synchronises the device; host buffer of 8 uint64: start, batch scanned, groups rebuilt,
@@ -164,9 +173,11 @@ int32_t ts_nstep_combine(const void* target_q, int32_t q_dtype, int64_t bsz, int
  * afterwards (one tree, one stream at a time): `stamp` is uint32[size], 16-byte aligned
  * (last-writer-wins arbitration of duplicated indices, segtree.py:40-49; entries carry a
  * per-call epoch so they never need resetting), `counter` is uint32[4] (grid-barrier
- * arrivals, epoch).  Batches of up to 16383 indices on trees of more than 4096 leaves run as
- * ONE cooperative launch (<= 148 CTAs that wait on each other: do not run two of them
- * concurrently on one device from different streams). */
+ * arrivals, epoch).  Batches of up to 16383 indices run as ONE launch: on trees of 4097 ..
+ * 2^20 leaves an ordinary launch whose CTAs never wait on each other (only counter[0] is
+ * used: "last CTA out finishes the top"); on larger trees a cooperative launch (<= 148 CTAs
+ * that wait on each other: do not run two of them concurrently on one device from
+ * different streams). */
 /* tree[index[j]] = value[j] for j < M (M < 2^31), then every ancestor recomputed bottom-up.
  * value is f32 or f64 (cast on store, segtree.py:91-92); value_stride 0 broadcasts value[0].
  * index outside [0,size) sets TS_FLAG_INDEX_RANGE in *err_flag and that item is skipped. */
