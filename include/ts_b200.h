@@ -65,7 +65,9 @@ int32_t ts_last_cuda_error(void);
  *   "segtree_group"     tiered kernel: 128 (default) or 256 nodes per warp-rebuilt group
  *   "segtree_max_ctas"  tiered kernel: CTAs of the cooperative launch (<= 148)
  *   "per_cluster"       PER sampling cluster: 0 = automatic, 8 (x512 threads) or 16 (x256)
- *   "pdl"               1 (default) = PER kernels use programmatic dependent launch, 0 = off */
+ *   "gae_balance"       1 = persistent GAE grids sized for equal work per CTA (default 0)
+ *   "pdl"               1 (default) = PER and GAE rows kernels use programmatic dependent
+ *                       launch, 0 = off */
 int32_t ts_tune_set(const char* key, int64_t value);
 /* Debug: globaltimer ns at the phase boundaries of the most recent small-batch tree update
  * (synchronises the device; host buffer of 8 uint64: start, batch scanned, groups rebuilt,

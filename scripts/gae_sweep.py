@@ -22,6 +22,8 @@ def main():
     p.add_argument("--horizon", type=int, default=2048)
     p.add_argument("--variants", default="1,2,3,4,5,6,7,8,9")
     p.add_argument("--iters", type=int, default=500)
+    p.add_argument("--knobs", default="", help="semicolon list of key=value,... sets to A/B, "
+                   "e.g. 'gae_balance=0,pdl=0;gae_balance=1,pdl=0;gae_balance=1,pdl=1'")
     a = p.parse_args()
     E, T = a.streams, a.horizon
     lib = L.lib()
@@ -38,8 +40,12 @@ def main():
 
     ref = None
     out = []
-    for v in [int(x) for x in a.variants.split(",")]:
+    knob_sets = [k for k in a.knobs.split(";") if k] or [""]
+    for v, knobs in [(int(x), k) for x in a.variants.split(",") for k in knob_sets]:
         L.check(lib.ts_tune_set(b"gae_rows_variant", v), "tune")
+        for kv in [x for x in knobs.split(",") if x]:
+            key, val = kv.split("=")
+            L.check(lib.ts_tune_set(key.encode(), int(val)), "tune " + key)
         adv.fill_(float("nan"))
         for _ in range(10):
             step()
@@ -57,7 +63,7 @@ def main():
             torch.cuda.synchronize()
             best = min(best, e0.elapsed_time(e1) * 1e3 / a.iters)
         gbs = E * T * 21 / (best * 1e-6) / 1e9
-        out.append({"variant": v, "us": best, "alg_GBps": gbs, "frac": gbs / peak,
+        out.append({"variant": v, "knobs": knobs, "us": best, "alg_GBps": gbs, "frac": gbs / peak,
                     "max_abs_diff_vs_first": err})
         print(json.dumps(out[-1]), flush=True)
     L.check(lib.ts_tune_set(b"gae_rows_variant", 0), "tune")

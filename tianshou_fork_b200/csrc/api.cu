@@ -10,6 +10,7 @@ int g_tune_gae_flat_stages = 0;
 int g_tune_segtree_group = 128;
 int g_tune_segtree_ranged = 1;
 int g_tune_pdl = 1;
+int g_tune_gae_balance = 0;
 int g_tune_per_cluster = 0;
 int g_tune_segtree_max_ctas = 148;
 }
@@ -56,6 +57,10 @@ extern "C" int32_t ts_tune_set(const char* key, int64_t value) {
     }
     if (strcmp(key, "segtree_ranged") == 0 && (value == 0 || value == 1)) {
         ts::g_tune_segtree_ranged = (int)value;
+        return TS_OK;
+    }
+    if (strcmp(key, "gae_balance") == 0 && (value == 0 || value == 1)) {
+        ts::g_tune_gae_balance = (int)value;
         return TS_OK;
     }
     if (strcmp(key, "pdl") == 0 && (value == 0 || value == 1)) {

@@ -372,11 +372,13 @@ gae_rows_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
         if (++p_stage == stages) p_stage = 0;
     };
 
+    pdl_launch_dependents();
     if (tid == 0) {
         for (int s = 0; s < stages; ++s) mbar_init(bar0 + 8u * s, 1u);
         fence_mbar_init();
     }
     __syncthreads();
+    pdl_wait();  // inputs may come from the kernel before (the critic's forward pass)
     if (tid == 0)
         while (p_it < stages && p_it < ntiles) issue();
 
@@ -1082,6 +1084,35 @@ constexpr RowsVariant kRowsVariants[] = {
 constexpr int kNumRowsVariants = (int)(sizeof(kRowsVariants) / sizeof(kRowsVariants[0]));
 constexpr int kRowsAutoTma = 5;  // 256 threads x 2 stages x 3 CTAs/SM: best of the C2 sweep (profiles/)
 
+// Persistent grid for `units` equal work items on at most `cap` co-resident CTAs.  Optional
+// balancing ("gae_balance"): with w = ceil(units / cap) items per CTA, ceil(units / w) CTAs all
+// get w or w - 1 items (4096 rows: 410 CTAs x 10 instead of 444 CTAs with 9 or 10).  Measured
+// SLOWER at C2 (32.9 vs 31.7 us): the extra 34 CTAs' loads in flight are worth more than the
+// even finish, so the default keeps the grid at the residency cap.
+inline unsigned balanced_grid(int64_t units, int64_t cap) {
+    if (units <= cap) return (unsigned)(units < 1 ? 1 : units);
+    if (!g_tune_gae_balance) return (unsigned)cap;
+    const int64_t w = (units + cap - 1) / cap;
+    return (unsigned)((units + w - 1) / w);
+}
+
+// launch with programmatic stream serialization when enabled (see ts_common.cuh)
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kern)(KArgs...), unsigned grid, unsigned block, size_t smem,
+                       cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = g_tune_pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 template <typename RewT, typename InT, typename OutT, int NT>
 int32_t launch_rows_tma(const void* rew, const void* v_s, const void* v_next,
                         const uint8_t* term, const uint8_t* trunc, int64_t E, int64_t T,
@@ -1099,14 +1130,14 @@ int32_t launch_rows_tma(const void* rew, const void* v_s, const void* v_next,
         if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
         attr_bytes = smem;
     }
-    const int64_t cap = (int64_t)kNumSMs * ctas_per_sm;
-    const unsigned grid = (unsigned)(E < cap ? E : cap);
+    const unsigned grid = balanced_grid(E, (int64_t)kNumSMs * ctas_per_sm);
     GlPow glp;
     glp.p[0] = 1.0;
     for (int j = 1; j <= VEC; ++j) glp.p[j] = glp.p[j - 1] * (gamma * lam);
-    kern<<<grid, NT, smem, stream>>>((const RewT*)rew, (const InT*)v_s, (const InT*)v_next, term,
-                                     trunc, (int)E, T, bs, vs, gamma, glp, (OutT*)adv,
-                                     (OutT*)ret, stages);
+    cudaError_t e = launch_pdl(kern, grid, NT, smem, stream, (const RewT*)rew, (const InT*)v_s,
+                               (const InT*)v_next, term, trunc, (int)E, T, bs, vs, gamma, glp,
+                               (OutT*)adv, (OutT*)ret, stages);
+    if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; (void)cudaGetLastError(); return TS_ERR_CUDA; }
     return check_launch();
 }
 
@@ -1179,8 +1210,7 @@ int32_t launch_flat_tma(const void* rew, const void* v_s, const void* v_next, co
     }
     const int ctas_per_sm = fits[stages] < want ? fits[stages] : want;
     const int64_t tiles = ((N & ~(int64_t)15) + L::TILE - 1) / L::TILE;
-    const int64_t cap = (int64_t)kNumSMs * ctas_per_sm;
-    const unsigned grid = (unsigned)(tiles < 1 ? 1 : (tiles < cap ? tiles : cap));
+    const unsigned grid = balanced_grid(tiles, (int64_t)kNumSMs * ctas_per_sm);
     GlPow glp;
     glp.p[0] = 1.0;
     for (int j = 1; j <= VEC; ++j) glp.p[j] = glp.p[j - 1] * (gamma * lam);
