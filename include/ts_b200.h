@@ -114,7 +114,9 @@ int32_t ts_gae_rows(const void* rew, const void* v_s, const void* v_s_next,
  *                               (output of ts_unfinished_index).
  *   offset[B+1], sub_size     : sub-buffer layout (_extend_offset, manager.py:38);
  *                               sub_size > 0 means equal sub-buffers (k = idx / sub_size).
- * workspace: ts_gae_flat_workspace_bytes(N) bytes, 16-byte aligned; contents are scratch.
+ * workspace: ts_gae_flat_workspace_bytes(N) bytes, 16-byte aligned, zero-initialised ONCE by
+ *   the caller and opaque afterwards (one stream at a time): the pipelined kernel keeps a call
+ *   count in it that tags its inter-CTA flags, so no call has to clear anything.
  */
 size_t ts_gae_flat_workspace_bytes(int64_t N);
 int32_t ts_gae_flat(const void* rew, const void* v_s, const void* v_s_next,

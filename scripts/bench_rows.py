@@ -113,7 +113,7 @@ def row_gae_flat():
         adv, ret = torch.empty(n, device=DEV), torch.empty(n, device=DEV)
         lib = L.lib()
         nbytes = lib.ts_gae_flat_workspace_bytes(n)
-        ws = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
+        ws = torch.zeros(nbytes, dtype=torch.uint8, device=DEV)
 
         def go(with_idx):
             L.check(lib.ts_gae_flat(L.ptr(rew), L.ptr(vs), L.ptr(vn), L.ptr(term), L.ptr(trunc),
@@ -140,7 +140,7 @@ def row_gae_flat_sweep():
         trunc = torch.zeros(n, dtype=torch.uint8, device=DEV)
         adv, ret = torch.empty(n, device=DEV), torch.empty(n, device=DEV)
         nbytes = lib.ts_gae_flat_workspace_bytes(n)
-        ws = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
+        ws = torch.zeros(nbytes, dtype=torch.uint8, device=DEV)
 
         def go(stream=None):
             L.check(lib.ts_gae_flat(L.ptr(rew), L.ptr(vs), L.ptr(vn), L.ptr(term), L.ptr(trunc),

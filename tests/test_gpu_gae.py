@@ -150,7 +150,7 @@ def test_flat_kernel_lookback_vs_oracle(N, p_end, variant):
     adv = torch.empty(N, dtype=torch.float64, device="cuda")
     ret = torch.empty(N, dtype=torch.float64, device="cuda")
     nbytes = L.lib().ts_gae_flat_workspace_bytes(N)
-    ws = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    ws = torch.zeros(nbytes, dtype=torch.uint8, device="cuda")
     for _ in range(3):  # workspace reuse across calls
         L.check(L.lib().ts_gae_flat(*[L.ptr(t) for t in g], None, None, None, None, 0, 0, N,
                                     0.99, 0.95, 1, 0, 1, L.ptr(adv), L.ptr(ret), L.ptr(ws),
@@ -179,11 +179,24 @@ def test_flat_kernel_neighbour_chain(gl):
     adv = torch.empty(N, dtype=torch.float64, device="cuda")
     ret = torch.empty(N, dtype=torch.float64, device="cuda")
     nbytes = L.lib().ts_gae_flat_workspace_bytes(N)
-    ws = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
-    L.check(L.lib().ts_gae_flat(*[L.ptr(t) for t in g], None, None, None, None, 0, 0, N, gamma,
-                                lam, 1, 0, 1, L.ptr(adv), L.ptr(ret), L.ptr(ws), nbytes,
-                                L.stream()), "ts_gae_flat")
+    ws = torch.zeros(nbytes, dtype=torch.uint8, device="cuda")
+    def call():
+        L.check(L.lib().ts_gae_flat(*[L.ptr(t) for t in g], None, None, None, None, 0, 0, N,
+                                    gamma, lam, 1, 0, 1, L.ptr(adv), L.ptr(ret), L.ptr(ws),
+                                    nbytes, L.stream()), "ts_gae_flat")
+
+    call()
     assert _close(adv.cpu().numpy(), ref_adv, 1e-9)
+    # The same workspace again with other rewards, then through the look-back kernel and back:
+    # head values of an earlier call must never be taken for this call's (flags carry a call tag).
+    for variant in (2, 2, 1, 2):
+        rew2 = rng.standard_normal(N)
+        g[0] = d(rew2)
+        L.check(L.lib().ts_tune_set(b"gae_flat_variant", variant), "tune")
+        adv.fill_(float("nan"))
+        call()
+        L.check(L.lib().ts_tune_set(b"gae_flat_variant", 0), "tune")
+        assert _close(adv.cpu().numpy(), orc.gae_return(v_s, v_n, rew2, z, gamma, lam), 1e-9)
 
 
 @pytest.mark.parametrize("B,cap,rotate", [(37, 1000, True), (700, 5, False), (300, 13, False),
@@ -215,7 +228,7 @@ def test_flat_kernel_with_indices_vs_oracle(variant, B, cap, rotate):
     adv = torch.empty(N, dtype=torch.float32, device="cuda")
     ret = torch.empty(N, dtype=torch.float32, device="cuda")
     nbytes = L.lib().ts_gae_flat_workspace_bytes(N)
-    ws = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    ws = torch.zeros(nbytes, dtype=torch.uint8, device="cuda")
     g = [d(rew), d(v_s), d(v_n), d(term.view(np.uint8)), d(trunc.view(np.uint8)), d(indices),
          d(buf_term.view(np.uint8)), d(unfinished), offset]
     for sub in (cap, 0):  # equal sub-buffers by division, then by binary search over offset

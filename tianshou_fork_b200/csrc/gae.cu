@@ -630,7 +630,7 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
                     const uint8_t* __restrict__ trunc, const FlatGather g, int64_t N,
                     double gamma, const GlPow glp, OutT* __restrict__ adv,
                     OutT* __restrict__ ret, int stages, double* __restrict__ heads,
-                    unsigned int* __restrict__ head_flags) {
+                    unsigned int* __restrict__ head_flags, unsigned int* __restrict__ sync) {
     using L = FlatTmaLayout<RewT, InT, OutT, NT, HAS_IDX>;
     using R = RowsTmaLayout<RewT, InT, OutT, NT>;
     constexpr int TILE = L::TILE;
@@ -687,12 +687,31 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     double carry = 0.0;
     const bool working = ntiles > 0 || blockIdx.x == 0;
     const int64_t p_ahead = k_hi * TILE;
+    pdl_launch_dependents();
+    // sync[1] = calls completed on this workspace, sync[2] = CTAs of this call that are done.
+    // Head flags carry the call's tag, so nothing has to be cleared between calls (and CUDA-graph
+    // replays, which cannot change an argument, still get a fresh tag each time).
+    unsigned int tag = 0u;
     if (tid == 0) {
         for (int s = 0; s < stages; ++s) mbar_init(bar0 + 8u * s, 1u);
         fence_mbar_init();
+    }
+    pdl_wait();  // inputs and the workspace may come from the kernel before
+    if (tid == 0) {
         while (p_it < stages && p_it < ntiles) issue();
+        tag = (__ldcg(sync + 1) + 1u) | 0x80000000u;
     }
     __syncthreads();
+    // a CTA's last act: the one that finishes last advances the call count
+    auto leave = [&]() {
+        if (tid == 0) {
+            __threadfence();
+            if (atomicAdd(sync + 2, 1u) == gridDim.x - 1u) {
+                sync[1] = tag & 0x7fffffffu;
+                sync[2] = 0u;
+            }
+        }
+    };
     FlatWindow<RewT, InT> W;
     if (working) {
         if (blockIdx.x == 0) {
@@ -757,7 +776,7 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
                         do {
                             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];"
                                          : "=r"(f) : "l"(head_flags + blockIdx.x - 1) : "memory");
-                        } while (f == 0u);
+                        } while (f != tag);
                         Xc = __ldcg(heads + blockIdx.x - 1);
                     }
                     s_carry = Xc;
@@ -772,8 +791,9 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
         if (blockIdx.x == 0 && tid == 0) {
             heads[0] = carry;
             __threadfence();
-            *(volatile unsigned int*)head_flags = 1u;
+            *(volatile unsigned int*)head_flags = tag;
         }
+        leave();
         return;
     }
 
@@ -898,9 +918,10 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     if (tid == 0) {
         heads[blockIdx.x] = carry;  // advantage of this range's first step, for a waiting neighbour
         __threadfence();
-        *(volatile unsigned int*)(head_flags + blockIdx.x) = 1u;
+        *(volatile unsigned int*)(head_flags + blockIdx.x) = tag;
         bulk_wait0();
     }
+    leave();
 }
 
 // ============================================================================================
@@ -909,7 +930,8 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
 // depends on) always started before it: ticket 0 is the LAST tile of the sequence.
 // ============================================================================================
 struct FlatWorkspace {
-    unsigned int* ticket;  // [4] (padding)
+    size_t clear_bytes;    // look-back kernel: ticket + status are zeroed before every call
+    unsigned int* ticket;  // [4]: look-back ticket | pipelined ranges: calls done, CTAs done
     unsigned int* status;  // [tiles] 0 = nothing, 1 = aggregate published, 2 = value published
     double* aggP;          // [tiles]
     double* aggX;          // [tiles]
@@ -1214,9 +1236,10 @@ int32_t launch_flat_tma(const void* rew, const void* v_s, const void* v_next, co
     GlPow glp;
     glp.p[0] = 1.0;
     for (int j = 1; j <= VEC; ++j) glp.p[j] = glp.p[j - 1] * (gamma * lam);
-    kern<<<grid, NT, smem, stream>>>((const RewT*)rew, (const InT*)v_s, (const InT*)v_next, term,
-                                     trunc, g, N, gamma, glp, (OutT*)adv, (OutT*)ret, stages,
-                                     ws.aggP, ws.status);
+    cudaError_t e = launch_pdl(kern, grid, NT, smem, stream, (const RewT*)rew, (const InT*)v_s,
+                               (const InT*)v_next, term, trunc, g, N, gamma, glp, (OutT*)adv,
+                               (OutT*)ret, stages, ws.aggP, ws.status, ws.ticket);
+    if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; (void)cudaGetLastError(); return TS_ERR_CUDA; }
     return check_launch();
 }
 
@@ -1241,6 +1264,10 @@ int32_t launch_flat(const void* rew, const void* v_s, const void* v_next, const 
                                                           lam, adv, ret, ws, stream);
         return launch_flat_tma<RewT, InT, OutT, false>(rew, v_s, v_next, term, trunc, g, N, gamma,
                                                        lam, adv, ret, ws, stream);
+    }
+    {
+        cudaError_t e = cudaMemsetAsync(ws.ticket, 0, ws.clear_bytes, stream);
+        if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
     }
     gae_flat_kernel<RewT, InT, OutT><<<(unsigned)flat_tiles(N), FLAT_NT, 0, stream>>>(
         (const RewT*)rew, (const InT*)v_s, (const InT*)v_next, term, trunc, indices, buf_term,
@@ -1336,8 +1363,7 @@ extern "C" int32_t ts_gae_flat(const void* rew, const void* v_s, const void* v_s
     ws.aggP = (double*)(w + 16 + status_bytes);
     ws.aggX = ws.aggP + tiles;
     ws.value = ws.aggX + tiles;
-    cudaError_t e = cudaMemsetAsync(w, 0, 16 + status_bytes, st);
-    if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
+    ws.clear_bytes = 16 + status_bytes;
 #define TS_GO(R, I, O)                                                                        \
     launch_flat<R, I, O>(rew, v_s, v_s_next, terminated, truncated, indices, buf_terminated, \
                          unfinished, offset, B, sub_size, N, gamma, gae_lambda, adv, ret, ws, \

@@ -55,7 +55,8 @@ def _workspace(nbytes: int, device: torch.device) -> torch.Tensor:
     key = (device.index or 0, torch.cuda.current_stream().cuda_stream)
     ws = _ws_cache.get(key)
     if ws is None or ws.numel() < nbytes:
-        ws = torch.empty(max(nbytes, 1 << 16), dtype=torch.uint8, device=device)
+        # zero-initialised once: the flat kernel keeps its call count in it (include/ts_b200.h)
+        ws = torch.zeros(max(nbytes, 1 << 16), dtype=torch.uint8, device=device)
         _ws_cache[key] = ws
     return ws
 
