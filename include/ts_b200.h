@@ -299,6 +299,17 @@ int32_t ts_ppo_loss(const float* logp, const float* value, const float* logp_old
 int32_t ts_gather_rows(const void* src, int64_t n_rows, int64_t row_bytes, const int64_t* index,
                        int64_t M, void* out, ts_stream_t stream);
 
+/* Frame-stack gather (ReplayBuffer.get with stack_num > 1, base.py:317-358; Atari-style
+ * save_only_last_obs buffers, atari_dqn.py:135-140): out[j, i, :] = src[g_i, :] with
+ * g_{k-1} = index[j] % total and g_{i-1} = prev(g_i) (episode-aware, manager.py:259-277; one
+ * ring is the B == 1 case), oldest frame first, k = stack_num <= 16.  When out_next is not NULL
+ * the stack ending at next(index[j]) (base.py:378, manager.py:280-297) is written there by the
+ * same launch: k + 1 frames read for 2k written.  Pure byte copy of rows of row_bytes bytes. */
+int32_t ts_gather_stack(const void* src, int64_t row_bytes, const int64_t* index, int64_t M,
+                        int32_t stack_num, const int64_t* offset, int64_t B, int64_t sub_size,
+                        const uint8_t* done, const int64_t* last_index, const int64_t* lengths,
+                        void* out, void* out_next, ts_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -211,6 +211,23 @@ def next_single(index, done, last_index: int, size: int) -> np.ndarray:
     return out
 
 
+def stack_gather(frames, index, stack_num: int, offset, done, last_index, lengths,
+                 from_next: bool = False) -> np.ndarray:
+    """``ReplayBuffer.get(index, key, stack_num)`` (tianshou/data/buffer/base.py:348-354):
+    ``stack = [val[indices]] + stack; indices = self.prev(indices)`` repeated ``stack_num``
+    times, stacked on ``axis = indices.ndim`` (oldest frame first).  ``from_next`` starts
+    from ``next(index)`` (the obs_next of ignore_obs_next buffers, base.py:378)."""
+    frames = np.asarray(frames)
+    idx = _i64(np.asarray(index).reshape(-1))
+    if from_next:
+        idx = next_index(idx, offset, done, last_index, lengths)
+    stack = []
+    for _ in range(stack_num):
+        stack = [frames[idx]] + stack
+        idx = prev_index(idx, offset, done, last_index, lengths)
+    return np.stack(stack, axis=1)
+
+
 class RingState:
     """Bookkeeping of N equal rings inside one contiguous storage.
 

@@ -214,6 +214,70 @@ def row_gather():
         assert torch.equal(out, src[idx])
 
 
+def row_gather_stack():
+    """N2: obs + obs_next frame stacks of an Atari-style buffer (stack 4, 84 x 84 u8 frames,
+    save_only_last_obs + ignore_obs_next): ts_gather_stack (one launch, k + 1 frames read for 2k
+    written) vs the composition of prev / next / row gathers it replaces, and the CPU oracle."""
+    B, cap, k, row = 16, 8192, 4, 84 * 84
+    total = B * cap
+    rng = np.random.default_rng(6)
+    frames_np = rng.integers(0, 256, (total, row)).astype(np.uint8)
+    offset = np.arange(B + 1, dtype=np.int64) * cap
+    lengths = np.full(B, cap, dtype=np.int64)
+    last = (offset[:-1] + rng.integers(0, cap, B)).astype(np.int64)
+    done = rng.random(total) < 1 / 1000
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+    frames, g_off, g_len, g_last, g_done = d(frames_np), d(offset), d(lengths), d(last), \
+        d(done.view(np.uint8))
+    lib = L.lib()
+    for bsz in (32, 256, 4096):
+        idx_np = rng.integers(0, total, bsz)
+        idx = d(idx_np)
+        out = torch.empty(bsz, k, row, dtype=torch.uint8, device=DEV)
+        out_next = torch.empty_like(out)
+
+        def fused(s):
+            L.check(lib.ts_gather_stack(L.ptr(frames), row, L.ptr(idx), bsz, k, L.ptr(g_off), B,
+                                        cap, L.ptr(g_done), L.ptr(g_last), L.ptr(g_len),
+                                        L.ptr(out), L.ptr(out_next), s), "gather_stack")
+
+        tmp = torch.empty(bsz, dtype=torch.int64, device=DEV)
+        tmp2 = torch.empty(bsz, dtype=torch.int64, device=DEV)
+        chain = torch.empty(2, k, bsz, dtype=torch.int64, device=DEV)
+        o2 = torch.empty(2, k, bsz, row, dtype=torch.uint8, device=DEV)
+
+        def composed(s):  # what get() did before: k x (row gather + prev), twice, then a stack
+            for half in range(2):
+                cur = idx
+                if half == 1:
+                    L.check(lib.ts_next_index(L.ptr(idx), bsz, L.ptr(g_off), B, cap, L.ptr(g_done),
+                                              L.ptr(g_last), L.ptr(g_len), L.ptr(tmp2), s), "next")
+                    cur = tmp2
+                for i in range(k - 1, -1, -1):
+                    L.check(lib.ts_gather_rows(L.ptr(frames), total, row, L.ptr(cur), bsz,
+                                               L.ptr(o2[half, i]), s), "rows")
+                    nxt = chain[half, i]
+                    L.check(lib.ts_prev_index(L.ptr(cur), bsz, L.ptr(g_off), B, cap, L.ptr(g_done),
+                                              L.ptr(g_last), L.ptr(g_len), L.ptr(nxt), s), "prev")
+                    cur = nxt
+
+        us = graph_us(fused)
+        cus = graph_us(composed, calls=2)
+        ref = cpu_us(lambda: (orc.stack_gather(frames_np, idx_np, k, offset, done, last, lengths),
+                              orc.stack_gather(frames_np, idx_np, k, offset, done, last, lengths,
+                                               from_next=True)), seconds=1.0)
+        fused(L.stream())
+        torch.cuda.synchronize()
+        want = orc.stack_gather(frames_np, idx_np, k, offset, done, last, lengths, from_next=True)
+        assert np.array_equal(out_next.cpu().numpy(), want)
+        alg = bsz * 4 * k * row  # SURVEY 8d: 2 x 28 224 read + 2 x 28 224 written per sample
+        moved = bsz * (3 * k + 1) * row
+        emit("N2 gather_stack obs+obs_next (graph)", bsz=bsz, k=k, row_bytes=row, us=us,
+             composed_launches_us=cus, cpu_port_us=ref, alg_GBps=alg / us / 1e3,
+             frac_of_measured_peak=alg / us / 1e3 / PEAK, moved_GBps=moved / us / 1e3,
+             moved_frac=moved / us / 1e3 / PEAK, samples_per_s=bsz / us * 1e6)
+
+
 def row_ppo():
     """a11: fused PPO loss forward + backward per minibatch (C3: N = 131 072)."""
     N = 131072
@@ -251,6 +315,6 @@ def row_ppo():
 
 if __name__ == "__main__":
     torch.cuda.set_device(0)
-    which = sys.argv[1:] or ["gae_flat", "nstep_index", "gather", "ppo"]
+    which = sys.argv[1:] or ["gae_flat", "nstep_index", "gather", "gather_stack", "ppo"]
     for w in which:
         globals()["row_" + w]()

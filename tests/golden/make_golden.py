@@ -370,6 +370,70 @@ def gen_ppo(ts, out):
     np.savez_compressed(os.path.join(out, "ppo.npz"), **flat)
 
 
+STACK_SPECS = [
+    # name, n_env, total, steps, stack_num, ragged, frame shape (make_golden.gen_stack)
+    ("atari_like", 4, 80, 13, 4, False, (6,)),
+    ("wrapped", 3, 30, 47, 4, True, (2, 3)),
+    ("deep", 2, 64, 25, 7, False, (4,)),
+]
+
+
+def stack_stream(rng, steps, n_env, ragged, frame_shape, hist):
+    """Add-stream of save_only_last_obs buffers: obs carries `hist` frames, the last is kept."""
+    for _ in range(steps):
+        ids = np.arange(n_env)
+        if ragged:
+            ids = ids[rng.random(n_env) < 0.7]
+            if ids.size == 0:
+                continue
+        m = ids.size
+        term = rng.random(m) < 0.2
+        trunc = (rng.random(m) < 0.1) & ~term
+        yield ids, dict(
+            obs=rng.integers(0, 256, (m, hist) + frame_shape).astype(np.uint8),
+            act=rng.integers(0, 4, m), rew=rng.standard_normal(m), terminated=term,
+            truncated=trunc, info={})
+
+
+def gen_stack(ts, out):
+    """Frame-stack gathers (base.py:317-358, 374-378): buf[q].obs / .obs_next of
+    ignore_obs_next + save_only_last_obs buffers (the Atari layout, atari_dqn.py:135-140),
+    a single ring with saved obs_next, and get() with an explicit stack_num."""
+    from tianshou.data import Batch, ReplayBuffer, VectorReplayBuffer
+
+    flat = {}
+    for i, (name, n_env, total, steps, k, ragged, fshape) in enumerate(STACK_SPECS):
+        rng = np.random.default_rng(700 + i)
+        buf = VectorReplayBuffer(total, n_env, stack_num=k, ignore_obs_next=True,
+                                 save_only_last_obs=True)
+        for ids, d in stack_stream(rng, steps, n_env, ragged, fshape, k):
+            buf.add(Batch(**d), buffer_ids=ids)
+        q = np.concatenate([np.arange(buf.maxsize), rng.integers(0, buf.maxsize, 40)])
+        data = buf[q]
+        flat.update({
+            f"{name}/frames": buf.obs, f"{name}/offset": buf._extend_offset,
+            f"{name}/done": buf.done, f"{name}/last_index": buf.last_index,
+            f"{name}/lengths": buf._lengths, f"{name}/query": q, f"{name}/obs": data.obs,
+            f"{name}/obs_next": data.obs_next,
+            f"{name}/get2": buf.get(q, "obs", stack_num=2),
+        })
+    # single ring, float frames, obs_next saved (both keys go through get())
+    rng = np.random.default_rng(750)
+    buf = ReplayBuffer(16, stack_num=3)
+    for _ in range(41):
+        term = rng.random() < 0.2
+        buf.add(Batch(obs=rng.standard_normal(5).astype(np.float32), act=0,
+                      rew=rng.standard_normal(), terminated=term,
+                      truncated=(not term) and rng.random() < 0.1,
+                      obs_next=rng.standard_normal(5).astype(np.float32), info={}))
+    q = np.arange(len(buf))
+    data = buf[q]
+    flat.update({"ring/frames": buf.obs, "ring/frames_next": buf.obs_next, "ring/done": buf.done,
+                 "ring/last_index": buf.last_index, "ring/size": np.array(len(buf)),
+                 "ring/query": q, "ring/obs": data.obs, "ring/obs_next": data.obs_next})
+    np.savez_compressed(os.path.join(out, "stack.npz"), **flat)
+
+
 def main():
     ts = import_reference()
     import numba
@@ -380,6 +444,7 @@ def main():
     gen_segtree(ts, HERE)
     gen_per(ts, HERE)
     gen_ppo(ts, HERE)
+    gen_stack(ts, HERE)
     with open(os.path.join(HERE, "versions.json"), "w") as f:
         json.dump({"tianshou": ts.__version__, "numpy": np.__version__,
                    "numba": numba.__version__, "reference": REF}, f, indent=1)

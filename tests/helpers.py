@@ -64,3 +64,38 @@ def c2_rollout(E, T, seed=0, p_term=1 / 200, p_trunc=1 / 1000):
     term = rng.random((E, T)) < p_term
     trunc = (rng.random((E, T)) < p_trunc) & ~term
     return rew, v_s, v_next, term, trunc
+
+
+STACK_SPECS = [
+    # name, n_env, total, steps, stack_num, ragged, frame shape (make_golden.gen_stack)
+    ("atari_like", 4, 80, 13, 4, False, (6,)),
+    ("wrapped", 3, 30, 47, 4, True, (2, 3)),
+    ("deep", 2, 64, 25, 7, False, (4,)),
+]
+
+
+def stack_stream(rng, steps, n_env, ragged, frame_shape, hist):
+    """The add-stream of make_golden.stack_stream, in the same RNG order."""
+    for _ in range(steps):
+        ids = np.arange(n_env)
+        if ragged:
+            ids = ids[rng.random(n_env) < 0.7]
+            if ids.size == 0:
+                continue
+        m = ids.size
+        term = rng.random(m) < 0.2
+        trunc = (rng.random(m) < 0.1) & ~term
+        yield ids, dict(
+            obs=rng.integers(0, 256, (m, hist) + frame_shape).astype(np.uint8),
+            act=rng.integers(0, 4, m), rew=rng.standard_normal(m), terminated=term,
+            truncated=trunc, info={})
+
+
+def random_rings(rng, B, cap, p_done=0.02):
+    """A plausible manager state: (offset[B+1], done[B*cap], last_index[B], lengths[B])."""
+    offset = np.arange(B + 1, dtype=np.int64) * cap
+    lengths = rng.integers(cap // 2, cap + 1, B).astype(np.int64)
+    lengths[0] = cap
+    last = (offset[:-1] + rng.integers(0, lengths)).astype(np.int64)
+    done = rng.random(B * cap) < p_done
+    return offset, done, last, lengths

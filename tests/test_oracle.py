@@ -256,3 +256,22 @@ def test_golden_ppo_loss():
         if not norm_adv:  # with norm_adv autograd also flows through mean/std: adv is an input
             assert np.allclose(dlogp, c["dlogp"], rtol=1e-10, atol=1e-15), name
         assert np.allclose(dvalue, c["dvalue"] / 0.5, rtol=1e-10, atol=1e-15), name
+
+
+def test_golden_stack_gather():
+    """Frame-stack gathers vs the reference's buf[q] (make_golden.gen_stack; base.py:317-378)."""
+    g = load_golden("stack")
+    for name, c in g.items():
+        if name == "ring":
+            size = int(c["size"])
+            args = (np.array([0, size]), c["done"], c["last_index"], np.array([size]))
+            assert np.array_equal(orc.stack_gather(c["frames"], c["query"], 3, *args), c["obs"])
+            assert np.array_equal(orc.stack_gather(c["frames_next"], c["query"], 3, *args),
+                                  c["obs_next"])
+            continue
+        args = (c["offset"], c["done"], c["last_index"], c["lengths"])
+        k = c["obs"].shape[1]
+        assert np.array_equal(orc.stack_gather(c["frames"], c["query"], k, *args), c["obs"]), name
+        assert np.array_equal(orc.stack_gather(c["frames"], c["query"], k, *args, from_next=True),
+                              c["obs_next"]), name
+        assert np.array_equal(orc.stack_gather(c["frames"], c["query"], 2, *args), c["get2"]), name

@@ -350,6 +350,8 @@ class ReplayBuffer:
         try:
             if stack_num == 1:
                 return _take(val, index)
+            if isinstance(val, torch.Tensor) and val.is_cuda and stack_num <= 16:
+                return self._stack_gather(val, index, stack_num)[0]
             stack: List[Any] = []
             indices = self._as_device_index(index)
             for _ in range(stack_num):
@@ -363,6 +365,36 @@ class ReplayBuffer:
                 raise exception
             return Batch()
 
+    def _stack_gather(self, val: torch.Tensor, index: IndexLike, stack_num: int,
+                      with_next: bool = False):
+        """``stack([val[prev^(k-1)(i)], ..., val[i]], axis=i.ndim)`` in one launch
+        (``ts_gather_stack``); with ``with_next`` also the stack that ends at ``next(i)``
+        (the ``obs_next`` of ``ignore_obs_next`` buffers, base.py:374-378)."""
+        if not isinstance(index, torch.Tensor):
+            arr = np.asarray(index, dtype=np.int64)
+            if arr.size and (arr.max() >= val.shape[0] or arr.min() < -val.shape[0]):
+                raise IndexError(f"index {arr.max()} is out of bounds for size {val.shape[0]}")
+        indices = self._as_device_index(index)
+        shape = tuple(indices.shape)
+        idx = indices.reshape(-1).contiguous()
+        st = self._state()
+        val = val if val.is_contiguous() else val.contiguous()
+        row_shape = tuple(val.shape[1:])
+        row_bytes = int(np.prod(row_shape, dtype=np.int64)) * val.element_size()
+        out = torch.empty((idx.numel(), stack_num) + row_shape, dtype=val.dtype,
+                          device=val.device)
+        out_next = torch.empty_like(out) if with_next else None
+        if idx.numel():
+            L.check(L.lib().ts_gather_stack(
+                L.ptr(val), row_bytes, L.ptr(idx), idx.numel(), stack_num, L.ptr(st["offset"]),
+                st["B"], st["sub_size"], L.ptr(self._done_u8()), L.ptr(st["last_index"]),
+                L.ptr(st["lengths"]), L.ptr(out), L.ptr(out_next) if with_next else None,
+                L.stream()), "ts_gather_stack")
+        out = out.reshape(shape + (stack_num,) + row_shape)
+        if with_next:
+            out_next = out_next.reshape(shape + (stack_num,) + row_shape)
+        return out, out_next
+
     def _as_device_index(self, index: IndexLike) -> torch.Tensor:
         if isinstance(index, torch.Tensor):
             return index.to(device=self.device, dtype=torch.int64)
@@ -375,11 +407,17 @@ class ReplayBuffer:
                 else self._as_device_index(np.arange(self.maxsize)[:len(self)][index])
         else:
             indices = self._as_device_index(index)
-        obs = self.get(indices, "obs")
-        if self._save_obs_next:
-            obs_next = self.get(indices, "obs_next", Batch())
+        obs_val = self._meta["obs"] if "obs" in self._meta else None
+        if (not self._save_obs_next and 1 < self.stack_num <= 16
+                and isinstance(obs_val, torch.Tensor) and obs_val.is_cuda):
+            # obs and obs[next(indices)] stacks from one pass over k + 1 frames
+            obs, obs_next = self._stack_gather(obs_val, indices, self.stack_num, with_next=True)
         else:
-            obs_next = self.get(self.next(indices), "obs", Batch())
+            obs = self.get(indices, "obs")
+            if self._save_obs_next:
+                obs_next = self.get(indices, "obs_next", Batch())
+            else:
+                obs_next = self.get(self.next(indices), "obs", Batch())
         return Batch(
             obs=obs,
             act=_take(self._meta["act"], indices),
