@@ -13,4 +13,6 @@ CMD="python bench.py --steps 20 --warmup 3 --skip-cpu --skip-e2e"
 $CMD > gpurun_out/plain.log 2>&1 && \
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:gae_rows -s 5 -c 1 -f -o gpurun_out/gae_top $CMD > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
-timeout 600 ncu --set full --clock-control none --cache-control none --import-source on -k regex:"tiered|cluster" -s 40 -c 2 -f -o gpurun_out/per_top $CMD > gpurun_out/ncu_full_per.log 2>&1; echo "ncu per rc=$?"
+timeout 600 ncu --set full --clock-control none --cache-control none --import-source on -k regex:"ranged|cluster" -s 40 -c 2 -f -o gpurun_out/per_top $CMD > gpurun_out/ncu_full_per.log 2>&1; echo "ncu per rc=$?"
+timeout 300 python scripts/bench_rows.py > gpurun_out/rows.jsonl 2> gpurun_out/rows.err; echo "rows rc=$?"
+timeout 300 python scripts/per_bench.py > gpurun_out/per_bench.jsonl 2> gpurun_out/per_bench.err; echo "per_bench rc=$?"
