@@ -36,7 +36,7 @@ E_PER_GPU, T_STEPS = 4096, 2048
 GAMMA, LAMBDA = 0.99, 0.95
 ALG_BYTES_PER_TRANSITION = 21  # rew 4 + v_s 4 + v_s_ 4 + end flag 1 + adv 4 + ret 4
 MOVED_BYTES_PER_TRANSITION = 22  # terminated and truncated are two separate bytes
-E2E_CHUNKS = int(os.environ.get("TS_E2E_CHUNKS", "4"))
+E2E_CHUNKS = int(os.environ.get("TS_E2E_CHUNKS", "2"))
 NCU_DRAM_BYTES_PER_LAUNCH = 117_464_320 + 26_714_368  # profiles/r01e_gae_ncu.md, shipped kernel
 PER_LEAVES, PER_BATCH, PER_ALPHA, PER_BETA = 1 << 20, 4096, 0.6, 0.4
 PER_ALG_BYTES_PER_SAMPLE = 664
@@ -301,11 +301,13 @@ def run_b200(args):
     if not args.skip_e2e:
         pipe = GaeHostPipeline(E, T, chunks=E2E_CHUNKS, device=dev)
         pipe.zero_copy = os.environ.get("TS_E2E_ZERO_COPY", "0") == "1"
+        pipe.overlap = os.environ.get("TS_E2E_OVERLAP", "1") == "1"
         h_adv = torch.empty(E, T, dtype=torch.float32).pin_memory()
         h_ret = torch.empty(E, T, dtype=torch.float32).pin_memory()
         Ke = max(3, min(K, 100))
         for _ in range(3):
             pipe.run(*host, h_adv, h_ret, GAMMA, LAMBDA)
+        pipe.join(stream)
         barrier()
         pipe.launches = 0
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -313,6 +315,7 @@ def run_b200(args):
             e0.record(stream)
             for _ in range(Ke):
                 pipe.run(*host, h_adv, h_ret, GAMMA, LAMBDA)
+            pipe.join(stream)  # every step's device->host copy has landed before the stop event
             e1.record(stream)
             barrier()
         ems = max_over_ranks(e0.elapsed_time(e1))
@@ -348,7 +351,8 @@ def run_b200(args):
                "link": pcie,
                "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
                "ms_per_step": ems / Ke, "steps": Ke,
-               "api": f"tianshou_fork_b200.pipeline.GaeHostPipeline.run ({E2E_CHUNKS} row chunks; H2D, compute and D2H streams)",
+               "api": f"tianshou_fork_b200.pipeline.GaeHostPipeline.run ({E2E_CHUNKS} row chunks; H2D, compute "
+                      f"and D2H streams; successive steps {'overlap' if pipe.overlap else 'do not overlap'} on the link)",
                "launches": pipe.launches}
 
     # ---- PER: sample + importance weights + update_weight, CUDA-graph replay ------------------

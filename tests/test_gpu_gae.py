@@ -350,7 +350,7 @@ def test_rows_pipelined_matches_register_kernel_f64(rows_variant):
         assert float((a - b).abs().max()) <= 1e-12 * float(a.abs().max())
 
 
-@pytest.mark.parametrize("mode", ["graph", "eager", "zero_copy"])
+@pytest.mark.parametrize("mode", ["graph", "eager", "zero_copy", "overlap"])
 def test_host_pipeline_matches_oracle(mode):
     """Pinned host buffers in and out (the e2e leg of bench.py): chunked copy/kernel/copy DAG
     replayed from a CUDA graph, the same DAG issued eagerly, and the zero-copy form where the
@@ -366,6 +366,7 @@ def test_host_pipeline_matches_oracle(mode):
     pipe = GaeHostPipeline(E, T, chunks=7)
     pipe.use_graph = mode == "graph"
     pipe.zero_copy = mode == "zero_copy"
+    pipe.overlap = mode == "overlap"
     for it in range(3):  # replays reuse the captured graph; results must not depend on it
         h_adv.fill_(float("nan"))
         h_ret.fill_(float("nan"))
@@ -378,3 +379,27 @@ def test_host_pipeline_matches_oracle(mode):
     pipe.run(*host, h_adv, h_ret, 0.99, 0.95)
     pipe.synchronize()
     assert _close(h_adv.numpy(), ref_adv2) and _close(h_ret.numpy(), ref_ret2)
+
+
+def test_host_pipeline_overlapped_calls():
+    """overlap=True: several passes over DIFFERENT host rollouts enqueued back to back (the
+    input copies of pass k+1 run under the output copies of pass k), all correct after one
+    synchronize(); the staging buffers are shared between the passes."""
+    from tianshou_fork_b200.pipeline import GaeHostPipeline
+    E, T, P = 300, 256, 5
+    pipe = GaeHostPipeline(E, T, chunks=4)
+    pipe.overlap = True
+    passes = []
+    for p in range(P):
+        rew, v_s, v_next, term, trunc = c2_rollout(E, T, seed=900 + p, p_term=1 / 40)
+        host = [torch.from_numpy(a).pin_memory() for a in
+                (rew, v_s, v_next, term.view(np.uint8), trunc.view(np.uint8))]
+        out = (torch.full((E, T), float("nan")).pin_memory(),
+               torch.full((E, T), float("nan")).pin_memory())
+        passes.append((host, out, orc.episodic_return_rows(rew, v_s, v_next, term, trunc,
+                                                           0.99, 0.95)))
+    for host, out, _ in passes:
+        pipe.run(*host, *out, 0.99, 0.95)
+    pipe.synchronize()
+    for host, (h_adv, h_ret), (ref_ret, ref_adv) in passes:
+        assert _close(h_adv.numpy(), ref_adv) and _close(h_ret.numpy(), ref_ret)

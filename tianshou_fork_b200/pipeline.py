@@ -51,6 +51,12 @@ class GaeHostPipeline:
         self.launches = 0
         self.use_graph = True
         self.zero_copy = False
+        # overlap=True: run() only enqueues on the three engine streams and does NOT order the
+        # caller's stream behind them, so the input copies of call k+1 run under the output copies
+        # of call k (the link is full duplex; H2D is the longer direction).  Outputs of every
+        # enqueued call are complete after join() / synchronize().
+        self.overlap = False
+        self._next_buffer = 0
         self._graph: torch.cuda.CUDAGraph | None = None
         self._graph_key = None
         self._cap_stream = torch.cuda.Stream(self.device)
@@ -79,6 +85,10 @@ class GaeHostPipeline:
                 "ts_gae_rows")
             self.launches += 1
             return
+        if self.overlap:
+            assert all(a.is_pinned() for a in args), "host buffers must be pinned"
+            self._enqueue(*args, gamma, gae_lambda, join=False)
+            return
         if not self.use_graph:
             self._enqueue(*args, gamma, gae_lambda)
             return
@@ -98,16 +108,23 @@ class GaeHostPipeline:
         self.launches += self._per_pass
 
     def _enqueue(self, rew, v_s, v_next, terminated, truncated, adv_out, ret_out, gamma,
-                 gae_lambda) -> None:
+                 gae_lambda, join: bool = True) -> None:
         lib = L.lib()
         cur = torch.cuda.current_stream(self.device)
-        for st in (self.s_h2d, self.s_comp, self.s_d2h):
-            st.wait_stream(cur)
+        # whatever the caller enqueued before (e.g. the kernel that fills the inputs) comes first
+        self.s_h2d.wait_stream(cur)
+        if join:
+            self.s_comp.wait_stream(cur)
+            self.s_d2h.wait_stream(cur)
+        cross_call = not join  # staging buffers may still be in use by the previous call
         T, nb = self.T, len(self.d_rew)
+        first = self._next_buffer if cross_call else 0  # keep rotating across overlapped calls
+        if cross_call:
+            self._next_buffer = (first + len(self.bounds)) % nb
         for c, (lo, hi) in enumerate(self.bounds):
-            b, n = c % nb, hi - lo
+            b, n = (first + c) % nb, hi - lo
             with torch.cuda.stream(self.s_h2d):
-                if c >= nb:
+                if c >= nb or cross_call:
                     self.s_h2d.wait_event(self.ev_kernel[b])  # inputs of chunk c - nb consumed
                 self.d_rew[b][:n].copy_(rew[lo:hi], non_blocking=True)
                 self.d_vs[b][:n].copy_(v_s[lo:hi], non_blocking=True)
@@ -117,7 +134,7 @@ class GaeHostPipeline:
                 self.ev_loaded[b].record(self.s_h2d)
             with torch.cuda.stream(self.s_comp):
                 self.s_comp.wait_event(self.ev_loaded[b])
-                if c >= nb:
+                if c >= nb or cross_call:
                     self.s_comp.wait_event(self.ev_stored[b])  # outputs of chunk c - nb copied out
                 L.check(lib.ts_gae_rows(
                     self.d_rew[b].data_ptr(), self.d_vs[b].data_ptr(), self.d_vn[b].data_ptr(),
@@ -132,8 +149,15 @@ class GaeHostPipeline:
                 adv_out[lo:hi].copy_(self.d_adv[b][:n], non_blocking=True)
                 ret_out[lo:hi].copy_(self.d_ret[b][:n], non_blocking=True)
                 self.ev_stored[b].record(self.s_d2h)
+        if join:
+            self.join()
+
+    def join(self, stream: torch.cuda.Stream | None = None) -> None:
+        """Order ``stream`` (default: the current one) behind everything enqueued so far."""
+        cur = stream or torch.cuda.current_stream(self.device)
         for st in (self.s_h2d, self.s_comp, self.s_d2h):
             cur.wait_stream(st)
 
     def synchronize(self) -> None:
+        self.join()
         torch.cuda.current_stream(self.device).synchronize()
