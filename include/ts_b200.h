@@ -310,6 +310,27 @@ int32_t ts_gather_stack(const void* src, int64_t row_bytes, const int64_t* index
                         const uint8_t* done, const int64_t* last_index, const int64_t* lengths,
                         void* out, void* out_next, ts_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Device-side add of one vectorised env step (rollouts produced on the GPU).
+ * Replaces: the loop over sub-buffers in ReplayBufferManager.add
+ *           (tianshou/data/buffer/manager.py:104-161), ReplayBuffer._add_index per transition
+ *           (tianshou/data/buffer/base.py:195-214) and `self._meta[ptrs] = batch` (manager.py:160).
+ * Transition j goes to sub-buffer buffer_ids[j] (NULL: j), each sub-buffer at most once per call.
+ * src/dst/row_bytes are HOST arrays of n_keys <= 16 entries: rows of the step [M, row_bytes]
+ * and the storage they are stored into [total, row_bytes] (device pointers).  ring = int64
+ * [B][2] (index, size); ep_rew/ep_len/ep_idx = running episode statistics; all device-resident
+ * and advanced in place.  Outputs (device, [M]): the global slot, and the episode return /
+ * length (0 unless done[j]) / start index, as _add_index returns them.  A sub-buffer id outside
+ * [0, B) sets TS_FLAG_INDEX_RANGE and skips the transition.
+ * ---------------------------------------------------------------------------------------- */
+int32_t ts_add_step(int32_t n_keys, const void* const* src, void* const* dst,
+                    const int64_t* row_bytes, int64_t M, const int64_t* buffer_ids,
+                    const void* rew, int32_t rew_dtype, const uint8_t* done,
+                    const int64_t* offset, int64_t B, int64_t* ring, int64_t* last_index,
+                    int64_t* lengths, double* ep_rew, int64_t* ep_len, int64_t* ep_idx,
+                    int64_t* ptr_out, double* ep_rew_out, int64_t* ep_len_out,
+                    int64_t* ep_idx_out, int32_t* err_flag, ts_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -278,6 +278,46 @@ def row_gather_stack():
              moved_frac=moved / us / 1e3 / PEAK, samples_per_s=bsz / us * 1e6)
 
 
+def row_add():
+    """N1: one vectorised env step added to a VectorReplayBuffer: add_device (one launch, no host
+    read of rew / done) vs the host-bookkeeping add() of this package vs the oracle's ring
+    bookkeeping alone on one core (the reference's add is a Python loop over sub-buffers)."""
+    for E, obs_dim in ((4096, 27), (64, 27)):
+        T = 256
+        rng = np.random.default_rng(8)
+        step = dict(obs=rng.standard_normal((E, obs_dim)).astype(np.float32),
+                    act=rng.standard_normal((E, 8)).astype(np.float32),
+                    rew=rng.standard_normal(E), terminated=rng.random(E) < 0.01,
+                    truncated=np.zeros(E, dtype=bool),
+                    obs_next=rng.standard_normal((E, obs_dim)).astype(np.float32))
+        dstep = ts.Batch(**{k: torch.from_numpy(v).to(DEV) for k, v in step.items()})
+        hbuf, dbuf = ts.VectorReplayBuffer(E * T, E), ts.VectorReplayBuffer(E * T, E)
+        for _ in range(3):
+            hbuf.add(ts.Batch(info={}, **step))
+            dbuf.add_device(dstep)
+
+        def wall(fn, n=100):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(n):
+                fn()
+            torch.cuda.synchronize()
+            return (time.perf_counter() - t0) / n * 1e6
+
+        host_us = wall(lambda: hbuf.add(ts.Batch(info={}, **step)))
+        dev_wall_us = wall(lambda: dbuf.add_device(dstep))
+        dev_gpu_us = gpu_us(lambda: dbuf.add_device(dstep), iters=100)
+        st = orc.RingState(E * T, E)
+        cus = cpu_us(lambda: st.add(step["rew"], step["terminated"], step["truncated"]),
+                     seconds=1.0)
+        row_bytes = 2 * obs_dim * 4 + 32 + 8 + 3
+        emit("N1 add one step", envs=E, bytes_per_transition=row_bytes,
+             add_device_wall_us=dev_wall_us, add_device_gpu_us=dev_gpu_us,
+             host_add_wall_us=host_us, cpu_port_bookkeeping_us=cus,
+             us_per_transition_device=dev_wall_us / E, us_per_transition_host_add=host_us / E,
+             reference_probe_us_per_transition=5.5)
+
+
 def row_ppo():
     """a11: fused PPO loss forward + backward per minibatch (C3: N = 131 072)."""
     N = 131072
@@ -315,6 +355,6 @@ def row_ppo():
 
 if __name__ == "__main__":
     torch.cuda.set_device(0)
-    which = sys.argv[1:] or ["gae_flat", "nstep_index", "gather", "gather_stack", "ppo"]
+    which = sys.argv[1:] or ["gae_flat", "nstep_index", "gather", "gather_stack", "add", "ppo"]
     for w in which:
         globals()["row_" + w]()

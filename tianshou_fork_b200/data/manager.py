@@ -69,6 +69,8 @@ class ReplayBufferManager(ReplayBuffer):
             self._ep_len[:] = 0
             self._ep_idx[:] = 0
         self._child_last[:] = 0
+        self._dev_add = None
+        self._ep_on_device = False
         self._version += 1
 
     def _set_batch_for_children(self) -> None:
@@ -113,6 +115,8 @@ class ReplayBufferManager(ReplayBuffer):
     def add(self, batch: Batch, buffer_ids: Optional[Union[np.ndarray, List[int]]] = None
             ) -> Tuple[np.ndarray, np.ndarray, np.ndarray, np.ndarray]:
         """Add one transition per listed sub-buffer (manager.py:104-161)."""
+        if getattr(self, "_ep_on_device", False):
+            self._pull_episode_stats()
         batch = self._prepare_add(batch, self._reserved_keys, stacked=True)
         if buffer_ids is None:
             buffer_ids = np.arange(self.buffer_num)
@@ -143,6 +147,137 @@ class ReplayBufferManager(ReplayBuffer):
             self._set_batch_for_children()
         self._meta[ptrs] = batch
         return ptrs, ep_rews, ep_lens, ep_idxs
+
+    # ---- device-side add ------------------------------------------------------
+    def _pull_episode_stats(self) -> None:
+        """Running episode statistics live on the device while ``add_device`` is in use."""
+        st = getattr(self, "_dev_add", None)
+        if st is not None and getattr(self, "_ep_on_device", False):
+            self._ep_rew[:] = st["ep_rew"].cpu().numpy()
+            self._ep_len[:] = st["ep_len"].cpu().numpy()
+            self._ep_idx[:] = st["ep_idx"].cpu().numpy()
+        self._ep_on_device = False
+
+    def _device_add_state(self) -> Dict[str, torch.Tensor]:
+        st = getattr(self, "_dev_add", None)
+        if st is None or self._dev_add_version != self._version:
+            self._pull_episode_stats()  # no-op unless the device copy is the newer one
+            dev = self.device
+            up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+            st = {"offset": up(self._extend_offset), "ring": up(self._rings),
+                  "last_index": up(np.asarray(self.last_index, dtype=np.int64)),
+                  "lengths": up(self._lengths), "ep_rew": up(self._ep_rew),
+                  "ep_len": up(self._ep_len), "ep_idx": up(self._ep_idx),
+                  "err": torch.zeros(1, dtype=torch.int32, device=dev)}
+            st["ptrs"] = [st[k].data_ptr() for k in ("offset", "ring", "last_index", "lengths",
+                                                     "ep_rew", "ep_len", "ep_idx", "err")]
+            self._dev_add = st
+        return st
+
+    def add_device(self, batch: Batch, buffer_ids: Optional[Union[np.ndarray, List[int]]] = None
+                   ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+        """``add`` for steps produced on the GPU: every value of ``batch`` is a CUDA tensor with
+        leading dimension ``len(buffer_ids)``; ONE launch advances the rings, the episode
+        statistics and stores every key (``ts_add_step``), with no host read of ``rew`` /
+        ``done``.  Same bookkeeping as manager.py:104-161 over base.py:195-214; returns
+        ``(ptrs, ep_rew, ep_len, ep_idx)`` as DEVICE tensors.  ``buffer_ids`` (host) must not
+        repeat a sub-buffer.  The ring pointers are mirrored on the host (they do not depend on
+        the data), so ``sample_indices`` / ``prev`` / ``next`` / ``__len__`` work as usual."""
+        import ctypes
+        src = batch.__dict__
+        assert all(k in src for k in ("obs", "act", "rew", "terminated", "truncated"))
+        vals: Dict[str, torch.Tensor] = {}
+        for key in self._reserved_keys:
+            v = src.get(key)
+            if v is None or (isinstance(v, Batch) and v.is_empty()):
+                continue
+            if not isinstance(v, torch.Tensor):
+                raise TypeError(f"add_device stores tensor-valued keys only (got {key})")
+            vals[key] = v
+        vals["done"] = torch.logical_or(vals["terminated"], vals["truncated"])
+        if self._save_only_last_obs:
+            vals["obs"] = vals["obs"][:, -1]
+        if not self._save_obs_next:
+            vals.pop("obs_next", None)
+        elif self._save_only_last_obs and "obs_next" in vals:
+            vals["obs_next"] = vals["obs_next"][:, -1]
+        full = buffer_ids is None
+        if full:
+            M = self.buffer_num
+        else:
+            ids = np.asarray(buffer_ids, dtype=np.int64)
+            M = int(ids.size)
+            assert len(np.unique(ids)) == M, "add_device: a sub-buffer may appear once per call"
+        rew = vals["rew"]
+        assert rew.ndim == 1 and rew.shape[0] == M
+        if rew.dtype != self.rew_dtype:
+            vals["rew"] = rew.to(self.rew_dtype)  # stored as float (manager.py:150)
+        if self._meta.is_empty() or not all(k in self._meta.__dict__ for k in vals):
+            sample = Batch(**{k: (v.to(torch.bool) if k in ("done", "terminated", "truncated")
+                                  else v) for k, v in vals.items()})
+            if self._meta.is_empty():
+                self._meta = create_value(sample, self.maxsize, stack=False, device=self.device)
+            else:
+                _alloc_missing(self._meta, sample, self.maxsize, False, self.device)
+            self._set_batch_for_children()
+            self._dev_add_keys = None
+        st = self._device_add_state()
+        names = tuple(sorted(vals))
+        cache = getattr(self, "_dev_add_keys", None)
+        if cache is None or cache["names"] != names:
+            stores = [self._meta[k] for k in names]
+            cache = {"names": names, "stores": stores, "n": len(names),
+                     "dst": (ctypes.c_void_p * len(names))(*[
+                         L.ptr(L.as_u8(t)) for t in stores]),
+                     "rb": (ctypes.c_int64 * len(names))(*[
+                         int(np.prod(t.shape[1:], dtype=np.int64)) * t.element_size()
+                         for t in stores])}
+            self._dev_add_keys = cache
+        keep, srcs = [], []
+        for k, store in zip(names, cache["stores"]):
+            v = vals[k]
+            if v.dtype != store.dtype:
+                v = v.to(store.dtype)
+            if not v.is_contiguous():
+                v = v.contiguous()
+            assert v.shape[0] == M and v.shape[1:] == store.shape[1:] and v.is_cuda, k
+            keep.append(v)
+            srcs.append(v.data_ptr())
+        c_src = (ctypes.c_void_p * cache["n"])(*srcs)
+        dev = self.device
+        g_ids = None if full else torch.from_numpy(ids).to(dev)
+        rew = keep[names.index("rew")]
+        done = keep[names.index("done")]
+        out_i = torch.empty((3, M), dtype=torch.int64, device=dev)
+        ep_rew_out = torch.empty(M, dtype=torch.float64, device=dev)
+        L.check(L.lib().ts_add_step(
+            cache["n"], c_src, cache["dst"], cache["rb"], M,
+            g_ids.data_ptr() if g_ids is not None else None, rew.data_ptr(), L.dtype_code(rew),
+            done.data_ptr(), st["ptrs"][0], self.buffer_num, st["ptrs"][1], st["ptrs"][2],
+            st["ptrs"][3], st["ptrs"][4], st["ptrs"][5], st["ptrs"][6], out_i[0].data_ptr(),
+            ep_rew_out.data_ptr(), out_i[1].data_ptr(), out_i[2].data_ptr(), st["ptrs"][7],
+            L.stream()), "ts_add_step")
+        # host mirror of the pointer bookkeeping (data-independent): _add_index lines :197-199
+        r = self._rings
+        if full:
+            ptr_local = r[:, 0].copy()
+            np.minimum(r[:, 1] + 1, self._sub_sizes, out=r[:, 1])
+            r[:, 0] = (ptr_local + 1) % self._sub_sizes
+            np.add(ptr_local, self._offset, out=self.last_index)
+            self._lengths[:] = r[:, 1]
+            self._child_last[:, 0] = ptr_local
+        else:
+            sub = self._sub_sizes[ids]
+            ptr_local = r[ids, 0].copy()
+            r[ids, 1] = np.minimum(r[ids, 1] + 1, sub)
+            r[ids, 0] = (ptr_local + 1) % sub
+            self.last_index[ids] = ptr_local + self._offset[ids]
+            self._lengths[ids] = r[ids, 1]
+            self._child_last[ids, 0] = ptr_local
+        self._ep_on_device = True
+        self._version += 1
+        self._dev_add_version = self._version
+        return out_i[0], ep_rew_out, out_i[1], out_i[2]
 
     # ---- sampling ------------------------------------------------------------------------------
     def unfinished_index(self) -> np.ndarray:
