@@ -178,12 +178,39 @@ def row_nstep_index():
             us = gpu_us(lambda: ts.BasePolicy.compute_nstep_return(
                 batch, buf, idx, lambda b, t: tq, 0.99, 3))
             cus = cpu_us(lambda: orc.compute_nstep_return(st, idx_np, lambda t: tq_np, 0.99, 3))
-            emit("a2 nstep", bsz=bsz, D=D, n_step=3, gpu_us=us, cpu_port_us=cus, speedup=cus / us)
+            # the two kernels alone (raw C-ABI in a CUDA graph): what the API numbers above hide
+            bst = buf._state()
+            term_u8, done_u8 = L.as_u8(buf.terminated), L.as_u8(buf.done)
+            rew_d = buf.rew.contiguous()
+            terminal = torch.empty(bsz, dtype=torch.int64, device=DEV)
+            rs = torch.empty(bsz, dtype=torch.float64, device=DEV)
+            cf = torch.empty(bsz, dtype=torch.float64, device=DEV)
+            outq = torch.empty_like(tq)
+            lib = L.lib()
+
+            def kernels(s):
+                L.check(lib.ts_nstep_chain(
+                    L.ptr(idx), bsz, L.ptr(rew_d), L.dtype_code(rew_d), L.ptr(done_u8),
+                    L.ptr(term_u8), L.ptr(bst["offset"]), bst["B"], bst["sub_size"],
+                    L.ptr(bst["last_index"]), L.ptr(bst["lengths"]), 0.99, 3, L.ptr(terminal),
+                    L.ptr(rs), L.ptr(cf), s), "chain")
+                L.check(lib.ts_nstep_combine(L.ptr(tq), L.dtype_code(tq), bsz, D, L.ptr(rs),
+                                             L.ptr(cf), L.ptr(outq), s), "combine")
+            kus = graph_us(kernels)
+            emit("a2 nstep", bsz=bsz, D=D, n_step=3, gpu_us=us, kernels_graph_us=kus,
+                 cpu_port_us=cus, speedup=cus / us, kernel_speedup=cus / kus)
         us_n = gpu_us(lambda: buf.next(idx))
         us_p = gpu_us(lambda: buf.prev(idx))
         cus = cpu_us(lambda: st.next(idx_np))
-        emit("a3/a4 next", M=bsz, B=E, gpu_us=us_n, prev_gpu_us=us_p, cpu_port_us=cus,
-             speedup=cus / us_n)
+        bst = buf._state()
+        done_u8 = L.as_u8(buf.done)
+        nout = torch.empty(bsz, dtype=torch.int64, device=DEV)
+        lib = L.lib()
+        kus = graph_us(lambda s: L.check(lib.ts_next_index(
+            L.ptr(idx), bsz, L.ptr(bst["offset"]), bst["B"], bst["sub_size"], L.ptr(done_u8),
+            L.ptr(bst["last_index"]), L.ptr(bst["lengths"]), L.ptr(nout), s), "next"))
+        emit("a3/a4 next", M=bsz, B=E, gpu_us=us_n, prev_gpu_us=us_p, kernel_graph_us=kus,
+             cpu_port_us=cus, speedup=cus / us_n, kernel_speedup=cus / kus)
     # many sub-buffers: the reference's njit loop is O(B * M)
     E2, T2 = 4096, 256
     buf2 = ts.VectorReplayBuffer(E2 * T2, E2)

@@ -75,6 +75,7 @@ SIGNATURES = {
 }
 
 _lib: Optional[ctypes.CDLL] = None
+_cuda_checked = False
 
 
 class TsError(RuntimeError):
@@ -106,10 +107,13 @@ def load() -> ctypes.CDLL:
 
 def lib() -> ctypes.CDLL:
     """The library, for compute calls: additionally requires a CUDA device."""
-    if not torch.cuda.is_available():
-        raise RuntimeError(
-            "tianshou_fork_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
-    return load()
+    global _cuda_checked
+    if not _cuda_checked:
+        if not torch.cuda.is_available():
+            raise RuntimeError(
+                "tianshou_fork_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        _cuda_checked = True
+    return _lib if _lib is not None else load()
 
 
 def check(code: int, what: str) -> None:

@@ -166,6 +166,9 @@ class ReplayBuffer:
             b = last.size
             self._dev_state = {"offset": t[: b + 1], "last_index": t[b + 1: 2 * b + 1],
                                "lengths": t[2 * b + 1:], "B": b, "sub_size": sub}
+            # raw addresses for the hot calls (the packed tensor stays alive in the dict)
+            p0 = t.data_ptr()
+            self._dev_state["ptrs"] = (p0, p0 + 8 * (b + 1), p0 + 8 * (2 * b + 1))
             self._dev_state_version = version
         return self._dev_state
 
@@ -174,6 +177,18 @@ class ReplayBuffer:
 
     def _neighbour(self, index: IndexLike, fn_name: str):
         st = self._state()
+        if (isinstance(index, torch.Tensor) and index.is_cuda and index.dtype == torch.int64
+                and index.is_contiguous()):
+            # device tensor in -> device tensor out: nothing but the launch
+            out = torch.empty_like(index)
+            n = index.numel()
+            if n:
+                off, last, lens = st["ptrs"]
+                L.check(getattr(L.lib(), fn_name)(
+                    index.data_ptr(), n, off, st["B"], st["sub_size"],
+                    self._meta.__dict__["done"].data_ptr(), last, lens, out.data_ptr(),
+                    L.stream()), fn_name)
+            return out
         scalar = _is_scalar(index)
         if isinstance(index, torch.Tensor):
             idx = index.to(device=self.device, dtype=torch.int64)
