@@ -97,6 +97,13 @@ __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;"
                  ::: "memory");
 }
+// split form: arrive as soon as this CTA is done with its peers' shared memory, wait before exit
+__device__ __forceinline__ void cluster_arrive() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cluster_wait() {
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 // read a double at the same shared-memory offset in CTA `rank` of the cluster
 __device__ __forceinline__ double dsmem_ld_f64(const double* local, uint32_t rank) {
     uint32_t addr = smem_u32(local), remote;
@@ -1107,7 +1114,8 @@ segtree_prefix_kernel(const double* __restrict__ tree, int64_t bound, int lg_bou
 // ============================================================================================
 // cluster shape: 8 x 512 (portable) or 16 x 256 (opt-in size) -- ts_tune_set("per_cluster")
 
-// max over every thread of the cluster (all threads must call; result valid in all threads)
+// max over every thread of the cluster (all threads must call; result valid in all threads).
+// The caller MUST execute cluster_wait() once afterwards, before returning from the kernel.
 template <int NT>
 __device__ __forceinline__ double cluster_max(double m, double* s_warp, double* s_cta) {
     const int tid = threadIdx.x;
@@ -1128,7 +1136,9 @@ __device__ __forceinline__ double cluster_max(double m, double* s_warp, double* 
     m = lane < nrank ? dsmem_ld_f64(s_cta, lane) : 0.0;
 #pragma unroll
     for (int d = 16; d >= 1; d >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, d));
-    cluster_sync_all();  // nobody leaves (or overwrites s_cta) while peers still read it
+    // nobody may leave while peers still read its s_cta: arrive now, the caller waits
+    // (cluster_wait) just before the kernel ends, under the normalising pass
+    cluster_arrive();
     return m;
 }
 
@@ -1281,6 +1291,7 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
         const double w = j == j0 ? w_first : weight[j];
         weight[j] = scale ? __ddiv_rn(w, wmax) : w;              // prio.py:101
     }
+    if (weight_norm) cluster_wait();  // second half of cluster_max's closing barrier
 }
 
 // After a tree change: this rank's {root, max_prio, min_prio} goes straight into every peer's
