@@ -65,6 +65,8 @@ int32_t ts_last_cuda_error(void);
  *   "segtree_group"     tiered kernel: 128 (default) or 256 nodes per warp-rebuilt group
  *   "segtree_max_ctas"  tiered kernel: CTAs of the cooperative launch (<= 148)
  *   "per_cluster"       PER sampling cluster: 0 = automatic, 8 (x512 threads) or 16 (x256)
+ *   "gae_rows_packed"   1 (default) = contiguous rows shorter than a 2048-step tile are walked as
+ *                       one sequence with row cuts (pipelined ranges), 0 = one row per tile
  *   "gae_balance"       1 = persistent GAE grids sized for equal work per CTA (default 0)
  *   "pdl"               1 (default) = PER and GAE rows kernels use programmatic dependent
  *                       launch, 0 = off */

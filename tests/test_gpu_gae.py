@@ -403,3 +403,27 @@ def test_host_pipeline_overlapped_calls():
     pipe.synchronize()
     for host, (h_adv, h_ret), (ref_ret, ref_adv) in passes:
         assert _close(h_adv.numpy(), ref_adv) and _close(h_ret.numpy(), ref_ret)
+
+
+@pytest.mark.parametrize("E,T", [(8192, 128), (2100, 512), (1100, 1000), (5000, 250),
+                                 (140000, 8), (1030, 1024), (700, 2040), (9000, 120)])
+def test_rows_short_rows_packed_vs_oracle(E, T):
+    """Contiguous rows shorter than a tile are walked as one sequence with a cut at every row
+    end (ts_tune "gae_rows_packed"): same numbers as the oracle and as the row-per-tile path."""
+    from tianshou_fork_b200 import _lib as L
+    rew, v_s, v_next, term, trunc = c2_rollout(E, T, seed=E + T, p_term=1 / 300, p_trunc=1 / 900)
+    ref_ret, ref_adv = orc.episodic_return_rows(rew, v_s, v_next, term, trunc, 0.99, 0.95)
+    d = lambda a: torch.from_numpy(a).cuda()
+    g = [d(rew), d(v_s), d(v_next), d(term.view(np.uint8)), d(trunc.view(np.uint8))]
+    outs = []
+    for packed in (1, 0):
+        L.check(L.lib().ts_tune_set(b"gae_rows_packed", packed), "tune")
+        adv = torch.full((E, T), float("nan"), device="cuda")
+        ret = torch.full((E, T), float("nan"), device="cuda")
+        L.check(L.lib().ts_gae_rows(*[L.ptr(t) for t in g], E, T, T, T, 0.99, 0.95, 0, 0, 0,
+                                    L.ptr(adv), L.ptr(ret), L.stream()), "ts_gae_rows")
+        outs.append((adv.cpu().numpy(), ret.cpu().numpy()))
+    L.check(L.lib().ts_tune_set(b"gae_rows_packed", 1), "tune")
+    for a, r in outs:
+        assert _close(a, ref_adv) and _close(r, ref_ret)
+    assert np.allclose(outs[0][0], outs[1][0], rtol=1e-6, atol=1e-6)

@@ -11,6 +11,7 @@ int g_tune_segtree_group = 128;
 int g_tune_segtree_ranged = 1;
 int g_tune_pdl = 1;
 int g_tune_gae_balance = 0;
+int g_tune_gae_rows_packed = 1;
 int g_tune_per_cluster = 0;
 int g_tune_segtree_max_ctas = 148;
 }
@@ -57,6 +58,10 @@ extern "C" int32_t ts_tune_set(const char* key, int64_t value) {
     }
     if (strcmp(key, "segtree_ranged") == 0 && (value == 0 || value == 1)) {
         ts::g_tune_segtree_ranged = (int)value;
+        return TS_OK;
+    }
+    if (strcmp(key, "gae_rows_packed") == 0 && (value == 0 || value == 1)) {
+        ts::g_tune_gae_rows_packed = (int)value;
         return TS_OK;
     }
     if (strcmp(key, "gae_balance") == 0 && (value == 0 || value == 1)) {

@@ -494,7 +494,17 @@ struct FlatGather {               // how value mask and unfinished tails are fou
     const int64_t* unfinished;    // per sub-buffer unfinished index or -1 (:380)
     const int64_t* offset;
     int64_t B, sub_size;
+    int64_t seg;                  // > 0: the sequence is rows of `seg` >= 8 steps, cut at every row end
 };
+
+// the end of a row of `seg` steps, if it falls inside the 8-step strip that starts at row position r
+__device__ __forceinline__ void seg_cut(uint32_t r, uint32_t seg, uint2& wc) {
+    const uint32_t qs = seg - 1u - r;  // steps from the strip's first element to the row's last
+    if (qs < (uint32_t)VEC) {
+        const uint32_t bit = 1u << (8 * (qs & 3u));
+        if (qs < 4u) wc.x |= bit; else wc.y |= bit;
+    }
+}
 
 // mask / cut of one transition from its flags (and, with indices, from the buffer)
 __device__ __forceinline__ void flat_flags(const FlatGather& g, int64_t idx, uint32_t t,
@@ -547,6 +557,7 @@ struct FlatWindow {
     InT vs[VEC], vn[VEC];
     uint2 wt, wc;
     int64_t idx[VEC];
+    int64_t first;  // sequence position of this lane's first step
     int nvalid;
 
     // issue the reads of this lane's 8 steps (all arrays are 16-byte aligned, i_first % 8 == 0)
@@ -556,6 +567,7 @@ struct FlatWindow {
                                          const uint8_t* __restrict__ trunc, const FlatGather& g,
                                          int64_t i_first, int64_t N, int lane) {
         const int64_t i0 = i_first + lane * VEC;
+        first = i0;
         const int64_t left = N - i0;
         nvalid = left >= VEC ? VEC : (left > 0 ? (int)left : 0);
         const int64_t at = nvalid > 0 ? i0 : 0;  // keep the address in range when nothing is read
@@ -574,6 +586,7 @@ struct FlatWindow {
                                            int lane, double& Pw, double& Xw) {
         wc.x |= wt.x;
         wc.y |= wt.y;
+        if (g.seg > 0) seg_cut((uint32_t)(first % g.seg), (uint32_t)g.seg, wc);
         if (g.indices != nullptr) {  // value mask / unfinished tails live in the buffer
             uint2 bt = make_uint2(0u, 0u), un = make_uint2(0u, 0u);
 #pragma unroll
@@ -699,12 +712,12 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     pdl_wait();  // inputs and the workspace may come from the kernel before
     if (tid == 0) {
         while (p_it < stages && p_it < ntiles) issue();
-        tag = (__ldcg(sync + 1) + 1u) | 0x80000000u;
+        if (sync != nullptr) tag = (__ldcg(sync + 1) + 1u) | 0x80000000u;
     }
     __syncthreads();
     // a CTA's last act: the one that finishes last advances the call count
     auto leave = [&]() {
-        if (tid == 0) {
+        if (tid == 0 && sync != nullptr) {
             __threadfence();
             if (atomicAdd(sync + 2, 1u) == gridDim.x - 1u) {
                 sync[1] = tag & 0x7fffffffu;
@@ -724,6 +737,7 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
                     const int64_t idx = g.indices != nullptr ? g.indices[i] : i;
                     bool masked;
                     flat_flags(g, idx, term[i], trunc[i], masked, cutl);
+                    if (g.seg > 0 && (i + 1) % g.seg == 0) cutl = true;
                     const double v1 = masked ? 0.0 : (double)v_next[i];
                     vsl = (double)v_s[i];
                     dl = fma(v1, gamma, (double)rew[i]) - vsl;
@@ -770,8 +784,9 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
                         Xc = fma(Pc, sX[w], Xc);
                         Pc *= sP[w];
                     }
-                    if (fabs(Pc) >= kCarryNegligible) {
+                    if (fabs(Pc) >= kCarryNegligible && head_flags != nullptr) {
                         // no boundary within reach: the neighbour's published head value
+                        // (never with row segments: a row end lies within the 2304 steps read)
                         unsigned int f;
                         do {
                             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];"
@@ -788,7 +803,7 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     }
     __syncthreads();
     if (ntiles == 0) {  // nothing but (for CTA 0) the ragged end: pass the value on
-        if (blockIdx.x == 0 && tid == 0) {
+        if (blockIdx.x == 0 && tid == 0 && heads != nullptr) {
             heads[0] = carry;
             __threadfence();
             *(volatile unsigned int*)head_flags = tag;
@@ -800,6 +815,10 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     int stage = 0;
     uint32_t parity = 0;
     int64_t k = k_hi - 1;
+    // row position of the current tile's first step, kept incrementally (tiles go down by TILE)
+    const uint32_t seg = (uint32_t)g.seg;
+    uint32_t r_tile = seg ? (uint32_t)((k * TILE) % g.seg) : 0u;
+    const uint32_t r_back = seg ? seg - (uint32_t)(TILE % g.seg) : 0u;
     for (int it = 0; it < ntiles; ++it, --k) {
         const int n = k == ntiles_all - 1 ? n_last : TILE;
         mbar_wait(bar0 + 8u * stage, parity);
@@ -864,6 +883,12 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
             }
         }
 
+        if (seg) {
+            seg_cut((r_tile + (uint32_t)e0) % seg, seg, wc);
+            r_tile += r_back;
+            if (r_tile >= seg) r_tile -= seg;
+        }
+
         double d[VEC];
 #pragma unroll
         for (int q = 0; q < VEC; ++q) {
@@ -916,9 +941,11 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
         if (++stage == stages) { stage = 0; parity ^= 1u; }
     }
     if (tid == 0) {
-        heads[blockIdx.x] = carry;  // advantage of this range's first step, for a waiting neighbour
-        __threadfence();
-        *(volatile unsigned int*)(head_flags + blockIdx.x) = tag;
+        if (heads != nullptr) {
+            heads[blockIdx.x] = carry;  // this range's first advantage, for a waiting neighbour
+            __threadfence();
+            *(volatile unsigned int*)(head_flags + blockIdx.x) = tag;
+        }
         bulk_wait0();
     }
     leave();
@@ -1163,6 +1190,11 @@ int32_t launch_rows_tma(const void* rew, const void* v_s, const void* v_next,
     return check_launch();
 }
 
+template <typename RewT, typename InT, typename OutT, bool HAS_IDX>
+int32_t launch_flat_tma(const void* rew, const void* v_s, const void* v_next, const uint8_t* term,
+                        const uint8_t* trunc, const FlatGather& g, int64_t N, double gamma,
+                        double lam, void* adv, void* ret, FlatWorkspace ws, cudaStream_t stream);
+
 template <typename RewT, typename InT, typename OutT>
 int32_t launch_rows(const void* rew, const void* v_s, const void* v_next, const uint8_t* term,
                     const uint8_t* trunc, int64_t E, int64_t T, int64_t bs, int64_t vs,
@@ -1176,6 +1208,18 @@ int32_t launch_rows(const void* rew, const void* v_s, const void* v_next, const 
                         E * ((T + 1023) / 1024) < 0x7fffffffLL;  // 32-bit tile counters
     int variant = g_tune_gae_rows_variant;
     if (variant < 0 || variant >= kNumRowsVariants) return TS_ERR_BAD_ARG;
+    // Short rows stored back to back (T < one 2048-step tile): the row-per-tile kernel would run
+    // its tiles mostly empty (T = 512: a quarter full).  The whole [E, T] block is instead walked
+    // as ONE sequence of E * T steps by the pipelined-ranges kernel, with a cut at every row end;
+    // a row end always lies within its 2304-step read-ahead, so it needs no workspace.
+    if (variant == 0 && g_tune_gae_rows_packed && bs == T && vs == T && T >= VEC && T < 2048 &&
+        E * T >= (1 << 20) && vec_ok && aligned(term, 16) && aligned(trunc, 16) &&
+        E * T < (1LL << 40)) {
+        const FlatGather g{nullptr, nullptr, nullptr, nullptr, 0, 0, T};
+        FlatWorkspace ws{};
+        return launch_flat_tma<RewT, InT, OutT, false>(rew, v_s, v_next, term, trunc, g, E * T,
+                                                       gamma, lam, adv, ret, ws, stream);
+    }
     // automatic: the pipelined kernel pays off once there are enough rows to keep the
     // persistent CTAs busy with several tiles each; short batches stay on the register kernel
     if (variant == 0) variant = (tma_ok && E * T >= (1 << 20)) ? kRowsAutoTma : 1;
@@ -1258,7 +1302,7 @@ int32_t launch_flat(const void* rew, const void* v_s, const void* v_next, const 
     // short sequences have too few tiles per CTA to amortise the read-ahead: look-back kernel
     if (variant == 0) variant = N >= (1 << 20) ? 2 : 1;
     if (variant == 2 && tma_ok) {
-        const FlatGather g{indices, buf_term, unfinished, offset, B, sub_size};
+        const FlatGather g{indices, buf_term, unfinished, offset, B, sub_size, 0};
         if (indices != nullptr)
             return launch_flat_tma<RewT, InT, OutT, true>(rew, v_s, v_next, term, trunc, g, N, gamma,
                                                           lam, adv, ret, ws, stream);

@@ -137,6 +137,7 @@ extern int g_tune_gae_flat_stages;   // pipelined ranges: stages of the ring (0 
 extern int g_tune_segtree_max_ctas;  // CTAs of the cooperative tree update (<= 148)
 extern int g_tune_per_cluster;       // PER sampling cluster: 0 auto, 8 (x512 threads) or 16 (x256)
 extern int g_tune_segtree_ranged;  // 1 (default): per-CTA leaf ranges with a shared-memory table; 0: tiered
+extern int g_tune_gae_rows_packed;  // 1 (default): short contiguous rows go through the pipelined-ranges kernel
 extern int g_tune_gae_balance;  // 1: persistent GAE grids sized so that all CTAs get equal work (measured slower: default 0)
 extern int g_tune_pdl;  // 1 (default): PER and GAE rows kernels are launched with programmatic stream serialization
 extern int g_tune_segtree_group;  // 128 (default) or 256 nodes per warp-rebuilt group
