@@ -251,23 +251,51 @@ def run_b200(args):
     stream = torch.cuda.current_stream()
     launches = 0
 
-    def gae_step():
+    def gae_step(s=None):
         L.check(lib.ts_gae_rows(
             d_rew.data_ptr(), d_vs.data_ptr(), d_vn.data_ptr(), d_term.data_ptr(),
             d_trunc.data_ptr(), E, T, T, T, GAMMA, LAMBDA, L.TS_F32, L.TS_F32, L.TS_F32,
-            adv.data_ptr(), ret.data_ptr(), stream.cuda_stream), "ts_gae_rows")
+            adv.data_ptr(), ret.data_ptr(), s if s is not None else stream.cuda_stream),
+            "ts_gae_rows")
 
     sampler = ClockSampler(local)
+    # The K timed steps are K launches of the same C-ABI call; they are issued as replays of a
+    # CUDA graph of GRAPH_STEPS launches (plus an eager remainder) so that the host never sits
+    # between two launches.  TS_BENCH_GRAPH_STEPS=1 times the plain eager loop instead.
+    graph_steps = max(1, min(K, int(os.environ.get("TS_BENCH_GRAPH_STEPS", "100"))))
+    graph = None
+    if graph_steps > 1:
+        try:
+            side = torch.cuda.Stream(dev)
+            side.wait_stream(stream)
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    gae_step(side.cuda_stream)
+            side.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=side):
+                for _ in range(graph_steps):
+                    gae_step(side.cuda_stream)
+        except Exception as e:  # pragma: no cover - capture is expected to work on the GPU box
+            print(f"graph capture of the GAE loop failed ({e}); timing the eager loop",
+                  file=sys.stderr)
+            graph, graph_steps = None, 1
+
+    def run_steps(n):
+        if graph is not None:
+            for _ in range(n // graph_steps):
+                graph.replay()
+            n = n % graph_steps
+        for _ in range(n):
+            gae_step()
 
     def timed_gae():
-        for _ in range(W):
-            gae_step()
+        run_steps(max(W, graph_steps if graph is not None else W))
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with sampler:
             e0.record(stream)
-            for _ in range(K):
-                gae_step()
+            run_steps(K)
             e1.record(stream)
             barrier()
         return e0.elapsed_time(e1)  # ms on the launching stream
@@ -386,6 +414,8 @@ def run_b200(args):
                        "streams_per_gpu": E, "horizon": T, "storage": "f32 values, u8 flags",
                        "l2": f"inputs+outputs {n_trans * 22 / 1e6:.0f} MB per step > 126 MB L2 "
                              "(no flush needed)",
+                       "timed_loop": (f"CUDA graph of {graph_steps} launches of ts_gae_rows, replayed"
+                                      if graph is not None else "eager launches of ts_gae_rows"),
                        "parallelism": f"env streams sharded over {world} GPU(s), no collective"},
             "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "cpu_baseline": cpu, "per": per,
