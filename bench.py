@@ -598,13 +598,15 @@ def run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
             "scaling": scaling,
             "workload": f"{world} shard(s) x 2^20-leaf f64 sum tree, global batch 4096, alpha 0.6 "
                         "beta 0.4; step = sample (descent + IS weights + batch-max norm) + "
-                        "update_weight (|td|+eps, pow, dedupe, tiered rebuild, one cooperative "
-                        "launch); " + how,
+                        "update_weight (|td|+eps, pow, last-writer table in shared memory, "
+                        "per-range rebuild, one launch; programmatic dependent launch on both "
+                        "kernels); " + how,
             "gpu_launches_per_step": launches_per_step,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak,
-                         "note": "latency-bound: ~20 dependent L2 round trips of ~0.5 us per "
-                                 "step, not bytes; tree is L2-resident"}}
+                         "note": "latency-bound: ~10 dependent L2 round trips of ~0.5 us per "
+                                 "step plus launch and barrier latency, not bytes; the tree is "
+                                 "L2-resident"}}
 
 
 _RESULT_FD = None
