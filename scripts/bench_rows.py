@@ -97,6 +97,33 @@ def fill_vec(buf, E, T, rng, p_term=1 / 1000, p_trunc=1 / 10000, rew3=True):
     return rew, term, trunc
 
 
+def row_gae_api():
+    """a1 through the drop-in API: BasePolicy.compute_episodic_return(batch, buffer, indices,
+    v_s_, v_s) on a device VectorReplayBuffer (sample(0), CUDA tensors in and out), beside the
+    oracle port on one core and the survey's probe of the reference (2.38 ms at C3)."""
+    for E, T in ((64, 2048), (4096, 2048)):
+        rng = np.random.default_rng(9)
+        buf = ts.VectorReplayBuffer(E * T, E, rew_dtype=torch.float32)
+        rew, term, trunc = fill_vec(buf, E, T, rng, 1 / 200, 1 / 1000, rew3=False)
+        batch, indices = buf.sample(0)
+        v_s = torch.randn(E * T, device=DEV)
+        v_n = torch.randn(E * T, device=DEV)
+        us = gpu_us(lambda: ts.BasePolicy.compute_episodic_return(batch, buf, indices, v_n, v_s,
+                                                                  0.99, 0.95), iters=100)
+        # same call with indices that are NOT the canonical tensor: general flat path
+        idx2 = indices.clone()
+        us_flat = gpu_us(lambda: ts.BasePolicy.compute_episodic_return(
+            batch, buf, idx2, v_n, v_s, 0.99, 0.95), iters=100)
+        r2 = rew.reshape(E, T).astype(np.float32)
+        vs_np, vn_np = v_s.cpu().numpy().reshape(E, T), v_n.cpu().numpy().reshape(E, T)
+        t2, c2 = term.reshape(E, T), trunc.reshape(E, T)
+        cus = cpu_us(lambda: orc.episodic_return_rows(r2, vs_np, vn_np, t2, c2, 0.99, 0.95),
+                     seconds=1.0)
+        emit("a1 compute_episodic_return (API)", E=E, T=T, canonical_us=us, general_indices_us=us_flat,
+             cpu_port_us=cus, speedup=cus / us,
+             reference_probe_us=2380.0 if (E, T) == (64, 2048) else None)
+
+
 def row_gae_flat():
     """a1, general form: arbitrary indices (a rotated buffer), decoupled look-back."""
     for E, T in ((4096, 2048), (64, 2048)):
@@ -382,6 +409,6 @@ def row_ppo():
 
 if __name__ == "__main__":
     torch.cuda.set_device(0)
-    which = sys.argv[1:] or ["gae_flat", "nstep_index", "gather", "gather_stack", "add", "ppo"]
+    which = sys.argv[1:] or ["gae_api", "gae_flat", "nstep_index", "gather", "gather_stack", "add", "ppo"]
     for w in which:
         globals()["row_" + w]()
