@@ -117,11 +117,20 @@ class ReplayBuffer:
 
     def __getstate__(self) -> Dict[str, Any]:
         """Pickle as host arrays (base.py:81-87; test/base/test_buffer.py:597-632)."""
+        if getattr(self, "_ep_on_device", False):
+            self._pull_episode_stats()  # manager: running episode statistics back to the host
         state = dict(self.__dict__)
-        meta = Batch(self._meta)
-        state["_meta"] = _batch_to_numpy_copy(meta)
-        state["_dev_state"] = None
+        if state.get("_parent") is not None:
+            state["_meta"] = Batch()  # a sub-buffer's storage is a view: the manager restores it
+        else:
+            state["_meta"] = _batch_to_numpy_copy(Batch(self._meta))
+        # caches that hold device addresses or ctypes arrays are rebuilt on demand
+        for key in ("_dev_state", "_dev_add", "_dev_add_keys", "_canon", "_cached_weight"):
+            if key in state:
+                state[key] = None
         state["_dev_state_version"] = -1
+        if "_dev_add_version" in state:
+            state["_dev_add_version"] = -1
         state["device"] = str(self.device)
         return state
 

@@ -60,6 +60,17 @@ class ReplayBufferManager(ReplayBuffer):
     def __len__(self) -> int:
         return int(self._lengths.sum())
 
+    def __setstate__(self, state: Dict[str, Any]) -> None:
+        """After unpickling, the sub-buffers alias the manager's bookkeeping rows and hold views
+        of its storage again (manager.py:60-62); NumPy views do not survive a pickle."""
+        super().__setstate__(state)
+        for k, buf in enumerate(self.buffers):
+            buf.__dict__["_ring"] = self._rings[k]
+            buf.__dict__["last_index"] = self._child_last[k]
+            buf.__dict__["_parent"] = self
+        if not self._meta.is_empty():
+            self._set_batch_for_children()
+
     def reset(self, keep_statistics: bool = False) -> None:
         self.last_index = self._offset.copy()  # manager.py:55
         self._lengths = np.zeros_like(self._offset)
