@@ -370,6 +370,153 @@ def gen_ppo(ts, out):
     np.savez_compressed(os.path.join(out, "ppo.npz"), **flat)
 
 
+PPO_UPDATE_SPECS = [
+    # name, kwargs of PPOPolicy, batch_size, repeat, number of update() calls
+    ("clip_norm", dict(eps_clip=0.2, value_clip=True, advantage_normalization=True, vf_coef=0.5,
+                       ent_coef=0.01, max_grad_norm=0.5, gae_lambda=0.95, discount_factor=0.99),
+     64, 2, 1),
+    ("rewnorm_recompute_dual", dict(eps_clip=0.1, dual_clip=3.0, value_clip=False,
+                                    advantage_normalization=False, recompute_advantage=True,
+                                    reward_normalization=True, vf_coef=0.25, ent_coef=0.0,
+                                    max_grad_norm=None, gae_lambda=0.9, discount_factor=0.97,
+                                    max_batchsize=300),
+     128, 3, 2),
+]
+
+
+def ppo_update_nets(torch):
+    """Actor / critic of the PPO-update goldens (shared with tests/test_gpu_ppo.py)."""
+
+    class Actor(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.net = torch.nn.Sequential(torch.nn.Linear(3, 64), torch.nn.Tanh(),
+                                           torch.nn.Linear(64, 4))
+
+        def forward(self, obs, state=None, info=None):
+            obs = torch.as_tensor(obs, dtype=torch.float32,
+                                  device=self.net[0].weight.device)
+            return self.net(obs), state
+
+    class Critic(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.net = torch.nn.Sequential(torch.nn.Linear(3, 64), torch.nn.Tanh(),
+                                           torch.nn.Linear(64, 1))
+
+        def forward(self, obs, **kw):
+            obs = torch.as_tensor(obs, dtype=torch.float32,
+                                  device=self.net[0].weight.device)
+            return self.net(obs)
+
+    return Actor, Critic
+
+
+def gen_ppo_update(ts, out):
+    """``PPOPolicy.update`` of the reference itself on CPU (policy/base.py:288-315 ->
+    ppo.py:87-162, a2c.py:83-117) over a 20 x 100 rollout (test/discrete/test_ppo.py:29-33
+    shape): returns / advantages / logp_old of the first ``process_fn``, the logged losses
+    of every minibatch, the return statistics and the parameters after the update(s)."""
+    import torch
+    from tianshou.data import Batch, VectorReplayBuffer
+    from tianshou.policy import PPOPolicy
+
+    Actor, Critic = ppo_update_nets(torch)
+    flat = {}
+    for name, kw, batch_size, repeat, n_updates in PPO_UPDATE_SPECS:
+        buf = VectorReplayBuffer(20 * 100, 20)
+        fill_vecbuf(buf, Batch, np.random.default_rng(700), 100, 20, 0.03, 0.01)
+        torch.manual_seed(1)
+        actor, critic = Actor(), Critic()
+        optim = torch.optim.Adam(list(actor.parameters()) + list(critic.parameters()), lr=3e-4)
+        for k, v in actor.state_dict().items():
+            flat[f"{name}/init/actor/{k}"] = v.numpy().copy()
+        for k, v in critic.state_dict().items():
+            flat[f"{name}/init/critic/{k}"] = v.numpy().copy()
+        policy = PPOPolicy(actor, critic, optim,
+                           lambda logits: torch.distributions.Categorical(logits=logits),
+                           action_scaling=False, **kw)
+        seen = []
+        inner = policy.process_fn
+
+        def spy(batch, buffer, indices, inner=inner, seen=seen):
+            batch = inner(batch, buffer, indices)
+            seen.append({k: np.asarray(batch[k].detach().numpy()).copy()
+                         for k in ("returns", "adv", "v_s", "logp_old")})
+            return batch
+
+        policy.process_fn = spy
+        np.random.seed(7)
+        for u in range(n_updates):
+            res = policy.update(0, buf, batch_size=batch_size, repeat=repeat)
+            for k, v in res.items():
+                flat[f"{name}/u{u}/{k}"] = np.asarray(v, dtype=np.float64)
+            for k, v in seen[u].items():
+                flat[f"{name}/u{u}/{k}"] = v
+            flat[f"{name}/u{u}/ret_rms"] = np.array(
+                [policy.ret_rms.mean, policy.ret_rms.var, policy.ret_rms.count], np.float64)
+        for k, v in actor.state_dict().items():
+            flat[f"{name}/final/actor/{k}"] = v.numpy().copy()
+        for k, v in critic.state_dict().items():
+            flat[f"{name}/final/critic/{k}"] = v.numpy().copy()
+    np.savez_compressed(os.path.join(out, "ppo_update.npz"), **flat)
+
+
+def gen_pg_a2c_update(ts, out):
+    """``PGPolicy.update`` (pg.py:87-120, 174-192) and ``A2CPolicy.update`` (a2c.py:77-161) of the
+    reference on the rollout of gen_ppo_update, with return normalisation on, two updates."""
+    import torch
+    from tianshou.data import Batch, VectorReplayBuffer
+    from tianshou.policy import A2CPolicy, PGPolicy
+
+    Actor, Critic = ppo_update_nets(torch)
+    flat = {}
+    for name in ("pg", "a2c"):
+        buf = VectorReplayBuffer(20 * 100, 20)
+        fill_vecbuf(buf, Batch, np.random.default_rng(700), 100, 20, 0.03, 0.01)
+        torch.manual_seed(2)
+        actor, critic = Actor(), Critic()
+        dist_fn = lambda logits: torch.distributions.Categorical(logits=logits)  # noqa: E731
+        if name == "pg":
+            optim = torch.optim.Adam(actor.parameters(), lr=1e-3)
+            policy = PGPolicy(actor, optim, dist_fn, discount_factor=0.95,
+                              reward_normalization=True, action_scaling=False)
+            keys = ("returns",)
+        else:
+            optim = torch.optim.Adam(list(actor.parameters()) + list(critic.parameters()),
+                                     lr=1e-3)
+            policy = A2CPolicy(actor, critic, optim, dist_fn, vf_coef=0.5, ent_coef=0.01,
+                               max_grad_norm=0.5, gae_lambda=0.9, discount_factor=0.98,
+                               reward_normalization=True, action_scaling=False)
+            keys = ("returns", "adv", "v_s")
+        for tag, net in (("actor", actor), ("critic", critic)):
+            for k, v in net.state_dict().items():
+                flat[f"{name}/init/{tag}/{k}"] = v.numpy().copy()
+        seen = []
+        inner = policy.process_fn
+
+        def spy(batch, buffer, indices, inner=inner, seen=seen, keys=keys):
+            batch = inner(batch, buffer, indices)
+            seen.append({k: np.asarray(batch[k].detach().numpy() if hasattr(batch[k], "detach")
+                                       else batch[k]).copy() for k in keys})
+            return batch
+
+        policy.process_fn = spy
+        np.random.seed(9)
+        for u in range(2):
+            res = policy.update(0, buf, batch_size=100, repeat=2)
+            for k, v in res.items():
+                flat[f"{name}/u{u}/{k}"] = np.asarray(v, dtype=np.float64)
+            for k, v in seen[u].items():
+                flat[f"{name}/u{u}/{k}"] = v
+            flat[f"{name}/u{u}/ret_rms"] = np.array(
+                [policy.ret_rms.mean, policy.ret_rms.var, policy.ret_rms.count], np.float64)
+        for tag, net in (("actor", actor), ("critic", critic)):
+            for k, v in net.state_dict().items():
+                flat[f"{name}/final/{tag}/{k}"] = v.numpy().copy()
+    np.savez_compressed(os.path.join(out, "pg_a2c_update.npz"), **flat)
+
+
 STACK_SPECS = [
     # name, n_env, total, steps, stack_num, ragged, frame shape (make_golden.gen_stack)
     ("atari_like", 4, 80, 13, 4, False, (6,)),
@@ -444,6 +591,8 @@ def main():
     gen_segtree(ts, HERE)
     gen_per(ts, HERE)
     gen_ppo(ts, HERE)
+    gen_ppo_update(ts, HERE)
+    gen_pg_a2c_update(ts, HERE)
     gen_stack(ts, HERE)
     with open(os.path.join(HERE, "versions.json"), "w") as f:
         json.dump({"tianshou": ts.__version__, "numpy": np.__version__,

@@ -99,3 +99,46 @@ def random_rings(rng, B, cap, p_done=0.02):
     last = (offset[:-1] + rng.integers(0, lengths)).astype(np.int64)
     done = rng.random(B * cap) < p_done
     return offset, done, last, lengths
+
+
+# ---- PPO update goldens (make_golden.gen_ppo_update) -------------------------------------------
+PPO_UPDATE_SPECS = [
+    # name, kwargs of PPOPolicy, batch_size, repeat, number of update() calls
+    ("clip_norm", dict(eps_clip=0.2, value_clip=True, advantage_normalization=True, vf_coef=0.5,
+                       ent_coef=0.01, max_grad_norm=0.5, gae_lambda=0.95, discount_factor=0.99),
+     64, 2, 1),
+    ("rewnorm_recompute_dual", dict(eps_clip=0.1, dual_clip=3.0, value_clip=False,
+                                    advantage_normalization=False, recompute_advantage=True,
+                                    reward_normalization=True, vf_coef=0.25, ent_coef=0.0,
+                                    max_grad_norm=None, gae_lambda=0.9, discount_factor=0.97,
+                                    max_batchsize=300),
+     128, 3, 2),
+]
+
+
+def ppo_update_nets(torch):
+    """Actor / critic of the PPO-update goldens (shared with tests/test_gpu_ppo.py)."""
+
+    class Actor(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.net = torch.nn.Sequential(torch.nn.Linear(3, 64), torch.nn.Tanh(),
+                                           torch.nn.Linear(64, 4))
+
+        def forward(self, obs, state=None, info=None):
+            obs = torch.as_tensor(obs, dtype=torch.float32,
+                                  device=self.net[0].weight.device)
+            return self.net(obs), state
+
+    class Critic(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.net = torch.nn.Sequential(torch.nn.Linear(3, 64), torch.nn.Tanh(),
+                                           torch.nn.Linear(64, 1))
+
+        def forward(self, obs, **kw):
+            obs = torch.as_tensor(obs, dtype=torch.float32,
+                                  device=self.net[0].weight.device)
+            return self.net(obs)
+
+    return Actor, Critic

@@ -148,3 +148,116 @@ def test_cartpole_shaped_ppo_update_end_to_end():
     assert np.allclose(result["loss"][:5], ref_losses[:5], rtol=1e-4, atol=1e-5)
     for p, q in zip(policy._params, params):
         assert torch.allclose(p, q, rtol=1e-3, atol=1e-4)
+
+
+# ---- PPOPolicy.update against the reference's own update (tests/golden/ppo_update.npz) -----------
+def _load_nets(case):
+    from helpers import ppo_update_nets
+    Actor, Critic = ppo_update_nets(torch)
+    actor, critic = Actor(), Critic()
+    for net, tag in ((actor, "actor"), (critic, "critic")):
+        sd = {k[len(f"init/{tag}/"):]: torch.from_numpy(v) for k, v in case.items()
+              if k.startswith(f"init/{tag}/")}
+        net.load_state_dict(sd)
+    return actor.cuda(), critic.cuda()
+
+
+@pytest.mark.parametrize("graph", [False, True], ids=["eager", "cuda_graph"])
+@pytest.mark.parametrize("name", ["clip_norm", "rewnorm_recompute_dual"])
+def test_ppo_update_vs_reference_update(name, graph):
+    """The reference's ``PPOPolicy.update`` (run on CPU by make_golden.gen_ppo_update) against
+    this package's on the same rollout, initial weights and numpy seed: returns / advantages /
+    logp_old of process_fn, every minibatch's logged losses, the running return statistics
+    and the parameters after the update(s).  Tolerances: f32 networks on two devices."""
+    import tianshou_fork_b200 as ts
+    from helpers import PPO_UPDATE_SPECS, fill
+    case = load_golden("ppo_update")[name]
+    _, kw, batch_size, repeat, n_updates = next(s for s in PPO_UPDATE_SPECS if s[0] == name)
+    buf = ts.VectorReplayBuffer(20 * 100, 20)
+    fill(buf, ts.Batch, 700, 100, 20, 0.03, 0.01)
+    actor, critic = _load_nets(case)
+    optim = torch.optim.Adam(list(actor.parameters()) + list(critic.parameters()), lr=3e-4)
+    policy = ts.PPOPolicy(actor, critic, optim,
+                          lambda logits: torch.distributions.Categorical(logits=logits),
+                          action_scaling=False, cuda_graph=graph, **kw)
+    seen = []
+    inner = policy.process_fn
+
+    def spy(batch, buffer, indices):
+        batch = inner(batch, buffer, indices)
+        seen.append({k: batch[k].detach().cpu().numpy().copy()
+                     for k in ("returns", "adv", "v_s", "logp_old")})
+        return batch
+
+    policy.process_fn = spy
+    np.random.seed(7)
+    for u in range(n_updates):
+        res = policy.update(0, buf, batch_size=batch_size, repeat=repeat)
+        tol = 1e-4 if u == 0 else 2e-3  # the second update starts from updated weights
+        for k in ("returns", "adv", "v_s", "logp_old"):
+            assert np.allclose(seen[u][k], case[f"u{u}/{k}"], rtol=tol, atol=tol), (u, k)
+        for k in ("loss", "loss/clip", "loss/vf", "loss/ent"):
+            got, want = np.asarray(res[k]), case[f"u{u}/{k}"]
+            assert got.shape == want.shape
+            assert np.allclose(got, want, rtol=5e-3, atol=5e-4), (u, k)
+            if u == 0:
+                assert np.allclose(got[:4], want[:4], rtol=1e-4, atol=1e-5), (u, k)
+        mean, var, count = case[f"u{u}/ret_rms"]
+        assert policy.ret_rms.count == int(count)
+        assert np.isclose(policy.ret_rms.mean.item(), mean, rtol=1e-3, atol=1e-4)
+        assert np.isclose(policy.ret_rms.var.item(), var, rtol=1e-3)
+    for net, tag in ((actor, "actor"), (critic, "critic")):
+        for k, v in net.state_dict().items():
+            assert np.allclose(v.cpu().numpy(), case[f"final/{tag}/{k}"], rtol=2e-3, atol=2e-4), k
+
+
+def test_graphed_learn_equals_eager_learn():
+    """cuda_graph=True replays the eager minibatch step kernel for kernel: same losses and
+    parameters (MuJoCo-like continuous actions, merged tail, two learn calls, lr change)."""
+    import tianshou_fork_b200 as ts
+    E, T, D, A = 8, 50, 11, 3
+    rng = np.random.default_rng(3)
+    buf = ts.VectorReplayBuffer(E * T, E)
+    for t in range(T):
+        buf.add(ts.Batch(obs=rng.standard_normal((E, D)).astype(np.float32),
+                         act=rng.standard_normal((E, A)).astype(np.float32),
+                         rew=rng.standard_normal(E), terminated=rng.random(E) < 0.05,
+                         truncated=np.zeros(E, bool),
+                         obs_next=rng.standard_normal((E, D)).astype(np.float32), info={}))
+
+    class Actor(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.mu = torch.nn.Sequential(torch.nn.Linear(D, 32), torch.nn.Tanh(),
+                                          torch.nn.Linear(32, A))
+            self.sigma = torch.nn.Parameter(torch.zeros(A))
+
+        def forward(self, obs, state=None, info=None):
+            mu = self.mu(obs)
+            return (mu, self.sigma.exp().expand_as(mu)), state
+
+    def dist_fn(mu, sigma):
+        return torch.distributions.Independent(torch.distributions.Normal(mu, sigma), 1)
+
+    out = []
+    for graph in (False, True):
+        torch.manual_seed(5)
+        actor = Actor().cuda()
+        critic = torch.nn.Sequential(torch.nn.Linear(D, 32), torch.nn.Tanh(),
+                                     torch.nn.Linear(32, 1)).cuda()
+        optim = torch.optim.Adam(list(actor.parameters()) + list(critic.parameters()), lr=1e-3)
+        policy = ts.PPOPolicy(actor, critic, optim, dist_fn, value_clip=True, max_grad_norm=0.5,
+                              cuda_graph=graph)
+        np.random.seed(11)
+        r1 = policy.update(0, buf, batch_size=96, repeat=3)  # 400 = 3 x 96 + merged 112
+        for g in optim.param_groups:
+            g["lr"] = 5e-4  # what an lr scheduler does between updates
+        r2 = policy.update(0, buf, batch_size=96, repeat=2)
+        out.append((r1, r2, [p.detach().clone() for p in policy._params]))
+    (e1, e2, ep), (g1, g2, gp) = out
+    assert len(g1["loss"]) == 12 and len(g2["loss"]) == 8
+    for a, b in ((e1, g1), (e2, g2)):
+        for k in a:
+            assert np.allclose(a[k], b[k], rtol=1e-5, atol=1e-6), k
+    for p, q in zip(ep, gp):
+        assert torch.allclose(p, q, rtol=1e-5, atol=1e-6)

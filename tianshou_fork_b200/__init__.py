@@ -16,12 +16,13 @@ from . import _lib
 from .data import (Batch, PrioritizedReplayBuffer, PrioritizedReplayBufferManager,
                    PrioritizedVectorReplayBuffer, ReplayBuffer, ReplayBufferManager,
                    SegmentTree, ShardedPrioritizedVectorReplayBuffer, VectorReplayBuffer)
-from .policy import BasePolicy, PPOPolicy, ppo_loss
+from .policy import A2CPolicy, BasePolicy, PGPolicy, PPOPolicy, ppo_loss
 
 __version__ = "0.1.0"
 
 __all__ = [
     "Batch", "ReplayBuffer", "ReplayBufferManager", "VectorReplayBuffer",
     "PrioritizedReplayBuffer", "PrioritizedReplayBufferManager",
-    "PrioritizedVectorReplayBuffer", "ShardedPrioritizedVectorReplayBuffer", "SegmentTree", "BasePolicy", "PPOPolicy", "ppo_loss",
+    "PrioritizedVectorReplayBuffer", "ShardedPrioritizedVectorReplayBuffer", "SegmentTree",
+    "BasePolicy", "PGPolicy", "A2CPolicy", "PPOPolicy", "ppo_loss",
 ]

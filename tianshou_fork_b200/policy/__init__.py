@@ -1,5 +1,8 @@
-"""Return estimators and the fused PPO loss (mirror of ``tianshou.policy`` for the hot path)."""
+"""Return estimators, the policies around them and the fused PPO loss (mirror of
+``tianshou.policy`` for the hot path: BasePolicy <- PGPolicy <- A2CPolicy <- PPOPolicy)."""
+from .a2c import A2CPolicy
 from .base import BasePolicy
-from .ppo import PPOPolicy, RunningMeanStd, ppo_loss
+from .pg import PGPolicy, RunningMeanStd
+from .ppo import PPOPolicy, ppo_loss
 
-__all__ = ["BasePolicy", "PPOPolicy", "RunningMeanStd", "ppo_loss"]
+__all__ = ["BasePolicy", "PGPolicy", "A2CPolicy", "PPOPolicy", "RunningMeanStd", "ppo_loss"]

@@ -17,6 +17,7 @@ from typing import Any, Callable, Dict, Optional, Tuple, Union
 
 import numpy as np
 import torch
+from torch import nn
 
 from .. import _lib as L
 from ..data.batch import Batch
@@ -85,16 +86,42 @@ def _buffer_layout(buffer: Any, device: torch.device):
             L.as_u8(_dev(buffer.terminated, device, torch.bool)))
 
 
-class BasePolicy:
+class BasePolicy(nn.Module):
     """Static return estimators with the reference's signatures (policy/base.py:317-440).
 
-    The surrounding ``update`` pipeline (``sample -> process_fn -> learn -> post_process_fn``,
-    policy/base.py:288-315) is kept for subclasses in this package.
+    Like the reference class it is a ``torch.nn.Module`` (``state_dict`` / ``train`` / ``eval``
+    work, policy/base.py:62-70) and keeps the surrounding ``update`` pipeline
+    (``sample -> process_fn -> learn -> post_process_fn``, policy/base.py:288-315).  The
+    constructor takes the reference's keyword arguments (policy/base.py:72-109); action
+    scaling / bounding is the Collector's concern (``map_action``) and is only recorded here.
     """
 
-    def __init__(self) -> None:
+    def __init__(
+        self,
+        observation_space: Any = None,
+        action_space: Any = None,
+        action_scaling: bool = False,
+        action_bound_method: Optional[str] = None,
+        lr_scheduler: Optional[Any] = None,
+    ) -> None:
+        if action_bound_method is not None:
+            assert action_bound_method in ("clip", "tanh")
+        super().__init__()
+        if isinstance(action_space, list):  # vector envs (policy/base.py:91-92)
+            action_space = action_space[0]
+        self.observation_space = observation_space
+        self.action_space = action_space
+        self.agent_id = 0
         self.updating = False
-        self.lr_scheduler = None
+        self.action_scaling = action_scaling
+        self.action_bound_method = action_bound_method
+        self.lr_scheduler = lr_scheduler
+
+    def set_agent_id(self, agent_id: int) -> None:
+        self.agent_id = agent_id
+
+    def forward(self, batch: Batch, state: Any = None, **kwargs: Any) -> Batch:
+        raise NotImplementedError
 
     # ---- update pipeline (policy/base.py:244-315) -----------------------------------------------
     def process_fn(self, batch: Batch, buffer: Any, indices: ArrayLike) -> Batch:

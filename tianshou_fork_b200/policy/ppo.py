@@ -12,6 +12,11 @@ What changes relative to the reference:
   minibatch (ppo.py:152-155).
 * minibatch indices come from the host ``np.random.permutation`` exactly as ``Batch.split``
   draws them (data/batch.py:896-912), so a seeded run visits the same minibatches.
+* ``cuda_graph=True`` (opt-in): one minibatch step -- index gather, actor and
+  critic forward, fused loss, backward, gradient clipping, optimiser step, loss logging -- is
+  captured once per minibatch size into a CUDA graph that advances its own cursor into the
+  epoch's permutation on the device, so ``learn`` is one graph launch per minibatch and one
+  host sync per call.  The arithmetic is the eager path's, kernel for kernel.
 """
 from __future__ import annotations
 
@@ -23,7 +28,8 @@ from torch import nn
 
 from .. import _lib as L
 from ..data.batch import Batch
-from .base import BasePolicy
+from .a2c import A2CPolicy
+from .pg import RunningMeanStd, _minibatches, _split_bounds  # noqa: F401 (re-exported)
 
 _loss_ws: Dict[int, torch.Tensor] = {}
 
@@ -92,33 +98,12 @@ def ppo_loss(logp: torch.Tensor, value: torch.Tensor, logp_old: torch.Tensor,
                           dual_clip, value_clip, norm_adv, eps)
 
 
-class RunningMeanStd:
-    """Running mean / variance of a stream (tianshou/utils/statistics.py:69-114) kept in
-    device scalars so that return normalisation (a2c.py:98-112) does not sync."""
-
-    def __init__(self, device: torch.device, eps: float = np.finfo(np.float32).eps.item()):
-        self.mean = torch.zeros((), dtype=torch.float64, device=device)
-        self.var = torch.ones((), dtype=torch.float64, device=device)
-        self.count = 0
-        self.eps = eps
-
-    def update(self, x: torch.Tensor) -> None:
-        x = x.to(torch.float64)
-        batch_mean, batch_var = x.mean(), x.var(unbiased=False)
-        batch_count = x.numel()
-        delta = batch_mean - self.mean
-        total = self.count + batch_count
-        new_mean = self.mean + delta * batch_count / total
-        m_a, m_b = self.var * self.count, batch_var * batch_count
-        m_2 = m_a + m_b + delta ** 2 * self.count * batch_count / total
-        self.mean, self.var, self.count = new_mean, m_2 / total, total
-
-
-class PPOPolicy(BasePolicy):
+class PPOPolicy(A2CPolicy):
     """PPO (arXiv:1707.06347) with GAE on the device and the fused clip loss.
 
     Constructor arguments follow the reference (ppo.py:63-86, a2c.py:48-75, pg.py:49-85):
-    ``actor(obs) -> (logits, state)``, ``critic(obs) -> value``, ``dist_fn(*logits)``.
+    ``actor(obs, state=, info=) -> (logits, state)``, ``critic(obs) -> value``,
+    ``dist_fn(*logits)``.  ``cuda_graph`` is this package's addition (see the module docstring).
     """
 
     def __init__(
@@ -132,115 +117,61 @@ class PPOPolicy(BasePolicy):
         value_clip: bool = False,
         advantage_normalization: bool = True,
         recompute_advantage: bool = False,
-        vf_coef: float = 0.5,
-        ent_coef: float = 0.01,
-        max_grad_norm: Optional[float] = None,
-        gae_lambda: float = 0.95,
-        max_batchsize: int = 256,
-        discount_factor: float = 0.99,
-        reward_normalization: bool = False,
-        lr_scheduler: Optional[Any] = None,
+        cuda_graph: bool = False,
+        **kwargs: Any,
     ) -> None:
-        super().__init__()
-        self.actor, self.critic, self.optim, self.dist_fn = actor, critic, optim, dist_fn
+        super().__init__(actor, critic, optim, dist_fn, **kwargs)
+        self._eps_clip = eps_clip
         assert dual_clip is None or dual_clip > 1.0, \
             "Dual-clip PPO parameter should greater than 1.0."
-        assert 0.0 <= gae_lambda <= 1.0, "GAE lambda should be in [0, 1]."
-        assert 0.0 <= discount_factor <= 1.0, "discount factor should be in [0, 1]"
-        self._eps_clip, self._dual_clip, self._value_clip = eps_clip, dual_clip, value_clip
-        self._norm_adv, self._recompute_adv = advantage_normalization, recompute_advantage
-        self._weight_vf, self._weight_ent, self._grad_norm = vf_coef, ent_coef, max_grad_norm
-        self._lambda, self._batch, self._gamma = gae_lambda, max_batchsize, discount_factor
-        self._rew_norm = reward_normalization
-        self._eps = 1e-8
-        self.lr_scheduler = lr_scheduler
-        self.device = next(actor.parameters()).device
-        self.ret_rms = RunningMeanStd(self.device)
-        self._params = list(actor.parameters()) + [
-            p for p in critic.parameters() if all(p is not q for q in actor.parameters())]
+        self._dual_clip = dual_clip
+        self._value_clip = value_clip
+        self._norm_adv = advantage_normalization
+        self._recompute_adv = recompute_advantage
+        self._cuda_graph = cuda_graph
+        self._graphs: Optional[_GraphedLearner] = None
 
-    # ---- forward (pg.py:122-160) ------------------------------------------------------------------
-    def __call__(self, batch: Batch, state: Any = None) -> Batch:
-        logits, hidden = self.actor(batch.obs, state=state)
-        dist = self.dist_fn(*logits) if isinstance(logits, tuple) else self.dist_fn(logits)
-        return Batch(logits=logits, state=hidden, dist=dist)
-
-    # ---- returns (a2c.py:83-117) ------------------------------------------------------------------
-    def _values(self, obs: torch.Tensor) -> torch.Tensor:
-        n = obs.shape[0]
-        # Batch.split(self._batch, shuffle=False, merge_last=True)  (a2c.py:88)
-        out = [self.critic(obs[lo:hi]) for lo, hi in _split_bounds(n, self._batch, True)]
-        return torch.cat(out, dim=0).flatten()
-
-    def _compute_returns(self, batch: Batch, buffer: Any, indices: torch.Tensor) -> Batch:
-        with torch.no_grad():
-            batch.v_s = self._values(batch.obs)  # old value
-            v_s_ = self._values(batch.obs_next)
-        v_s = batch.v_s
-        if self._rew_norm:  # unnormalize v_s & v_s_  (a2c.py:98-100)
-            scale = torch.sqrt(self.ret_rms.var + self._eps).to(v_s.dtype)
-            v_s, v_s_ = v_s * scale, v_s_ * scale
-        unnormalized_returns, advantages = self.compute_episodic_return(
-            batch, buffer, indices, v_s_, v_s, gamma=self._gamma, gae_lambda=self._lambda)
-        if self._rew_norm:  # a2c.py:110-112
-            batch.returns = unnormalized_returns / torch.sqrt(
-                self.ret_rms.var + self._eps).to(unnormalized_returns.dtype)
-            self.ret_rms.update(unnormalized_returns)
-        else:
-            batch.returns = unnormalized_returns
-        batch.returns = batch.returns.to(batch.v_s.dtype)
-        batch.adv = advantages.to(batch.v_s.dtype)
-        return batch
-
-    def process_fn(self, batch: Batch, buffer: Any, indices: torch.Tensor) -> Batch:
-        if self._recompute_adv:
+    def process_fn(self, batch: Batch, buffer: Any, indices: Any) -> Batch:
+        if self._recompute_adv:  # ppo.py:90-92
             self._buffer, self._indices = buffer, indices
         batch = self._compute_returns(batch, buffer, indices)
-        act = batch.act
-        if not isinstance(act, torch.Tensor):
-            act = torch.as_tensor(np.asarray(act), device=self.device)
-        batch.act = act.to(self.device)
+        batch.act = self._act_tensor(batch)
         with torch.no_grad():
-            batch.logp_old = self._log_prob(self(batch).dist, batch.act)
+            batch.logp_old = self._dist(batch.obs)[2].log_prob(batch.act)  # ppo.py:95-96
         return batch
 
-    @staticmethod
-    def _log_prob(dist, act: torch.Tensor) -> torch.Tensor:
-        return dist.log_prob(act)
+    def _flat(self, t: torch.Tensor, n: int, what: str) -> torch.Tensor:
+        t = t.detach().reshape(-1).float().contiguous()
+        assert t.numel() == n, f"{what} must be one scalar per transition"
+        return t
+
+    def _minibatch_step(self, obs, act, mb, logp_old, adv, returns, v_s) -> torch.Tensor:
+        """ppo.py:106-151 for one minibatch; returns the four logged scalars (device)."""
+        dist = self._dist(obs)[2]
+        logp = dist.log_prob(act)
+        value = self.critic(obs).flatten()
+        clip_loss, vf_loss, _ = ppo_loss(
+            logp, value, logp_old, adv, returns, v_s, mb, self._eps_clip,
+            self._dual_clip, self._value_clip, self._norm_adv, self._eps)
+        ent_loss = dist.entropy().mean()
+        loss = clip_loss + self._weight_vf * vf_loss - self._weight_ent * ent_loss
+        self.optim.zero_grad()
+        loss.backward()
+        if self._grad_norm:
+            nn.utils.clip_grad_norm_(self._params, max_norm=self._grad_norm)
+        self.optim.step()
+        return torch.stack([loss.detach(), clip_loss.detach(), vf_loss.detach(),
+                            ent_loss.detach()])
 
     # ---- learn (ppo.py:99-162) ------------------------------------------------------------------
     def learn(self, batch: Batch, batch_size: int, repeat: int, **kwargs: Any
               ) -> Dict[str, List[float]]:
-        n = len(batch)
-        logged: List[torch.Tensor] = []
-        for step in range(repeat):
-            if self._recompute_adv and step > 0:
-                batch = self._compute_returns(batch, self._buffer, self._indices)
-            logp_old = batch.logp_old.detach().reshape(-1).float().contiguous()
-            adv = batch.adv.detach().reshape(-1).float().contiguous()
-            returns = batch.returns.detach().reshape(-1).float().contiguous()
-            v_s = batch.v_s.detach().reshape(-1).float().contiguous()
-            assert logp_old.numel() == n, "log_prob must be one scalar per transition"
-            perm = torch.from_numpy(np.random.permutation(n)).to(self.device)  # batch.py:905
-            for lo, hi in _split_bounds(n, batch_size, merge_last=True):
-                mb = perm[lo:hi]
-                obs, act = batch.obs[mb], batch.act[mb]
-                dist = self(Batch(obs=obs)).dist
-                logp = self._log_prob(dist, act)
-                value = self.critic(obs).flatten()
-                clip_loss, vf_loss, _ = ppo_loss(
-                    logp, value, logp_old, adv, returns, v_s, mb, self._eps_clip,
-                    self._dual_clip, self._value_clip, self._norm_adv, self._eps)
-                ent_loss = dist.entropy().mean()
-                loss = clip_loss + self._weight_vf * vf_loss - self._weight_ent * ent_loss
-                self.optim.zero_grad()
-                loss.backward()
-                if self._grad_norm:
-                    nn.utils.clip_grad_norm_(self._params, max_norm=self._grad_norm)
-                self.optim.step()
-                logged.append(torch.stack([loss.detach(), clip_loss.detach(),
-                                           vf_loss.detach(), ent_loss.detach()]))
-        table = torch.stack(logged).cpu().numpy() if logged else np.zeros((0, 4))  # one sync
+        if self._cuda_graph:
+            if self._graphs is None:
+                self._graphs = _GraphedLearner(self)
+            table = self._graphs.learn(batch, batch_size, repeat)
+        else:
+            table = self._learn_eager(batch, batch_size, repeat)
         return {
             "loss": table[:, 0].tolist(),
             "loss/clip": table[:, 1].tolist(),
@@ -248,17 +179,163 @@ class PPOPolicy(BasePolicy):
             "loss/ent": table[:, 3].tolist(),
         }
 
+    def _learn_eager(self, batch: Batch, batch_size: int, repeat: int) -> np.ndarray:
+        n = len(batch)
+        logged: List[torch.Tensor] = []
+        for step in range(repeat):
+            if self._recompute_adv and step > 0:
+                batch = self._compute_returns(batch, self._buffer, self._indices)
+            logp_old = self._flat(batch.logp_old, n, "log_prob")
+            adv = self._flat(batch.adv, n, "adv")
+            returns = self._flat(batch.returns, n, "returns")
+            v_s = self._flat(batch.v_s, n, "v_s")
+            for mb in _minibatches(n, batch_size, self.device):
+                logged.append(self._minibatch_step(batch.obs[mb], batch.act[mb], mb, logp_old,
+                                                   adv, returns, v_s))
+        return torch.stack(logged).cpu().numpy() if logged else np.zeros((0, 4))  # one sync
 
-def _split_bounds(n: int, size: int, merge_last: bool) -> List[Tuple[int, int]]:
-    """Chunk boundaries of ``Batch.split`` (data/batch.py:896-912)."""
-    if size == -1:
-        size = n
-    assert size >= 1
-    merge_last = merge_last and n % size > 0
-    out = []
-    for idx in range(0, n, size):
-        if merge_last and idx + size + size >= n:
-            out.append((idx, n))
-            break
-        out.append((idx, min(idx + size, n)))
-    return out
+
+class _GraphedLearner:
+    """``PPOPolicy.learn`` as CUDA-graph replays.
+
+    Static device state: the update's rows (``obs``, ``act``, ``logp_old``, ``adv``, ``returns``,
+    ``v_s``), the concatenated permutations of all epochs, a cursor into them, and the loss
+    log with its row counter.  A graph for minibatch size m reads ``perm[cursor : cursor + m]``,
+    runs ``PPOPolicy._minibatch_step`` and advances cursor and row itself, so replays need no
+    host input.  Graphs are keyed by (m, learning rates, train/eval mode) and dropped when a
+    static buffer has to grow.  Warm-up iterations run for real on a side stream (allocator
+    and lazy optimiser state), after which parameters, module buffers and optimiser state are
+    restored in place, so capture does not change the training trajectory.
+    """
+
+    LOG_ROWS = 1 << 16
+
+    def __init__(self, policy: PPOPolicy) -> None:
+        self.p = policy
+        self.dev = policy.device
+        self.static: Dict[str, torch.Tensor] = {}
+        self.graphs: Dict[Any, torch.cuda.CUDAGraph] = {}
+        optim = policy.optim
+        ok = isinstance(optim, (torch.optim.Adam, torch.optim.AdamW, torch.optim.RMSprop)) or (
+            isinstance(optim, torch.optim.SGD)
+            and all(g["dampening"] == 0 or g["momentum"] == 0 for g in optim.param_groups))
+        if not ok:
+            raise ValueError("cuda_graph=True supports Adam, AdamW, RMSprop and SGD without "
+                             f"dampening (their fresh state is all zeros); got {type(optim)}")
+        for g in optim.param_groups:
+            if "capturable" in g:
+                g["capturable"] = True
+        for st in optim.state.values():  # an optimiser that already stepped on the host
+            if torch.is_tensor(st.get("step")) and not st["step"].is_cuda:
+                st["step"] = st["step"].to(self.dev)
+        self.cursor = torch.zeros(1, dtype=torch.int64, device=self.dev)
+        self.row = torch.zeros(1, dtype=torch.int64, device=self.dev)
+        # one spare row: warm-up iterations log there, so a capture in the middle of a learn
+        # call (the merged tail's size) does not overwrite rows already written
+        self.log = torch.zeros(self.LOG_ROWS + 1, 4, dtype=torch.float32, device=self.dev)
+
+    # ---- static rows ---------------------------------------------------------------------------
+    def _fit(self, key: str, src: torch.Tensor) -> None:
+        cur = self.static.get(key)
+        if (cur is None or cur.shape[0] < src.shape[0] or cur.shape[1:] != src.shape[1:]
+                or cur.dtype != src.dtype):
+            self.static[key] = torch.empty_like(src, device=self.dev)
+            self.graphs.clear()  # captured addresses are stale
+            cur = self.static[key]
+        cur[:src.shape[0]].copy_(src)
+
+    def _load_returns(self, batch: Batch, n: int) -> None:
+        p = self.p
+        self._fit("adv", p._flat(batch.adv, n, "adv"))
+        self._fit("returns", p._flat(batch.returns, n, "returns"))
+        self._fit("v_s", p._flat(batch.v_s, n, "v_s"))
+
+    # ---- capture -------------------------------------------------------------------------------
+    def _body(self, m: int) -> None:
+        s, p = self.static, self.p
+        mb = s["perm"].index_select(0, self.cursor + s["arange"][:m])
+        vals = p._minibatch_step(s["obs"].index_select(0, mb), s["act"].index_select(0, mb), mb,
+                                 s["logp_old"], s["adv"], s["returns"], s["v_s"])
+        self.log.index_copy_(0, self.row, vals[None])
+        self.cursor += m
+        self.row += 1
+
+    def _modules_state(self) -> List[torch.Tensor]:
+        p = self.p
+        return list(p._params) + list(p.actor.buffers()) + list(p.critic.buffers())
+
+    def _capture(self, m: int) -> torch.cuda.CUDAGraph:
+        p, optim = self.p, self.p.optim
+        live = self._modules_state() + [self.cursor, self.row]
+        saved = [t.detach().clone() for t in live]
+        saved_opt = {q: {k: v.detach().clone() for k, v in st.items() if torch.is_tensor(v)}
+                     for q, st in optim.state.items()}
+        side = torch.cuda.Stream(device=self.dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                self.cursor.zero_()
+                self.row.fill_(self.LOG_ROWS)
+                self._body(m)
+        torch.cuda.current_stream().wait_stream(side)
+
+        def restore() -> None:
+            with torch.no_grad():
+                for t, v in zip(live, saved):
+                    t.copy_(v)
+                for q, st in optim.state.items():
+                    for k, v in st.items():
+                        if torch.is_tensor(v):
+                            old = saved_opt.get(q, {}).get(k)
+                            v.copy_(old) if old is not None else v.zero_()
+        restore()
+        graph = torch.cuda.CUDAGraph()
+        self.cursor.zero_()
+        with torch.cuda.graph(graph):
+            self._body(m)
+        restore()  # capture launches nothing, but leave cursor / row exactly as they were
+        return graph
+
+    def _graph(self, m: int) -> torch.cuda.CUDAGraph:
+        key = (m, tuple(float(g["lr"]) for g in self.p.optim.param_groups), self.p.training)
+        g = self.graphs.get(key)
+        if g is None:
+            g = self.graphs[key] = self._capture(m)
+        return g
+
+    # ---- learn ---------------------------------------------------------------------------------
+    def learn(self, batch: Batch, batch_size: int, repeat: int) -> np.ndarray:
+        p = self.p
+        n = len(batch)
+        if not isinstance(batch.obs, torch.Tensor):
+            raise NotImplementedError("cuda_graph=True needs tensor observations")
+        bounds = _split_bounds(n, batch_size, merge_last=True)
+        if repeat <= 0 or not bounds:
+            return np.zeros((0, 4))
+        self._fit("obs", batch.obs)
+        self._fit("act", batch.act)
+        self._fit("logp_old", p._flat(batch.logp_old, n, "log_prob"))
+        self._load_returns(batch, n)
+        perms = np.concatenate([np.random.permutation(n) for _ in range(repeat)])  # batch.py:905
+        self._fit("perm", torch.from_numpy(perms).to(self.dev))
+        m_max = max(hi - lo for lo, hi in bounds)
+        if "arange" not in self.static or self.static["arange"].numel() < m_max:
+            self.static["arange"] = torch.arange(m_max, dtype=torch.int64, device=self.dev)
+            self.graphs.clear()
+        self.cursor.zero_()
+        self.row.zero_()
+        tables: List[np.ndarray] = []
+        rows = 0
+        for step in range(repeat):
+            if p._recompute_adv and step > 0:
+                batch = p._compute_returns(batch, p._buffer, p._indices)
+                self._load_returns(batch, n)
+            for lo, hi in bounds:
+                if rows == self.LOG_ROWS:  # log full: read it out and start over
+                    tables.append(self.log[:rows].cpu().numpy().copy())
+                    self.row.zero_()
+                    rows = 0
+                self._graph(hi - lo).replay()
+                rows += 1
+        tables.append(self.log[:rows].cpu().numpy())  # the one sync of a normal-sized learn
+        return np.concatenate(tables) if len(tables) > 1 else tables[0]
