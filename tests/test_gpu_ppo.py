@@ -69,7 +69,7 @@ class _Actor(torch.nn.Module):
         self.net = torch.nn.Sequential(torch.nn.Linear(obs_dim, 64), torch.nn.Tanh(),
                                        torch.nn.Linear(64, n_act))
 
-    def forward(self, obs, state=None):
+    def forward(self, obs, state=None, info=None):
         return self.net(obs), state
 
 
@@ -261,3 +261,53 @@ def test_graphed_learn_equals_eager_learn():
             assert np.allclose(a[k], b[k], rtol=1e-5, atol=1e-6), k
     for p, q in zip(ep, gp):
         assert torch.allclose(p, q, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("name", ["pg", "a2c"])
+def test_pg_a2c_update_vs_reference_update(name):
+    """``PGPolicy.update`` / ``A2CPolicy.update`` of the reference (make_golden.gen_pg_a2c_update,
+    return normalisation on, two updates) against this package's device-resident versions."""
+    import tianshou_fork_b200 as ts
+    from helpers import fill
+    case = load_golden("pg_a2c_update")[name]
+    buf = ts.VectorReplayBuffer(20 * 100, 20)
+    fill(buf, ts.Batch, 700, 100, 20, 0.03, 0.01)
+    actor, critic = _load_nets(case)
+    dist_fn = lambda logits: torch.distributions.Categorical(logits=logits)  # noqa: E731
+    if name == "pg":
+        optim = torch.optim.Adam(actor.parameters(), lr=1e-3)
+        policy = ts.PGPolicy(actor, optim, dist_fn, discount_factor=0.95,
+                             reward_normalization=True, action_scaling=False)
+        keys = ("returns",)
+    else:
+        optim = torch.optim.Adam(list(actor.parameters()) + list(critic.parameters()), lr=1e-3)
+        policy = ts.A2CPolicy(actor, critic, optim, dist_fn, vf_coef=0.5, ent_coef=0.01,
+                              max_grad_norm=0.5, gae_lambda=0.9, discount_factor=0.98,
+                              reward_normalization=True, action_scaling=False)
+        keys = ("returns", "adv", "v_s")
+    seen = []
+    inner = policy.process_fn
+
+    def spy(batch, buffer, indices):
+        batch = inner(batch, buffer, indices)
+        seen.append({k: batch[k].detach().cpu().numpy().copy() for k in keys})
+        return batch
+
+    policy.process_fn = spy
+    np.random.seed(9)
+    for u in range(2):
+        res = policy.update(0, buf, batch_size=100, repeat=2)
+        tol = 1e-5 if (u == 0 and name == "pg") else (1e-4 if u == 0 else 3e-3)
+        for k in keys:
+            assert np.allclose(seen[u][k], case[f"u{u}/{k}"], rtol=tol, atol=tol), (u, k)
+        for k in res:
+            got, want = np.asarray(res[k]), case[f"u{u}/{k}"]
+            assert got.shape == want.shape
+            assert np.allclose(got, want, rtol=5e-3, atol=5e-4), (u, k)
+        mean, var, count = case[f"u{u}/ret_rms"]
+        assert policy.ret_rms.count == int(count)
+        assert np.isclose(policy.ret_rms.mean.item(), mean, rtol=1e-3, atol=1e-4)
+        assert np.isclose(policy.ret_rms.var.item(), var, rtol=1e-3)
+    for net, tag in ((actor, "actor"), (critic, "critic")):
+        for k, v in net.state_dict().items():
+            assert np.allclose(v.cpu().numpy(), case[f"final/{tag}/{k}"], rtol=3e-3, atol=3e-4), k
