@@ -254,8 +254,16 @@ class _GraphedLearner:
     def _body(self, m: int) -> None:
         s, p = self.static, self.p
         mb = s["perm"].index_select(0, self.cursor + s["arange"][:m])
-        vals = p._minibatch_step(s["obs"].index_select(0, mb), s["act"].index_select(0, mb), mb,
-                                 s["logp_old"], s["adv"], s["returns"], s["v_s"])
+        # argument validation of torch.distributions reads a device flag on the host
+        # (``if not valid.all()``), which a stream capture cannot contain
+        validate = torch.distributions.Distribution._validate_args
+        torch.distributions.Distribution.set_default_validate_args(False)
+        try:
+            vals = p._minibatch_step(
+                s["obs"].index_select(0, mb), s["act"].index_select(0, mb), mb,
+                s["logp_old"], s["adv"], s["returns"], s["v_s"])
+        finally:
+            torch.distributions.Distribution.set_default_validate_args(validate)
         self.log.index_copy_(0, self.row, vals[None])
         self.cursor += m
         self.row += 1
