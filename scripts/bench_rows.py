@@ -407,8 +407,113 @@ def row_ppo():
              cpu_port_fwd_us=cus, speedup_vs_eager=eus / us)
 
 
+def row_learn():
+    """C3 (BASELINE.json configs[2]): PPOPolicy.learn at Ant shape (obs 27, act 8, 64 x 64 tanh
+    MLPs, Independent Normal), wall time per minibatch: this package eager and CUDA-graphed,
+    against the reference's learn() arithmetic (ppo.py:99-162: Batch.split fancy-index copies,
+    eager elementwise loss, four .item() syncs) in torch eager on the same GPU and on the CPU."""
+    D, A = 27, 8
+
+    class Actor(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.mu = torch.nn.Sequential(torch.nn.Linear(D, 64), torch.nn.Tanh(),
+                                          torch.nn.Linear(64, 64), torch.nn.Tanh(),
+                                          torch.nn.Linear(64, A))
+            self.sigma = torch.nn.Parameter(torch.zeros(A))
+
+        def forward(self, obs, state=None, info=None):
+            mu = self.mu(obs)
+            return (mu, self.sigma.exp().expand_as(mu)), state
+
+    def dist_fn(mu, sigma):
+        return torch.distributions.Independent(torch.distributions.Normal(mu, sigma), 1)
+
+    def nets(dev):
+        torch.manual_seed(0)
+        actor = Actor().to(dev)
+        critic = torch.nn.Sequential(torch.nn.Linear(D, 64), torch.nn.Tanh(),
+                                     torch.nn.Linear(64, 64), torch.nn.Tanh(),
+                                     torch.nn.Linear(64, 1)).to(dev)
+        optim = torch.optim.Adam(list(actor.parameters()) + list(critic.parameters()), lr=3e-4)
+        return actor, critic, optim
+
+    def data(n, dev):
+        g = torch.Generator().manual_seed(1)
+        r = lambda *sh: torch.randn(*sh, generator=g)
+        v_s = r(n)
+        return dict(obs=r(n, D).to(dev), act=r(n, A).to(dev), v_s=v_s.to(dev),
+                    adv=r(n).to(dev), returns=(v_s + 0.3 * r(n)).to(dev),
+                    logp_old=(-11.0 + 0.3 * r(n)).to(dev))
+
+    def reference_learn(d, actor, critic, optim, bs, dev):
+        n = d["obs"].shape[0]
+        params = list(actor.parameters()) + list(critic.parameters())
+        perm = np.random.permutation(n)
+        out = []
+        for lo in range(0, n, bs):
+            idx = perm[lo:lo + bs]
+            mb = {k: v[idx] for k, v in d.items()}  # Batch.split: a fancy-index copy per key
+            dist = dist_fn(*actor(mb["obs"])[0])
+            a = mb["adv"]
+            a = (a - a.mean()) / (a.std() + 1e-8)
+            ratio = (dist.log_prob(mb["act"]) - mb["logp_old"]).exp().float()
+            ratio = ratio.reshape(ratio.size(0), -1).transpose(0, 1)
+            s1, s2 = ratio * a, ratio.clamp(0.8, 1.2) * a
+            clip_loss = -torch.min(s1, s2).mean()
+            value = critic(mb["obs"]).flatten()
+            v_clip = mb["v_s"] + (value - mb["v_s"]).clamp(-0.2, 0.2)
+            vf_loss = torch.max((mb["returns"] - value).pow(2),
+                                (mb["returns"] - v_clip).pow(2)).mean()
+            ent = dist.entropy().mean()
+            loss = clip_loss + 0.25 * vf_loss - 0.0 * ent
+            optim.zero_grad()
+            loss.backward()
+            torch.nn.utils.clip_grad_norm_(params, max_norm=0.5)
+            optim.step()
+            out.append((clip_loss.item(), vf_loss.item(), ent.item(), loss.item()))
+        return out
+
+    def wall_us(fn, reps=3):
+        fn()
+        best = 1e30
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            fn()
+            torch.cuda.synchronize()
+            best = min(best, time.perf_counter() - t0)
+        return best * 1e6
+
+    for bs, count in ((64, 256), (1024, 128)):
+        n = bs * count
+        res = {}
+        for mode in ("eager", "cuda_graph"):
+            actor, critic, optim = nets(DEV)
+            pol = ts.PPOPolicy(actor, critic, optim, dist_fn, eps_clip=0.2, value_clip=True,
+                               vf_coef=0.25, ent_coef=0.0, max_grad_norm=0.5,
+                               cuda_graph=(mode == "cuda_graph"))
+            batch = ts.Batch(**data(n, DEV))
+            res[mode] = wall_us(lambda: pol.learn(batch, bs, 1)) / count
+        actor, critic, optim = nets(DEV)
+        d = data(n, DEV)
+        res["ref_gpu"] = wall_us(lambda: reference_learn(d, actor, critic, optim, bs, DEV)) / count
+        cpu = torch.device("cpu")
+        actor, critic, optim = nets(cpu)
+        nc = bs * 32
+        dc = data(nc, cpu)
+        res["ref_cpu"] = wall_us(lambda: reference_learn(dc, actor, critic, optim, bs, cpu),
+                                 reps=2) / 32
+        emit("C3 PPOPolicy.learn per minibatch", minibatch=bs, minibatches=count,
+             this_eager_us=res["eager"], this_cuda_graph_us=res["cuda_graph"],
+             reference_arithmetic_torch_gpu_us=res["ref_gpu"],
+             reference_arithmetic_torch_cpu_us=res["ref_cpu"], cpu_threads=torch.get_num_threads(),
+             speedup_graph_vs_ref_gpu=res["ref_gpu"] / res["cuda_graph"],
+             speedup_graph_vs_ref_cpu=res["ref_cpu"] / res["cuda_graph"])
+
+
 if __name__ == "__main__":
     torch.cuda.set_device(0)
-    which = sys.argv[1:] or ["gae_api", "gae_flat", "nstep_index", "gather", "gather_stack", "add", "ppo"]
+    which = sys.argv[1:] or ["gae_api", "gae_flat", "nstep_index", "gather", "gather_stack", "add", "ppo", "learn"]
     for w in which:
         globals()["row_" + w]()
