@@ -517,6 +517,61 @@ def gen_pg_a2c_update(ts, out):
     np.savez_compressed(os.path.join(out, "pg_a2c_update.npz"), **flat)
 
 
+DQN_UPDATE_SPECS = [
+    # name, DQNPolicy kwargs, PER kwargs, sample size, updates
+    ("double_n3", dict(discount_factor=0.97, estimation_step=3, target_update_freq=2,
+                       is_double=True), dict(alpha=0.6, beta=0.4), 64, 6),
+    ("nature_n1_huber", dict(discount_factor=0.9, estimation_step=1, target_update_freq=0,
+                             is_double=False, clip_loss_grad=True),
+     dict(alpha=0.8, beta=1.0), 48, 4),
+]
+
+
+def gen_dqn_update(ts, out):
+    """``DQNPolicy.update`` of the reference (dqn.py:98-194 through policy/base.py:288-315) on a
+    ``PrioritizedVectorReplayBuffer``: per update the sampled indices, the importance weights
+    handed to ``process_fn``, the n-step returns, the loss, and after ``post_process_fn`` the
+    leaves at the sampled indices plus ``_max_prio`` / ``_min_prio``; parameters at the end."""
+    import torch
+    from tianshou.data import Batch, PrioritizedVectorReplayBuffer
+    from tianshou.policy import DQNPolicy
+
+    Actor, _ = ppo_update_nets(torch)
+    flat = {}
+    for name, kw, per_kw, bsz, n_updates in DQN_UPDATE_SPECS:
+        buf = PrioritizedVectorReplayBuffer(20 * 100, 20, **per_kw)
+        fill_vecbuf(buf, Batch, np.random.default_rng(800), 100, 20, 0.03, 0.01)
+        torch.manual_seed(3)
+        net = Actor()
+        optim = torch.optim.Adam(net.parameters(), lr=1e-3)
+        for k, v in net.state_dict().items():
+            flat[f"{name}/init/actor/{k}"] = v.numpy().copy()
+        policy = DQNPolicy(net, optim, **kw)
+        seen = []
+        inner = policy.process_fn
+
+        def spy(batch, buffer, indices, inner=inner, seen=seen):
+            rec = {"indices": np.asarray(indices).copy(),
+                   "weight_in": np.asarray(batch.weight).copy()}
+            batch = inner(batch, buffer, indices)
+            rec["returns"] = batch.returns.detach().numpy().copy()
+            seen.append(rec)
+            return batch
+
+        policy.process_fn = spy
+        np.random.seed(13)
+        for u in range(n_updates):
+            res = policy.update(bsz, buf)
+            for k, v in seen[u].items():
+                flat[f"{name}/u{u}/{k}"] = v
+            flat[f"{name}/u{u}/loss"] = np.float64(res["loss"])
+            flat[f"{name}/u{u}/leaves"] = np.asarray(buf.weight[seen[u]["indices"]], np.float64)
+            flat[f"{name}/u{u}/prio"] = np.array([buf._max_prio, buf._min_prio], np.float64)
+        for k, v in net.state_dict().items():
+            flat[f"{name}/final/actor/{k}"] = v.numpy().copy()
+    np.savez_compressed(os.path.join(out, "dqn_update.npz"), **flat)
+
+
 STACK_SPECS = [
     # name, n_env, total, steps, stack_num, ragged, frame shape (make_golden.gen_stack)
     ("atari_like", 4, 80, 13, 4, False, (6,)),
@@ -593,6 +648,7 @@ def main():
     gen_ppo(ts, HERE)
     gen_ppo_update(ts, HERE)
     gen_pg_a2c_update(ts, HERE)
+    gen_dqn_update(ts, HERE)
     gen_stack(ts, HERE)
     with open(os.path.join(HERE, "versions.json"), "w") as f:
         json.dump({"tianshou": ts.__version__, "numpy": np.__version__,

@@ -142,3 +142,13 @@ def ppo_update_nets(torch):
             return self.net(obs)
 
     return Actor, Critic
+
+
+DQN_UPDATE_SPECS = [
+    # name, DQNPolicy kwargs, PER kwargs, sample size, updates
+    ("double_n3", dict(discount_factor=0.97, estimation_step=3, target_update_freq=2,
+                       is_double=True), dict(alpha=0.6, beta=0.4), 64, 6),
+    ("nature_n1_huber", dict(discount_factor=0.9, estimation_step=1, target_update_freq=0,
+                             is_double=False, clip_loss_grad=True),
+     dict(alpha=0.8, beta=1.0), 48, 4),
+]

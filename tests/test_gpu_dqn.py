@@ -1,0 +1,55 @@
+"""DQNPolicy.update on a PrioritizedVectorReplayBuffer against the reference's own update
+(tests/golden/dqn_update.npz, written by make_golden.gen_dqn_update): the whole C4 pipeline
+sample (PER) -> n-step return -> learn -> update_weight, several updates in a row."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", ["double_n3", "nature_n1_huber"])
+def test_dqn_per_update_vs_reference_update(name):
+    import tianshou_fork_b200 as ts
+    from helpers import DQN_UPDATE_SPECS, fill, ppo_update_nets
+    case = load_golden("dqn_update")[name]
+    _, kw, per_kw, bsz, n_updates = next(s for s in DQN_UPDATE_SPECS if s[0] == name)
+    buf = ts.PrioritizedVectorReplayBuffer(20 * 100, 20, **per_kw)
+    fill(buf, ts.Batch, 800, 100, 20, 0.03, 0.01)
+    Actor, _ = ppo_update_nets(torch)
+    net = Actor()
+    net.load_state_dict({k[len("init/actor/"):]: torch.from_numpy(v) for k, v in case.items()
+                         if k.startswith("init/actor/")})
+    net = net.cuda()
+    optim = torch.optim.Adam(net.parameters(), lr=1e-3)
+    policy = ts.DQNPolicy(net, optim, **kw)
+    seen = []
+    inner = policy.process_fn
+
+    def spy(batch, buffer, indices):
+        rec = {"indices": indices.cpu().numpy().copy(),
+               "weight_in": batch.weight.cpu().numpy().copy()}
+        batch = inner(batch, buffer, indices)
+        rec["returns"] = batch.returns.detach().cpu().numpy().copy()
+        seen.append(rec)
+        return batch
+
+    policy.process_fn = spy
+    np.random.seed(13)
+    for u in range(n_updates):
+        res = policy.update(bsz, buf)
+        # identical host uniforms + (nearly) identical leaves => identical sampled indices
+        assert np.array_equal(seen[u]["indices"], case[f"u{u}/indices"]), u
+        assert np.allclose(seen[u]["weight_in"], case[f"u{u}/weight_in"], rtol=1e-4, atol=1e-6)
+        assert seen[u]["returns"].shape == case[f"u{u}/returns"].shape
+        assert np.allclose(seen[u]["returns"], case[f"u{u}/returns"], rtol=1e-3, atol=1e-4)
+        assert np.isclose(res["loss"], case[f"u{u}/loss"], rtol=1e-3, atol=1e-5)
+        leaves = buf.weight[torch.from_numpy(case[f"u{u}/indices"]).cuda()]
+        leaves = leaves.cpu().numpy() if isinstance(leaves, torch.Tensor) else np.asarray(leaves)
+        assert np.allclose(leaves, case[f"u{u}/leaves"], rtol=1e-3, atol=1e-4)
+        assert np.allclose([buf._max_prio, buf._min_prio], case[f"u{u}/prio"], rtol=1e-3,
+                           atol=1e-4)
+    for k, v in net.state_dict().items():
+        assert np.allclose(v.cpu().numpy(), case[f"final/actor/{k}"], rtol=3e-3, atol=3e-4), k

@@ -16,7 +16,7 @@ from . import _lib
 from .data import (Batch, PrioritizedReplayBuffer, PrioritizedReplayBufferManager,
                    PrioritizedVectorReplayBuffer, ReplayBuffer, ReplayBufferManager,
                    SegmentTree, ShardedPrioritizedVectorReplayBuffer, VectorReplayBuffer)
-from .policy import A2CPolicy, BasePolicy, PGPolicy, PPOPolicy, ppo_loss
+from .policy import A2CPolicy, BasePolicy, DQNPolicy, PGPolicy, PPOPolicy, ppo_loss
 
 __version__ = "0.1.0"
 
@@ -24,5 +24,5 @@ __all__ = [
     "Batch", "ReplayBuffer", "ReplayBufferManager", "VectorReplayBuffer",
     "PrioritizedReplayBuffer", "PrioritizedReplayBufferManager",
     "PrioritizedVectorReplayBuffer", "ShardedPrioritizedVectorReplayBuffer", "SegmentTree",
-    "BasePolicy", "PGPolicy", "A2CPolicy", "PPOPolicy", "ppo_loss",
+    "BasePolicy", "PGPolicy", "A2CPolicy", "PPOPolicy", "DQNPolicy", "ppo_loss",
 ]
