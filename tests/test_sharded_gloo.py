@@ -91,3 +91,49 @@ def test_shard_layout_rejects_unaligned():
     assert not is_exact_layout(cap, 8)  # 10^6 per shard straddles subtrees
     size, per_rank, cap, off = shard_layout(8 << 20, 128, 8, 7)
     assert cap == 1 << 20 and off == 7 << 20 and is_exact_layout(cap, 8)
+
+
+def _dp_worker(rank: int, world: int, port: int, q):
+    try:
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        from tianshou_fork_b200.policy.base import BasePolicy
+        torch.manual_seed(0)  # identical replicas
+        net = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.Tanh(), torch.nn.Linear(7, 2))
+        x_all = torch.randn(world * 6, 5)
+        y_all = torch.randn(world * 6, 2)
+        pol = BasePolicy()
+        pol.set_data_parallel(True)
+        # rank-local loss on this rank's rows, then the averaged gradient
+        (net(x_all[rank * 6:(rank + 1) * 6]) - y_all[rank * 6:(rank + 1) * 6]).pow(2).mean().backward()
+        pol._sync_grads(net.parameters())
+        got = [p.grad.clone() for p in net.parameters()]
+        net.zero_grad()
+        (net(x_all) - y_all).pow(2).mean().backward()  # one learner over every rank's rows
+        for g, p in zip(got, net.parameters()):
+            assert torch.allclose(g, p.grad, rtol=1e-5, atol=1e-7)
+        pol.set_data_parallel(False)
+        before = [p.grad.clone() for p in net.parameters()]
+        pol._sync_grads(net.parameters())  # disabled: untouched, no collective
+        assert all(torch.equal(a, p.grad) for a, p in zip(before, net.parameters()))
+        dist.destroy_process_group()
+        q.put((rank, "ok"))
+    except Exception:
+        import traceback
+        q.put((rank, traceback.format_exc()))
+
+
+def test_data_parallel_gradient_average_gloo():
+    """SURVEY 8e, learner row: per-rank gradients summed over the group and divided by its
+    size equal the gradient of one learner over all ranks' (equal-sized) minibatches."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_dp_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(60)
+    assert all(msg == "ok" for _, msg in results), results

@@ -96,6 +96,7 @@ class A2CPolicy(PGPolicy):
                 loss = actor_loss + self._weight_vf * vf_loss - self._weight_ent * ent_loss
                 self.optim.zero_grad()
                 loss.backward()
+                self._sync_grads(self._params)
                 if self._grad_norm:
                     nn.utils.clip_grad_norm_(self._params, max_norm=self._grad_norm)
                 self.optim.step()

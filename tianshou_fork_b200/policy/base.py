@@ -86,6 +86,27 @@ def _buffer_layout(buffer: Any, device: torch.device):
             L.as_u8(_dev(buffer.terminated, device, torch.bool)))
 
 
+def allreduce_mean_grads(params: Any, group: Any = None) -> None:
+    """Average ``p.grad`` over the process group with ONE collective: the gradients of the
+    path's networks are a few hundred KB, so they travel as a single flat bucket (NCCL over
+    NVLink on GPUs, capturable in a CUDA graph; gloo in the CPU tests)."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        raise RuntimeError("set_data_parallel() needs an initialised torch.distributed group")
+    world = dist.get_world_size(group)
+    grads = [p.grad for p in params if p.grad is not None]
+    if world == 1 or not grads:
+        return
+    flat = torch.cat([g.reshape(-1) for g in grads])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    flat.div_(world)
+    offset = 0
+    for g in grads:
+        n = g.numel()
+        g.copy_(flat[offset:offset + n].view_as(g))
+        offset += n
+
+
 class BasePolicy(nn.Module):
     """Static return estimators with the reference's signatures (policy/base.py:317-440).
 
@@ -119,6 +140,19 @@ class BasePolicy(nn.Module):
 
     def set_agent_id(self, agent_id: int) -> None:
         self.agent_id = agent_id
+
+    # ---- data-parallel learners --------------------------------------------------
+    def set_data_parallel(self, enabled: bool = True, group: Any = None) -> None:
+        """One process per GPU, each with its own env streams / samples: after ``backward`` the
+        gradients are summed over ``group`` and divided by its size, so every rank applies the
+        same step.  Per-minibatch advantage normalisation stays rank-local (ppo.py:109-113
+        normalises over the minibatch it sees)."""
+        self._dp_group = (group,) if enabled else None
+
+    def _sync_grads(self, params: Any) -> None:
+        dp = getattr(self, "_dp_group", None)
+        if dp is not None:
+            allreduce_mean_grads(params, dp[0])
 
     def forward(self, batch: Batch, state: Any = None, **kwargs: Any) -> Batch:
         raise NotImplementedError

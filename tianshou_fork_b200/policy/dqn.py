@@ -123,6 +123,7 @@ class DQNPolicy(BasePolicy):
             loss = (td_error.pow(2) * weight).mean()
         batch.weight = td_error.detach()  # prio-buffer
         loss.backward()
+        self._sync_grads(self.model.parameters())
         self.optim.step()
         self._iter += 1
         return {"loss": loss.item()}

@@ -147,6 +147,7 @@ class PGPolicy(BasePolicy):
                 log_prob = dist.log_prob(act_all[mb]).reshape(len(ret), -1).transpose(0, 1)
                 loss = -(log_prob * ret).mean()
                 loss.backward()
+                self._sync_grads(self.actor.parameters())
                 self.optim.step()
                 logged.append(loss.detach())
         losses = torch.stack(logged).cpu().tolist() if logged else []  # one sync per learn
