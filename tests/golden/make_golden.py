@@ -572,6 +572,54 @@ def gen_dqn_update(ts, out):
     np.savez_compressed(os.path.join(out, "dqn_update.npz"), **flat)
 
 
+CACHED_SPECS = [
+    # name, main size, cached buffers, max episode length, steps, p_done, ragged
+    ("roomy", 64, 4, 12, 60, 0.15, False),
+    ("main_wraps", 20, 3, 8, 90, 0.2, True),
+    ("long_episodes", 30, 5, 6, 50, 0.05, True),   # cached rings wrap before an episode ends
+]
+
+
+def gen_cached(ts, out):
+    """``CachedReplayBuffer`` of the reference (cached.py:8-96) driven by a seeded add stream:
+    what every ``add`` returns, and after the stream the bookkeeping, ``sample_indices(0)``,
+    ``prev`` / ``next`` over the whole capacity, ``unfinished_index`` and the stored fields."""
+    from tianshou.data import Batch, CachedReplayBuffer, ReplayBuffer
+
+    flat = {}
+    for name, main, n_cached, ep_len, steps, p_done, ragged in CACHED_SPECS:
+        buf = CachedReplayBuffer(ReplayBuffer(main), n_cached, ep_len)
+        rng = np.random.default_rng(900)
+        rets = []
+        for t in range(steps):
+            ids = np.arange(n_cached)
+            if ragged:
+                ids = ids[rng.random(n_cached) < 0.7]
+                if ids.size == 0:
+                    continue
+            m = ids.size
+            term = rng.random(m) < p_done
+            trunc = (rng.random(m) < p_done / 3) & ~term
+            b = Batch(obs=rng.standard_normal((m, 2)).astype(np.float32),
+                      act=rng.integers(0, 4, m), rew=rng.standard_normal(m), terminated=term,
+                      truncated=trunc, obs_next=rng.standard_normal((m, 2)).astype(np.float32),
+                      info={})
+            ptr, ep_rew, ep_l, ep_idx = buf.add(b, buffer_ids=ids)
+            rets.append(np.stack([ptr, ep_rew, ep_l, ep_idx], 1).astype(np.float64))
+        flat[f"{name}/add_returns"] = np.concatenate(rets)
+        flat[f"{name}/lengths"] = buf._lengths.copy()
+        flat[f"{name}/last_index"] = buf.last_index.copy()
+        flat[f"{name}/len"] = np.int64(len(buf))
+        allidx = np.arange(buf.maxsize)
+        flat[f"{name}/all"] = buf.sample_indices(0)
+        flat[f"{name}/prev"] = buf.prev(allidx)
+        flat[f"{name}/next"] = buf.next(allidx)
+        flat[f"{name}/unfinished"] = buf.unfinished_index()
+        for k in ("obs", "act", "rew", "done", "terminated", "obs_next"):
+            flat[f"{name}/{k}"] = np.asarray(buf._meta[k]).copy()
+    np.savez_compressed(os.path.join(out, "cached.npz"), **flat)
+
+
 STACK_SPECS = [
     # name, n_env, total, steps, stack_num, ragged, frame shape (make_golden.gen_stack)
     ("atari_like", 4, 80, 13, 4, False, (6,)),
@@ -649,6 +697,7 @@ def main():
     gen_ppo_update(ts, HERE)
     gen_pg_a2c_update(ts, HERE)
     gen_dqn_update(ts, HERE)
+    gen_cached(ts, HERE)
     gen_stack(ts, HERE)
     with open(os.path.join(HERE, "versions.json"), "w") as f:
         json.dump({"tianshou": ts.__version__, "numpy": np.__version__,

@@ -152,3 +152,11 @@ DQN_UPDATE_SPECS = [
                              is_double=False, clip_loss_grad=True),
      dict(alpha=0.8, beta=1.0), 48, 4),
 ]
+
+
+CACHED_SPECS = [
+    # name, main size, cached buffers, max episode length, steps, p_done, ragged
+    ("roomy", 64, 4, 12, 60, 0.15, False),
+    ("main_wraps", 20, 3, 8, 90, 0.2, True),
+    ("long_episodes", 30, 5, 6, 50, 0.05, True),   # cached rings wrap before an episode ends
+]

@@ -3,12 +3,14 @@ from .batch import Batch
 from .segtree import SegmentTree
 from .buffer import ReplayBuffer
 from .manager import ReplayBufferManager, VectorReplayBuffer
+from .cached import CachedReplayBuffer
 from .prio import (PrioritizedReplayBuffer, PrioritizedReplayBufferManager,
                    PrioritizedVectorReplayBuffer)
 from .sharded import ShardedPrioritizedVectorReplayBuffer
 
 __all__ = [
     "Batch", "SegmentTree", "ReplayBuffer", "ReplayBufferManager", "VectorReplayBuffer",
+    "CachedReplayBuffer",
     "PrioritizedReplayBuffer", "PrioritizedReplayBufferManager",
     "PrioritizedVectorReplayBuffer", "ShardedPrioritizedVectorReplayBuffer",
 ]

@@ -141,7 +141,10 @@ class ReplayBuffer:
 
     def reset(self, keep_statistics: bool = False) -> None:
         """Clear all the data in replay buffer and episode statistics (base.py:134-139)."""
-        self.last_index = np.array([0])
+        if self.__dict__.get("_parent") is not None:
+            self.last_index[:] = 0  # a sub-buffer's row of its manager's table: keep the alias
+        else:
+            self.last_index = np.array([0])
         self._ring[:] = 0
         if not keep_statistics:
             self._ep = {"rew": 0.0, "len": 0, "idx": 0}
