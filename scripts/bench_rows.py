@@ -512,6 +512,108 @@ def row_learn():
              speedup_graph_vs_ref_cpu=res["ref_cpu"] / res["cuda_graph"])
 
 
+def row_dqn():
+    """C4 (BASELINE.json configs[3]) through the public API: DQNPolicy.update(bsz, buffer) on a
+    PrioritizedVectorReplayBuffer of 2^20 Atari-shaped transitions (84 x 84 u8 frames, stack 4,
+    obs_next from next(), 16 sub-buffers), n-step 3, Nature CNN.  Wall time per segment of the
+    update pipeline (policy/base.py:288-315) and of the networks alone."""
+    E, T, A = 16, 1 << 16, 6
+    buf = ts.PrioritizedVectorReplayBuffer(E * T, E, alpha=0.6, beta=0.4, stack_num=4,
+                                           ignore_obs_next=True, save_only_last_obs=True)
+    rng = np.random.default_rng(4)
+    for t in range(2):
+        buf.add(ts.Batch(obs=np.zeros((E, 4, 84, 84), np.uint8), act=np.zeros(E, np.int64),
+                         rew=np.zeros(E), terminated=np.zeros(E, bool),
+                         truncated=np.zeros(E, bool), info={}))
+    n = E * T
+    term = rng.random(n) < 1 / 1000
+    trunc = (rng.random(n) < 1 / 10000) & ~term
+    buf._meta.rew.copy_(torch.from_numpy(rng.choice(np.array([-1.0, 0.0, 1.0]), n,
+                                                    p=[0.05, 0.9, 0.05])))
+    buf._meta.act.copy_(torch.from_numpy(rng.integers(0, A, n)))
+    buf._meta.terminated.copy_(torch.from_numpy(term))
+    buf._meta.truncated.copy_(torch.from_numpy(trunc))
+    buf._meta.done.copy_(torch.from_numpy(term | trunc))
+    buf._meta.obs.random_(0, 256)
+    buf._rings[:, 0], buf._rings[:, 1] = 0, T
+    buf._lengths[:] = T
+    buf.last_index[:] = np.arange(E) * T + T - 1
+    buf._version += 1
+    for b in buf.buffers:
+        b._index, b._size = 0, T
+    buf.update_weight(torch.arange(n, device=DEV), torch.randn(n, device=DEV))
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.c = torch.nn.Sequential(
+                torch.nn.Conv2d(4, 32, 8, 4), torch.nn.ReLU(), torch.nn.Conv2d(32, 64, 4, 2),
+                torch.nn.ReLU(), torch.nn.Conv2d(64, 64, 3, 1), torch.nn.ReLU(),
+                torch.nn.Flatten(), torch.nn.Linear(3136, 512), torch.nn.ReLU(),
+                torch.nn.Linear(512, A))
+
+        def forward(self, obs, state=None, info=None):
+            return self.c(obs.float() * (1.0 / 255)), state
+
+    def wall(fn, iters):
+        for _ in range(5):
+            fn()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(iters):
+            fn()
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / iters * 1e6
+
+    for bsz in (32, 256):
+        torch.manual_seed(0)
+        net = Net().to(DEV)
+        optim = torch.optim.Adam(net.parameters(), lr=1e-4)
+        pol = ts.DQNPolicy(net, optim, 0.99, estimation_step=3, target_update_freq=500)
+        np.random.seed(0)
+        iters = 100
+        total = wall(lambda: pol.update(bsz, buf), iters)
+        seg = {}
+        state = {}
+
+        def s_sample():
+            state["b"], state["i"] = buf.sample(bsz)
+
+        def s_process():
+            state["b"].weight = state["w"].clone()
+            pol.process_fn(state["b"], buf, state["i"])
+
+        def s_learn():
+            state["b"].weight = state["w"].clone()
+            pol.learn(state["b"])
+
+        def s_post():
+            pol.post_process_fn(state["b"], buf, state["i"])
+
+        seg["sample"] = wall(s_sample, iters)
+        state["w"] = state["b"].weight
+        seg["process_fn"] = wall(s_process, iters)
+        seg["learn"] = wall(s_learn, iters)
+        seg["post_process_fn"] = wall(s_post, iters)
+        obs = state["b"].obs
+        tgt = torch.randn(bsz, device=DEV)
+        act = state["b"].act.long().reshape(-1, 1)
+
+        def nets_only():  # target forward x2 (double DQN) + online forward/backward + Adam
+            with torch.no_grad():
+                net(obs)[0]
+                pol.model_old(obs)[0]
+            optim.zero_grad()
+            q = net(obs)[0].gather(1, act).squeeze(1)
+            ((tgt - q) ** 2).mean().backward()
+            optim.step()
+
+        seg["networks_only"] = wall(nets_only, iters)
+        emit("C4 DQNPolicy.update through the API", bsz=bsz, update_wall_us=total,
+             **{k + "_us": v for k, v in seg.items()},
+             data_path_share=1.0 - seg["networks_only"] / total)
+
+
 if __name__ == "__main__":
     torch.cuda.set_device(0)
     which = sys.argv[1:] or ["gae_api", "gae_flat", "nstep_index", "gather", "gather_stack", "add", "ppo", "learn"]

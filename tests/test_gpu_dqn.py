@@ -10,8 +10,9 @@ from conftest import load_golden
 pytestmark = pytest.mark.gpu
 
 
+@pytest.mark.parametrize("graph", [False, True], ids=["eager", "cuda_graph"])
 @pytest.mark.parametrize("name", ["double_n3", "nature_n1_huber"])
-def test_dqn_per_update_vs_reference_update(name):
+def test_dqn_per_update_vs_reference_update(name, graph):
     import tianshou_fork_b200 as ts
     from helpers import DQN_UPDATE_SPECS, fill, ppo_update_nets
     case = load_golden("dqn_update")[name]
@@ -24,7 +25,7 @@ def test_dqn_per_update_vs_reference_update(name):
                          if k.startswith("init/actor/")})
     net = net.cuda()
     optim = torch.optim.Adam(net.parameters(), lr=1e-3)
-    policy = ts.DQNPolicy(net, optim, **kw)
+    policy = ts.DQNPolicy(net, optim, cuda_graph=graph, **kw)
     seen = []
     inner = policy.process_fn
 
@@ -36,15 +37,18 @@ def test_dqn_per_update_vs_reference_update(name):
         seen.append(rec)
         return batch
 
-    policy.process_fn = spy
+    if not graph:  # the spy reads device values on the host, which a captured body cannot
+        policy.process_fn = spy
     np.random.seed(13)
     for u in range(n_updates):
         res = policy.update(bsz, buf)
-        # identical host uniforms + (nearly) identical leaves => identical sampled indices
-        assert np.array_equal(seen[u]["indices"], case[f"u{u}/indices"]), u
-        assert np.allclose(seen[u]["weight_in"], case[f"u{u}/weight_in"], rtol=1e-4, atol=1e-6)
-        assert seen[u]["returns"].shape == case[f"u{u}/returns"].shape
-        assert np.allclose(seen[u]["returns"], case[f"u{u}/returns"], rtol=1e-3, atol=1e-4)
+        if not graph:
+            # identical host uniforms + (nearly) identical leaves => identical sampled indices
+            assert np.array_equal(seen[u]["indices"], case[f"u{u}/indices"]), u
+            assert np.allclose(seen[u]["weight_in"], case[f"u{u}/weight_in"], rtol=1e-4,
+                               atol=1e-6)
+            assert seen[u]["returns"].shape == case[f"u{u}/returns"].shape
+            assert np.allclose(seen[u]["returns"], case[f"u{u}/returns"], rtol=1e-3, atol=1e-4)
         assert np.isclose(res["loss"], case[f"u{u}/loss"], rtol=1e-3, atol=1e-5)
         leaves = buf.weight[torch.from_numpy(case[f"u{u}/indices"]).cuda()]
         leaves = leaves.cpu().numpy() if isinstance(leaves, torch.Tensor) else np.asarray(leaves)
@@ -53,3 +57,35 @@ def test_dqn_per_update_vs_reference_update(name):
                            atol=1e-4)
     for k, v in net.state_dict().items():
         assert np.allclose(v.cpu().numpy(), case[f"final/actor/{k}"], rtol=3e-3, atol=3e-4), k
+
+
+def test_graphed_update_sees_transitions_added_between_updates():
+    """cuda_graph=True on a uniform VectorReplayBuffer that keeps growing: the replayed graph
+    reads the refreshed ring bookkeeping, so eager and graphed runs stay identical."""
+    import tianshou_fork_b200 as ts
+    from helpers import ppo_update_nets
+    Actor, _ = ppo_update_nets(torch)
+    out = []
+    for graph in (False, True):
+        rng = np.random.default_rng(5)
+        buf = ts.VectorReplayBuffer(8 * 64, 8)
+        torch.manual_seed(4)
+        net = Actor().cuda()
+        optim = torch.optim.Adam(net.parameters(), lr=1e-3)
+        policy = ts.DQNPolicy(net, optim, 0.95, estimation_step=2, target_update_freq=3,
+                              cuda_graph=graph)
+        np.random.seed(21)
+        losses = []
+        for t in range(40):
+            term = rng.random(8) < 0.1
+            buf.add(ts.Batch(obs=rng.standard_normal((8, 3)).astype(np.float32),
+                             act=rng.integers(0, 4, 8), rew=rng.standard_normal(8),
+                             terminated=term, truncated=np.zeros(8, bool),
+                             obs_next=rng.standard_normal((8, 3)).astype(np.float32), info={}))
+            if t >= 4:
+                losses.append(policy.update(16, buf)["loss"])
+        out.append((losses, [p.detach().clone() for p in net.parameters()]))
+    (le, pe), (lg, pg) = out
+    assert np.allclose(le, lg, rtol=1e-5, atol=1e-6)
+    for a, b in zip(pe, pg):
+        assert torch.allclose(a, b, rtol=1e-5, atol=1e-6)

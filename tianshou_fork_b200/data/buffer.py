@@ -174,10 +174,18 @@ class ReplayBuffer:
         if self._dev_state is None or self._dev_state_version != version:
             off, last, lens, sub = self._layout()
             packed = np.concatenate([off, last, lens]).astype(np.int64)
-            t = torch.from_numpy(packed).to(self.device)
+            old = self._dev_state["packed"] if self._dev_state is not None else None
+            if old is not None and old.numel() == packed.size:
+                # refresh in place (stream-ordered): kernels already captured into a CUDA graph
+                # keep reading the bookkeeping at the same addresses
+                t = old
+                t.copy_(torch.from_numpy(packed))
+            else:
+                t = torch.from_numpy(packed).to(self.device)
             b = last.size
             self._dev_state = {"offset": t[: b + 1], "last_index": t[b + 1: 2 * b + 1],
-                               "lengths": t[2 * b + 1:], "B": b, "sub_size": sub}
+                               "lengths": t[2 * b + 1:], "B": b, "sub_size": sub,
+                               "packed": t}
             # raw addresses for the hot calls (the packed tensor stays alive in the dict)
             p0 = t.data_ptr()
             self._dev_state["ptrs"] = (p0, p0 + 8 * (b + 1), p0 + 8 * (2 * b + 1))

@@ -6,6 +6,11 @@ importance weights, ``csrc/segtree.cu``) -> ``process_fn`` = ``compute_nstep_ret
 (``csrc/nstep.cu``, the target network evaluated on ``buffer[terminal]``) -> ``learn`` ->
 ``post_process_fn`` = ``buffer.update_weight(indices, td_error)`` (policy/base.py:285-286).
 The only host read is the logged ``loss.item()`` the reference API returns (dqn.py:194).
+
+``cuda_graph=True`` (opt-in) captures that whole pipeline for a given
+(buffer, sample size) once and replays it per ``update``: the host draws the uniforms (PER) or
+the indices (uniform replay) from ``np.random`` exactly as the reference does, uploads them
+into a static tensor, refreshes the buffer's ring bookkeeping in place and launches one graph.
 """
 from __future__ import annotations
 
@@ -16,6 +21,7 @@ import numpy as np
 import torch
 
 from ..data.batch import Batch
+from . import _graph as G
 from .base import BasePolicy
 
 
@@ -33,9 +39,12 @@ class DQNPolicy(BasePolicy):
         reward_normalization: bool = False,
         is_double: bool = True,
         clip_loss_grad: bool = False,
+        cuda_graph: bool = False,
         **kwargs: Any,
     ) -> None:
         super().__init__(**kwargs)
+        self._cuda_graph = cuda_graph
+        self._graphed: Dict[Any, "_GraphedUpdate"] = {}
         self.model = model
         self.optim = optim
         self.eps = 0.0
@@ -104,9 +113,8 @@ class DQNPolicy(BasePolicy):
         return Batch(logits=logits, act=act, state=hidden)
 
     # ---- learn (dqn.py:172-194) -------------------------------------------------------------------
-    def learn(self, batch: Batch, **kwargs: Any) -> Dict[str, float]:
-        if self._target and self._iter % self._freq == 0:
-            self.sync_weight()
+    def _learn_step(self, batch: Batch) -> torch.Tensor:
+        """dqn.py:175-192 without the target sync, the iteration count and the host read."""
         self.optim.zero_grad()
         weight = batch.pop("weight", 1.0)
         q = self(batch).logits
@@ -125,8 +133,23 @@ class DQNPolicy(BasePolicy):
         loss.backward()
         self._sync_grads(self.model.parameters())
         self.optim.step()
+        return loss.detach()
+
+    def learn(self, batch: Batch, **kwargs: Any) -> Dict[str, float]:
+        if self._target and self._iter % self._freq == 0:
+            self.sync_weight()
+        loss = self._learn_step(batch)
         self._iter += 1
         return {"loss": loss.item()}
+
+    def update(self, sample_size: int, buffer: Optional[Any], **kwargs: Any) -> Dict[str, Any]:
+        if not self._cuda_graph or buffer is None or sample_size <= 0 or len(buffer) == 0:
+            return super().update(sample_size, buffer, **kwargs)
+        key = (id(buffer), int(sample_size))
+        g = self._graphed.get(key)
+        if g is None:
+            g = self._graphed[key] = _GraphedUpdate(self, buffer, int(sample_size))
+        return g.update()
 
     def exploration_noise(self, act: Any, batch: Batch) -> Any:
         """Epsilon-greedy on the host RNG, as the reference draws it (dqn.py:196-210)."""
@@ -143,3 +166,79 @@ class DQNPolicy(BasePolicy):
         rand_act = q.argmax(axis=1)
         a[rand_mask] = rand_act[rand_mask]
         return torch.as_tensor(a, device=act.device) if is_tensor else a
+
+
+class _GraphedUpdate:
+    """``DQNPolicy.update(sample_size, buffer)`` as one CUDA-graph replay.
+
+    Static inputs: the step's uniforms (prioritized buffers: ``np.random.rand``, prio.py:61) or
+    its indices (uniform buffers: the buffer's own host draw).  Body: PER descent + importance
+    weights -> ``buffer[idx]`` gathers -> n-step return with the target network on
+    ``buffer[terminal]`` -> loss, backward, optimiser step -> ``update_weight``.  Everything
+    the body reads of the buffer's bookkeeping sits at fixed device addresses that ``_state()``
+    refreshes in place, so transitions added between updates are seen by the next replay.
+    Graphs are keyed by learning rates, beta and train/eval mode.
+    """
+
+    def __init__(self, policy: DQNPolicy, buffer: Any, bsz: int) -> None:
+        self.p, self.buf, self.bsz = policy, buffer, bsz
+        self.dev = policy.device
+        self.per = hasattr(buffer, "sample_with_uniforms")
+        G.prepare_optimizer(policy.optim, self.dev)
+        self.u = torch.zeros(bsz, dtype=torch.float64, device=self.dev)
+        self.idx = torch.zeros(bsz, dtype=torch.int64, device=self.dev)
+        self.loss = torch.zeros(1, dtype=torch.float32, device=self.dev)
+        self.graphs: Dict[Any, torch.cuda.CUDAGraph] = {}
+
+    def _draw(self) -> None:
+        if self.per and not self.buf.device_rng:
+            self.u.copy_(torch.from_numpy(np.random.rand(self.bsz)))
+        elif self.per:
+            self.u.copy_(torch.rand(self.bsz, dtype=torch.float64, device=self.dev))
+        else:
+            self.idx.copy_(self.buf.sample_indices(self.bsz))
+
+    def _body(self) -> None:
+        p, buf = self.p, self.buf
+        idx = buf.sample_with_uniforms(self.u) if self.per else self.idx
+        batch = buf[idx]
+        batch = p.process_fn(batch, buf, idx)
+        self.loss.copy_(p._learn_step(batch).reshape(1))
+        p.post_process_fn(batch, buf, idx)
+
+    def _guarded(self):
+        p, buf = self.p, self.buf
+        out = list(p.model.parameters()) + list(p.model.buffers())
+        if self.per:  # the warm-up iterations really update priorities
+            out += [buf.weight._value, buf._prio]
+        return out
+
+    def _key(self) -> tuple:
+        buf = self.buf  # storage identity: a re-allocated field invalidates captured addresses
+        return (G.lr_key(self.p.optim), getattr(buf, "_beta", None), self.p.training,
+                tuple(id(v) for v in buf._meta.values()))
+
+    def update(self) -> Dict[str, float]:
+        p, buf = self.p, self.buf
+        p.updating = True
+        if p._target and p._iter % p._freq == 0:
+            p.sync_weight()
+        buf._state()  # ring bookkeeping of transitions added since the last update, in place
+        key = self._key()
+        graph = self.graphs.get(key)
+        if graph is None:
+            self._draw_for_warmup()
+            graph = self.graphs[key] = G.capture(self._body, self._guarded, p.optim, self.dev)
+        self._draw()
+        graph.replay()
+        p._iter += 1
+        if p.lr_scheduler is not None:
+            p.lr_scheduler.step()
+        p.updating = False
+        return {"loss": self.loss.item()}
+
+    def _draw_for_warmup(self) -> None:
+        """Warm-up inputs must not consume the host RNG stream the real updates draw from."""
+        state = np.random.get_state()
+        self._draw()
+        np.random.set_state(state)

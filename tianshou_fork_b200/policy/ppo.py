@@ -27,6 +27,7 @@ import torch
 from torch import nn
 
 from .. import _lib as L
+from . import _graph as G
 from ..data.batch import Batch
 from .a2c import A2CPolicy
 from .pg import RunningMeanStd, _minibatches, _split_bounds  # noqa: F401 (re-exported)
@@ -216,19 +217,7 @@ class _GraphedLearner:
         self.dev = policy.device
         self.static: Dict[str, torch.Tensor] = {}
         self.graphs: Dict[Any, torch.cuda.CUDAGraph] = {}
-        optim = policy.optim
-        ok = isinstance(optim, (torch.optim.Adam, torch.optim.AdamW, torch.optim.RMSprop)) or (
-            isinstance(optim, torch.optim.SGD)
-            and all(g["dampening"] == 0 or g["momentum"] == 0 for g in optim.param_groups))
-        if not ok:
-            raise ValueError("cuda_graph=True supports Adam, AdamW, RMSprop and SGD without "
-                             f"dampening (their fresh state is all zeros); got {type(optim)}")
-        for g in optim.param_groups:
-            if "capturable" in g:
-                g["capturable"] = True
-        for st in optim.state.values():  # an optimiser that already stepped on the host
-            if torch.is_tensor(st.get("step")) and not st["step"].is_cuda:
-                st["step"] = st["step"].to(self.dev)
+        G.prepare_optimizer(policy.optim, self.dev)
         self.cursor = torch.zeros(1, dtype=torch.int64, device=self.dev)
         self.row = torch.zeros(1, dtype=torch.int64, device=self.dev)
         # one spare row: warm-up iterations log there, so a capture in the middle of a learn
@@ -255,61 +244,29 @@ class _GraphedLearner:
     def _body(self, m: int) -> None:
         s, p = self.static, self.p
         mb = s["perm"].index_select(0, self.cursor + s["arange"][:m])
-        # argument validation of torch.distributions reads a device flag on the host
-        # (``if not valid.all()``), which a stream capture cannot contain
-        validate = torch.distributions.Distribution._validate_args
-        torch.distributions.Distribution.set_default_validate_args(False)
-        try:
+        with G.no_distribution_validation():
             vals = p._minibatch_step(
                 s["obs"].index_select(0, mb), s["act"].index_select(0, mb), mb,
                 s["logp_old"], s["adv"], s["returns"], s["v_s"])
-        finally:
-            torch.distributions.Distribution.set_default_validate_args(validate)
         self.log.index_copy_(0, self.row, vals[None])
         self.cursor += m
         self.row += 1
 
-    def _modules_state(self) -> List[torch.Tensor]:
+    def _guarded(self) -> List[torch.Tensor]:
         p = self.p
-        return list(p._params) + list(p.actor.buffers()) + list(p.critic.buffers())
+        return (list(p._params) + list(p.actor.buffers()) + list(p.critic.buffers())
+                + [self.cursor, self.row])
 
-    def _capture(self, m: int) -> torch.cuda.CUDAGraph:
-        p, optim = self.p, self.p.optim
-        live = self._modules_state() + [self.cursor, self.row]
-        saved = [t.detach().clone() for t in live]
-        saved_opt = {q: {k: v.detach().clone() for k, v in st.items() if torch.is_tensor(v)}
-                     for q, st in optim.state.items()}
-        side = torch.cuda.Stream(device=self.dev)
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
-            for _ in range(3):
-                self.cursor.zero_()
-                self.row.fill_(self.LOG_ROWS)
-                self._body(m)
-        torch.cuda.current_stream().wait_stream(side)
-
-        def restore() -> None:
-            with torch.no_grad():
-                for t, v in zip(live, saved):
-                    t.copy_(v)
-                for q, st in optim.state.items():
-                    for k, v in st.items():
-                        if torch.is_tensor(v):
-                            old = saved_opt.get(q, {}).get(k)
-                            v.copy_(old) if old is not None else v.zero_()
-        restore()
-        graph = torch.cuda.CUDAGraph()
+    def _warm_row(self) -> None:
         self.cursor.zero_()
-        with torch.cuda.graph(graph):
-            self._body(m)
-        restore()  # capture launches nothing, but leave cursor / row exactly as they were
-        return graph
+        self.row.fill_(self.LOG_ROWS)  # warm-up iterations log into the spare row
 
     def _graph(self, m: int) -> torch.cuda.CUDAGraph:
-        key = (m, tuple(float(g["lr"]) for g in self.p.optim.param_groups), self.p.training)
+        key = (m, G.lr_key(self.p.optim), self.p.training)
         g = self.graphs.get(key)
         if g is None:
-            g = self.graphs[key] = self._capture(m)
+            g = self.graphs[key] = G.capture(lambda: self._body(m), self._guarded,
+                                             self.p.optim, self.dev, self._warm_row)
         return g
 
     # ---- learn ---------------------------------------------------------------------------------
