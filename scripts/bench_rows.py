@@ -573,6 +573,11 @@ def row_dqn():
         np.random.seed(0)
         iters = 100
         total = wall(lambda: pol.update(bsz, buf), iters)
+        torch.manual_seed(0)
+        net_g = Net().to(DEV)
+        pol_g = ts.DQNPolicy(net_g, torch.optim.Adam(net_g.parameters(), lr=1e-4), 0.99,
+                             estimation_step=3, target_update_freq=500, cuda_graph=True)
+        graphed = wall(lambda: pol_g.update(bsz, buf), iters)
         seg = {}
         state = {}
 
@@ -610,6 +615,7 @@ def row_dqn():
 
         seg["networks_only"] = wall(nets_only, iters)
         emit("C4 DQNPolicy.update through the API", bsz=bsz, update_wall_us=total,
+             update_cuda_graph_wall_us=graphed, speedup_graph=total / graphed,
              **{k + "_us": v for k, v in seg.items()},
              data_path_share=1.0 - seg["networks_only"] / total)
 

@@ -177,7 +177,9 @@ class _GraphedUpdate:
     ``buffer[terminal]`` -> loss, backward, optimiser step -> ``update_weight``.  Everything
     the body reads of the buffer's bookkeeping sits at fixed device addresses that ``_state()``
     refreshes in place, so transitions added between updates are seen by the next replay.
-    Graphs are keyed by learning rates, beta and train/eval mode.
+    Graphs are keyed by learning rates, beta, train/eval mode and whether the update is one
+    that copies the online weights into the target network (the reference does that inside
+    ``learn``, i.e. after the targets were computed with the old target network).
     """
 
     def __init__(self, policy: DQNPolicy, buffer: Any, bsz: int) -> None:
@@ -188,6 +190,7 @@ class _GraphedUpdate:
         self.u = torch.zeros(bsz, dtype=torch.float64, device=self.dev)
         self.idx = torch.zeros(bsz, dtype=torch.int64, device=self.dev)
         self.loss = torch.zeros(1, dtype=torch.float32, device=self.dev)
+        self.last_indices = torch.zeros(bsz, dtype=torch.int64, device=self.dev)
         self.graphs: Dict[Any, torch.cuda.CUDAGraph] = {}
 
     def _draw(self) -> None:
@@ -198,17 +201,22 @@ class _GraphedUpdate:
         else:
             self.idx.copy_(self.buf.sample_indices(self.bsz))
 
-    def _body(self) -> None:
+    def _body(self, sync: bool) -> None:
         p, buf = self.p, self.buf
         idx = buf.sample_with_uniforms(self.u) if self.per else self.idx
+        self.last_indices.copy_(idx)  # what this update sampled, for callers that log it
         batch = buf[idx]
         batch = p.process_fn(batch, buf, idx)
+        if sync:  # the reference syncs inside learn(): AFTER the targets, BEFORE the step
+            p.sync_weight()
         self.loss.copy_(p._learn_step(batch).reshape(1))
         p.post_process_fn(batch, buf, idx)
 
     def _guarded(self):
         p, buf = self.p, self.buf
         out = list(p.model.parameters()) + list(p.model.buffers())
+        if p._target:  # the warm-up of the syncing variant overwrites the target network
+            out += list(p.model_old.parameters()) + list(p.model_old.buffers())
         if self.per:  # the warm-up iterations really update priorities
             out += [buf.weight._value, buf._prio]
         return out
@@ -221,14 +229,14 @@ class _GraphedUpdate:
     def update(self) -> Dict[str, float]:
         p, buf = self.p, self.buf
         p.updating = True
-        if p._target and p._iter % p._freq == 0:
-            p.sync_weight()
+        sync = bool(p._target and p._iter % p._freq == 0)  # dqn.py:173-174
         buf._state()  # ring bookkeeping of transitions added since the last update, in place
-        key = self._key()
+        key = self._key() + (sync,)
         graph = self.graphs.get(key)
         if graph is None:
             self._draw_for_warmup()
-            graph = self.graphs[key] = G.capture(self._body, self._guarded, p.optim, self.dev)
+            graph = self.graphs[key] = G.capture(lambda: self._body(sync), self._guarded,
+                                                 p.optim, self.dev)
         self._draw()
         graph.replay()
         p._iter += 1
