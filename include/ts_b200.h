@@ -301,6 +301,15 @@ int32_t ts_ppo_loss(const float* logp, const float* value, const float* logp_old
 int32_t ts_gather_rows(const void* src, int64_t n_rows, int64_t row_bytes, const int64_t* index,
                        int64_t M, void* out, ts_stream_t stream);
 
+/* Multi-field gather: the small per-transition fields of buffer[indices] -- act, rew,
+ * terminated, truncated, done, flat info / policy entries (tianshou/data/buffer/base.py:379-389,
+ * one NumPy fancy-index copy per key there) -- in one launch: dst[f][j,:] = src[f][index[j],:]
+ * for n_fields <= 8 fields of row_bytes[f] bytes each.  src / dst / row_bytes are HOST arrays of
+ * device pointers / sizes; every storage has n_rows rows; negative indices wrap like NumPy's. */
+int32_t ts_gather_fields(int32_t n_fields, const void* const* src, void* const* dst,
+                         const int64_t* row_bytes, int64_t n_rows, const int64_t* index,
+                         int64_t M, ts_stream_t stream);
+
 /* Frame-stack gather (ReplayBuffer.get with stack_num > 1, base.py:317-358; Atari-style
  * save_only_last_obs buffers, atari_dqn.py:135-140): out[j, i, :] = src[g_i, :] with
  * g_{k-1} = index[j] % total and g_{i-1} = prev(g_i) (episode-aware, manager.py:259-277; one

@@ -100,3 +100,32 @@ def test_gather_stack_abi_vs_oracle(row_shape, dtype, k, B, cap, M):
                                     B, cap, L.ptr(g_done), L.ptr(g_last), L.ptr(g_len),
                                     L.ptr(out), None, L.stream()), "ts_gather_stack")
     assert np.array_equal(out.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("m", [1, 33, 4096])
+def test_fused_field_gather_equals_per_key_indexing(m):
+    """buffer[indices]: act / rew / flags gathered by one ts_gather_fields launch
+    (base.py:379-389 copies key by key) -- byte-exact against torch indexing, for 1-D and 2-D
+    index arrays, negative indices and mixed row widths (u8 flags, f64 rew, f32[3] actions)."""
+    import tianshou_fork_b200 as ts
+    rng = np.random.default_rng(m)
+    E, T = 4, 50
+    buf = ts.VectorReplayBuffer(E * T, E)
+    for t in range(T):
+        buf.add(ts.Batch(obs=rng.standard_normal((E, 5)).astype(np.float32),
+                         act=rng.standard_normal((E, 3)).astype(np.float32),
+                         rew=rng.standard_normal(E), terminated=rng.random(E) < 0.1,
+                         truncated=rng.random(E) < 0.05,
+                         obs_next=rng.standard_normal((E, 5)).astype(np.float32), info={}))
+    idx = rng.integers(-E * T, E * T, m)
+    for index in (idx, torch.from_numpy(idx).cuda(), idx[: (m // 2) * 2].reshape(2, -1)):
+        if np.size(index) == 0 if not isinstance(index, torch.Tensor) else index.numel() == 0:
+            continue
+        got = buf[index]
+        ti = torch.as_tensor(index).cuda()
+        for k in ("act", "rew", "terminated", "truncated", "done"):
+            want = buf._meta[k][ti]
+            assert got[k].dtype == want.dtype and got[k].shape == want.shape, k
+            assert torch.equal(got[k], want), k
+    lib_out = buf._take_fields(("act", "rew", "done"), torch.from_numpy(idx).cuda())
+    assert torch.equal(lib_out[0], buf._meta.act[torch.from_numpy(idx).cuda()])

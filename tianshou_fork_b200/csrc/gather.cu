@@ -198,6 +198,53 @@ gather_stack_kernel(const V* __restrict__ src, int64_t row_vecs, const int64_t* 
     }
 }
 
+// ============================================================================================
+// Multi-field gather: the small per-transition fields of buffer[indices] (act, rew, terminated,
+// truncated, done, ...; data/buffer/base.py:379-389) in ONE launch instead of one indexing
+// launch per key.  The field table travels in the kernel parameters.  One thread per
+// (row, field); rows here are a few bytes (scalars, small action vectors), wide rows go through
+// ts_gather_rows / ts_gather_stack.
+// ============================================================================================
+constexpr int kMaxFields = 8;
+struct FieldArgs {
+    const uint8_t* src[kMaxFields];
+    uint8_t* dst[kMaxFields];
+    int32_t row_bytes[kMaxFields];
+    int32_t unit[kMaxFields];  // widest access the pointers and the pitch allow: 1, 2, 4 or 8
+    int32_t n;
+};
+
+__global__ void __launch_bounds__(256)
+gather_fields_kernel(FieldArgs a, int64_t n_rows, const int64_t* __restrict__ index, int64_t M) {
+    const int64_t total = M * a.n;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total;
+         t += (int64_t)gridDim.x * blockDim.x) {
+        const int f = (int)(t % a.n);
+        const int64_t j = t / a.n;
+        int64_t r = __ldg(index + j);
+        if (r < 0) r += n_rows;  // numpy-style negative index
+        const int rb = a.row_bytes[f];
+        const uint8_t* s = a.src[f] + r * rb;
+        uint8_t* d = a.dst[f] + j * rb;
+        switch (a.unit[f]) {
+            case 8:
+                for (int c = 0; c < rb; c += 8)
+                    *(uint2*)(d + c) = __ldg((const uint2*)(s + c));
+                break;
+            case 4:
+                for (int c = 0; c < rb; c += 4)
+                    *(uint32_t*)(d + c) = __ldg((const uint32_t*)(s + c));
+                break;
+            case 2:
+                for (int c = 0; c < rb; c += 2)
+                    *(uint16_t*)(d + c) = __ldg((const uint16_t*)(s + c));
+                break;
+            default:
+                for (int c = 0; c < rb; ++c) d[c] = __ldg(s + c);
+        }
+    }
+}
+
 }  // namespace
 }  // namespace ts
 
@@ -274,5 +321,36 @@ extern "C" int32_t ts_gather_rows(const void* src, int64_t n_rows, int64_t row_b
     else
         gather_rows_kernel<uint8_t><<<(unsigned)blocks, 256, 0, st>>>(
             (const uint8_t*)src, n_rows, row_bytes, index, M, (uint8_t*)out);
+    return check_launch();
+}
+
+extern "C" int32_t ts_gather_fields(int32_t n_fields, const void* const* src, void* const* dst,
+                                    const int64_t* row_bytes, int64_t n_rows,
+                                    const int64_t* index, int64_t M, ts_stream_t stream) {
+    if (n_fields < 0 || n_fields > kMaxFields || M < 0 || n_rows < 0) return TS_ERR_BAD_ARG;
+    if (n_fields == 0 || M == 0) return TS_OK;
+    if (!src || !dst || !row_bytes || !index) return TS_ERR_BAD_ARG;
+    FieldArgs a;
+    a.n = 0;
+    for (int f = 0; f < n_fields; ++f) {
+        if (row_bytes[f] < 0 || row_bytes[f] > (1 << 20)) return TS_ERR_BAD_ARG;
+        if (row_bytes[f] == 0) continue;
+        if (!src[f] || !dst[f]) return TS_ERR_BAD_ARG;
+        const int k = a.n++;
+        a.src[k] = (const uint8_t*)src[f];
+        a.dst[k] = (uint8_t*)dst[f];
+        a.row_bytes[k] = (int32_t)row_bytes[f];
+        int unit = 8;
+        while (unit > 1 && (row_bytes[f] % unit != 0 || !aligned(src[f], unit) ||
+                            !aligned(dst[f], unit)))
+            unit >>= 1;
+        a.unit[k] = unit;
+    }
+    if (a.n == 0) return TS_OK;
+    const int64_t total = M * a.n;
+    int64_t blocks = (total + 255) / 256;
+    const int64_t cap = (int64_t)kNumSMs * 8;
+    if (blocks > cap) blocks = cap;
+    gather_fields_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a, n_rows, index, M);
     return check_launch();
 }

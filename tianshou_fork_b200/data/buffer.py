@@ -17,6 +17,7 @@ Out of scope here: HDF5 save/load, ``from_data``.
 """
 from __future__ import annotations
 
+import ctypes
 from typing import Any, Dict, List, Optional, Tuple, Union
 
 import numpy as np
@@ -430,6 +431,42 @@ class ReplayBuffer:
             out_next = out_next.reshape(shape + (stack_num,) + row_shape)
         return out, out_next
 
+    def _take_fields(self, keys: Tuple[str, ...], indices: torch.Tensor) -> List[Any]:
+        """``[self._meta[k][indices] for k in keys]`` with ONE launch (``ts_gather_fields``)
+        for the keys stored as small-row CUDA tensors; anything else (nested batches, wide
+        rows) is indexed on its own.  base.py:379-389 does one fancy-index copy per key."""
+        out: List[Any] = [None] * len(keys)
+        fused: List[int] = []
+        for i, k in enumerate(keys):
+            v = self._meta[k]
+            if (isinstance(v, torch.Tensor) and v.is_cuda and v.is_contiguous() and v.ndim >= 1
+                    and v.shape[0] > 0 and v[0].numel() * v.element_size() <= 256):
+                fused.append(i)
+            else:
+                out[i] = _take(v, indices)
+        if fused and not (indices.is_cuda and indices.dtype == torch.int64):
+            indices = indices.to(device=self.device, dtype=torch.int64)
+        if len(fused) < 2 or len(fused) > 8 or indices.numel() == 0 or indices.ndim == 0:
+            for i in fused:
+                out[i] = _take(self._meta[keys[i]], indices)
+            return out
+        idx = indices.reshape(-1)
+        idx = idx if idx.is_contiguous() else idx.contiguous()
+        m, nf = idx.numel(), len(fused)
+        src, dst, rb = (ctypes.c_void_p * nf)(), (ctypes.c_void_p * nf)(), (ctypes.c_int64 * nf)()
+        n_rows = 0
+        for j, i in enumerate(fused):
+            v = self._meta.__dict__[keys[i]]
+            n_rows = v.shape[0]
+            o = torch.empty(tuple(indices.shape) + tuple(v.shape[1:]), dtype=v.dtype,
+                            device=v.device)
+            out[i] = o
+            src[j], dst[j] = v.data_ptr(), o.data_ptr()
+            rb[j] = (v.numel() // n_rows) * v.element_size()
+        L.check(L.lib().ts_gather_fields(nf, src, dst, rb, n_rows, idx.data_ptr(), m,
+                                         L.stream()), "ts_gather_fields")
+        return out
+
     def _as_device_index(self, index: IndexLike) -> torch.Tensor:
         if isinstance(index, torch.Tensor):
             return index.to(device=self.device, dtype=torch.int64)
@@ -453,13 +490,15 @@ class ReplayBuffer:
                 obs_next = self.get(indices, "obs_next", Batch())
             else:
                 obs_next = self.get(self.next(indices), "obs", Batch())
+        act, rew, terminated, truncated, done = self._take_fields(
+            ("act", "rew", "terminated", "truncated", "done"), indices)
         return Batch(
             obs=obs,
-            act=_take(self._meta["act"], indices),
-            rew=_take(self._meta["rew"], indices),
-            terminated=_take(self._meta["terminated"], indices),
-            truncated=_take(self._meta["truncated"], indices),
-            done=_take(self._meta["done"], indices),
+            act=act,
+            rew=rew,
+            terminated=terminated,
+            truncated=truncated,
+            done=done,
             obs_next=obs_next,
             info=self.get(indices, "info", Batch()),
             policy=self.get(indices, "policy", Batch()),
