@@ -131,7 +131,18 @@ def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return t.data_ptr()
 
 
+try:  # raw handles straight from the C bindings: torch.cuda.current_stream() walks through
+    # device-index parsing and availability checks in Python, ~15 us per call
+    _raw_stream = torch._C._cuda_getCurrentRawStream
+    _cur_device = torch._C._cuda_getDevice
+except AttributeError:  # pragma: no cover - older/newer torch without the private hooks
+    _raw_stream = _cur_device = None
+
+
 def stream() -> int:
+    """``cudaStream_t`` of torch's current stream on the current device."""
+    if _raw_stream is not None:
+        return _raw_stream(_cur_device())
     return torch.cuda.current_stream().cuda_stream
 
 

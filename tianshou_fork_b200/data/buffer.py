@@ -381,6 +381,8 @@ class ReplayBuffer:
         if key not in self._meta and default_value is not None:
             return default_value
         val = self._meta[key]
+        if isinstance(val, Batch) and val.is_empty():
+            return Batch()  # what the reference's loop ends in (IndexError -> Batch(), :355-358)
         if stack_num is None:
             stack_num = self.stack_num
         try:
@@ -437,34 +439,34 @@ class ReplayBuffer:
         rows) is indexed on its own.  base.py:379-389 does one fancy-index copy per key."""
         out: List[Any] = [None] * len(keys)
         fused: List[int] = []
+        meta = self._meta.__dict__
         for i, k in enumerate(keys):
-            v = self._meta[k]
-            if (isinstance(v, torch.Tensor) and v.is_cuda and v.is_contiguous() and v.ndim >= 1
-                    and v.shape[0] > 0 and v[0].numel() * v.element_size() <= 256):
+            v = meta[k]
+            if (isinstance(v, torch.Tensor) and v.is_cuda and v.ndim >= 1 and v.shape[0] > 0
+                    and v.is_contiguous() and v.stride(0) * v.element_size() <= 256):
                 fused.append(i)
             else:
                 out[i] = _take(v, indices)
-        if fused and not (indices.is_cuda and indices.dtype == torch.int64):
-            indices = indices.to(device=self.device, dtype=torch.int64)
-        if len(fused) < 2 or len(fused) > 8 or indices.numel() == 0 or indices.ndim == 0:
+        nf = len(fused)
+        if nf < 2 or nf > 8 or indices.ndim == 0 or indices.numel() == 0:
             for i in fused:
-                out[i] = _take(self._meta[keys[i]], indices)
+                out[i] = _take(meta[keys[i]], indices)
             return out
-        idx = indices.reshape(-1)
-        idx = idx if idx.is_contiguous() else idx.contiguous()
-        m, nf = idx.numel(), len(fused)
-        src, dst, rb = (ctypes.c_void_p * nf)(), (ctypes.c_void_p * nf)(), (ctypes.c_int64 * nf)()
+        if not (indices.is_cuda and indices.dtype == torch.int64 and indices.is_contiguous()):
+            indices = indices.to(device=self.device, dtype=torch.int64).contiguous()
+        shape = tuple(indices.shape)
+        arr_p, arr_i = _FIELD_ARRAYS[nf]
+        src, dst, rb = arr_p(), arr_p(), arr_i()
         n_rows = 0
         for j, i in enumerate(fused):
-            v = self._meta.__dict__[keys[i]]
+            v = meta[keys[i]]
             n_rows = v.shape[0]
-            o = torch.empty(tuple(indices.shape) + tuple(v.shape[1:]), dtype=v.dtype,
-                            device=v.device)
+            o = torch.empty(shape + tuple(v.shape[1:]), dtype=v.dtype, device=v.device)
             out[i] = o
             src[j], dst[j] = v.data_ptr(), o.data_ptr()
-            rb[j] = (v.numel() // n_rows) * v.element_size()
-        L.check(L.lib().ts_gather_fields(nf, src, dst, rb, n_rows, idx.data_ptr(), m,
-                                         L.stream()), "ts_gather_fields")
+            rb[j] = v.stride(0) * v.element_size() if v.ndim > 1 else v.element_size()
+        L.check(L.lib().ts_gather_fields(nf, src, dst, rb, n_rows, indices.data_ptr(),
+                                         indices.numel(), L.stream()), "ts_gather_fields")
         return out
 
     def _as_device_index(self, index: IndexLike) -> torch.Tensor:
@@ -506,6 +508,10 @@ class ReplayBuffer:
 
 
 # ---- helpers ---------------------------------------------------------------------------------
+# ctypes array types of the field table, by field count (creating a type per call is slow)
+_FIELD_ARRAYS = {n: (ctypes.c_void_p * n, ctypes.c_int64 * n) for n in range(1, 9)}
+
+
 def _host(x: Any) -> np.ndarray:
     if isinstance(x, torch.Tensor):
         return x.detach().cpu().numpy()

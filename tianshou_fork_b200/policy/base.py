@@ -53,7 +53,7 @@ def _float_dev(x: Any, device: torch.device) -> torch.Tensor:
 
 
 def _workspace(nbytes: int, device: torch.device) -> torch.Tensor:
-    key = (device.index or 0, torch.cuda.current_stream().cuda_stream)
+    key = (device.index or 0, L.stream())
     ws = _ws_cache.get(key)
     if ws is None or ws.numel() < nbytes:
         # zero-initialised once: the flat kernel keeps its call count in it (include/ts_b200.h)
