@@ -418,7 +418,7 @@ class ReplayBuffer:
         st = self._state()
         val = val if val.is_contiguous() else val.contiguous()
         row_shape = tuple(val.shape[1:])
-        row_bytes = int(np.prod(row_shape, dtype=np.int64)) * val.element_size()
+        row_bytes = val.stride(0) * val.element_size() if val.ndim > 1 else val.element_size()
         out = torch.empty((idx.numel(), stack_num) + row_shape, dtype=val.dtype,
                           device=val.device)
         out_next = torch.empty_like(out) if with_next else None
@@ -471,6 +471,8 @@ class ReplayBuffer:
 
     def _as_device_index(self, index: IndexLike) -> torch.Tensor:
         if isinstance(index, torch.Tensor):
+            if index.is_cuda and index.dtype == torch.int64 and index.device == self.device:
+                return index  # `.to` with nothing to do still costs a dispatcher round trip
             return index.to(device=self.device, dtype=torch.int64)
         return torch.from_numpy(np.asarray(index, dtype=np.int64)).to(self.device)
 
