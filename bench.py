@@ -53,6 +53,8 @@ def parse_args():
     p.add_argument("--skip-per", action="store_true")
     p.add_argument("--skip-e2e", action="store_true")
     p.add_argument("--skip-cpu", action="store_true")
+    p.add_argument("--skip-updates", action="store_true",
+                   help="skip the C3 PPOPolicy.learn / C4 DQNPolicy.update legs")
     return p.parse_args()
 
 
@@ -403,6 +405,11 @@ def run_b200(args):
                                    "sample": f"{pn} steps, median {pmed * 1e6:.1f} us"}
             per["speedup_vs_cpu_port"] = per["value"] / pv
 
+    # ---- C3 / C4 through the public API (rank 0, N == 1 only; reported beside the headline) ----
+    updates = None
+    if rank == 0 and world == 1 and not args.skip_updates and not args.skip_e2e:
+        updates = run_updates()
+
     if rank == 0:
         line = {
             "metric": "GAE transitions/s", "value": value, "unit": "transitions/s",
@@ -418,11 +425,39 @@ def run_b200(args):
                                       if graph is not None else "eager launches of ts_gae_rows"),
                        "parallelism": f"env streams sharded over {world} GPU(s), no collective"},
             "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": launches,
-            "roofline": roofline, "cpu_baseline": cpu, "per": per,
+            "roofline": roofline, "cpu_baseline": cpu, "per": per, "updates": updates,
         }
         emit_result(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_updates():
+    """BASELINE.json configs[2] and configs[3] through the public API: wall time per minibatch
+    of PPOPolicy.learn (Ant shape) and per DQNPolicy.update (Atari shape, PER 2^20), eager and
+    CUDA-graphed, with the reference's learn() arithmetic in torch eager on the same GPU and on
+    the host beside it (scripts/bench_rows.py row_learn / row_dqn).  Never fails the bench."""
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        import bench_rows
+        bench_rows.ROWS.clear()
+        bench_rows.row_learn()
+        bench_rows.row_dqn()
+        out = {"unit": "us (wall, per minibatch / per update)"}
+        for r in bench_rows.ROWS:
+            if r["row"].startswith("C3"):
+                out[f"c3_ppo_learn_mb{r['minibatch']}"] = {
+                    "cuda_graph": r["this_cuda_graph_us"], "eager": r["this_eager_us"],
+                    "reference_arithmetic_same_gpu": r["reference_arithmetic_torch_gpu_us"],
+                    "reference_arithmetic_cpu": r["reference_arithmetic_torch_cpu_us"],
+                    "cpu_threads": r["cpu_threads"]}
+            else:
+                out[f"c4_dqn_update_bsz{r['bsz']}"] = {
+                    "cuda_graph": r["update_cuda_graph_wall_us"], "eager": r["update_wall_us"],
+                    "networks_only_eager": r["networks_only_us"]}
+        return out
+    except Exception as e:  # reported, not fatal: the headline legs above are already measured
+        return {"error": f"{type(e).__name__}: {e}"}
 
 
 def run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):

@@ -69,8 +69,12 @@ def cpu_us(fn, seconds=2.0):
     return float(np.median(t)) * 1e6
 
 
+ROWS = []  # every emitted row, for callers that import this module (bench.py)
+
+
 def emit(row, **kw):
-    print(json.dumps(dict(row=row, **kw)), flush=True)
+    ROWS.append(dict(row=row, **kw))
+    print(json.dumps(ROWS[-1]), flush=True)
 
 
 def fill_vec(buf, E, T, rng, p_term=1 / 1000, p_trunc=1 / 10000, rew3=True):
