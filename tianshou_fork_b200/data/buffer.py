@@ -476,6 +476,15 @@ class ReplayBuffer:
             return index.to(device=self.device, dtype=torch.int64)
         return torch.from_numpy(np.asarray(index, dtype=np.int64)).to(self.device)
 
+    def obs_next_of(self, index: IndexLike) -> Any:
+        """The ``obs_next`` entry of ``buffer[index]`` alone (base.py:374-378): what a target
+        network reads of the n-step terminal transitions (dqn.py:85-86), without gathering the
+        other keys."""
+        indices = self._as_device_index(index)
+        if self._save_obs_next:
+            return self.get(indices, "obs_next", Batch())
+        return self.get(self.next(indices), "obs", Batch())
+
     def __getitem__(self, index: Union[slice, IndexLike]) -> Batch:
         """``buffer[index]``: gather copies of every stored key (base.py:360-389)."""
         if isinstance(index, slice):

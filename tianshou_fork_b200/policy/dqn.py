@@ -77,7 +77,11 @@ class DQNPolicy(BasePolicy):
 
     # ---- target (dqn.py:84-96) --------------------------------------------------------------------
     def _target_q(self, buffer: Any, indices: Any) -> torch.Tensor:
-        batch = buffer[indices]  # batch.obs_next: s_{t+n}
+        if hasattr(buffer, "obs_next_of"):  # only obs_next (s_{t+n}) and info are read below
+            batch = Batch(obs_next=buffer.obs_next_of(indices),
+                          info=buffer.get(indices, "info", Batch()))
+        else:
+            batch = buffer[indices]  # batch.obs_next: s_{t+n}
         result = self(batch, input="obs_next")
         if self._target:  # target_Q = Q_old(s_, argmax(Q_new(s_, *)))
             target_q = self(batch, model="model_old", input="obs_next").logits
