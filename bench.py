@@ -629,8 +629,9 @@ def run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
     us = ms * 1e3 / steps
     value = PER_BATCH * steps / (ms * 1e-3)  # global samples/s (the batch is global for N > 1)
     achieved = PER_BATCH * PER_ALG_BYTES_PER_SAMPLE / (us * 1e-6) / 1e9
+    e2e = per_e2e(torch, dev) if world == 1 else None
     return {"metric": "PER samples/s", "value": value, "unit": "samples/s", "us_per_step": us,
-            "scaling": scaling,
+            "e2e": e2e, "scaling": scaling,
             "workload": f"{world} shard(s) x 2^20-leaf f64 sum tree, global batch 4096, alpha 0.6 "
                         "beta 0.4; step = sample (descent + IS weights + batch-max norm) + "
                         "update_weight (|td|+eps, pow, last-writer table in shared memory, "
@@ -642,6 +643,58 @@ def run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
                          "note": "latency-bound: ~10 dependent L2 round trips of ~0.5 us per "
                                  "step plus launch and barrier latency, not bytes; the tree is "
                                  "L2-resident"}}
+
+
+def per_e2e(torch, dev):
+    """The PER step through the reference-facing class with HOST buffers: uniforms drawn by
+    np.random on the host (prio.py:61) and copied in, sampled indices and importance weights
+    read back to the host, host td-errors copied in for update_weight -- every step, inside the
+    timed region (wall clock around the loop, one sync at the end: every step already ends in a
+    blocking device-to-host read)."""
+    try:
+        import tianshou_fork_b200 as ts
+        buf = ts.PrioritizedVectorReplayBuffer(PER_LEAVES, 16, alpha=PER_ALPHA, beta=PER_BETA)
+        E = 16
+        for _ in range(2):  # allocate storage; the ring bookkeeping is then declared full
+            buf.add(ts.Batch(obs=np.zeros((E, 1), np.float32), act=np.zeros(E, np.int64),
+                             rew=np.zeros(E), terminated=np.zeros(E, bool),
+                             truncated=np.zeros(E, bool),
+                             obs_next=np.zeros((E, 1), np.float32), info={}))
+        T = PER_LEAVES // E
+        buf._rings[:, 0], buf._rings[:, 1] = 0, T
+        buf._lengths[:] = T
+        buf.last_index[:] = np.arange(E) * T + T - 1
+        buf._version += 1
+        rng = np.random.default_rng(3)
+        buf.update_weight(torch.arange(PER_LEAVES, device=dev),
+                          torch.from_numpy(rng.standard_normal(PER_LEAVES).astype(np.float32)
+                                           ).to(dev))
+        tds = [rng.standard_normal(PER_BATCH).astype(np.float32) for _ in range(8)]
+
+        def step(i):
+            idx = buf.sample_indices(PER_BATCH)            # host uniforms -> device descent
+            w = buf._cached_weight[1]                      # IS weights of the same launch
+            idx_h, w_h = idx.cpu().numpy(), w.cpu().numpy()  # the learner's host copies
+            buf.update_weight(idx_h, tds[i % 8])           # host td-errors -> device tree
+            return idx_h, w_h
+
+        for i in range(20):
+            step(i)
+        torch.cuda.synchronize()
+        steps = 300
+        t0 = time.perf_counter()
+        for i in range(steps):
+            step(i)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        return {"value": PER_BATCH * steps / dt, "unit": "samples/s",
+                "us_per_step": dt / steps * 1e6,
+                "h2d_bytes_per_step": PER_BATCH * (8 + 8 + 4),
+                "d2h_bytes_per_step": PER_BATCH * (8 + 8),
+                "api": "PrioritizedVectorReplayBuffer.sample_indices + importance weights + "
+                       "update_weight with NumPy arrays in and out"}
+    except Exception as e:  # reported, not fatal
+        return {"error": f"{type(e).__name__}: {e}"}
 
 
 _RESULT_FD = None
