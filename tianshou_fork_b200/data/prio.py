@@ -34,34 +34,6 @@ from .manager import ReplayBufferManager
 from .segtree import SegmentTree
 
 
-_PIN_SLOTS = 4
-_pin_ring: dict = {}
-
-
-def _pinned_upload(arr: np.ndarray, device: torch.device) -> torch.Tensor:
-    """Host array -> new device tensor through rotating pinned buffers; a slot is reused only
-    after the copy that last read it has completed (event per slot)."""
-    key = (arr.dtype.str, device.index)
-    ring = _pin_ring.get(key)
-    if ring is None or ring["bufs"][0].numel() < arr.size:
-        n = max(arr.size, 4096)
-        t = torch.from_numpy(np.empty(0, arr.dtype)).dtype
-        ring = _pin_ring[key] = {
-            "bufs": [torch.empty(n, dtype=t).pin_memory() for _ in range(_PIN_SLOTS)],
-            "events": [None] * _PIN_SLOTS, "next": 0}
-    slot = ring["next"]
-    ring["next"] = (slot + 1) % _PIN_SLOTS
-    ev = ring["events"][slot]
-    if ev is not None:
-        ev.synchronize()
-    stage = ring["bufs"][slot][:arr.size]
-    stage.numpy()[:] = arr.reshape(-1)
-    out = stage.to(device, non_blocking=True).reshape(arr.shape)
-    ev = ring["events"][slot] = ev if ev is not None else torch.cuda.Event()
-    ev.record()
-    return out
-
-
 class PrioritizedReplayBuffer(ReplayBuffer):
     """Prioritized Experience Replay, arXiv:1511.05952 (prio.py:9-105)."""
 
@@ -114,9 +86,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
     def _uniforms(self, batch_size: int) -> torch.Tensor:
         if self.device_rng:
             return torch.rand(batch_size, dtype=torch.float64, device=self.device)
-        # prio.py:61 draws on the host; the draw travels through a small ring of pinned
-        # staging buffers so that the copy is asynchronous (a pageable source makes it blocking)
-        return _pinned_upload(np.random.rand(batch_size), self.device)
+        return torch.from_numpy(np.random.rand(batch_size)).to(self.device)  # prio.py:61
 
     def sample_indices(self, batch_size: int) -> torch.Tensor:
         """Stratified-by-priority indices (prio.py:59-64).  The importance weights of the
@@ -161,18 +131,11 @@ class PrioritizedReplayBuffer(ReplayBuffer):
                       ) -> None:
         """``weight[index] = (|new_weight| + eps) ** alpha`` plus max/min tracking
         (prio.py:78-89), one launch, no host sync when given CUDA tensors."""
-        if isinstance(index, np.ndarray) and index.dtype == np.int64 and index.size:
-            idx = _pinned_upload(index, self.device).reshape(-1)
-        else:
-            idx = self.weight._dev_index(index)
+        idx = self.weight._dev_index(index)
         if isinstance(new_weight, torch.Tensor):
             td = new_weight.detach().to(self.device)
         else:
-            arr = np.asarray(new_weight)
-            if arr.dtype in (np.float32, np.float64) and arr.size:
-                td = _pinned_upload(arr, self.device)
-            else:
-                td = torch.as_tensor(arr, device=self.device)
+            td = torch.as_tensor(np.asarray(new_weight), device=self.device)
         if td.dtype not in (torch.float32, torch.float64):
             td = td.to(torch.float64)
         td = td.reshape(-1).contiguous()
