@@ -626,6 +626,9 @@ def row_dqn():
 
 if __name__ == "__main__":
     torch.cuda.set_device(0)
+    for kv in [x for x in os.environ.get("TS_TUNE", "").split(",") if x]:  # A/B of tuning knobs
+        key, val = kv.split("=")
+        L.check(L.lib().ts_tune_set(key.encode(), int(val)), "tune " + key)
     which = sys.argv[1:] or ["gae_api", "gae_flat", "nstep_index", "gather", "gather_stack", "add", "ppo", "learn"]
     for w in which:
         globals()["row_" + w]()

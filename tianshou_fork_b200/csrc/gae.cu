@@ -637,7 +637,9 @@ struct FlatTmaLayout {
 };
 
 template <typename RewT, typename InT, typename OutT, int NT, bool HAS_IDX>
-__global__ void __launch_bounds__(NT, 768 / NT)  // 3 x 256 threads per SM: <= 80 registers
+// 3 x 256 threads per SM (<= 80 registers) without indices; with them a stage is 45 KB and only
+// two CTAs fit an SM's shared memory anyway, so the index arithmetic gets 128 registers
+__global__ void __launch_bounds__(NT, HAS_IDX ? 2 : 768 / NT)
 gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
                     const InT* __restrict__ v_next, const uint8_t* __restrict__ term,
                     const uint8_t* __restrict__ trunc, const FlatGather g, int64_t N,
@@ -843,21 +845,33 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
                     *(reinterpret_cast<const longlong2*>(in + L::OFF_IDX) + (e0 / 2 + q));
                 id[2 * q] = a.x; id[2 * q + 1] = a.y;
             }
-            if (g.buf_term != nullptr) {
-                uint32_t m_lo = 0, m_hi = 0;
+            // strips of consecutive indices are the rule (batch order is chronological inside
+            // a sub-buffer, manager.py:187-192)
+            bool consec = true;
 #pragma unroll
-                for (int q = 0; q < VEC; ++q) {
-                    const uint32_t bit = __ldg(g.buf_term + id[q]) != 0 ? 1u << (8 * (q & 3)) : 0u;
-                    if (q < 4) m_lo |= bit; else m_hi |= bit;
+            for (int q = 1; q < VEC; ++q) consec = consec && id[q] == id[0] + q;
+            if (g.buf_term != nullptr) {
+                const uintptr_t a0 = reinterpret_cast<uintptr_t>(g.buf_term + id[0]);
+                if (consec && (a0 & 7) == 0) {
+                    // the eight mask bytes are one aligned word: one dependent load, not eight
+                    wt = __ldg(reinterpret_cast<const uint2*>(g.buf_term + id[0]));
+                } else if (consec && (a0 & 3) == 0) {
+                    wt.x = __ldg(reinterpret_cast<const uint32_t*>(g.buf_term + id[0]));
+                    wt.y = __ldg(reinterpret_cast<const uint32_t*>(g.buf_term + id[0] + 4));
+                } else {
+                    uint32_t m_lo = 0, m_hi = 0;
+#pragma unroll
+                    for (int q = 0; q < VEC; ++q) {
+                        const uint32_t bit =
+                            __ldg(g.buf_term + id[q]) != 0 ? 1u << (8 * (q & 3)) : 0u;
+                        if (q < 4) m_lo |= bit; else m_hi |= bit;
+                    }
+                    wt.x = m_lo; wt.y = m_hi;
                 }
-                wt.x = m_lo; wt.y = m_hi;
             }
             if (g.unfinished != nullptr) {
                 // a strip of consecutive indices touches at most two sub-buffers of >= 8 steps:
                 // two sub-buffer look-ups instead of eight
-                bool consec = true;
-#pragma unroll
-                for (int q = 1; q < VEC; ++q) consec = consec && id[q] == id[0] + q;
                 const int64_t s0 = sub_of(id[0], g.offset, g.B, g.sub_size);
                 const int64_t s7 = sub_of(id[VEC - 1], g.offset, g.B, g.sub_size);
                 if (consec && s7 - s0 <= 1) {
