@@ -89,3 +89,30 @@ def test_graphed_update_sees_transitions_added_between_updates():
     assert np.allclose(le, lg, rtol=1e-5, atol=1e-6)
     for a, b in zip(pe, pg):
         assert torch.allclose(a, b, rtol=1e-5, atol=1e-6)
+
+
+def test_policy_with_captured_graphs_pickles():
+    """A policy that has captured CUDA graphs pickles (the graphs are dropped and re-captured)."""
+    import pickle
+    import tianshou_fork_b200 as ts
+    from helpers import ppo_update_nets
+    Actor, _ = ppo_update_nets(torch)
+    rng = np.random.default_rng(1)
+    buf = ts.VectorReplayBuffer(4 * 32, 4)
+    for _ in range(32):
+        buf.add(ts.Batch(obs=rng.standard_normal((4, 3)).astype(np.float32),
+                         act=rng.integers(0, 4, 4), rew=rng.standard_normal(4),
+                         terminated=rng.random(4) < 0.1, truncated=np.zeros(4, bool),
+                         obs_next=rng.standard_normal((4, 3)).astype(np.float32), info={}))
+    net = Actor().cuda()
+    policy = ts.DQNPolicy(net, torch.optim.Adam(net.parameters(), lr=1e-3), 0.9,
+                          estimation_step=2, cuda_graph=True)
+    np.random.seed(0)
+    a = policy.update(8, buf)["loss"]
+    clone = pickle.loads(pickle.dumps(policy))
+    assert clone._graphed == {} and np.isfinite(a)
+    np.random.seed(5)
+    l1 = policy.update(8, buf)["loss"]
+    np.random.seed(5)
+    l2 = clone.update(8, buf)["loss"]  # re-captures against its own copies of the networks
+    assert np.isclose(l1, l2, rtol=1e-5)

@@ -141,6 +141,15 @@ class BasePolicy(nn.Module):
     def set_agent_id(self, agent_id: int) -> None:
         self.agent_id = agent_id
 
+    def __getstate__(self) -> Dict[str, Any]:
+        """Captured CUDA graphs hold device addresses: they are rebuilt after unpickling."""
+        state = dict(self.__dict__)
+        if state.get("_graphs") is not None:
+            state["_graphs"] = None
+        if state.get("_graphed"):
+            state["_graphed"] = {}
+        return state
+
     # ---- data-parallel learners (SURVEY.md 8e) --------------------------------------------------
     def set_data_parallel(self, enabled: bool = True, group: Any = None) -> None:
         """One process per GPU, each with its own env streams / samples: after ``backward`` the
