@@ -91,12 +91,20 @@ def test_graphed_update_sees_transitions_added_between_updates():
         assert torch.allclose(a, b, rtol=1e-5, atol=1e-6)
 
 
+class _QNet(torch.nn.Module):  # module level: picklable
+    def __init__(self):
+        super().__init__()
+        self.net = torch.nn.Sequential(torch.nn.Linear(3, 32), torch.nn.Tanh(),
+                                       torch.nn.Linear(32, 4))
+
+    def forward(self, obs, state=None, info=None):
+        return self.net(obs), state
+
+
 def test_policy_with_captured_graphs_pickles():
     """A policy that has captured CUDA graphs pickles (the graphs are dropped and re-captured)."""
     import pickle
     import tianshou_fork_b200 as ts
-    from helpers import ppo_update_nets
-    Actor, _ = ppo_update_nets(torch)
     rng = np.random.default_rng(1)
     buf = ts.VectorReplayBuffer(4 * 32, 4)
     for _ in range(32):
@@ -104,7 +112,7 @@ def test_policy_with_captured_graphs_pickles():
                          act=rng.integers(0, 4, 4), rew=rng.standard_normal(4),
                          terminated=rng.random(4) < 0.1, truncated=np.zeros(4, bool),
                          obs_next=rng.standard_normal((4, 3)).astype(np.float32), info={}))
-    net = Actor().cuda()
+    net = _QNet().cuda()
     policy = ts.DQNPolicy(net, torch.optim.Adam(net.parameters(), lr=1e-3), 0.9,
                           estimation_step=2, cuda_graph=True)
     np.random.seed(0)
