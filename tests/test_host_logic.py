@@ -36,3 +36,26 @@ def test_batch_split_matches_reference_boundaries():
     got = np.concatenate([m.a for m in b.split(3)])
     np.random.seed(3)
     assert np.array_equal(got, np.random.permutation(10))
+
+
+def test_batch_conveniences():
+    """Batch.update / copy / shape / cat / arithmetic on host leaves (no GPU needed)."""
+    import numpy as np
+    from tianshou_fork_b200.data.batch import Batch
+    a = Batch(obs=np.arange(6.0).reshape(3, 2), info=Batch(t=np.arange(3)), empty=Batch())
+    b = a.copy()
+    b.obs[0, 0] = 99.0
+    assert a.obs[0, 0] == 0.0 and a.shape == [3]
+    c = Batch.cat([a, b])
+    assert len(c) == 6 and c.info.t.tolist() == [0, 1, 2, 0, 1, 2] and c.empty.is_empty()
+    a.cat_(b)
+    assert len(a) == 6 and a.obs[3, 0] == 99.0
+    a.update(rew=np.ones(6), obs=np.zeros((6, 2)))
+    assert set(a.keys()) == {"obs", "info", "empty", "rew"} and a.obs.sum() == 0
+    d = Batch(x=np.array([1.0, 2.0]))
+    e = d * 2 + 1
+    assert e.x.tolist() == [3.0, 5.0] and d.x.tolist() == [1.0, 2.0]
+    d /= 2
+    assert d.x.tolist() == [0.5, 1.0]
+    parts = list(Batch(x=np.arange(10)).split(4, shuffle=False, merge_last=True))
+    assert [len(p) for p in parts] == [4, 6]

@@ -5,7 +5,9 @@ object/heterogeneous support; SURVEY.md 2.1 #8 marks that machinery out of scope
 return / replay path needs is: attribute and key access, fancy indexing of every leaf
 (``batch[indices]``), scatter assignment (``storage[ptrs] = batch``), ``len``, ``keys``,
 ``pop``, ``is_empty``, nested batches (``obs`` dicts, ``info``), storage allocation
-(``_create_value``, batch.py:94-131) and ``split`` (batch.py:896-912).  Leaves may be NumPy
+(``_create_value``, batch.py:94-131), ``split`` (batch.py:896-912), and the small conveniences
+callers lean on (``update``, ``copy``, ``shape``, ``cat`` / ``cat_`` of same-keyed batches,
+``+ * /``).  Leaves may be NumPy
 arrays (host) or torch tensors (device); device-resident buffers keep torch CUDA leaves.
 """
 from __future__ import annotations
@@ -194,6 +196,101 @@ class Batch:
             else:
                 out.__dict__[k] = np.stack([np.asanyarray(v) for v in vs], axis=axis)
         return out
+
+    def update(self, batch: Optional[Union[dict, "Batch"]] = None, **kwargs: Any) -> None:
+        """Set / overwrite keys like ``dict.update`` (batch.py:816-825)."""
+        if batch is not None:
+            for k, v in (batch.items() if isinstance(batch, (dict, Batch)) else batch):
+                self.__dict__[k] = _to_leaf(v)
+        for k, v in kwargs.items():
+            self.__dict__[k] = _to_leaf(v)
+
+    def copy(self) -> "Batch":
+        out = Batch()
+        for k, v in self.items():
+            if isinstance(v, Batch):
+                out.__dict__[k] = v.copy()
+            elif isinstance(v, torch.Tensor):
+                out.__dict__[k] = v.clone()
+            else:
+                out.__dict__[k] = np.array(v, copy=True)
+        return out
+
+    @property
+    def shape(self) -> List[int]:
+        """Common leading shape of the leaves (batch.py:878-894)."""
+        if self.is_empty():
+            return []
+        shapes = []
+        for v in self.values():
+            if isinstance(v, Batch):
+                if not v.is_empty(recurse=True):
+                    shapes.append(list(v.shape))
+            else:
+                shapes.append(list(getattr(v, "shape", [])))
+        if not shapes:
+            return []
+        n = min(len(sh) for sh in shapes)
+        out = []
+        for d in range(n):
+            if len({sh[d] for sh in shapes}) != 1:
+                break
+            out.append(shapes[0][d])
+        return out
+
+    @staticmethod
+    def cat(batches: List[Union[dict, "Batch"]]) -> "Batch":
+        """Concatenate along the first axis (batch.py:664-703); the batches share their keys."""
+        bs = [b if isinstance(b, Batch) else Batch(b) for b in batches]
+        bs = [b for b in bs if not b.is_empty(recurse=True)]
+        out = Batch()
+        if not bs:
+            return out
+        for k in bs[0].keys():
+            vs = [b[k] for b in bs]
+            if isinstance(vs[0], Batch):
+                out.__dict__[k] = Batch() if vs[0].is_empty() else Batch.cat(vs)
+            elif isinstance(vs[0], torch.Tensor):
+                out.__dict__[k] = torch.cat(vs, dim=0)
+            else:
+                out.__dict__[k] = np.concatenate([np.asanyarray(v) for v in vs], axis=0)
+        return out
+
+    def cat_(self, batches: Union["Batch", List[Union[dict, "Batch"]]]) -> None:
+        if isinstance(batches, (Batch, dict)):
+            batches = [batches]
+        merged = Batch.cat(([self] if not self.is_empty() else []) + list(batches))
+        self.__dict__.clear()
+        self.__dict__.update(merged.__dict__)
+
+    def _apply(self, fn) -> "Batch":
+        for k, v in self.items():
+            if isinstance(v, Batch):
+                if not v.is_empty():
+                    v._apply(fn)
+            else:
+                self.__dict__[k] = fn(k, v)
+        return self
+
+    def __iadd__(self, other: Union["Batch", Number]) -> "Batch":
+        if isinstance(other, Batch):
+            return self._apply(lambda k, v: v + other[k])
+        return self._apply(lambda k, v: v + other)
+
+    def __add__(self, other: Union["Batch", Number]) -> "Batch":
+        return self.copy().__iadd__(other)
+
+    def __imul__(self, value: Number) -> "Batch":
+        return self._apply(lambda k, v: v * value)
+
+    def __mul__(self, value: Number) -> "Batch":
+        return self.copy().__imul__(value)
+
+    def __itruediv__(self, value: Number) -> "Batch":
+        return self._apply(lambda k, v: v / value)
+
+    def __truediv__(self, value: Number) -> "Batch":
+        return self.copy().__itruediv__(value)
 
     def split(self, size: int, shuffle: bool = True, merge_last: bool = False
               ) -> Iterator["Batch"]:
