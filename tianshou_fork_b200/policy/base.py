@@ -37,6 +37,9 @@ def _device_of(buffer: Any) -> torch.device:
 
 def _dev(x: Any, device: torch.device, dtype: Optional[torch.dtype] = None) -> torch.Tensor:
     if isinstance(x, torch.Tensor):
+        if (x.device == device and (dtype is None or x.dtype == dtype) and not x.requires_grad
+                and x.is_contiguous()):
+            return x  # nothing to do: every no-op torch call below still costs ~1-2 us of host time
         t = x.detach().to(device)
     else:
         t = torch.from_numpy(np.ascontiguousarray(np.asarray(x))).to(device)
@@ -45,11 +48,15 @@ def _dev(x: Any, device: torch.device, dtype: Optional[torch.dtype] = None) -> t
     return t.contiguous()
 
 
+def _flat(t: torch.Tensor) -> torch.Tensor:
+    return t if t.ndim == 1 else t.reshape(-1)
+
+
 def _float_dev(x: Any, device: torch.device) -> torch.Tensor:
     t = _dev(x, device)
     if t.dtype not in (torch.float32, torch.float64):
         t = t.to(torch.float64)
-    return t.reshape(-1).contiguous()
+    return t if t.ndim == 1 else t.reshape(-1).contiguous()
 
 
 def _workspace(nbytes: int, device: torch.device) -> torch.Tensor:
@@ -231,7 +238,9 @@ class BasePolicy(nn.Module):
         n = rew.numel()
         canon = buffer.is_canonical(indices) if hasattr(buffer, "is_canonical") else None
         off, last, lens, B, sub, buf_done, buf_term = _buffer_layout(buffer, dev)
-        idx = _dev(indices, dev, torch.int64).reshape(-1)
+        idx = _dev(indices, dev, torch.int64)
+        if idx.ndim != 1:
+            idx = idx.reshape(-1)
         assert idx.numel() == n, "indices must address one buffer slot per batch element"
 
         if v_s_ is None:
@@ -264,16 +273,16 @@ class BasePolicy(nn.Module):
             # the rows kernel runs without indices, unfinished list or look-back.  The batch's
             # own rew/flags are read (a caller may have rewritten batch.rew, e.g. GAIL).
             E, T = canon
-            term = L.as_u8(_dev(batch.terminated, dev, torch.bool).reshape(-1))
-            trunc = L.as_u8(_dev(batch.truncated, dev, torch.bool).reshape(-1))
+            term = L.as_u8(_flat(_dev(batch.terminated, dev, torch.bool)))
+            trunc = L.as_u8(_flat(_dev(batch.truncated, dev, torch.bool)))
             L.check(lib.ts_gae_rows(
                 L.ptr(rew), L.ptr(vs), L.ptr(vn), L.ptr(term), L.ptr(trunc), E, T, T, T,
                 float(gamma), float(gae_lambda), L.dtype_code(rew), L.dtype_code(vs),
                 L.TS_F64 if out_dtype == torch.float64 else L.TS_F32, L.ptr(adv), L.ptr(ret),
                 L.stream()), "ts_gae_rows")
         else:
-            term = L.as_u8(_dev(batch.terminated, dev, torch.bool).reshape(-1))
-            trunc = L.as_u8(_dev(batch.truncated, dev, torch.bool).reshape(-1))
+            term = L.as_u8(_flat(_dev(batch.terminated, dev, torch.bool)))
+            trunc = L.as_u8(_flat(_dev(batch.truncated, dev, torch.bool)))
             unfinished = torch.empty(B, dtype=torch.int64, device=dev)
             L.check(lib.ts_unfinished_index(L.ptr(buf_done), L.ptr(last), L.ptr(lens), B,
                                             L.ptr(unfinished), L.stream()),
@@ -314,7 +323,7 @@ class BasePolicy(nn.Module):
         rew = buffer.rew if isinstance(buffer, ReplayBuffer) else _dev(buffer.rew, dev)
         if rew.dtype not in (torch.float32, torch.float64):
             rew = rew.to(torch.float64)
-        idx = _dev(indice, dev, torch.int64).reshape(-1)
+        idx = _flat(_dev(indice, dev, torch.int64))
         bsz = idx.numel()
         terminal = torch.empty(bsz, dtype=torch.int64, device=dev)
         ret_sum = torch.empty(bsz, dtype=torch.float64, device=dev)
