@@ -59,3 +59,17 @@ def test_batch_conveniences():
     assert d.x.tolist() == [0.5, 1.0]
     parts = list(Batch(x=np.arange(10)).split(4, shuffle=False, merge_last=True))
     assert [len(p) for p in parts] == [4, 6]
+
+
+def test_converters():
+    import numpy as np
+    import torch
+    from tianshou_fork_b200.data import Batch, to_numpy, to_torch, to_torch_as
+    b = Batch(a=torch.arange(3), n=Batch(x=np.ones(2)))
+    nb = to_numpy(b)
+    assert isinstance(nb.a, np.ndarray) and isinstance(b.a, torch.Tensor)  # a copy is converted
+    t = to_torch(nb, dtype=torch.float32)
+    assert t.a.dtype == torch.int64 and t.n.x.dtype == torch.float32  # dtype applies to floats
+    y = torch.zeros(1, dtype=torch.float64)
+    assert to_torch_as(np.ones(2, np.float32), y).dtype == torch.float64
+    assert to_numpy(3).shape == () and to_numpy([1, 2]).tolist() == [1, 2]

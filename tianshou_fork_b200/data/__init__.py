@@ -1,5 +1,6 @@
 """Device-resident data structures (mirror of ``tianshou.data`` for the hot path)."""
 from .batch import Batch
+from .converter import to_numpy, to_torch, to_torch_as
 from .segtree import SegmentTree
 from .buffer import ReplayBuffer
 from .manager import ReplayBufferManager, VectorReplayBuffer
@@ -9,7 +10,7 @@ from .prio import (PrioritizedReplayBuffer, PrioritizedReplayBufferManager,
 from .sharded import ShardedPrioritizedVectorReplayBuffer
 
 __all__ = [
-    "Batch", "SegmentTree", "ReplayBuffer", "ReplayBufferManager", "VectorReplayBuffer",
+    "Batch", "to_numpy", "to_torch", "to_torch_as", "SegmentTree", "ReplayBuffer", "ReplayBufferManager", "VectorReplayBuffer",
     "CachedReplayBuffer",
     "PrioritizedReplayBuffer", "PrioritizedReplayBufferManager",
     "PrioritizedVectorReplayBuffer", "ShardedPrioritizedVectorReplayBuffer",

@@ -228,7 +228,8 @@ class _GraphedUpdate:
     def _key(self) -> tuple:
         buf = self.buf  # storage identity: a re-allocated field invalidates captured addresses
         return (G.lr_key(self.p.optim), getattr(buf, "_beta", None), self.p.training,
-                tuple(id(v) for v in buf._meta.values()))
+                tuple(v.data_ptr() if isinstance(v, torch.Tensor) else id(v)
+                      for v in buf._meta.values()))
 
     def update(self) -> Dict[str, float]:
         p, buf = self.p, self.buf
