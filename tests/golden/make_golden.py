@@ -620,6 +620,48 @@ def gen_cached(ts, out):
     np.savez_compressed(os.path.join(out, "cached.npz"), **flat)
 
 
+def gen_sample(ts, out):
+    """Seeded ``sample_indices(batch_size > 0)`` of the reference (base.py:276-305,
+    manager.py:163-192): the draws come from the global ``np.random`` stream, so a port that
+    makes the same calls in the same order returns the same indices."""
+    from tianshou.data import Batch, ReplayBuffer, VectorReplayBuffer
+
+    flat = {}
+    # name, buffers, total, steps, kwargs
+    specs = [("vec_partial", 4, 40, 7, {}), ("vec_wrapped", 3, 30, 25, {}),
+             ("vec_stack_avail", 4, 64, 11, dict(stack_num=3, sample_avail=True)),
+             ("vec_one_empty", 5, 50, 6, {})]
+    for name, nb, total, steps, kw in specs:
+        buf = VectorReplayBuffer(total, nb, **kw)
+        rng = np.random.default_rng(950)
+        for t in range(steps):
+            ids = np.arange(nb if name != "vec_one_empty" else nb - 1)
+            m = ids.size
+            term = rng.random(m) < 0.15
+            buf.add(Batch(obs=rng.standard_normal((m, 2)).astype(np.float32),
+                          act=rng.integers(0, 3, m), rew=rng.standard_normal(m),
+                          terminated=term, truncated=np.zeros(m, bool),
+                          obs_next=rng.standard_normal((m, 2)).astype(np.float32), info={}),
+                    buffer_ids=ids)
+        np.random.seed(31)
+        for i, bsz in enumerate((1, 7, 64)):
+            flat[f"{name}/draw{i}"] = buf.sample_indices(bsz)
+    for name, size, steps, kw in [("ring", 16, 9, {}), ("ring_wrapped", 16, 41, {}),
+                                  ("ring_stack_avail", 32, 20,
+                                   dict(stack_num=4, sample_avail=True))]:
+        buf = ReplayBuffer(size, **kw)
+        rng = np.random.default_rng(951)
+        for t in range(steps):
+            buf.add(Batch(obs=rng.standard_normal(2).astype(np.float32), act=int(rng.integers(3)),
+                          rew=float(rng.standard_normal()), terminated=bool(rng.random() < 0.2),
+                          truncated=False, obs_next=rng.standard_normal(2).astype(np.float32),
+                          info={}))
+        np.random.seed(32)
+        for i, bsz in enumerate((1, 5, 40)):
+            flat[f"{name}/draw{i}"] = buf.sample_indices(bsz)
+    np.savez_compressed(os.path.join(out, "sample.npz"), **flat)
+
+
 STACK_SPECS = [
     # name, n_env, total, steps, stack_num, ragged, frame shape (make_golden.gen_stack)
     ("atari_like", 4, 80, 13, 4, False, (6,)),
@@ -698,6 +740,7 @@ def main():
     gen_pg_a2c_update(ts, HERE)
     gen_dqn_update(ts, HERE)
     gen_cached(ts, HERE)
+    gen_sample(ts, HERE)
     gen_stack(ts, HERE)
     with open(os.path.join(HERE, "versions.json"), "w") as f:
         json.dump({"tianshou": ts.__version__, "numpy": np.__version__,

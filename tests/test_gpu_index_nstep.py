@@ -177,3 +177,44 @@ def test_nstep_known_answers_from_reference_tests():
         r = ts.BasePolicy.compute_nstep_return(ts.Batch(), buf, indices, target_q_fn, gamma=.1,
                                                n_step=n).returns
         assert np.allclose(r.cpu().numpy().ravel(), expect), n
+
+
+def test_seeded_sample_indices_vs_reference():
+    """sample_indices(batch_size > 0) draws from the global np.random stream in the reference's
+    call order (base.py:276-305, manager.py:163-192): a seeded run returns the reference's
+    indices (tests/golden/sample.npz, make_golden.gen_sample)."""
+    import tianshou_fork_b200 as ts
+    g = load_golden("sample")
+    specs = [("vec_partial", 4, 40, 7, {}), ("vec_wrapped", 3, 30, 25, {}),
+             ("vec_stack_avail", 4, 64, 11, dict(stack_num=3, sample_avail=True)),
+             ("vec_one_empty", 5, 50, 6, {})]
+    for name, nb, total, steps, kw in specs:
+        buf = ts.VectorReplayBuffer(total, nb, **kw)
+        rng = np.random.default_rng(950)
+        for t in range(steps):
+            ids = np.arange(nb if name != "vec_one_empty" else nb - 1)
+            m = ids.size
+            term = rng.random(m) < 0.15
+            buf.add(ts.Batch(obs=rng.standard_normal((m, 2)).astype(np.float32),
+                             act=rng.integers(0, 3, m), rew=rng.standard_normal(m),
+                             terminated=term, truncated=np.zeros(m, bool),
+                             obs_next=rng.standard_normal((m, 2)).astype(np.float32), info={}),
+                    buffer_ids=ids)
+        np.random.seed(31)
+        for i, bsz in enumerate((1, 7, 64)):
+            got = buf.sample_indices(bsz).cpu().numpy()
+            assert np.array_equal(got, g[name][f"draw{i}"]), (name, bsz)
+    for name, size, steps, kw in [("ring", 16, 9, {}), ("ring_wrapped", 16, 41, {}),
+                                  ("ring_stack_avail", 32, 20,
+                                   dict(stack_num=4, sample_avail=True))]:
+        buf = ts.ReplayBuffer(size, **kw)
+        rng = np.random.default_rng(951)
+        for t in range(steps):
+            buf.add(ts.Batch(obs=rng.standard_normal(2).astype(np.float32),
+                             act=int(rng.integers(3)), rew=float(rng.standard_normal()),
+                             terminated=bool(rng.random() < 0.2), truncated=False,
+                             obs_next=rng.standard_normal(2).astype(np.float32), info={}))
+        np.random.seed(32)
+        for i, bsz in enumerate((1, 5, 40)):
+            got = buf.sample_indices(bsz).cpu().numpy()
+            assert np.array_equal(got, g[name][f"draw{i}"]), (name, bsz)
