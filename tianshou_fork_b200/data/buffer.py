@@ -13,7 +13,7 @@ Index arguments may be Python ints, lists, NumPy arrays or CUDA tensors; NumPy/i
 NumPy/int out, CUDA tensor in -> CUDA tensor out.  ``sample_indices`` / ``sample`` return CUDA
 tensors so that the whole update stays on the device.
 
-Out of scope here: HDF5 save/load, ``from_data``.
+Out of scope here: HDF5 save/load (no h5py in this image).
 """
 from __future__ import annotations
 
@@ -139,6 +139,28 @@ class ReplayBuffer:
         self.__dict__.update(state)
         self.__dict__["device"] = torch.device(state["device"])
         self.__dict__["_meta"] = state["_meta"].to_torch(device=self.device)
+
+    @classmethod
+    def from_data(cls, obs: Any, act: Any, rew: Any, terminated: Any, truncated: Any,
+                  done: Any, obs_next: Any) -> "ReplayBuffer":
+        """A full buffer over existing arrays (offline datasets; base.py:108-132).  The arrays
+        are uploaded once; they need not be HDF5 datasets."""
+        size = len(obs)
+        assert all(len(d) == size for d in [obs, act, rew, terminated, truncated, done,
+                                            obs_next]), \
+            "Lengths of all hdf5 datasets need to be equal."
+        buf = cls(size)
+        if size == 0:
+            return buf
+        as_arr = lambda x: x if isinstance(x, torch.Tensor) else np.asarray(x)  # noqa: E731
+        batch = Batch(obs=as_arr(obs), act=as_arr(act), rew=as_arr(rew),
+                      terminated=as_arr(terminated), truncated=as_arr(truncated),
+                      done=as_arr(done), obs_next=as_arr(obs_next))
+        buf.set_batch(batch)
+        for k in ("terminated", "truncated", "done"):
+            buf._meta.__dict__[k] = buf._meta[k].to(torch.bool)
+        buf._size = size
+        return buf
 
     def reset(self, keep_statistics: bool = False) -> None:
         """Clear all the data in replay buffer and episode statistics (base.py:134-139)."""
