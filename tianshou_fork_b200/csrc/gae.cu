@@ -873,7 +873,11 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
                 // a strip of consecutive indices touches at most two sub-buffers of >= 8 steps:
                 // two sub-buffer look-ups instead of eight
                 const int64_t s0 = sub_of(id[0], g.offset, g.B, g.sub_size);
-                const int64_t s7 = sub_of(id[VEC - 1], g.offset, g.B, g.sub_size);
+                // equal sub-buffers: the strip's last index is in s0 or, past its end, in s0 + 1
+                // (one division per strip instead of two)
+                const int64_t s7 = (consec && g.sub_size > 0)
+                    ? s0 + (id[0] - s0 * g.sub_size + (VEC - 1) >= g.sub_size ? 1 : 0)
+                    : sub_of(id[VEC - 1], g.offset, g.B, g.sub_size);
                 if (consec && s7 - s0 <= 1) {
                     const int64_t u0 = __ldg(g.unfinished + s0) - id[0];
                     const int64_t u7 = s7 != s0 ? __ldg(g.unfinished + s7) - id[0] : -1;
