@@ -124,3 +124,20 @@ def test_policy_with_captured_graphs_pickles():
     np.random.seed(5)
     l2 = clone.update(8, buf)["loss"]  # re-captures against its own copies of the networks
     assert np.isclose(l1, l2, rtol=1e-5)
+
+
+@pytest.mark.parametrize("graph", [False, True], ids=["eager", "cuda_graph"])
+def test_dqn_with_per_learns_the_point_task(graph):
+    """End to end like test/discrete/test_dqn.py (collect -> update, a reward threshold at the
+    end): prioritized sampling, 3-step returns with a target network and update_weight."""
+    import importlib.util
+    import os
+    import sys
+    ex = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples")
+    sys.path.insert(0, ex)
+    spec = importlib.util.spec_from_file_location("dqn_point", os.path.join(ex, "dqn_point.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    hist = mod.run(steps=600, graph=graph, seed=1)
+    assert hist[-1] > hist[0] + 0.2, hist  # epsilon-greedy start is near the random -0.95
+    assert hist[-1] > -0.7, hist

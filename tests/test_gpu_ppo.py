@@ -311,3 +311,20 @@ def test_pg_a2c_update_vs_reference_update(name):
     for net, tag in ((actor, "actor"), (critic, "critic")):
         for k, v in net.state_dict().items():
             assert np.allclose(v.cpu().numpy(), case[f"final/{tag}/{k}"], rtol=3e-3, atol=3e-4), k
+
+
+@pytest.mark.parametrize("graph", [False, True], ids=["eager", "cuda_graph"])
+def test_ppo_learns_the_point_task(graph):
+    """End to end like test/discrete/test_ppo.py (collect -> update -> reset, a reward
+    threshold at the end): rollouts through add(), GAE and the fused loss on the device."""
+    import importlib.util
+    import os
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                        "examples", "ppo_point.py")
+    spec = importlib.util.spec_from_file_location("ppo_point", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    hist = mod.run(iterations=25, graph=graph, seed=1)
+    first, last = np.mean(hist[:3]), np.mean(hist[-3:])
+    assert last > first + 0.25, (first, last)  # a random policy drifts around -0.95
+    assert last > -0.6, hist[-3:]
