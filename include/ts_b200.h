@@ -310,6 +310,15 @@ int32_t ts_gather_fields(int32_t n_fields, const void* const* src, void* const* 
                          const int64_t* row_bytes, int64_t n_rows, const int64_t* index,
                          int64_t M, ts_stream_t stream);
 
+/* Multi-field scatter, the inverse of ts_gather_fields: dst[f][index[j],:] = src[f][j,:].
+ * Replaces `self._meta[ptrs] = batch` of ReplayBufferManager.add
+ * (tianshou/data/buffer/manager.py:160; one fancy-index assignment per key there): the rows of
+ * one vectorised env step, uploaded as one packed buffer, go into the storage of every key in
+ * one launch.  Indices must be distinct; an index outside [-n_rows, n_rows) is skipped. */
+int32_t ts_scatter_fields(int32_t n_fields, const void* const* src, void* const* dst,
+                          const int64_t* row_bytes, int64_t n_rows, const int64_t* index,
+                          int64_t M, ts_stream_t stream);
+
 /* Frame-stack gather (ReplayBuffer.get with stack_num > 1, base.py:317-358; Atari-style
  * save_only_last_obs buffers, atari_dqn.py:135-140): out[j, i, :] = src[g_i, :] with
  * g_{k-1} = index[j] % total and g_{i-1} = prev(g_i) (episode-aware, manager.py:259-277; one

@@ -88,3 +88,31 @@ def test_add_device_atari_frames_and_stack():
     data = buf[c["query"]]
     assert np.array_equal(data.obs.cpu().numpy(), c["obs"])
     assert np.array_equal(data.obs_next.cpu().numpy(), c["obs_next"])
+
+
+@pytest.mark.parametrize("n_env,frame", [(16, (27,)), (10, (84, 84)), (64, (3,))])
+def test_packed_host_add_equals_per_key_assignment(n_env, frame):
+    """ReplayBufferManager.add with NumPy steps: one packed upload + ts_scatter_fields
+    (manager.py:160 assigns key by key) -- storage byte-equal to the per-key path, over ragged
+    ids, ring wrap-around and u8 frames."""
+    import tianshou_fork_b200 as ts
+    dtype = np.uint8 if len(frame) == 2 else np.float32
+    bufs = [ts.VectorReplayBuffer(n_env * 12, n_env) for _ in range(2)]
+    bufs[1]._store_packed = lambda ptrs, batch: False  # reference-style per-key assignment
+    rng = np.random.default_rng(2)
+    for t in range(40):
+        ids = np.arange(n_env)
+        if t % 3 == 1:
+            ids = ids[rng.random(n_env) < 0.6]
+            if ids.size == 0:
+                continue
+        m = ids.size
+        step = dict(obs=(rng.random((m,) + frame) * 255).astype(dtype),
+                    act=rng.integers(0, 5, m), rew=rng.standard_normal(m),
+                    terminated=rng.random(m) < 0.1, truncated=rng.random(m) < 0.05,
+                    obs_next=(rng.random((m,) + frame) * 255).astype(dtype), info={})
+        outs = [b.add(ts.Batch(**step), buffer_ids=ids) for b in bufs]
+        for x, y in zip(*outs):
+            assert np.array_equal(x, y)
+    for k in ("obs", "act", "rew", "terminated", "truncated", "done", "obs_next"):
+        assert torch.equal(bufs[0]._meta[k], bufs[1]._meta[k]), k

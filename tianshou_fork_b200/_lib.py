@@ -69,6 +69,7 @@ SIGNATURES = {
                                       _sz, _vp]),
     "ts_gather_rows": (_i32, [_vp, _i64, _i64, _vp, _i64, _vp, _vp]),
     "ts_gather_fields": (_i32, [_i32, _vp, _vp, _vp, _i64, _vp, _i64, _vp]),
+    "ts_scatter_fields": (_i32, [_i32, _vp, _vp, _vp, _i64, _vp, _i64, _vp]),
     "ts_add_step": (_i32, [_i32, _vp, _vp, _vp, _i64, _vp, _vp, _i32, _vp, _vp, _i64] + [_vp] * 11
                     + [_vp]),
     "ts_gather_stack": (_i32, [_vp, _i64, _vp, _i64, _i32, _vp, _i64, _i64, _vp, _vp, _vp, _vp,

@@ -245,6 +245,44 @@ gather_fields_kernel(FieldArgs a, int64_t n_rows, const int64_t* __restrict__ in
     }
 }
 
+// The inverse of gather_fields_kernel: dst[f][index[j], :] = src[f][j, :] -- one vectorised env
+// step written into the storage of every key in one launch (manager.py:160 does one fancy-index
+// assignment per key).  Indices are distinct (one slot per sub-buffer per step).
+__global__ void __launch_bounds__(256)
+scatter_fields_kernel(FieldArgs a, int64_t n_rows, const int64_t* __restrict__ index, int64_t M) {
+    // one WARP per (row, field): rows range from one flag byte to a 7 KB Atari frame
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t total = M * a.n;
+    for (int64_t t = warp; t < total; t += nwarps) {
+        const int f = (int)(t % a.n);
+        const int64_t j = t / a.n;
+        int64_t r = __ldg(index + j);
+        if (r < 0) r += n_rows;
+        if (r < 0 || r >= n_rows) continue;  // never write outside the storage
+        const int rb = a.row_bytes[f];
+        const uint8_t* s = a.src[f] + j * rb;
+        uint8_t* d = a.dst[f] + r * rb;
+        switch (a.unit[f]) {
+            case 8:
+                for (int c = lane * 8; c < rb; c += 256)
+                    *(uint2*)(d + c) = __ldg((const uint2*)(s + c));
+                break;
+            case 4:
+                for (int c = lane * 4; c < rb; c += 128)
+                    *(uint32_t*)(d + c) = __ldg((const uint32_t*)(s + c));
+                break;
+            case 2:
+                for (int c = lane * 2; c < rb; c += 64)
+                    *(uint16_t*)(d + c) = __ldg((const uint16_t*)(s + c));
+                break;
+            default:
+                for (int c = lane; c < rb; c += 32) d[c] = __ldg(s + c);
+        }
+    }
+}
+
 }  // namespace
 }  // namespace ts
 
@@ -324,9 +362,9 @@ extern "C" int32_t ts_gather_rows(const void* src, int64_t n_rows, int64_t row_b
     return check_launch();
 }
 
-extern "C" int32_t ts_gather_fields(int32_t n_fields, const void* const* src, void* const* dst,
-                                    const int64_t* row_bytes, int64_t n_rows,
-                                    const int64_t* index, int64_t M, ts_stream_t stream) {
+static int32_t launch_fields(bool scatter, int32_t n_fields, const void* const* src,
+                             void* const* dst, const int64_t* row_bytes, int64_t n_rows,
+                             const int64_t* index, int64_t M, ts_stream_t stream) {
     if (n_fields < 0 || n_fields > kMaxFields || M < 0 || n_rows < 0) return TS_ERR_BAD_ARG;
     if (n_fields == 0 || M == 0) return TS_OK;
     if (!src || !dst || !row_bytes || !index) return TS_ERR_BAD_ARG;
@@ -347,10 +385,25 @@ extern "C" int32_t ts_gather_fields(int32_t n_fields, const void* const* src, vo
         a.unit[k] = unit;
     }
     if (a.n == 0) return TS_OK;
-    const int64_t total = M * a.n;
+    const int64_t total = scatter ? M * a.n * 32 : M * a.n;  // scatter: a warp per item
     int64_t blocks = (total + 255) / 256;
     const int64_t cap = (int64_t)kNumSMs * 8;
     if (blocks > cap) blocks = cap;
-    gather_fields_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a, n_rows, index, M);
+    if (scatter)
+        scatter_fields_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a, n_rows, index, M);
+    else
+        gather_fields_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a, n_rows, index, M);
     return check_launch();
+}
+
+extern "C" int32_t ts_gather_fields(int32_t n_fields, const void* const* src, void* const* dst,
+                                    const int64_t* row_bytes, int64_t n_rows,
+                                    const int64_t* index, int64_t M, ts_stream_t stream) {
+    return launch_fields(false, n_fields, src, dst, row_bytes, n_rows, index, M, stream);
+}
+
+extern "C" int32_t ts_scatter_fields(int32_t n_fields, const void* const* src, void* const* dst,
+                                     const int64_t* row_bytes, int64_t n_rows,
+                                     const int64_t* index, int64_t M, ts_stream_t stream) {
+    return launch_fields(true, n_fields, src, dst, row_bytes, n_rows, index, M, stream);
 }
