@@ -34,6 +34,11 @@ def _is_scalar(index: Any) -> bool:
         isinstance(index, np.ndarray) and index.ndim == 0)
 
 
+_NP_OF_TORCH = {torch.float32: np.float32, torch.float64: np.float64, torch.int64: np.int64,
+                torch.int32: np.int32, torch.uint8: np.uint8, torch.bool: np.bool_,
+                torch.int16: np.int16, torch.int8: np.int8, torch.float16: np.float16}
+
+
 class ReplayBuffer:
     """Circular buffer with device-resident storage (tianshou/data/buffer/base.py:11-389)."""
 
@@ -360,11 +365,58 @@ class ReplayBuffer:
                                       device=self.device)
         elif not set(batch.keys()).issubset(self._meta.keys()):
             _alloc_missing(self._meta, batch, self.maxsize, not stacked_batch, self.device)
-        if stacked_batch:
-            self._meta[ptr] = batch
-        else:
-            self._meta[ptr] = _unsqueeze0(batch)
+        rows = batch if stacked_batch else _unsqueeze0(batch)
+        if not self._store_packed(ptr, rows):
+            self._meta[ptr] = rows
         return ptr, ep_rew, ep_len, ep_idx
+
+    def _store_packed(self, ptrs: np.ndarray, batch: Batch) -> bool:
+        """``self._meta[ptrs] = batch`` (manager.py:160) for a step that arrives as NumPy
+        arrays: the slot indices and the rows of every key travel to the device as ONE packed
+        buffer (one copy instead of two per key) and are written by one ``ts_scatter_fields``
+        launch.  Returns False (nothing written) for anything it does not cover -- nested
+        non-empty batches, device tensors, a shape that does not match the storage."""
+        m = int(ptrs.size)
+        if m == 0:
+            return True
+        meta = self._meta.__dict__
+        fields = []
+        for k, v in batch.items():
+            dst = meta.get(k)
+            if isinstance(v, Batch):
+                if v.is_empty() and isinstance(dst, Batch):
+                    continue
+                return False
+            if not (isinstance(v, np.ndarray) and isinstance(dst, torch.Tensor) and dst.is_cuda
+                    and dst.is_contiguous() and v.shape == (m,) + tuple(dst.shape[1:])):
+                return False
+            np_dtype = _NP_OF_TORCH.get(dst.dtype)
+            if np_dtype is None:
+                return False
+            fields.append((dst, np.ascontiguousarray(v, dtype=np_dtype)))
+        if len(fields) > 8 or set(batch.keys()) != set(k for k in meta if k in batch):
+            return False
+        for k in meta:  # the reference zero-fills stored keys the step does not carry
+            if k not in batch and not isinstance(meta[k], Batch):
+                return False
+        offsets, total = [], 8 * m
+        for dst, arr in fields:
+            offsets.append(total)
+            total += (arr.nbytes + 7) & ~7
+        packed = np.empty(total, dtype=np.uint8)
+        packed[:8 * m] = np.ascontiguousarray(ptrs, dtype=np.int64).view(np.uint8)
+        for off, (dst, arr) in zip(offsets, fields):
+            packed[off:off + arr.nbytes] = arr.reshape(-1).view(np.uint8)
+        dev_packed = torch.from_numpy(packed).to(self.device)
+        base = dev_packed.data_ptr()
+        nf = len(fields)
+        src, dsts, rb = ((ctypes.c_void_p * nf)(), (ctypes.c_void_p * nf)(),
+                         (ctypes.c_int64 * nf)())
+        for j, (off, (dst, arr)) in enumerate(zip(offsets, fields)):
+            src[j], dsts[j], rb[j] = base + off, dst.data_ptr(), arr.nbytes // m
+        L.check(L.lib().ts_scatter_fields(nf, src, dsts, rb, self.maxsize, base, m, L.stream()),
+                "ts_scatter_fields")
+        return True
 
     # ---- sampling / gathers ------------------------------------------------------------------
     def _all_indices_host(self) -> np.ndarray:
