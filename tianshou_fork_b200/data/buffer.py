@@ -379,6 +379,8 @@ class ReplayBuffer:
         m = int(ptrs.size)
         if m == 0:
             return True
+        if m > 1 and np.unique(ptrs).size != m:
+            return False  # a slot written twice in one call: keep NumPy's last-writer order
         meta = self._meta.__dict__
         fields = []
         for k, v in batch.items():
