@@ -48,23 +48,49 @@ nstep_chain_kernel(const int64_t* __restrict__ indice, int64_t bsz,
 
         double r[kMaxRegSteps];
         int m = 0;         // number of rewards collected = gammas (:520)
-        bool ended = false;
         int64_t first = now;
+        if (n_step <= kMaxRegSteps) {
+            // A chain that has not ended moves one slot forward per step (a step at `last`
+            // always ends it: either done[last] or the unfinished tail), so the n_step
+            // candidate slots are known up front: fetch their flags and rewards in ONE round
+            // of independent loads and resolve the chain in registers, instead of one
+            // dependent L2 round trip per step.
+            int64_t pos[kMaxRegSteps];
+            uint8_t dn[kMaxRegSteps];
+            int64_t rel = pymod(now - start + 1, cur_len);
+#pragma unroll
+            for (int n = 0; n < kMaxRegSteps; ++n) {
+                if (n < n_step) {
+                    pos[n] = n == 0 ? now : rel + start;
+                    if (n > 0 && ++rel == cur_len) rel = 0;
+                    dn[n] = done[pos[n]];
+                    r[n] = (double)rew[pos[n]];
+                }
+            }
+#pragma unroll
+            for (int n = 0; n < kMaxRegSteps; ++n) {
+                if (n < n_step && m == n) {  // the chain is still alive at step n
+                    now = pos[n];
+                    m = n + 1;
+                    if (dn[n] != 0 || (unfinished_exists && now == last)) m = -m;  // ended
+                }
+            }
+            if (m < 0) m = -m;
+        } else {
 #pragma unroll 1
-        for (int n = 0; n < n_step; ++n) {
-            const bool d = done[now] != 0;
-            const bool end = d || (unfinished_exists && now == last);
-            if (n < kMaxRegSteps) r[n] = (double)rew[now];
-            m = n + 1;
-            if (end) { ended = true; break; }
-            if (n + 1 < n_step) {
-                // _next_index (manager.py:295-296); `now == last` with done[last] set was
-                // caught above, so here end_flag of next() is zero unless now == last.
-                const int64_t ef = (now == last);
-                now = pymod(now - start + 1 - ef, cur_len) + start;
+            for (int n = 0; n < n_step; ++n) {
+                const bool d = done[now] != 0;
+                const bool end = d || (unfinished_exists && now == last);
+                m = n + 1;
+                if (end) break;
+                if (n + 1 < n_step) {
+                    // _next_index (manager.py:295-296); `now == last` with done[last] set was
+                    // caught above, so here end_flag of next() is zero unless now == last.
+                    const int64_t ef = (now == last);
+                    now = pymod(now - start + 1 - ef, cur_len) + start;
+                }
             }
         }
-        (void)ended;
         // Horner, last collected reward first (:518-522 restricted to the surviving steps)
         double acc = 0.0;
         if (m <= kMaxRegSteps) {
