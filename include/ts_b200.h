@@ -149,6 +149,18 @@ int32_t ts_unfinished_index(const uint8_t* done, const int64_t* last_index,
                             const int64_t* lengths, int64_t B, int64_t* out,
                             ts_stream_t stream);
 
+/* Unfinished tails as cut flags at BATCH positions, for a batch that is the buffer's own
+ * chronological listing (sample_indices(0), tianshou/data/buffer/manager.py:187-192): sub-buffer
+ * k occupies batch positions run_first[k] + j, j < lengths[k], with buffer index
+ * (ring_start[k] + j) % lengths[k] + offset[k].  Sets flags[pos] = 1 (uint8[N], otherwise
+ * untouched) where the reference sets end_flag[np.isin(indices, unfinished_index())]
+ * (tianshou/policy/base.py:379-380): B look-ups instead of a pass over the N indices, so that
+ * ts_gae_flat can run without them. */
+int32_t ts_mark_unfinished(const uint8_t* done, const int64_t* last_index,
+                           const int64_t* lengths, const int64_t* offset,
+                           const int64_t* ring_start, const int64_t* run_first, int64_t B,
+                           int64_t N, uint8_t* flags, ts_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------
  * n-step TD target.
  * Replaces: BasePolicy.compute_nstep_return (tianshou/policy/base.py:386-440) and numba

@@ -123,7 +123,26 @@ def row_gae_api():
         t2, c2 = term.reshape(E, T), trunc.reshape(E, T)
         cus = cpu_us(lambda: orc.episodic_return_rows(r2, vs_np, vn_np, t2, c2, 0.99, 0.95),
                      seconds=1.0)
+        # ragged sub-buffers (every other env stream is 8 steps short): sample(0) is a listing
+        # of runs, not [E, T] rows -> ts_mark_unfinished + the flat kernel without indices
+        buf._rings[::2, 1] = T - 8
+        buf._rings[::2, 0] = T - 8
+        buf._lengths[::2] = T - 8
+        buf.last_index[::2] -= 8
+        for b in buf.buffers[::2]:
+            b._index, b._size = T - 8, T - 8
+        buf._version += 1
+        rb, ri = buf.sample(0)
+        nr = len(rb)
+        rvs, rvn = v_s[:nr].contiguous(), v_n[:nr].contiguous()
+        assert buf.listing_runs(ri) is not None
+        us_runs = gpu_us(lambda: ts.BasePolicy.compute_episodic_return(
+            rb, buf, ri, rvn, rvs, 0.99, 0.95), iters=100)
+        ri2 = ri.clone()
+        us_runs_idx = gpu_us(lambda: ts.BasePolicy.compute_episodic_return(
+            rb, buf, ri2, rvn, rvs, 0.99, 0.95), iters=100)
         emit("a1 compute_episodic_return (API)", E=E, T=T, canonical_us=us, general_indices_us=us_flat,
+             ragged_listing_us=us_runs, ragged_indexed_us=us_runs_idx,
              cpu_port_us=cus, speedup=cus / us,
              reference_probe_us=2380.0 if (E, T) == (64, 2048) else None)
 

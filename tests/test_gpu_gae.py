@@ -427,3 +427,47 @@ def test_rows_short_rows_packed_vs_oracle(E, T):
     for a, r in outs:
         assert _close(a, ref_adv) and _close(r, ref_ret)
     assert np.allclose(outs[0][0], outs[1][0], rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize("case", ["ragged", "wrapped"])
+def test_listing_runs_path_equals_indexed_path(case, monkeypatch):
+    """sample(0) of ragged / wrapped sub-buffers: the batch is the buffer's own listing, so
+    compute_episodic_return marks the unfinished tails at batch positions (ts_mark_unfinished)
+    and runs the flat kernel without indices.  Same result as the indexed path (taken when the
+    index tensor is not the listing itself) and as the oracle."""
+    import tianshou_fork_b200 as ts
+    from oracle import oracle as orc
+    from tianshou_fork_b200.policy import base as policy_base
+    monkeypatch.setattr(policy_base, "LISTING_MIN_N", 1 << 12)  # take the path at test size
+    rng = np.random.default_rng(77)
+    E, cap = 24, 4096
+    buf = ts.VectorReplayBuffer(E * cap, E, rew_dtype=torch.float32)
+    steps = 4096 + 700 if case == "wrapped" else 3800
+    alive = np.ones(E, bool)
+    for t in range(steps):
+        if case == "ragged" and t % 500 == 499:  # some env streams stop contributing
+            alive[rng.integers(0, E)] = False
+        ids = np.flatnonzero(alive) if case == "ragged" else np.arange(E)
+        m = ids.size
+        buf.add(ts.Batch(obs=np.zeros((m, 1), np.float32), act=np.zeros(m, np.int64),
+                         rew=rng.standard_normal(m).astype(np.float32),
+                         terminated=rng.random(m) < 0.01, truncated=rng.random(m) < 0.003,
+                         obs_next=np.zeros((m, 1), np.float32), info={}), buffer_ids=ids)
+    batch, indices = buf.sample(0)
+    n = len(batch)
+    assert n >= 1 << 16 and buf.is_canonical(indices) is None
+    assert buf.listing_runs(indices) is not None
+    v_s = torch.randn(n, device="cuda")
+    v_n = torch.randn(n, device="cuda")
+    ret_a, adv_a = ts.BasePolicy.compute_episodic_return(batch, buf, indices, v_n, v_s, 0.99, 0.95)
+    other = indices.clone()  # same values, not the listing tensor -> indexed kernel
+    assert buf.listing_runs(other) is None
+    ret_b, adv_b = ts.BasePolicy.compute_episodic_return(batch, buf, other, v_n, v_s, 0.99, 0.95)
+    assert torch.equal(adv_a, adv_b) and torch.equal(ret_a, ret_b)
+    idx = indices.cpu().numpy()
+    want_ret, want_adv = orc.compute_episodic_return(
+        batch.rew.cpu().numpy(), batch.terminated.cpu().numpy(), batch.truncated.cpu().numpy(),
+        buf.terminated.cpu().numpy()[idx], idx, buf.unfinished_index(),
+        v_s_=v_n.cpu().numpy(), v_s=v_s.cpu().numpy(), gamma=0.99, gae_lambda=0.95)
+    assert np.allclose(adv_a.cpu().numpy(), want_adv, rtol=1e-5, atol=1e-5)
+    assert np.allclose(ret_a.cpu().numpy(), want_ret, rtol=1e-5, atol=1e-5)

@@ -43,6 +43,7 @@ SIGNATURES = {
     "ts_prev_index": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     "ts_next_index": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     "ts_unfinished_index": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp]),
+    "ts_mark_unfinished": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
     "ts_nstep_chain": (_i32, [_vp, _i64, _vp, _i32, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _f64,
                               _i32, _vp, _vp, _vp, _vp]),
     "ts_nstep_combine": (_i32, [_vp, _i32, _i64, _i64, _vp, _vp, _vp, _vp]),

@@ -57,6 +57,29 @@ inline unsigned grid_for(int64_t n, int threads) {
     return (unsigned)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
+// Unfinished tails as cut flags at BATCH positions, for a batch that is the buffer's own
+// chronological listing (sample_indices(0), manager.py:187-192): sub-buffer k occupies batch
+// positions run_first[k] + j with buffer index (ring_start[k] + j) % lengths[k] + offset[k].
+// Replaces `end_flag[np.isin(indices, buffer.unfinished_index())] = True`
+// (policy/base.py:379-380) without touching the N indices: B look-ups instead of N.
+__global__ void mark_unfinished_kernel(const uint8_t* __restrict__ done,
+                                       const int64_t* __restrict__ last_index,
+                                       const int64_t* __restrict__ lengths,
+                                       const int64_t* __restrict__ offset,
+                                       const int64_t* __restrict__ ring_start,
+                                       const int64_t* __restrict__ run_first, int64_t B,
+                                       int64_t N, uint8_t* __restrict__ flags) {
+    const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= B) return;
+    const int64_t len = lengths[k];
+    if (len <= 0) return;
+    const int64_t last = last_index[k];
+    if (done[last] != 0) return;  // the newest episode of this sub-buffer is finished
+    const int64_t rel = pymod(last - offset[k] - ring_start[k], len);
+    const int64_t pos = run_first[k] + rel;
+    if (pos >= 0 && pos < N) flags[pos] = 1;
+}
+
 }  // namespace
 }  // namespace ts
 
@@ -99,5 +122,17 @@ extern "C" int32_t ts_unfinished_index(const uint8_t* done, const int64_t* last_
     if (B <= 0 || !done || !last_index || !lengths || !out) return TS_ERR_BAD_ARG;
     unfinished_kernel<<<grid_for(B, 128), 128, 0, (cudaStream_t)stream>>>(done, last_index,
                                                                           lengths, B, out);
+    return check_launch();
+}
+
+extern "C" int32_t ts_mark_unfinished(const uint8_t* done, const int64_t* last_index,
+                                      const int64_t* lengths, const int64_t* offset,
+                                      const int64_t* ring_start, const int64_t* run_first,
+                                      int64_t B, int64_t N, uint8_t* flags, ts_stream_t stream) {
+    if (B <= 0 || N < 0 || !done || !last_index || !lengths || !offset || !ring_start ||
+        !run_first || !flags)
+        return TS_ERR_BAD_ARG;
+    mark_unfinished_kernel<<<grid_for(B, 128), 128, 0, (cudaStream_t)stream>>>(
+        done, last_index, lengths, offset, ring_start, run_first, B, N, flags);
     return check_launch();
 }

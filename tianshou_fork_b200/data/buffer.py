@@ -131,7 +131,8 @@ class ReplayBuffer:
         else:
             state["_meta"] = _batch_to_numpy_copy(Batch(self._meta))
         # caches that hold device addresses or ctypes arrays are rebuilt on demand
-        for key in ("_dev_state", "_dev_add", "_dev_add_keys", "_canon", "_cached_weight"):
+        for key in ("_dev_state", "_dev_add", "_dev_add_keys", "_canon", "_listing",
+                    "_cached_weight"):
             if key in state:
                 state[key] = None
         state["_dev_state_version"] = -1

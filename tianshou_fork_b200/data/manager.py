@@ -330,7 +330,24 @@ class ReplayBufferManager(ReplayBuffer):
                                     output_size=total)
         first = torch.cumsum(sizes, 0) - sizes
         j = torch.arange(total, device=dev) - first[k]
-        return (start[k] + j) % torch.clamp(sizes[k], min=1) + off[k]
+        out = (start[k] + j) % torch.clamp(sizes[k], min=1) + off[k]
+        # remembered so that the return estimators can treat a batch that IS this listing as
+        # runs of consecutive slots instead of N arbitrary indices (listing_runs)
+        self._listing = {"ptr": out.data_ptr(), "n": out.numel(), "version": self._version,
+                         "start": start.contiguous(), "first": first.contiguous(), "keep": out}
+        return out
+
+    def listing_runs(self, indices: Any) -> Optional[Dict[str, torch.Tensor]]:
+        """If ``indices`` is the tensor the last ``sample_indices(0)`` returned for the current
+        contents (ragged or wrapped sub-buffers), the run table of that listing: sub-buffer k
+        sits at batch positions ``first[k] + j`` with buffer index
+        ``(start[k] + j) % lengths[k] + offset[k]``."""
+        c = getattr(self, "_listing", None)
+        if (c is not None and isinstance(indices, torch.Tensor)
+                and c["version"] == self._version and indices.data_ptr() == c["ptr"]
+                and indices.numel() == c["n"]):
+            return c
+        return None
 
     def is_canonical(self, indices: Any) -> Optional[Tuple[int, int]]:
         """Whether ``indices`` is the tensor the last ``sample_indices(0)`` returned for the
