@@ -662,6 +662,77 @@ def gen_sample(ts, out):
     np.savez_compressed(os.path.join(out, "sample.npz"), **flat)
 
 
+HER_SPECS = [
+    # name, vector buffers (0: single ring), total size, steps, ignore_obs_next, horizon, future_k
+    ("ring", 0, 64, 50, False, 12, 8.0),
+    ("ring_wrapped", 0, 40, 70, False, 10, 4.0),
+    ("ring_no_obs_next", 0, 64, 50, True, 12, 8.0),
+    ("vector", 3, 90, 40, False, 12, 8.0),
+]
+
+
+def her_stream(rng, steps, n_env):
+    """Goal-reaching walks on a line (dict observations) in the RNG order shared with the tests."""
+    pos = rng.integers(0, 4, n_env)
+    age = np.zeros(n_env, int)
+    goal = 5
+    for _ in range(steps):
+        act = rng.integers(0, 2, n_env)
+        nxt = np.clip(pos + 2 * act - 1, 0, 6)
+        age += 1
+        term = nxt == goal
+        trunc = (age >= 9) & ~term
+        mk = lambda p: dict(observation=p[:, None].astype(np.float32),  # noqa: E731
+                            achieved_goal=p[:, None].astype(np.float32),
+                            desired_goal=np.full((n_env, 1), goal, np.float32))
+        yield dict(obs=mk(pos), act=act, rew=term.astype(np.float64), terminated=term,
+                   truncated=trunc, obs_next=mk(nxt), info={})
+        done = term | trunc
+        pos = np.where(done, rng.integers(0, 4, n_env), nxt)
+        age = np.where(done, 0, age)
+
+
+def her_reward(ag, g):
+    return (ag == g).all(axis=-1).astype(np.float32)
+
+
+def gen_her(ts, out):
+    """``HERReplayBuffer`` / ``HERVectorReplayBuffer`` of the reference (her.py:8-197,
+    vecbuf.py:71-91): after seeded ``sample_indices`` calls the sampled indices, the re-written
+    goals and rewards in the storage, and the storage after ``_restore_cache``."""
+    from tianshou.data import Batch, HERReplayBuffer, HERVectorReplayBuffer
+
+    flat = {}
+    for name, nb, total, steps, ignore, horizon, k in HER_SPECS:
+        kw = dict(compute_reward_fn=her_reward, horizon=horizon, future_k=k,
+                  ignore_obs_next=ignore)
+        buf = HERVectorReplayBuffer(total, nb, **kw) if nb else HERReplayBuffer(total, **kw)
+        rng = np.random.default_rng(970)
+        for step in her_stream(rng, steps, max(nb, 1)):
+            if nb:
+                buf.add(Batch(**step), buffer_ids=np.arange(nb))
+            else:
+                buf.add(Batch(**{k2: (v[0] if not isinstance(v, dict) else
+                                      {a: b[0] for a, b in v.items()})
+                                 for k2, v in step.items()}))
+
+        def snap(tag):
+            flat[f"{name}/{tag}/goal"] = np.asarray(buf._meta.obs.desired_goal).copy()
+            flat[f"{name}/{tag}/rew"] = np.asarray(buf._meta.rew).copy()
+            if not ignore:
+                flat[f"{name}/{tag}/goal_next"] = np.asarray(
+                    buf._meta.obs_next.desired_goal).copy()
+
+        snap("orig")
+        np.random.seed(5)
+        for r, bsz in enumerate((6, 11)):
+            flat[f"{name}/draw{r}/indices"] = buf.sample_indices(bsz)
+            snap(f"draw{r}")
+        buf._restore_cache()
+        snap("restored")
+    np.savez_compressed(os.path.join(out, "her.npz"), **flat)
+
+
 STACK_SPECS = [
     # name, n_env, total, steps, stack_num, ragged, frame shape (make_golden.gen_stack)
     ("atari_like", 4, 80, 13, 4, False, (6,)),
@@ -741,6 +812,7 @@ def main():
     gen_dqn_update(ts, HERE)
     gen_cached(ts, HERE)
     gen_sample(ts, HERE)
+    gen_her(ts, HERE)
     gen_stack(ts, HERE)
     with open(os.path.join(HERE, "versions.json"), "w") as f:
         json.dump({"tianshou": ts.__version__, "numpy": np.__version__,
