@@ -263,12 +263,14 @@ def test_graphed_learn_equals_eager_learn():
         assert torch.allclose(p, q, rtol=1e-5, atol=1e-6)
 
 
-@pytest.mark.parametrize("name", ["pg", "a2c"])
+@pytest.mark.parametrize("name", ["pg", "a2c", "a2c_cuda_graph"])
 def test_pg_a2c_update_vs_reference_update(name):
     """``PGPolicy.update`` / ``A2CPolicy.update`` of the reference (make_golden.gen_pg_a2c_update,
     return normalisation on, two updates) against this package's device-resident versions."""
     import tianshou_fork_b200 as ts
     from helpers import fill
+    graph = name.endswith("_cuda_graph")
+    name = name.split("_")[0]
     case = load_golden("pg_a2c_update")[name]
     buf = ts.VectorReplayBuffer(20 * 100, 20)
     fill(buf, ts.Batch, 700, 100, 20, 0.03, 0.01)
@@ -283,7 +285,8 @@ def test_pg_a2c_update_vs_reference_update(name):
         optim = torch.optim.Adam(list(actor.parameters()) + list(critic.parameters()), lr=1e-3)
         policy = ts.A2CPolicy(actor, critic, optim, dist_fn, vf_coef=0.5, ent_coef=0.01,
                               max_grad_norm=0.5, gae_lambda=0.9, discount_factor=0.98,
-                              reward_normalization=True, action_scaling=False)
+                              reward_normalization=True, action_scaling=False,
+                              cuda_graph=graph)
         keys = ("returns", "adv", "v_s")
     seen = []
     inner = policy.process_fn

@@ -27,9 +27,8 @@ import torch
 from torch import nn
 
 from .. import _lib as L
-from . import _graph as G
 from ..data.batch import Batch
-from .a2c import A2CPolicy
+from .a2c import A2CPolicy, _GraphedLearner
 from .pg import RunningMeanStd, _minibatches, _split_bounds  # noqa: F401 (re-exported)
 
 _loss_ws: Dict[int, torch.Tensor] = {}
@@ -121,7 +120,7 @@ class PPOPolicy(A2CPolicy):
         cuda_graph: bool = False,
         **kwargs: Any,
     ) -> None:
-        super().__init__(actor, critic, optim, dist_fn, **kwargs)
+        super().__init__(actor, critic, optim, dist_fn, cuda_graph=cuda_graph, **kwargs)
         self._eps_clip = eps_clip
         assert dual_clip is None or dual_clip > 1.0, \
             "Dual-clip PPO parameter should greater than 1.0."
@@ -129,8 +128,8 @@ class PPOPolicy(A2CPolicy):
         self._value_clip = value_clip
         self._norm_adv = advantage_normalization
         self._recompute_adv = recompute_advantage
-        self._cuda_graph = cuda_graph
-        self._graphs: Optional[_GraphedLearner] = None
+
+    _graph_fields = ("logp_old", "adv", "returns", "v_s")  # per-sample constants of a step
 
     def process_fn(self, batch: Batch, buffer: Any, indices: Any) -> Batch:
         if self._recompute_adv:  # ppo.py:90-92
@@ -140,11 +139,6 @@ class PPOPolicy(A2CPolicy):
         with torch.no_grad():
             batch.logp_old = self._dist(batch.obs)[2].log_prob(batch.act)  # ppo.py:95-96
         return batch
-
-    def _flat(self, t: torch.Tensor, n: int, what: str) -> torch.Tensor:
-        t = t.detach().reshape(-1).float().contiguous()
-        assert t.numel() == n, f"{what} must be one scalar per transition"
-        return t
 
     def _minibatch_step(self, obs, act, mb, logp_old, adv, returns, v_s) -> torch.Tensor:
         """ppo.py:106-151 for one minibatch; returns the four logged scalars (device)."""
@@ -168,140 +162,10 @@ class PPOPolicy(A2CPolicy):
     # ---- learn (ppo.py:99-162) ------------------------------------------------------------------
     def learn(self, batch: Batch, batch_size: int, repeat: int, **kwargs: Any
               ) -> Dict[str, List[float]]:
-        if self._cuda_graph:
-            if self._graphs is None:
-                self._graphs = _GraphedLearner(self)
-            table = self._graphs.learn(batch, batch_size, repeat)
-        else:
-            table = self._learn_eager(batch, batch_size, repeat)
+        table = self._learn_table(batch, batch_size, repeat)
         return {
             "loss": table[:, 0].tolist(),
             "loss/clip": table[:, 1].tolist(),
             "loss/vf": table[:, 2].tolist(),
             "loss/ent": table[:, 3].tolist(),
         }
-
-    def _learn_eager(self, batch: Batch, batch_size: int, repeat: int) -> np.ndarray:
-        n = len(batch)
-        logged: List[torch.Tensor] = []
-        for step in range(repeat):
-            if self._recompute_adv and step > 0:
-                batch = self._compute_returns(batch, self._buffer, self._indices)
-            logp_old = self._flat(batch.logp_old, n, "log_prob")
-            adv = self._flat(batch.adv, n, "adv")
-            returns = self._flat(batch.returns, n, "returns")
-            v_s = self._flat(batch.v_s, n, "v_s")
-            for mb in _minibatches(n, batch_size, self.device):
-                logged.append(self._minibatch_step(batch.obs[mb], batch.act[mb], mb, logp_old,
-                                                   adv, returns, v_s))
-        return torch.stack(logged).cpu().numpy() if logged else np.zeros((0, 4))  # one sync
-
-
-class _GraphedLearner:
-    """``PPOPolicy.learn`` as CUDA-graph replays.
-
-    Static device state: the update's rows (``obs``, ``act``, ``logp_old``, ``adv``, ``returns``,
-    ``v_s``), the concatenated permutations of all epochs, a cursor into them, and the loss
-    log with its row counter.  A graph for minibatch size m reads ``perm[cursor : cursor + m]``,
-    runs ``PPOPolicy._minibatch_step`` and advances cursor and row itself, so replays need no
-    host input.  Graphs are keyed by (m, learning rates, train/eval mode) and dropped when a
-    static buffer has to grow.  Warm-up iterations run for real on a side stream (allocator
-    and lazy optimiser state), after which parameters, module buffers and optimiser state are
-    restored in place, so capture does not change the training trajectory.
-    """
-
-    LOG_ROWS = 1 << 16
-
-    def __init__(self, policy: PPOPolicy) -> None:
-        self.p = policy
-        self.dev = policy.device
-        self.static: Dict[str, torch.Tensor] = {}
-        self.graphs: Dict[Any, torch.cuda.CUDAGraph] = {}
-        G.prepare_optimizer(policy.optim, self.dev)
-        self.cursor = torch.zeros(1, dtype=torch.int64, device=self.dev)
-        self.row = torch.zeros(1, dtype=torch.int64, device=self.dev)
-        # one spare row: warm-up iterations log there, so a capture in the middle of a learn
-        # call (the merged tail's size) does not overwrite rows already written
-        self.log = torch.zeros(self.LOG_ROWS + 1, 4, dtype=torch.float32, device=self.dev)
-
-    # ---- static rows ---------------------------------------------------------------------------
-    def _fit(self, key: str, src: torch.Tensor) -> None:
-        cur = self.static.get(key)
-        if (cur is None or cur.shape[0] < src.shape[0] or cur.shape[1:] != src.shape[1:]
-                or cur.dtype != src.dtype):
-            self.static[key] = torch.empty_like(src, device=self.dev)
-            self.graphs.clear()  # captured addresses are stale
-            cur = self.static[key]
-        cur[:src.shape[0]].copy_(src)
-
-    def _load_returns(self, batch: Batch, n: int) -> None:
-        p = self.p
-        self._fit("adv", p._flat(batch.adv, n, "adv"))
-        self._fit("returns", p._flat(batch.returns, n, "returns"))
-        self._fit("v_s", p._flat(batch.v_s, n, "v_s"))
-
-    # ---- capture -------------------------------------------------------------------------------
-    def _body(self, m: int) -> None:
-        s, p = self.static, self.p
-        mb = s["perm"].index_select(0, self.cursor + s["arange"][:m])
-        with G.no_distribution_validation():
-            vals = p._minibatch_step(
-                s["obs"].index_select(0, mb), s["act"].index_select(0, mb), mb,
-                s["logp_old"], s["adv"], s["returns"], s["v_s"])
-        self.log.index_copy_(0, self.row, vals[None])
-        self.cursor += m
-        self.row += 1
-
-    def _guarded(self) -> List[torch.Tensor]:
-        p = self.p
-        return (list(p._params) + list(p.actor.buffers()) + list(p.critic.buffers())
-                + [self.cursor, self.row])
-
-    def _warm_row(self) -> None:
-        self.cursor.zero_()
-        self.row.fill_(self.LOG_ROWS)  # warm-up iterations log into the spare row
-
-    def _graph(self, m: int) -> torch.cuda.CUDAGraph:
-        key = (m, G.lr_key(self.p.optim), self.p.training)
-        g = self.graphs.get(key)
-        if g is None:
-            g = self.graphs[key] = G.capture(lambda: self._body(m), self._guarded,
-                                             self.p.optim, self.dev, self._warm_row)
-        return g
-
-    # ---- learn ---------------------------------------------------------------------------------
-    def learn(self, batch: Batch, batch_size: int, repeat: int) -> np.ndarray:
-        p = self.p
-        n = len(batch)
-        if not isinstance(batch.obs, torch.Tensor):
-            raise NotImplementedError("cuda_graph=True needs tensor observations")
-        bounds = _split_bounds(n, batch_size, merge_last=True)
-        if repeat <= 0 or not bounds:
-            return np.zeros((0, 4))
-        self._fit("obs", batch.obs)
-        self._fit("act", batch.act)
-        self._fit("logp_old", p._flat(batch.logp_old, n, "log_prob"))
-        self._load_returns(batch, n)
-        perms = np.concatenate([np.random.permutation(n) for _ in range(repeat)])  # batch.py:905
-        self._fit("perm", torch.from_numpy(perms).to(self.dev))
-        m_max = max(hi - lo for lo, hi in bounds)
-        if "arange" not in self.static or self.static["arange"].numel() < m_max:
-            self.static["arange"] = torch.arange(m_max, dtype=torch.int64, device=self.dev)
-            self.graphs.clear()
-        self.cursor.zero_()
-        self.row.zero_()
-        tables: List[np.ndarray] = []
-        rows = 0
-        for step in range(repeat):
-            if p._recompute_adv and step > 0:
-                batch = p._compute_returns(batch, p._buffer, p._indices)
-                self._load_returns(batch, n)
-            for lo, hi in bounds:
-                if rows == self.LOG_ROWS:  # log full: read it out and start over
-                    tables.append(self.log[:rows].cpu().numpy().copy())
-                    self.row.zero_()
-                    rows = 0
-                self._graph(hi - lo).replay()
-                rows += 1
-        tables.append(self.log[:rows].cpu().numpy())  # the one sync of a normal-sized learn
-        return np.concatenate(tables) if len(tables) > 1 else tables[0]
