@@ -28,15 +28,20 @@ def main():
     E, T = a.streams, a.horizon
     lib = L.lib()
     dev = torch.device("cuda:0")
-    d = [torch.from_numpy(x).to(dev) for x in bench.rollout(E, T, 0)]
-    adv = torch.empty(E, T, device=dev)
-    ret = torch.empty(E, T, device=dev)
+    # TS_SWEEP_ROTATE distinct input / output sets, visited round robin (no L2 reuse across launches)
+    rot = max(1, int(os.environ.get("TS_SWEEP_ROTATE", "3")))
+    sets = [([torch.from_numpy(x).to(dev) for x in bench.rollout(E, T, s)],
+             torch.empty(E, T, device=dev), torch.empty(E, T, device=dev)) for s in range(rot)]
+    d, adv, ret = sets[0]
+    turn = [0]
     st = torch.cuda.current_stream()
     peak, _ = bench.measured_peaks()
 
     def step():
-        L.check(lib.ts_gae_rows(*[t.data_ptr() for t in d], E, T, T, T, 0.99, 0.95, 0, 0, 0,
-                                adv.data_ptr(), ret.data_ptr(), st.cuda_stream), "gae")
+        di, ai, ri = sets[turn[0] % rot]
+        turn[0] += 1
+        L.check(lib.ts_gae_rows(*[t.data_ptr() for t in di], E, T, T, T, 0.99, 0.95, 0, 0, 0,
+                                ai.data_ptr(), ri.data_ptr(), st.cuda_stream), "gae")
 
     ref = None
     out = []
@@ -47,7 +52,8 @@ def main():
             key, val = kv.split("=")
             L.check(lib.ts_tune_set(key.encode(), int(val)), "tune " + key)
         adv.fill_(float("nan"))
-        for _ in range(10):
+        turn[0] = 0
+        for _ in range(3 * rot):
             step()
         torch.cuda.synchronize()
         if ref is None:

@@ -1149,7 +1149,7 @@ constexpr RowsVariant kRowsVariants[] = {
     {128, 6, 2},   // 9
 };
 constexpr int kNumRowsVariants = (int)(sizeof(kRowsVariants) / sizeof(kRowsVariants[0]));
-constexpr int kRowsAutoTma = 5;  // 256 threads x 2 stages x 3 CTAs/SM: best of the C2 sweep (profiles/)
+constexpr int kRowsAutoTma = 4;  // 256 threads x 3 stages x 2 CTAs/SM: best on distinct buffers (r01k_rows_variants.md)
 
 // Persistent grid for `units` equal work items on at most `cap` co-resident CTAs.  Optional
 // balancing ("gae_balance"): with w = ceil(units / cap) items per CTA, ceil(units / w) CTAs all
