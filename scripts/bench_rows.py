@@ -148,32 +148,41 @@ def row_gae_api():
 
 
 def row_gae_flat():
-    """a1, general form: arbitrary indices (a rotated buffer), decoupled look-back."""
+    """a1, general form (ts_gae_flat): one flattened sequence, with and without indices.
+    Successive launches rotate over 3 distinct input / output sets (no L2 reuse across launches)."""
+    ROT = 3
     for E, T in ((4096, 2048), (64, 2048)):
         n = E * T
-        rng = np.random.default_rng(1)
-        rew = torch.from_numpy(rng.random(n, dtype=np.float32)).to(DEV)
-        vs = torch.from_numpy(rng.standard_normal(n, dtype=np.float32)).to(DEV)
-        vn = torch.from_numpy(rng.standard_normal(n, dtype=np.float32)).to(DEV)
-        term = torch.from_numpy((rng.random(n) < 1 / 200).view(np.uint8)).to(DEV)
-        trunc = torch.zeros(n, dtype=torch.uint8, device=DEV)
-        idx = torch.arange(n, device=DEV)
+        sets = []
+        for r in range(ROT):
+            rng = np.random.default_rng(1 + r)
+            sets.append(dict(
+                rew=torch.from_numpy(rng.random(n, dtype=np.float32)).to(DEV),
+                vs=torch.from_numpy(rng.standard_normal(n, dtype=np.float32)).to(DEV),
+                vn=torch.from_numpy(rng.standard_normal(n, dtype=np.float32)).to(DEV),
+                term=torch.from_numpy((rng.random(n) < 1 / 200).view(np.uint8)).to(DEV),
+                trunc=torch.zeros(n, dtype=torch.uint8, device=DEV),
+                idx=torch.arange(n, device=DEV),
+                adv=torch.empty(n, device=DEV), ret=torch.empty(n, device=DEV)))
         unf = torch.full((E,), -1, dtype=torch.int64, device=DEV)
         off = torch.arange(E + 1, device=DEV) * T
-        adv, ret = torch.empty(n, device=DEV), torch.empty(n, device=DEV)
         lib = L.lib()
         nbytes = lib.ts_gae_flat_workspace_bytes(n)
         ws = torch.zeros(nbytes, dtype=torch.uint8, device=DEV)
+        turn = [0]
 
         def go(with_idx):
-            L.check(lib.ts_gae_flat(L.ptr(rew), L.ptr(vs), L.ptr(vn), L.ptr(term), L.ptr(trunc),
-                                    L.ptr(idx) if with_idx else None,
-                                    L.ptr(term) if with_idx else None,
+            d = sets[turn[0] % ROT]
+            turn[0] += 1
+            L.check(lib.ts_gae_flat(L.ptr(d["rew"]), L.ptr(d["vs"]), L.ptr(d["vn"]),
+                                    L.ptr(d["term"]), L.ptr(d["trunc"]),
+                                    L.ptr(d["idx"]) if with_idx else None,
+                                    L.ptr(d["term"]) if with_idx else None,
                                     L.ptr(unf) if with_idx else None, L.ptr(off), E, T, n, 0.99,
-                                    0.95, 0, 0, 0, L.ptr(adv), L.ptr(ret), L.ptr(ws), nbytes,
-                                    L.stream()), "flat")
+                                    0.95, 0, 0, 0, L.ptr(d["adv"]), L.ptr(d["ret"]), L.ptr(ws),
+                                    nbytes, L.stream()), "flat")
         for with_idx, bpt in ((False, 21), (True, 30)):
-            us = gpu_us(lambda: go(with_idx), iters=100)
+            us = gpu_us(lambda: go(with_idx), iters=99)
             emit("a1 gae_flat", E=E, T=T, indices=with_idx, us=us, alg_bytes_per_transition=bpt,
                  GBps=n * bpt / us / 1e3, frac_of_measured_peak=n * bpt / us / 1e3 / PEAK)
 
