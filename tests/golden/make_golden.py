@@ -572,54 +572,6 @@ def gen_dqn_update(ts, out):
     np.savez_compressed(os.path.join(out, "dqn_update.npz"), **flat)
 
 
-CACHED_SPECS = [
-    # name, main size, cached buffers, max episode length, steps, p_done, ragged
-    ("roomy", 64, 4, 12, 60, 0.15, False),
-    ("main_wraps", 20, 3, 8, 90, 0.2, True),
-    ("long_episodes", 30, 5, 6, 50, 0.05, True),   # cached rings wrap before an episode ends
-]
-
-
-def gen_cached(ts, out):
-    """``CachedReplayBuffer`` of the reference (cached.py:8-96) driven by a seeded add stream:
-    what every ``add`` returns, and after the stream the bookkeeping, ``sample_indices(0)``,
-    ``prev`` / ``next`` over the whole capacity, ``unfinished_index`` and the stored fields."""
-    from tianshou.data import Batch, CachedReplayBuffer, ReplayBuffer
-
-    flat = {}
-    for name, main, n_cached, ep_len, steps, p_done, ragged in CACHED_SPECS:
-        buf = CachedReplayBuffer(ReplayBuffer(main), n_cached, ep_len)
-        rng = np.random.default_rng(900)
-        rets = []
-        for t in range(steps):
-            ids = np.arange(n_cached)
-            if ragged:
-                ids = ids[rng.random(n_cached) < 0.7]
-                if ids.size == 0:
-                    continue
-            m = ids.size
-            term = rng.random(m) < p_done
-            trunc = (rng.random(m) < p_done / 3) & ~term
-            b = Batch(obs=rng.standard_normal((m, 2)).astype(np.float32),
-                      act=rng.integers(0, 4, m), rew=rng.standard_normal(m), terminated=term,
-                      truncated=trunc, obs_next=rng.standard_normal((m, 2)).astype(np.float32),
-                      info={})
-            ptr, ep_rew, ep_l, ep_idx = buf.add(b, buffer_ids=ids)
-            rets.append(np.stack([ptr, ep_rew, ep_l, ep_idx], 1).astype(np.float64))
-        flat[f"{name}/add_returns"] = np.concatenate(rets)
-        flat[f"{name}/lengths"] = buf._lengths.copy()
-        flat[f"{name}/last_index"] = buf.last_index.copy()
-        flat[f"{name}/len"] = np.int64(len(buf))
-        allidx = np.arange(buf.maxsize)
-        flat[f"{name}/all"] = buf.sample_indices(0)
-        flat[f"{name}/prev"] = buf.prev(allidx)
-        flat[f"{name}/next"] = buf.next(allidx)
-        flat[f"{name}/unfinished"] = buf.unfinished_index()
-        for k in ("obs", "act", "rew", "done", "terminated", "obs_next"):
-            flat[f"{name}/{k}"] = np.asarray(buf._meta[k]).copy()
-    np.savez_compressed(os.path.join(out, "cached.npz"), **flat)
-
-
 def gen_sample(ts, out):
     """Seeded ``sample_indices(batch_size > 0)`` of the reference (base.py:276-305,
     manager.py:163-192): the draws come from the global ``np.random`` stream, so a port that
@@ -660,77 +612,6 @@ def gen_sample(ts, out):
         for i, bsz in enumerate((1, 5, 40)):
             flat[f"{name}/draw{i}"] = buf.sample_indices(bsz)
     np.savez_compressed(os.path.join(out, "sample.npz"), **flat)
-
-
-HER_SPECS = [
-    # name, vector buffers (0: single ring), total size, steps, ignore_obs_next, horizon, future_k
-    ("ring", 0, 64, 50, False, 12, 8.0),
-    ("ring_wrapped", 0, 40, 70, False, 10, 4.0),
-    ("ring_no_obs_next", 0, 64, 50, True, 12, 8.0),
-    ("vector", 3, 90, 40, False, 12, 8.0),
-]
-
-
-def her_stream(rng, steps, n_env):
-    """Goal-reaching walks on a line (dict observations) in the RNG order shared with the tests."""
-    pos = rng.integers(0, 4, n_env)
-    age = np.zeros(n_env, int)
-    goal = 5
-    for _ in range(steps):
-        act = rng.integers(0, 2, n_env)
-        nxt = np.clip(pos + 2 * act - 1, 0, 6)
-        age += 1
-        term = nxt == goal
-        trunc = (age >= 9) & ~term
-        mk = lambda p: dict(observation=p[:, None].astype(np.float32),  # noqa: E731
-                            achieved_goal=p[:, None].astype(np.float32),
-                            desired_goal=np.full((n_env, 1), goal, np.float32))
-        yield dict(obs=mk(pos), act=act, rew=term.astype(np.float64), terminated=term,
-                   truncated=trunc, obs_next=mk(nxt), info={})
-        done = term | trunc
-        pos = np.where(done, rng.integers(0, 4, n_env), nxt)
-        age = np.where(done, 0, age)
-
-
-def her_reward(ag, g):
-    return (ag == g).all(axis=-1).astype(np.float32)
-
-
-def gen_her(ts, out):
-    """``HERReplayBuffer`` / ``HERVectorReplayBuffer`` of the reference (her.py:8-197,
-    vecbuf.py:71-91): after seeded ``sample_indices`` calls the sampled indices, the re-written
-    goals and rewards in the storage, and the storage after ``_restore_cache``."""
-    from tianshou.data import Batch, HERReplayBuffer, HERVectorReplayBuffer
-
-    flat = {}
-    for name, nb, total, steps, ignore, horizon, k in HER_SPECS:
-        kw = dict(compute_reward_fn=her_reward, horizon=horizon, future_k=k,
-                  ignore_obs_next=ignore)
-        buf = HERVectorReplayBuffer(total, nb, **kw) if nb else HERReplayBuffer(total, **kw)
-        rng = np.random.default_rng(970)
-        for step in her_stream(rng, steps, max(nb, 1)):
-            if nb:
-                buf.add(Batch(**step), buffer_ids=np.arange(nb))
-            else:
-                buf.add(Batch(**{k2: (v[0] if not isinstance(v, dict) else
-                                      {a: b[0] for a, b in v.items()})
-                                 for k2, v in step.items()}))
-
-        def snap(tag):
-            flat[f"{name}/{tag}/goal"] = np.asarray(buf._meta.obs.desired_goal).copy()
-            flat[f"{name}/{tag}/rew"] = np.asarray(buf._meta.rew).copy()
-            if not ignore:
-                flat[f"{name}/{tag}/goal_next"] = np.asarray(
-                    buf._meta.obs_next.desired_goal).copy()
-
-        snap("orig")
-        np.random.seed(5)
-        for r, bsz in enumerate((6, 11)):
-            flat[f"{name}/draw{r}/indices"] = buf.sample_indices(bsz)
-            snap(f"draw{r}")
-        buf._restore_cache()
-        snap("restored")
-    np.savez_compressed(os.path.join(out, "her.npz"), **flat)
 
 
 STACK_SPECS = [
@@ -810,9 +691,7 @@ def main():
     gen_ppo_update(ts, HERE)
     gen_pg_a2c_update(ts, HERE)
     gen_dqn_update(ts, HERE)
-    gen_cached(ts, HERE)
     gen_sample(ts, HERE)
-    gen_her(ts, HERE)
     gen_stack(ts, HERE)
     with open(os.path.join(HERE, "versions.json"), "w") as f:
         json.dump({"tianshou": ts.__version__, "numpy": np.__version__,

@@ -154,43 +154,3 @@ DQN_UPDATE_SPECS = [
 ]
 
 
-CACHED_SPECS = [
-    # name, main size, cached buffers, max episode length, steps, p_done, ragged
-    ("roomy", 64, 4, 12, 60, 0.15, False),
-    ("main_wraps", 20, 3, 8, 90, 0.2, True),
-    ("long_episodes", 30, 5, 6, 50, 0.05, True),   # cached rings wrap before an episode ends
-]
-
-
-HER_SPECS = [
-    # name, vector buffers (0: single ring), total size, steps, ignore_obs_next, horizon, future_k
-    ("ring", 0, 64, 50, False, 12, 8.0),
-    ("ring_wrapped", 0, 40, 70, False, 10, 4.0),
-    ("ring_no_obs_next", 0, 64, 50, True, 12, 8.0),
-    ("vector", 3, 90, 40, False, 12, 8.0),
-]
-
-
-def her_stream(rng, steps, n_env):
-    """Goal-reaching walks on a line (dict observations) in the RNG order shared with the tests."""
-    pos = rng.integers(0, 4, n_env)
-    age = np.zeros(n_env, int)
-    goal = 5
-    for _ in range(steps):
-        act = rng.integers(0, 2, n_env)
-        nxt = np.clip(pos + 2 * act - 1, 0, 6)
-        age += 1
-        term = nxt == goal
-        trunc = (age >= 9) & ~term
-        mk = lambda p: dict(observation=p[:, None].astype(np.float32),  # noqa: E731
-                            achieved_goal=p[:, None].astype(np.float32),
-                            desired_goal=np.full((n_env, 1), goal, np.float32))
-        yield dict(obs=mk(pos), act=act, rew=term.astype(np.float64), terminated=term,
-                   truncated=trunc, obs_next=mk(nxt), info={})
-        done = term | trunc
-        pos = np.where(done, rng.integers(0, 4, n_env), nxt)
-        age = np.where(done, 0, age)
-
-
-def her_reward(ag, g):
-    return (ag == g).all(axis=-1).astype(np.float32)

@@ -13,8 +13,8 @@ All arithmetic runs in hand-written CUDA kernels (``csrc/*.cu``) behind the C-AB
 ``include/ts_b200.h``; there is no CPU or eager-PyTorch fallback.
 """
 from . import _lib
-from .data import (Batch, to_numpy, to_torch, to_torch_as, CachedReplayBuffer, HERReplayBuffer, HERReplayBufferManager,
-                   HERVectorReplayBuffer, PrioritizedReplayBuffer, PrioritizedReplayBufferManager,
+from .data import (Batch, to_numpy, to_torch, to_torch_as,
+                   PrioritizedReplayBuffer, PrioritizedReplayBufferManager,
                    PrioritizedVectorReplayBuffer, ReplayBuffer, ReplayBufferManager,
                    SegmentTree, ShardedPrioritizedVectorReplayBuffer, VectorReplayBuffer)
 from .policy import A2CPolicy, BasePolicy, DQNPolicy, PGPolicy, PPOPolicy, ppo_loss
@@ -22,8 +22,7 @@ from .policy import A2CPolicy, BasePolicy, DQNPolicy, PGPolicy, PPOPolicy, ppo_l
 __version__ = "0.1.0"
 
 __all__ = [
-    "Batch", "to_numpy", "to_torch", "to_torch_as", "ReplayBuffer", "ReplayBufferManager", "VectorReplayBuffer", "CachedReplayBuffer",
-    "HERReplayBuffer", "HERReplayBufferManager", "HERVectorReplayBuffer",
+    "Batch", "to_numpy", "to_torch", "to_torch_as", "ReplayBuffer", "ReplayBufferManager", "VectorReplayBuffer",
     "PrioritizedReplayBuffer", "PrioritizedReplayBufferManager",
     "PrioritizedVectorReplayBuffer", "ShardedPrioritizedVectorReplayBuffer", "SegmentTree",
     "BasePolicy", "PGPolicy", "A2CPolicy", "PPOPolicy", "DQNPolicy", "ppo_loss",

@@ -976,7 +976,10 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
 // ============================================================================================
 struct FlatWorkspace {
     size_t clear_bytes;    // look-back kernel: ticket + status are zeroed before every call
-    unsigned int* ticket;  // [4]: look-back ticket | pipelined ranges: calls done, CTAs done
+    unsigned int* ticket;  // [1]: look-back ticket, the word right before `status`
+    unsigned int* sync;    // [3]: pipelined ranges: -, calls done, CTAs done.  NEVER cleared by the
+                           // look-back path: the call count makes the head-flag tags unique for the
+                           // lifetime of the workspace (stale flags of an earlier call never match)
     unsigned int* status;  // [tiles] 0 = nothing, 1 = aggregate published, 2 = value published
     double* aggP;          // [tiles]
     double* aggX;          // [tiles]
@@ -1300,7 +1303,7 @@ int32_t launch_flat_tma(const void* rew, const void* v_s, const void* v_next, co
     for (int j = 1; j <= VEC; ++j) glp.p[j] = glp.p[j - 1] * (gamma * lam);
     cudaError_t e = launch_pdl(kern, grid, NT, smem, stream, (const RewT*)rew, (const InT*)v_s,
                                (const InT*)v_next, term, trunc, g, N, gamma, glp, (OutT*)adv,
-                               (OutT*)ret, stages, ws.aggP, ws.status, ws.ticket);
+                               (OutT*)ret, stages, ws.aggP, ws.status, ws.sync);
     if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; (void)cudaGetLastError(); return TS_ERR_CUDA; }
     return check_launch();
 }
@@ -1420,12 +1423,13 @@ extern "C" int32_t ts_gae_flat(const void* rew, const void* v_s, const void* v_s
     const size_t status_bytes = ((tiles * 4 + 15) / 16) * 16;
     char* w = (char*)workspace;
     FlatWorkspace ws;
-    ws.ticket = (unsigned int*)w;
+    ws.sync = (unsigned int*)w;           // words 0..2
+    ws.ticket = (unsigned int*)(w + 12);  // word 3, contiguous with status: one memset clears both
     ws.status = (unsigned int*)(w + 16);
     ws.aggP = (double*)(w + 16 + status_bytes);
     ws.aggX = ws.aggP + tiles;
     ws.value = ws.aggX + tiles;
-    ws.clear_bytes = 16 + status_bytes;
+    ws.clear_bytes = 4 + status_bytes;
 #define TS_GO(R, I, O)                                                                        \
     launch_flat<R, I, O>(rew, v_s, v_s_next, terminated, truncated, indices, buf_terminated, \
                          unfinished, offset, B, sub_size, N, gamma, gae_lambda, adv, ret, ws, \

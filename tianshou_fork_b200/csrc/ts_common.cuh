@@ -35,6 +35,10 @@ __host__ __device__ __forceinline__ int64_t pymod(int64_t a, int64_t m) {
 // (vecbuf.py:35), else binary search over _extend_offset (manager.py:38).
 __device__ __forceinline__ int64_t sub_of(int64_t idx, const int64_t* __restrict__ offset,
                                           int64_t B, int64_t sub_size) {
+    // A single ring has nothing to look up.  Its `%` is by the CURRENT size (base.py:158-168),
+    // which kernels read from the device bookkeeping (offset[1], lengths[0]); `sub_size` is a
+    // by-value launch argument that a captured CUDA graph would freeze while the ring fills.
+    if (B == 1) return 0;
     if (sub_size > 0) {
         if ((((uint64_t)idx | (uint64_t)sub_size) >> 32) == 0)  // the usual case: 32-bit divide
             return (int64_t)((uint32_t)idx / (uint32_t)sub_size);

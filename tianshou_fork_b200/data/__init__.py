@@ -4,15 +4,12 @@ from .converter import to_numpy, to_torch, to_torch_as
 from .segtree import SegmentTree
 from .buffer import ReplayBuffer
 from .manager import ReplayBufferManager, VectorReplayBuffer
-from .cached import CachedReplayBuffer
-from .her import HERReplayBuffer, HERReplayBufferManager, HERVectorReplayBuffer
 from .prio import (PrioritizedReplayBuffer, PrioritizedReplayBufferManager,
                    PrioritizedVectorReplayBuffer)
 from .sharded import ShardedPrioritizedVectorReplayBuffer
 
 __all__ = [
     "Batch", "to_numpy", "to_torch", "to_torch_as", "SegmentTree", "ReplayBuffer", "ReplayBufferManager", "VectorReplayBuffer",
-    "CachedReplayBuffer", "HERReplayBuffer", "HERReplayBufferManager", "HERVectorReplayBuffer",
     "PrioritizedReplayBuffer", "PrioritizedReplayBufferManager",
     "PrioritizedVectorReplayBuffer", "ShardedPrioritizedVectorReplayBuffer",
 ]

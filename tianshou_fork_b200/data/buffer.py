@@ -192,11 +192,14 @@ class ReplayBuffer:
         """(extend_offset[B+1], last_index[B], lengths[B], sub_size) for the index kernels.
 
         A single ring takes ``%`` by its CURRENT size (base.py:158-168), which is the manager
-        formula (manager.py:267-276) with one sub-buffer of capacity ``size``."""
+        formula (manager.py:267-276) with one sub-buffer of capacity ``size``.  The current
+        size travels in the device arrays only (``offset[1]``, ``lengths[0]``); the by-value
+        ``sub_size`` is the constant capacity, so a captured graph stays valid while the ring
+        fills (the kernels never divide by it when B == 1)."""
         size = max(self._size, 1)
         return (np.array([0, size], dtype=np.int64),
                 np.asarray(self.last_index, dtype=np.int64).reshape(1),
-                np.array([self._size], dtype=np.int64), size)
+                np.array([self._size], dtype=np.int64), max(self.maxsize, 1))
 
     def _state(self) -> Dict[str, torch.Tensor]:
         version = self._version + (self._parent._version if self._parent is not None else 0)

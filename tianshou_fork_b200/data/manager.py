@@ -319,8 +319,10 @@ class ReplayBufferManager(ReplayBuffer):
             E, T = canon
             off = torch.arange(E, device=dev, dtype=torch.int64) * self._equal_sub
             out = (off[:, None] + torch.arange(T, device=dev, dtype=torch.int64)[None]).reshape(-1)
+            # "keep" holds the tensor alive so that its address cannot be handed to another
+            # tensor while this record is valid (is_canonical compares addresses)
             self._canon = {"ptr": out.data_ptr(), "n": out.numel(), "E": E, "T": T,
-                           "version": self._version}
+                           "version": self._version, "keep": out}
             return out
         sizes = torch.from_numpy(self._rings[:, 1].copy()).to(dev)
         start = torch.from_numpy(self._rings[:, 0].copy()).to(dev)

@@ -65,6 +65,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         idx = self.weight._dev_index(index)
         if idx.numel() == 0:
             return
+        self._cached_weight = None  # the tree changes: weights of an earlier draw are stale
         t = self.weight
         L.check(L.lib().ts_per_init_weight(
             L.ptr(t._value), t._size, t._bound, L.ptr(idx), idx.numel(), float(self._alpha),
@@ -81,6 +82,15 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         ptr, ep_rew, ep_len, ep_idx = super().add(batch, buffer_ids)
         self.init_weight(ptr)
         return ptr, ep_rew, ep_len, ep_idx
+
+    def add_device(self, batch: Batch, buffer_ids: Optional[Union[np.ndarray, List[int]]] = None):
+        """Device-side ``add`` (manager ``add_device``) followed by ``init_weight`` of the slots
+        it wrote, as ``add`` does (prio.py:50-57); the slot indices never leave the device."""
+        if not isinstance(self, ReplayBufferManager):
+            raise NotImplementedError("add_device needs a buffer manager (VectorReplayBuffer)")
+        out = ReplayBufferManager.add_device(self, batch, buffer_ids)
+        self.init_weight(out[0])
+        return out
 
     # ---- sampling ------------------------------------------------------------------------------
     def _uniforms(self, batch_size: int) -> torch.Tensor:
@@ -142,6 +152,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         assert td.numel() == idx.numel()
         if idx.numel() == 0:
             return
+        self._cached_weight = None
         t = self.weight
         L.check(L.lib().ts_per_update(
             L.ptr(t._value), t._size, t._bound, L.ptr(idx), L.ptr(td), L.dtype_code(td),

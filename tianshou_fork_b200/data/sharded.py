@@ -101,7 +101,7 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
         self._slots.zero_()
         self._symm = symm_mem.rendezvous(self._slots, grp)
         self._peer_ptrs = int(self._symm.buffer_ptrs_dev)
-        self._state = torch.zeros(2, dtype=torch.int64, device=self.device)
+        self._p2p_state = torch.zeros(2, dtype=torch.int64, device=self.device)
         torch.cuda.synchronize(self.device)
         dist.barrier(group=self.group)
 
@@ -112,7 +112,7 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
         device copies + one 24-byte all-gather; no host sync."""
         if self.exchange == "p2p":
             L.check(L.lib().ts_per_publish(
-                L.ptr(self.weight._value), L.ptr(self._prio), L.ptr(self._state),
+                L.ptr(self.weight._value), L.ptr(self._prio), L.ptr(self._p2p_state),
                 self._peer_ptrs, self.world_size, self.rank, L.stream()), "ts_per_publish")
             return  # the global extrema are adopted by the next sampling kernel
         self._mine3[0:1].copy_(self.weight._value[1:2])
@@ -130,6 +130,11 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
         self.sync_roots()
         return out
 
+    def add_device(self, batch, buffer_ids=None):
+        out = super().add_device(batch, buffer_ids)  # init_weight(ptrs) inside
+        self.sync_roots()
+        return out
+
     def sample_with_uniforms(self, u: torch.Tensor) -> torch.Tensor:
         """``u`` must hold the SAME draws on every rank (same seed, or broadcast)."""
         assert u.is_cuda and u.dtype == torch.float64 and u.is_contiguous()
@@ -140,7 +145,7 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
         if self.exchange == "p2p":
             L.check(L.lib().ts_per_sample_p2p(
                 L.ptr(t._value), t._bound, L.ptr(u), m, L.ptr(self._slots), self._peer_ptrs,
-                L.ptr(self._state), self.world_size, self.rank, L.ptr(self._prio),
+                L.ptr(self._p2p_state), self.world_size, self.rank, L.ptr(self._prio),
                 float(self._beta), int(self._weight_norm), L.ptr(idx), L.ptr(w), L.ptr(t._err),
                 L.stream()), "ts_per_sample_p2p")
             self._cached_weight = (idx, w)
@@ -170,11 +175,12 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
             td = td.to(torch.float64)
         td = td.reshape(-1).contiguous()
         assert td.numel() == idx.numel()
+        self._cached_weight = None
         t = self.weight
         # update + publish in one launch (the record must go out even for an empty batch)
         L.check(L.lib().ts_per_update_publish(
             L.ptr(t._value), t._size, t._bound, L.ptr(idx), L.ptr(td), L.dtype_code(td),
             idx.numel(), float(self._alpha), L.ptr(self._prio), L.ptr(t._stamp),
-            L.ptr(t._counter), L.ptr(t._err), L.ptr(self._state), self._peer_ptrs,
+            L.ptr(t._counter), L.ptr(t._err), L.ptr(self._p2p_state), self._peer_ptrs,
             self.world_size, self.rank, L.stream()), "ts_per_update_publish")
         self._prio_f32 = td.dtype == torch.float32

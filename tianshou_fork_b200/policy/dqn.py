@@ -155,22 +155,6 @@ class DQNPolicy(BasePolicy):
             g = self._graphed[key] = _GraphedUpdate(self, buffer, int(sample_size))
         return g.update()
 
-    def exploration_noise(self, act: Any, batch: Batch) -> Any:
-        """Epsilon-greedy on the host RNG, as the reference draws it (dqn.py:196-210)."""
-        if np.isclose(self.eps, 0.0):
-            return act
-        is_tensor = isinstance(act, torch.Tensor)
-        a = act.cpu().numpy().copy() if is_tensor else act
-        bsz = len(a)
-        rand_mask = np.random.rand(bsz) < self.eps
-        q = np.random.rand(bsz, self.max_action_num)  # [0, 1]
-        if hasattr(batch.obs, "mask"):
-            m = batch.obs.mask
-            q += m.cpu().numpy() if isinstance(m, torch.Tensor) else m
-        rand_act = q.argmax(axis=1)
-        a[rand_mask] = rand_act[rand_mask]
-        return torch.as_tensor(a, device=act.device) if is_tensor else a
-
 
 class _GraphedUpdate:
     """``DQNPolicy.update(sample_size, buffer)`` as one CUDA-graph replay.
