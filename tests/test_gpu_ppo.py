@@ -323,7 +323,7 @@ def test_ppo_learns_the_point_task(graph):
     import importlib.util
     import os
     path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
-                        "examples", "ppo_point.py")
+                        "tests", "ppo_point_task.py")
     spec = importlib.util.spec_from_file_location("ppo_point", path)
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
