@@ -7,15 +7,23 @@ Headline metric (BASELINE.json): GAE transitions/s on configs[1], the synthetic 
 4096 env streams x 2048 steps per GPU, gamma 0.99, lambda 0.95 (weak scaling: every rank owns
 its own 4096 streams, as VectorReplayBuffer sub-buffers shard with no communication).
 A "step" is one pass of ``ts_gae_rows`` (C-ABI) over the rank's rollout, resident in HBM.
-The same JSON line also carries: ``e2e`` (host pinned buffers in/out through the package's
-host pipeline, PCIe copies inside the timed region), ``roofline`` (algorithmic 21 B/transition
-over the CUDA-event kernel time vs MEASURED_PEAKS.json), ``cpu_baseline`` (the oracle port on
-the box's host cores, bounded sample), ``per`` (PER samples/s on configs[3]: 2^20 leaves, batch
-4096, sample + importance weights + update_weight per step, CUDA-graph replay) and ``clocks``.
+The same JSON line also carries: ``e2e`` (the drop-in call
+``BasePolicy.compute_episodic_return(batch, buffer, indices, v_s_, v_s)`` with NumPy arrays in
+and float64 NumPy arrays out, as the reference's callers use it -- host-to-device and
+device-to-host copies inside the timed region; ``e2e.pipelined`` is the package's own
+pinned-tensor pipeline with f32 outputs and cross-step overlap), ``roofline`` (algorithmic
+21 B/transition over the CUDA-event kernel time vs MEASURED_PEAKS.json), ``cpu_baseline`` (the
+oracle on the box's host cores, bounded sample: the C port and the numba port), ``per`` (PER
+samples/s on configs[3] / configs[4], a complete object of its own: value, roofline,
+cpu_baseline, e2e, and at N > 1 a bit-exactness check against the oracle's single global tree),
+``updates`` (C3 / C4 through the policy classes; at N > 1 the data-parallel learner) and
+``clocks``.
 
 ``--impl reference`` times the CPU restatement of the reference (oracle/, the numba kernels
-re-stated in C) on all host threads; it is the one place besides ``cpu_baseline`` where
-bench.py executes oracle/ code, and only as the thing being compared against.
+re-stated in C) over the FULL workload of this arm's config on all host cores (explicit thread
+count = os.cpu_count(), identical at every N: torchrun's OMP_NUM_THREADS=1 is not inherited); it
+is the one place besides ``cpu_baseline`` where bench.py executes oracle/ code, and only as the
+thing being compared against.
 """
 from __future__ import annotations
 
@@ -77,6 +85,26 @@ def measured_peaks():
         with open(path) as f:
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def host_info():
+    """CPU model, core count and the versions that pin a CPU baseline."""
+    model = "unknown"
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name"):
+                    model = line.split(":", 1)[1].strip()
+                    break
+    except OSError:
+        pass
+    info = {"cpu_model": model, "host_cpus": os.cpu_count(), "numpy": np.__version__}
+    try:
+        import numba
+        info["numba"] = numba.__version__
+    except Exception:
+        info["numba"] = None
+    return info
 
 
 class ClockSampler:
@@ -170,16 +198,70 @@ def cpu_per(seconds: float):
     return PER_BATCH / med, med, len(times)
 
 
+def cpu_gae_numba(seconds: float, rows: int, T: int):
+    """The reference's own technology on one core: numba _gae_return + the NumPy glue of
+    compute_episodic_return (oracle/oracle_nb.py, calibrated against the imported reference in
+    profiles/r02_reference_cpu.json: 1.01x its time at C2).  transitions/s, or None without numba."""
+    try:
+        from oracle import oracle_nb as nb
+        nb.warm()
+    except Exception:
+        return None
+    rew, v_s, v_next, term, trunc = rollout(rows, T, seed=1234)
+    n = rows * T
+    r64 = rew.reshape(-1).astype(np.float64)  # the reference stores rewards as f64 (manager.py:150)
+    t, c = term.reshape(-1).astype(bool), trunc.reshape(-1).astype(bool)
+    idx = np.arange(n)
+    unf = np.flatnonzero(~(t | c).reshape(rows, T)[:, -1]) * T + T - 1
+    vs, vn = v_s.reshape(-1), v_next.reshape(-1)
+    f = lambda: nb.compute_episodic_return(r64, t, c, t, idx, unf, vn, vs, GAMMA, LAMBDA)  # noqa: E731
+    f()
+    times, t0 = [], time.perf_counter()
+    while time.perf_counter() - t0 < seconds or len(times) < 3:
+        a = time.perf_counter()
+        f()
+        times.append(time.perf_counter() - a)
+    med = float(np.median(times))
+    return n / med, med, len(times)
+
+
+def cpu_per_numba(seconds: float):
+    """One PER step the way the reference runs it (prio.py:59-102 over segtree.py:87-137: numba
+    array kernels + NumPy), one core; samples/s or None without numba."""
+    try:
+        from oracle import oracle_nb as nb
+        nb.warm()
+    except Exception:
+        return None
+    rng = np.random.default_rng(2)
+    per = nb.PER(PER_LEAVES, PER_ALPHA, PER_BETA)
+    per.set_leaves(np.arange(PER_LEAVES),
+                   (np.abs(rng.standard_normal(PER_LEAVES)) + 1e-7) ** PER_ALPHA)
+    tds = [rng.standard_normal(PER_BATCH).astype(np.float32) for _ in range(8)]
+    times, t0, i = [], time.perf_counter(), 0
+    while time.perf_counter() - t0 < seconds or len(times) < 5:
+        a = time.perf_counter()
+        idx = per.sample_indices(PER_BATCH)
+        per.batch_weight(idx)
+        per.update_weight(idx, tds[i % 8])
+        times.append(time.perf_counter() - a)
+        i += 1
+    med = float(np.median(times))
+    return PER_BATCH / med, med, len(times)
+
+
 def run_reference(args):
-    """--impl reference: the reference's CPU algorithm on the host cores (rank 0 only)."""
+    """--impl reference: the reference's CPU algorithm on the host cores (rank 0 only; the other
+    ranks exit without work).  Each step is one pass over the FULL workload of this arm's config
+    (args.streams x args.horizon transitions); the thread count is explicit and the same at
+    every N."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     from oracle import oracle as orc
-    threads = orc.max_threads()
-    rows = min(args.streams, 1024)
-    # each "step" is one pass over a bounded sample of the workload: rows x T transitions
+    threads = max(1, os.cpu_count() or 1)
+    rows = args.streams
     rew, v_s, v_next, term, trunc = rollout(rows, args.horizon, seed=1234)
-    f = lambda th: orc.episodic_return_rows(rew, v_s, v_next, term, trunc, GAMMA, LAMBDA, th)
+    f = lambda th: orc.episodic_return_rows(rew, v_s, v_next, term, trunc, GAMMA, LAMBDA, th)  # noqa: E731
     for _ in range(max(args.warmup, 1)):
         f(threads)
     steps = max(1, min(args.steps, 200))
@@ -189,23 +271,33 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     value = rows * args.horizon * steps / dt
     one, _, _ = cpu_gae(1, 2.0, min(rows, 256), args.horizon)
+    nb1 = cpu_gae_numba(3.0, min(rows, 512), args.horizon)
     per, per_med, _ = cpu_per(3.0)
+    per_nb = cpu_per_numba(3.0)
+    info = host_info()
     line = {
         "impl": "reference", "metric": "GAE transitions/s", "value": value,
         "unit": "transitions/s", "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
         "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "vs_baseline": None, "dtype": "f64 arithmetic, f32 storage", "data": "synthetic",
         "config": {"workload": "GAE sweep 4096 streams x 2048 steps per GPU, gamma 0.99 "
                                "lambda 0.95 (BASELINE.json configs[1])",
                    "streams_per_gpu": args.streams, "horizon": args.horizon},
         "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": threads,
                          "kind": "port",
-                         "sample": f"{rows} streams x {args.horizon} steps per pass, OpenMP over "
-                                   f"streams ({threads} threads); 1 thread: {one:.3e}"},
+                         "sample": f"the full workload: {rows} streams x {args.horizon} steps per "
+                                   f"pass, OpenMP over streams, {threads} threads (explicit, not "
+                                   f"OMP_NUM_THREADS); C port 1 thread: {one:.3e}; numba port "
+                                   "(the reference's technology) 1 core: "
+                                   + (f"{nb1[0]:.3e}" if nb1 else "numba unavailable"),
+                         "port_1thread": one, "numba_port_1core": nb1[0] if nb1 else None,
+                         **info},
         "e2e": {"value": value, "unit": "transitions/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
         "per": {"metric": "PER samples/s", "value": per, "unit": "samples/s", "cores": 1,
-                "us_per_step": per_med * 1e6,
+                "us_per_step": per_med * 1e6, "kind": "port",
+                "numba_port": ({"value": per_nb[0], "us_per_step": per_nb[1] * 1e6}
+                               if per_nb else None),
                 "workload": "2^20 leaves, batch 4096, sample + weights + update_weight"},
         "gpu_launches": 0,
     }
@@ -220,7 +312,6 @@ def run_b200(args):
     import torch.distributed as dist
 
     from tianshou_fork_b200 import _lib as L
-    from tianshou_fork_b200.pipeline import GaeHostPipeline
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -337,84 +428,49 @@ def run_b200(args):
                 "moved_bytes_per_launch": n_trans * MOVED_BYTES_PER_TRANSITION,
                 "us_per_launch": kernel_s * 1e6}
 
-    # ---- e2e: pinned host buffers in and out through the package's host pipeline --------------
+    # ---- e2e: the drop-in call with host arrays in and out ------------------------------------------
     e2e = None
     if not args.skip_e2e:
-        pipe = GaeHostPipeline(E, T, chunks=E2E_CHUNKS, device=dev)
-        pipe.zero_copy = os.environ.get("TS_E2E_ZERO_COPY", "0") == "1"
-        pipe.overlap = os.environ.get("TS_E2E_OVERLAP", "1") == "1"
-        h_adv = torch.empty(E, T, dtype=torch.float32).pin_memory()
-        h_ret = torch.empty(E, T, dtype=torch.float32).pin_memory()
-        Ke = max(3, min(K, 100))
-        for _ in range(3):
-            pipe.run(*host, h_adv, h_ret, GAMMA, LAMBDA)
-        pipe.join(stream)
-        barrier()
-        pipe.launches = 0
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        with sampler:
-            e0.record(stream)
-            for _ in range(Ke):
-                pipe.run(*host, h_adv, h_ret, GAMMA, LAMBDA)
-            pipe.join(stream)  # every step's device->host copy has landed before the stop event
-            e1.record(stream)
-            barrier()
-        ems = max_over_ranks(e0.elapsed_time(e1))
-        if rank == 0:  # the copied-back result is the real one
-            assert torch.allclose(h_adv, adv.cpu(), rtol=0, atol=0)
-        # what the link can do: one big pinned copy each way, then both at once (context for e2e)
-        def link_gbs(fn, nbytes):
-            best = 1e9
-            for _ in range(3):
-                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                torch.cuda.synchronize()
-                a.record(stream)
-                fn()
-                b.record(stream)
-                torch.cuda.synchronize()
-                best = min(best, a.elapsed_time(b))
-            return nbytes / (best * 1e-3) / 1e9
-        s2 = torch.cuda.Stream(dev)
-        nb_in, nb_out = host[0].numel() * 4, h_adv.numel() * 4
-
-        def both():
-            s2.wait_stream(stream)
-            with torch.cuda.stream(s2):
-                h_adv.copy_(adv, non_blocking=True)
-            d_rew.copy_(host[0], non_blocking=True)
-            stream.wait_stream(s2)
-        pcie = {"h2d_GBps": link_gbs(lambda: d_rew.copy_(host[0], non_blocking=True), nb_in),
-                "d2h_GBps": link_gbs(lambda: h_adv.copy_(adv, non_blocking=True), nb_out),
-                "duplex_GBps": link_gbs(both, nb_in + nb_out)}
-        pcie["floor_ms_per_step"] = max(pipe.h2d_bytes / pcie["h2d_GBps"],
-                                        pipe.d2h_bytes / pcie["d2h_GBps"]) / 1e6
-        e2e = {"value": n_trans * world * Ke / (ems * 1e-3), "unit": "transitions/s",
-               "link": pcie,
-               "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
-               "ms_per_step": ems / Ke, "steps": Ke,
-               "api": f"tianshou_fork_b200.pipeline.GaeHostPipeline.run ({E2E_CHUNKS} row chunks; H2D, compute "
-                      f"and D2H streams; successive steps {'overlap' if pipe.overlap else 'do not overlap'} on the link)",
-               "launches": pipe.launches}
+        e2e = run_e2e(torch, dist, L, args, dev, rank, world, host, sets, barrier, max_over_ranks,
+                      sampler, K)
 
     # ---- PER: sample + importance weights + update_weight, CUDA-graph replay ------------------
     per = None
     if not args.skip_per:
         per = run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks)
 
-    # ---- CPU baseline (rank 0, N == 1 only): oracle port on the box's host cores --------------
+    # ---- CPU baseline (rank 0, N == 1 only): the oracle on the box's host cores -----------------
     cpu = None
     if rank == 0 and world == 1 and not args.skip_cpu:
-        v1, med1, n1 = cpu_gae(1, 8.0, 512, T)
+        v1, med1, n1 = cpu_gae(1, 6.0, 512, T)
+        nbr = cpu_gae_numba(6.0, 512, T)
         cpu = {"value": v1, "unit": "transitions/s", "cores": 1, "kind": "port",
                "sample": f"512 streams x {T} steps per pass, {n1} passes, median "
                          f"{med1 * 1e3:.2f} ms; oracle/ts_oracle.c (C restatement of numba "
                          "_gae_return + value mask + end flags), f32 in / f64 out",
-               "host_cpus": os.cpu_count()}
+               "numba_port": ({"value": nbr[0], "unit": "transitions/s", "cores": 1,
+                               "sample": f"512 streams x {T} steps per pass, {nbr[2]} passes, "
+                                         f"median {nbr[1] * 1e3:.2f} ms; oracle/oracle_nb.py: numba "
+                                         "_gae_return + the NumPy glue of compute_episodic_return "
+                                         "(np.isin, value mask, f64 temporaries) as the reference "
+                                         "runs it; 1.01x the imported reference's time in the "
+                                         "build container (profiles/r02_reference_cpu.json)"}
+                              if nbr else None),
+               **host_info()}
         if per is not None:
-            pv, pmed, pn = cpu_per(4.0)
+            pv, pmed, pn = cpu_per(3.0)
             per["cpu_baseline"] = {"value": pv, "unit": "samples/s", "cores": 1, "kind": "port",
-                                   "sample": f"{pn} steps, median {pmed * 1e6:.1f} us"}
+                                   "sample": f"{pn} steps, median {pmed * 1e6:.1f} us "
+                                             "(oracle/ts_oracle.c orc_per_step)", **host_info()}
             per["speedup_vs_cpu_port"] = per["value"] / pv
+            pnb = cpu_per_numba(3.0)
+            if pnb:
+                per["cpu_baseline"]["numba_port"] = {
+                    "value": pnb[0], "unit": "samples/s", "cores": 1,
+                    "sample": f"{pnb[2]} steps, median {pnb[1] * 1e6:.1f} us; oracle/oracle_nb.py: "
+                              "the reference's numba array kernels + NumPy (0.64x the imported "
+                              "reference's step time in the build container, i.e. faster than it)"}
+                per["speedup_vs_numba_port"] = per["value"] / pnb[0]
 
     # ---- C3 / C4 through the public API (rank 0, N == 1 only; reported beside the headline) ----
     updates = None
@@ -425,8 +481,8 @@ def run_b200(args):
         line = {
             "metric": "GAE transitions/s", "value": value, "unit": "transitions/s",
             "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64 arithmetic, f32 storage", "data": "synthetic",
             "config": {"workload": "GAE sweep 4096 streams x 2048 steps per GPU, gamma 0.99 "
                                    "lambda 0.95 (BASELINE.json configs[1])",
                        "streams_per_gpu": E, "horizon": T, "storage": "f32 values, u8 flags",
@@ -443,6 +499,163 @@ def run_b200(args):
         emit_result(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_e2e(torch, dist, L, args, dev, rank, world, host, sets, barrier, max_over_ranks, sampler,
+            K):
+    """End to end through the reference-facing call.
+
+    The rollout sits in a device-resident ``VectorReplayBuffer`` (filled through ``add``);
+    ``indices`` is what ``buffer.sample_indices(0)`` returns.  Every timed step calls
+    ``BasePolicy.compute_episodic_return(batch, buffer, indices, v_s_, v_s, gamma, gae_lambda)``
+    (tianshou/policy/base.py:337-346) with ``batch.rew / terminated / truncated`` and the critic
+    values as NumPy arrays (views of pinned host memory, so the copies are DMA from pinned
+    memory as the contract asks) and gets ``(returns, advantage)`` back as float64 NumPy arrays
+    like numba's.  Host-to-device and device-to-host copies are inside the timed region; the call
+    is synchronous (it returns host arrays), so successive steps do not overlap."""
+    import tianshou_fork_b200 as ts
+    from tianshou_fork_b200.pipeline import GaeHostPipeline, gae_host_call
+    E, T = args.streams, args.horizon
+    n_trans = E * T
+    stream = torch.cuda.current_stream()
+    rew_h, vs_h, vn_h, term_h, trunc_h = host  # pinned torch tensors [E, T]
+    buf = ts.VectorReplayBuffer(E * T, E, rew_dtype=torch.float32)
+    z = np.zeros(E, np.uint8)
+    rew_np, term_np, trunc_np = rew_h.numpy(), term_h.numpy().view(bool), trunc_h.numpy().view(bool)
+    for t in range(T):
+        buf.add(ts.Batch(obs=z, act=z, rew=rew_np[:, t], terminated=term_np[:, t],
+                         truncated=trunc_np[:, t], obs_next=z, info={}))
+    indices = buf.sample_indices(0)
+    assert buf.is_canonical(indices) == (E, T)
+    batch_np = ts.Batch(rew=rew_np.reshape(-1), terminated=term_np.reshape(-1),
+                        truncated=trunc_np.reshape(-1))
+    vs_np, vn_np = vs_h.numpy().reshape(-1), vn_h.numpy().reshape(-1)
+    hc = gae_host_call(dev)
+
+    def call(batch=batch_np, vn=vn_np, vs=vs_np, **kw):
+        return ts.BasePolicy.compute_episodic_return(batch, buf, indices, vn, vs, GAMMA, LAMBDA,
+                                                     **kw)
+
+    Ke = max(3, min(K, 50))
+    for _ in range(3):
+        ret, adv = call()
+    assert isinstance(adv, np.ndarray) and adv.dtype == np.float64
+    if rank == 0:  # the copied-back result is the real one (f64 here, f32 from the device leg)
+        d_adv = sets[0][1].cpu().numpy().reshape(-1)
+        assert np.allclose(adv, d_adv, rtol=1e-5, atol=1e-4)
+    barrier()
+    h0, d0, l0 = hc.h2d_bytes, hc.d2h_bytes, hc.launches
+    with sampler:
+        t0 = time.perf_counter()
+        for _ in range(Ke):
+            ret, adv = call()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        barrier()
+    ems = max_over_ranks(dt * 1e3)
+    h2d, d2h = (hc.h2d_bytes - h0) // Ke, (hc.d2h_bytes - d0) // Ke
+    launches = hc.launches - l0
+
+    def wall(fn, n=5):
+        fn()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(n):
+            fn()
+        torch.cuda.synchronize()
+        return max_over_ranks((time.perf_counter() - t0) / n * 1e3)
+
+    # variants of the same call (context, not the headline)
+    ms_f32 = wall(lambda: call(out_dtype=torch.float32))
+    dev_batch = ts.Batch(rew=buf.rew, terminated=buf.terminated, truncated=buf.truncated)
+    ms_devbatch = wall(lambda: call(batch=dev_batch))
+    pageable = [np.array(a) for a in (vn_np, vs_np)]
+    pb = ts.Batch(rew=np.array(batch_np.rew), terminated=np.array(batch_np.terminated),
+                  truncated=np.array(batch_np.truncated))
+    ms_pageable = wall(lambda: call(batch=pb, vn=pageable[0], vs=pageable[1]), n=3)
+
+    # ---- the package's own pinned-tensor pipeline (f32 out, successive steps overlap) ----------
+    pipe = GaeHostPipeline(E, T, chunks=E2E_CHUNKS, device=dev)
+    pipe.overlap = os.environ.get("TS_E2E_OVERLAP", "1") == "1"
+    h_adv = torch.empty(E, T, dtype=torch.float32).pin_memory()
+    h_ret = torch.empty(E, T, dtype=torch.float32).pin_memory()
+    for _ in range(3):
+        pipe.run(*host, h_adv, h_ret, GAMMA, LAMBDA)
+    pipe.join(stream)
+    barrier()
+    Kp = max(3, min(K, 50))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(Kp):
+        pipe.run(*host, h_adv, h_ret, GAMMA, LAMBDA)
+    pipe.join(stream)  # every step's device->host copy has landed before the stop event
+    e1.record(stream)
+    barrier()
+    pms = max_over_ranks(e0.elapsed_time(e1))
+
+    # ---- what the link can do: one big pinned copy each way, both at once; all ranks at once -----
+    d_rew, d_adv_t = sets[0][0][0], sets[0][1]
+
+    def link_gbs(fn, nbytes):
+        best = 1e9
+        for _ in range(3):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()  # N > 1: every rank copies at the same time (shared PCIe switches / NUMA)
+            a.record(stream)
+            fn()
+            b.record(stream)
+            torch.cuda.synchronize()
+            best = min(best, a.elapsed_time(b))
+        return nbytes / (best * 1e-3) / 1e9
+
+    s2 = torch.cuda.Stream(dev)
+    nb_in, nb_out = rew_h.numel() * 4, h_adv.numel() * 4
+
+    def both():
+        s2.wait_stream(stream)
+        with torch.cuda.stream(s2):
+            h_adv.copy_(d_adv_t, non_blocking=True)
+        d_rew.copy_(rew_h, non_blocking=True)
+        stream.wait_stream(s2)
+
+    link = {"h2d_GBps": link_gbs(lambda: d_rew.copy_(rew_h, non_blocking=True), nb_in),
+            "d2h_GBps": link_gbs(lambda: h_adv.copy_(d_adv_t, non_blocking=True), nb_out),
+            "duplex_GBps": link_gbs(both, nb_in + nb_out),
+            "how": "134 MB pinned copies, best of 3, per rank with all ranks copying concurrently"}
+
+    def total(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t)
+        return float(t.item())
+
+    for k in ("h2d_GBps", "d2h_GBps", "duplex_GBps"):
+        link["aggregate_" + k] = total(link[k])
+    link["floor_ms_per_step"] = max(h2d / link["h2d_GBps"], d2h / link["d2h_GBps"],
+                                    (h2d + d2h) / link["duplex_GBps"]) / 1e6
+    return {
+        "value": n_trans * world * Ke / (ems * 1e-3), "unit": "transitions/s",
+        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ems / Ke,
+        "steps": Ke, "launches_per_step": launches // Ke,
+        "api": "BasePolicy.compute_episodic_return(batch, buffer, indices, v_s_, v_s, gamma, "
+               "gae_lambda): batch.rew f32 / terminated / truncated and v_s_, v_s f32 as NumPy "
+               "arrays (pinned host memory) in, (returns, advantage) float64 NumPy arrays out; "
+               "buffer = device-resident VectorReplayBuffer, indices = buffer.sample_indices(0); "
+               "synchronous call, wall clock, max over ranks",
+        "variants_ms_per_step": {
+            "float32_out (out_dtype=torch.float32, this package's extension)": ms_f32,
+            "batch fields already on the device (batch = buffer storage), NumPy values": ms_devbatch,
+            "pageable NumPy arrays (bounced through pinned buffers by the call)": ms_pageable},
+        "pipelined": {
+            "value": n_trans * world * Kp / (pms * 1e-3), "unit": "transitions/s",
+            "ms_per_step": pms / Kp, "h2d_bytes_per_step": pipe.h2d_bytes,
+            "d2h_bytes_per_step": pipe.d2h_bytes,
+            "api": f"tianshou_fork_b200.pipeline.GaeHostPipeline.run: pinned torch tensors, f32 "
+                   f"outputs, {E2E_CHUNKS} row chunks, successive steps overlap on the link "
+                   "(not the reference's signature)"},
+        "link": link,
+    }
 
 
 def run_updates():

@@ -678,9 +678,129 @@ def gen_stack(ts, out):
     np.savez_compressed(os.path.join(out, "stack.npz"), **flat)
 
 
+def gen_c4(ts, out):
+    """BASELINE.json configs[3] at FULL size on the reference itself:
+    ``PrioritizedVectorReplayBuffer(2^20, 16)`` with wrapped rings, then for batch 32 / 256 /
+    4096: ``sample_indices`` (prio.py:59-64), ``buffer[idx].weight`` (:91-102),
+    ``compute_nstep_return`` n = 3 with D = 1 and 51 (policy/base.py:386-440),
+    ``update_weight`` with 5 % duplicated indices (prio.py:78-89); plus ``prev`` / ``next`` of
+    4096 random indices.  Inputs are regenerated from seeds by tests/helpers.py."""
+    import hashlib
+
+    import torch
+    from tianshou.data import Batch, PrioritizedVectorReplayBuffer
+    from tianshou.policy import BasePolicy
+
+    sys.path.insert(0, os.path.dirname(HERE))
+    import helpers as H
+
+    rew, term, trunc = H.c4_stream()
+    E, sub = H.C4_E, H.C4_SUB
+    buf = PrioritizedVectorReplayBuffer(E * sub, E, alpha=0.6, beta=0.4)
+    zeros = np.zeros(E, np.uint8)
+    for t in range(rew.shape[0]):
+        buf.add(Batch(obs=zeros, act=zeros, rew=rew[t], terminated=term[t], truncated=trunc[t],
+                      obs_next=zeros, info={}))
+    size = E * sub
+    buf.weight[np.arange(size)] = H.c4_leaves()
+    flat = {
+        "c4/rew_sha": np.frombuffer(hashlib.sha256(buf.rew.tobytes()).digest(), np.uint8),
+        "c4/done_sha": np.frombuffer(hashlib.sha256(buf.done.tobytes()).digest(), np.uint8),
+        "c4/last_index": buf.last_index.copy(), "c4/lengths": buf._lengths.copy(),
+        "c4/unfinished": buf.unfinished_index(), "c4/root0": np.array(buf.weight.reduce()),
+    }
+    rng = np.random.default_rng(4002)
+    q = rng.integers(0, size, 4096)
+    flat["c4/q"], flat["c4/prev"], flat["c4/next"] = q, buf.prev(q), buf.next(q)
+    for bsz in H.C4_BATCHES:
+        np.random.seed(2000 + bsz)
+        idx = buf.sample_indices(bsz)
+        batch = buf[idx]
+        flat[f"c4/b{bsz}/idx"] = idx.copy()
+        flat[f"c4/b{bsz}/weight"] = np.asarray(batch.weight).copy()
+        for D in H.C4_DIMS:
+            def target_q_fn(buffer, terminal, D=D):
+                t = torch.from_numpy(H.c4_target_q(terminal, D))
+                return t if D > 1 else t.flatten()
+
+            r = BasePolicy.compute_nstep_return(Batch(), buf, idx, target_q_fn, gamma=0.99,
+                                                n_step=3).returns.numpy()
+            flat[f"c4/b{bsz}/d{D}/returns_sha"] = np.frombuffer(
+                hashlib.sha256(np.ascontiguousarray(r).tobytes()).digest(), np.uint8)
+            flat[f"c4/b{bsz}/d{D}/returns_head"] = r[:64].copy()
+        td = rng.standard_normal(bsz).astype(np.float32)
+        idx_u = idx.copy()
+        k = bsz // 20
+        idx_u[:k] = idx_u[k:2 * k]
+        buf.update_weight(idx_u, td)
+        uniq = np.unique(idx_u)
+        flat[f"c4/b{bsz}/leaves"] = buf.weight[uniq].copy()
+        flat[f"c4/b{bsz}/root"] = np.array(buf.weight.reduce())
+        flat[f"c4/b{bsz}/prio"] = np.array([buf._max_prio, buf._min_prio])
+    np.savez_compressed(os.path.join(out, "c4.npz"), **flat)
+
+
+def gen_ppo_ant(ts, out):
+    """BASELINE.json configs[2]: ``PPOPolicy.update`` of the reference on CPU over an Ant-shaped
+    rollout (obs 27, act 8, 64 envs x 2048 steps = 131 072 transitions, Gaussian actor, minibatch
+    1024, one repeat; policy/base.py:288-315 -> ppo.py:87-162, a2c.py:83-117).  Stored: a strided
+    sample + sums of returns / adv / v_s / logp_old, every minibatch's losses, final weights."""
+    import torch
+    from tianshou.data import Batch, VectorReplayBuffer
+    from tianshou.policy import PPOPolicy
+
+    sys.path.insert(0, os.path.dirname(HERE))
+    import helpers as H
+
+    A = H.ANT
+    obs, act, rew, term, trunc = H.ant_rollout()
+    buf = VectorReplayBuffer(A["E"] * A["T"], A["E"])
+    for t in range(A["T"]):
+        buf.add(Batch(obs=obs[t], act=act[t], rew=rew[t], terminated=term[t], truncated=trunc[t],
+                      obs_next=obs[t + 1], info={}))
+    Actor, Critic = H.ant_nets(torch)
+    torch.manual_seed(2)
+    actor, critic = Actor(), Critic()
+    optim = torch.optim.Adam(list(actor.parameters()) + list(critic.parameters()), lr=3e-4)
+    flat = {}
+    for k, v in actor.state_dict().items():
+        flat[f"ant/init/actor/{k}"] = v.numpy().copy()
+    for k, v in critic.state_dict().items():
+        flat[f"ant/init/critic/{k}"] = v.numpy().copy()
+    policy = PPOPolicy(actor, critic, optim, H.ant_dist(torch), action_scaling=False, **H.ANT_KW)
+    seen = {}
+    inner = policy.process_fn
+
+    def spy(batch, buffer, indices):
+        batch = inner(batch, buffer, indices)
+        for k in ("returns", "adv", "v_s", "logp_old"):
+            seen[k] = np.asarray(batch[k].detach().numpy(), dtype=np.float64).copy()
+        return batch
+
+    policy.process_fn = spy
+    np.random.seed(13)
+    res = policy.update(0, buf, batch_size=A["batch_size"], repeat=A["repeat"])
+    for k, v in res.items():
+        flat[f"ant/{k}"] = np.asarray(v, dtype=np.float64)
+    for k, v in seen.items():
+        flat[f"ant/{k}_sample"] = v[::37].astype(np.float32)
+        flat[f"ant/{k}_stats"] = np.array([v.sum(), np.abs(v).sum(), (v * v).sum()])
+    for k, v in actor.state_dict().items():
+        flat[f"ant/final/actor/{k}"] = v.numpy().copy()
+    for k, v in critic.state_dict().items():
+        flat[f"ant/final/critic/{k}"] = v.numpy().copy()
+    np.savez_compressed(os.path.join(out, "ppo_ant.npz"), **flat)
+
+
 def main():
     ts = import_reference()
     import numba
+
+    only = sys.argv[1:]  # e.g. `make_golden.py c4 ppo_ant` regenerates just those files
+    if only:
+        for name in only:
+            globals()[f"gen_{name}"](ts, HERE)
+        return
 
     gen_gae(ts, HERE)
     gen_index(ts, HERE)
@@ -693,6 +813,8 @@ def main():
     gen_dqn_update(ts, HERE)
     gen_sample(ts, HERE)
     gen_stack(ts, HERE)
+    gen_c4(ts, HERE)
+    gen_ppo_ant(ts, HERE)
     with open(os.path.join(HERE, "versions.json"), "w") as f:
         json.dump({"tianshou": ts.__version__, "numpy": np.__version__,
                    "numba": numba.__version__, "reference": REF}, f, indent=1)

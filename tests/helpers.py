@@ -154,3 +154,100 @@ DQN_UPDATE_SPECS = [
 ]
 
 
+
+
+# ---- BASELINE.json configs[3] at full size (make_golden.gen_c4) ----------------------------------
+C4_E, C4_SUB, C4_EXTRA = 16, 65536, 1234       # 16 sub-buffers x 65 536 = 2^20 slots, rings wrapped
+C4_BATCHES = (32, 256, 4096)
+C4_DIMS = (1, 51)
+
+
+def c4_stream(seed=4000):
+    """SURVEY.md 8d C4 rollout: rew in {-1, 0, 1} with P = (.05, .9, .05), terminated ~ B(1/1000),
+    truncated ~ B(1/10000) & ~terminated; ``[steps, E]`` arrays, steps = 65 536 + 1234 so every
+    ring has wrapped."""
+    rng = np.random.default_rng(seed)
+    steps = C4_SUB + C4_EXTRA
+    rew = rng.choice(np.array([-1.0, 0.0, 1.0]), size=(steps, C4_E), p=[0.05, 0.9, 0.05])
+    term = rng.random((steps, C4_E)) < 1 / 1000
+    trunc = (rng.random((steps, C4_E)) < 1 / 10000) & ~term
+    return rew, term, trunc
+
+
+def c4_leaves(seed=4001):
+    rng = np.random.default_rng(seed)
+    return (np.abs(rng.standard_normal(C4_E * C4_SUB)) + np.finfo(np.float32).eps) ** 0.6
+
+
+def c4_target_q(idx, D):
+    """Deterministic ``target_q_fn`` table: exact in f32 on any library (integer hash / 2^16)."""
+    idx = np.asarray(idx, dtype=np.int64)
+    h = (idx[:, None] * 2654435761 + np.arange(D, dtype=np.int64)[None] * 40503) % 65536
+    return (h / 65536.0 - 0.5).astype(np.float32)
+
+
+def c4_final_storage(rew, term, trunc):
+    """What the rings hold after the stream: slot j of a sub-buffer keeps the LAST step t with
+    t % sub == j.  Returns ``[E * sub]`` arrays in storage order plus (ring index, last_index)."""
+    steps = rew.shape[0]
+    t_of_slot = np.arange(C4_SUB)
+    t_of_slot = np.where(t_of_slot + C4_SUB < steps, t_of_slot + C4_SUB, t_of_slot)
+    pick = lambda a: np.ascontiguousarray(a[t_of_slot].T).reshape(-1)  # noqa: E731
+    ring_index = steps % C4_SUB
+    last = np.arange(C4_E, dtype=np.int64) * C4_SUB + (ring_index - 1) % C4_SUB
+    return pick(rew), pick(term), pick(trunc), ring_index, last
+
+
+# ---- BASELINE.json configs[2]: Ant-shaped PPO update (make_golden.gen_ppo_ant) -------------------
+ANT = dict(E=64, T=2048, obs=27, act=8, batch_size=1024, repeat=1)
+ANT_KW = dict(eps_clip=0.2, value_clip=True, advantage_normalization=True, vf_coef=0.25,
+              ent_coef=0.0, max_grad_norm=0.5, gae_lambda=0.95, discount_factor=0.99,
+              max_batchsize=131072)
+
+
+def ant_rollout(seed=4100):
+    """``[T, E, ...]`` arrays of an Ant-shaped rollout (obs 27, act 8, 64 envs x 2048 steps)."""
+    rng = np.random.default_rng(seed)
+    T, E = ANT["T"], ANT["E"]
+    obs = rng.standard_normal((T + 1, E, ANT["obs"]), dtype=np.float32)
+    act = rng.standard_normal((T, E, ANT["act"]), dtype=np.float32)
+    rew = rng.standard_normal((T, E))
+    term = rng.random((T, E)) < 1 / 500
+    trunc = (rng.random((T, E)) < 1 / 1000) & ~term
+    return obs, act, rew, term, trunc
+
+
+def ant_nets(torch):
+    """Gaussian actor with a state-independent log-std (examples/mujoco ActorProb shape) and a
+    critic, two 64 x 64 tanh MLPs."""
+
+    class Actor(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.mu = torch.nn.Sequential(
+                torch.nn.Linear(ANT["obs"], 64), torch.nn.Tanh(), torch.nn.Linear(64, 64),
+                torch.nn.Tanh(), torch.nn.Linear(64, ANT["act"]))
+            self.sigma = torch.nn.Parameter(torch.full((ANT["act"],), -0.5))
+
+        def forward(self, obs, state=None, info=None):
+            obs = torch.as_tensor(obs, dtype=torch.float32, device=self.sigma.device)
+            mu = self.mu(obs)
+            return (mu, self.sigma.exp().expand_as(mu)), state
+
+    class Critic(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.net = torch.nn.Sequential(
+                torch.nn.Linear(ANT["obs"], 64), torch.nn.Tanh(), torch.nn.Linear(64, 64),
+                torch.nn.Tanh(), torch.nn.Linear(64, 1))
+
+        def forward(self, obs, **kw):
+            obs = torch.as_tensor(obs, dtype=torch.float32, device=self.net[0].weight.device)
+            return self.net(obs)
+
+    return Actor, Critic
+
+
+def ant_dist(torch):
+    return lambda mu, sigma: torch.distributions.Independent(
+        torch.distributions.Normal(mu, sigma), 1)

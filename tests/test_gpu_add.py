@@ -118,17 +118,33 @@ def test_packed_host_add_equals_per_key_assignment(n_env, frame):
         assert torch.equal(bufs[0]._meta[k], bufs[1]._meta[k]), k
 
 
-def test_device_simulator_loop_learns():
-    """examples/ppo_point_device.py: simulator on the GPU -> add_device -> canonical GAE ->
-    PPO update -> reset, several iterations; the reward improves like the host-env loop."""
-    import importlib.util
-    import os
-    import sys
-    ex = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples")
-    sys.path.insert(0, ex)
-    spec = importlib.util.spec_from_file_location("ppo_point_device",
-                                                  os.path.join(ex, "ppo_point_device.py"))
-    mod = importlib.util.module_from_spec(spec)
-    spec.loader.exec_module(mod)
-    hist, rate = mod.run(iterations=12, envs=512, steps=32, graph=True, seed=2)
-    assert hist[-1] > hist[0] + 0.25 and rate > 0, hist
+def test_add_device_on_a_prioritized_buffer_initialises_the_leaves():
+    """``add_device`` on a PrioritizedVectorReplayBuffer calls ``init_weight`` on the slots it
+    wrote like ``add`` does (prio.py:50-57): same tree as a twin filled through the host path,
+    and transitions added on the device are sampled."""
+    import tianshou_fork_b200 as ts
+    rng = np.random.default_rng(4)
+    E, cap = 4, 16
+    dev_buf = ts.PrioritizedVectorReplayBuffer(E * cap, E, alpha=0.7, beta=0.5)
+    host_buf = ts.PrioritizedVectorReplayBuffer(E * cap, E, alpha=0.7, beta=0.5)
+    for t in range(23):  # wraps
+        ids = np.arange(E) if t % 3 else np.array([0, 2])
+        m = ids.size
+        step = dict(obs=rng.standard_normal((m, 3)).astype(np.float32),
+                    act=rng.integers(0, 4, m), rew=rng.standard_normal(m),
+                    terminated=rng.random(m) < 0.2, truncated=np.zeros(m, bool))
+        host_buf.add(ts.Batch(info={}, **step), buffer_ids=ids)
+        dev_buf.add_device(ts.Batch(**{k: torch.from_numpy(v).cuda() for k, v in step.items()}),
+                           buffer_ids=ids)
+        if t == 9:  # raise max_prio so later init_weight values differ from 1
+            for b in (host_buf, dev_buf):
+                b.update_weight(np.array([1, 17]), np.array([3.0, 0.25]))
+    assert torch.equal(dev_buf.weight._value, host_buf.weight._value)
+    assert dev_buf.weight.reduce() > 0
+    np.random.seed(3)
+    a = dev_buf.sample_indices(64).cpu().numpy()
+    np.random.seed(3)
+    b = host_buf.sample_indices(64).cpu().numpy()
+    assert np.array_equal(a, b)
+    with pytest.raises(NotImplementedError):
+        ts.PrioritizedReplayBuffer(8, 0.6, 0.4).add_device(ts.Batch())

@@ -126,18 +126,38 @@ def test_policy_with_captured_graphs_pickles():
     assert np.isclose(l1, l2, rtol=1e-5)
 
 
-@pytest.mark.parametrize("graph", [False, True], ids=["eager", "cuda_graph"])
-def test_dqn_with_per_learns_the_point_task(graph):
-    """End to end like test/discrete/test_dqn.py (collect -> update, a reward threshold at the
-    end): prioritized sampling, 3-step returns with a target network and update_weight."""
-    import importlib.util
-    import os
-    import sys
-    ex = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples")
-    sys.path.insert(0, ex)
-    spec = importlib.util.spec_from_file_location("dqn_point", os.path.join(ex, "dqn_point.py"))
-    mod = importlib.util.module_from_spec(spec)
-    spec.loader.exec_module(mod)
-    hist = mod.run(steps=600, graph=graph, seed=1)
-    assert hist[-1] > hist[0] + 0.2, hist  # epsilon-greedy start is near the random -0.95
-    assert hist[-1] > -0.7, hist
+@pytest.mark.parametrize("prio", [False, True], ids=["ring", "prioritized_ring"])
+def test_graphed_update_on_a_growing_single_ring(prio):
+    """cuda_graph=True on a plain (Prioritized)ReplayBuffer that is still filling: a single ring
+    takes ``%`` by its CURRENT size (base.py:158-168), which the captured kernels read from the
+    device bookkeeping -- the by-value ``sub_size`` launch argument is frozen at capture time and
+    must not be used for it.  Eager and graphed runs stay identical while the ring grows, wraps
+    and keeps going."""
+    import tianshou_fork_b200 as ts
+    from helpers import ppo_update_nets
+    Actor, _ = ppo_update_nets(torch)
+    out = []
+    for graph in (False, True):
+        rng = np.random.default_rng(6)
+        buf = ts.PrioritizedReplayBuffer(48, 0.6, 0.4) if prio else ts.ReplayBuffer(48)
+        torch.manual_seed(4)
+        net = Actor().cuda()
+        optim = torch.optim.Adam(net.parameters(), lr=1e-3)
+        policy = ts.DQNPolicy(net, optim, 0.95, estimation_step=3, target_update_freq=3,
+                              cuda_graph=graph)
+        np.random.seed(22)
+        losses, nexts = [], []
+        for t in range(70):
+            buf.add(ts.Batch(obs=rng.standard_normal(3).astype(np.float32),
+                             act=int(rng.integers(0, 4)), rew=float(rng.standard_normal()),
+                             terminated=bool(rng.random() < 0.1), truncated=False,
+                             obs_next=rng.standard_normal(3).astype(np.float32), info={}))
+            if t >= 6:
+                losses.append(policy.update(8, buf)["loss"])
+                nexts.append(buf.next(np.arange(len(buf))))
+        out.append((losses, nexts, [p.detach().clone() for p in net.parameters()]))
+    (le, ne, pe), (lg, ng, pg) = out
+    assert np.allclose(le, lg, rtol=1e-5, atol=1e-6)
+    assert all(np.array_equal(a, b) for a, b in zip(ne, ng))
+    for a, b in zip(pe, pg):
+        assert torch.allclose(a, b, rtol=1e-5, atol=1e-6)

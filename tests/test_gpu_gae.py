@@ -240,8 +240,8 @@ def test_flat_kernel_with_indices_vs_oracle(variant, B, cap, rotate):
 
 
 def test_c2_full_size_properties():
-    """BASELINE.json configs[1] at full size (4096 x 2048): oracle parity on a row sample and
-    size-independent properties over the whole array."""
+    """BASELINE.json configs[1] at full size (4096 x 2048): the WHOLE array against the oracle
+    (SURVEY.md 8d), plus size-independent properties."""
     from tianshou_fork_b200 import _lib as L
     E, T = 4096, 2048
     rew, v_s, v_next, term, trunc = c2_rollout(E, T, seed=0)
@@ -258,10 +258,17 @@ def test_c2_full_size_properties():
 
     run(g_rew, adv, ret)
     a, r = adv.cpu().numpy(), ret.cpu().numpy()
-    rows = np.r_[0:8, 2000:2008, E - 8:E]
-    ref_ret, ref_adv = orc.episodic_return_rows(rew[rows], v_s[rows], v_next[rows], term[rows],
-                                                trunc[rows], 0.99, 0.95)
-    assert _close(a[rows], ref_adv) and _close(r[rows], ref_ret)
+    ref_ret, ref_adv = orc.episodic_return_rows(rew, v_s, v_next, term, trunc, 0.99, 0.95,
+                                                threads=orc.max_threads())
+    assert _close(a, ref_adv) and _close(r, ref_ret)  # all 8 388 608 transitions
+    # f64 outputs of the same launch shape: 1e-9
+    adv64 = torch.empty(E, T, dtype=torch.float64, device="cuda")
+    ret64 = torch.empty(E, T, dtype=torch.float64, device="cuda")
+    L.check(L.lib().ts_gae_rows(L.ptr(g_rew), L.ptr(g_vs), L.ptr(g_vn), L.ptr(g_term),
+                                L.ptr(g_trunc), E, T, T, T, 0.99, 0.95, 0, 0, 1,
+                                L.ptr(adv64), L.ptr(ret64), L.stream()), "ts_gae_rows")
+    assert _close(adv64.cpu().numpy(), ref_adv, 1e-9) and _close(ret64.cpu().numpy(), ref_ret, 1e-9)
+    del adv64, ret64
     # returns = advantage + v_s  (policy/base.py:382)
     assert np.allclose(r, a + v_s, rtol=0, atol=1e-5 * np.abs(r).max())
     # one-step Bellman identity away from episode ends: A_t = delta_t + gl * A_{t+1}
@@ -471,3 +478,112 @@ def test_listing_runs_path_equals_indexed_path(case, monkeypatch):
         v_s_=v_n.cpu().numpy(), v_s=v_s.cpu().numpy(), gamma=0.99, gae_lambda=0.95)
     assert np.allclose(adv_a.cpu().numpy(), want_adv, rtol=1e-5, atol=1e-5)
     assert np.allclose(ret_a.cpu().numpy(), want_ret, rtol=1e-5, atol=1e-5)
+
+
+def test_c2_full_size_through_the_drop_in_api():
+    """configs[1] through ``VectorReplayBuffer.add`` -> ``sample(0)`` ->
+    ``BasePolicy.compute_episodic_return``: the canonical batch (rows kernel) and the same batch
+    with a foreign index tensor (indexed flat kernel), every one of the 8 388 608 transitions
+    against the oracle; NumPy in -> NumPy f64 out like the reference."""
+    import tianshou_fork_b200 as ts
+    E, T = 4096, 2048
+    rew, v_s, v_next, term, trunc = c2_rollout(E, T, seed=1)
+    buf = ts.VectorReplayBuffer(E * T, E, rew_dtype=torch.float32)
+    z = np.zeros(E, np.uint8)
+    for t in range(T):
+        buf.add(ts.Batch(obs=z, act=z, rew=rew[:, t], terminated=term[:, t],
+                         truncated=trunc[:, t], obs_next=z, info={}))
+    batch, indices = buf.sample(0)
+    assert buf.is_canonical(indices) == (E, T)
+    ref_ret, ref_adv = orc.episodic_return_rows(rew, v_s, v_next, term, trunc, 0.99, 0.95,
+                                                threads=orc.max_threads())
+    g_vs, g_vn = torch.from_numpy(v_s).cuda().view(-1), torch.from_numpy(v_next).cuda().view(-1)
+    ret, adv = ts.BasePolicy.compute_episodic_return(batch, buf, indices, g_vn, g_vs, 0.99, 0.95)
+    assert _close(adv.cpu().numpy(), ref_adv.ravel()) and _close(ret.cpu().numpy(), ref_ret.ravel())
+    other = indices.clone()
+    assert buf.is_canonical(other) is None
+    ret2, adv2 = ts.BasePolicy.compute_episodic_return(batch, buf, other, g_vn, g_vs, 0.99, 0.95)
+    assert _close(adv2.cpu().numpy(), ref_adv.ravel())
+    assert _close(ret2.cpu().numpy(), ref_ret.ravel())
+    # the reference's calling convention: NumPy arrays in, float64 NumPy arrays out
+    ret3, adv3 = ts.BasePolicy.compute_episodic_return(
+        batch, buf, indices, v_next.ravel(), v_s.ravel(), 0.99, 0.95)
+    assert isinstance(ret3, np.ndarray) and ret3.dtype == np.float64
+    assert _close(adv3, ref_adv.ravel(), 1e-9) and _close(ret3, ref_ret.ravel(), 1e-9)
+
+
+def test_flat_workspace_shared_by_big_and_small_calls():
+    """One workspace, one stream: pipelined ranges (2^21 steps, gamma = lambda = 1, no episode
+    end: every range waits for its neighbour's tagged head value), then a short sequence through
+    the look-back kernel, then the big one again with other rewards.  The look-back path must not
+    reset the call counter the tags derive from (a stale head value would be accepted)."""
+    from tianshou_fork_b200 import _lib as L
+    N, n_small = 1 << 21, 100_000
+    rng = np.random.default_rng(12)
+    v_s = rng.standard_normal(N).astype(np.float32)
+    v_n = rng.standard_normal(N).astype(np.float32)
+    z = np.zeros(N, dtype=bool)
+    d = lambda a: torch.from_numpy(a).cuda()
+    nbytes = L.lib().ts_gae_flat_workspace_bytes(N)
+    ws = torch.zeros(nbytes, dtype=torch.uint8, device="cuda")
+    adv = torch.empty(N, dtype=torch.float64, device="cuda")
+    ret = torch.empty(N, dtype=torch.float64, device="cuda")
+
+    def call(g_rew, n):
+        L.check(L.lib().ts_gae_flat(L.ptr(g_rew), L.ptr(g[0]), L.ptr(g[1]), L.ptr(g[2]),
+                                    L.ptr(g[2]), None, None, None, None, 0, 0, n, 1.0, 1.0, 1, 0,
+                                    1, L.ptr(adv), L.ptr(ret), L.ptr(ws), nbytes, L.stream()),
+                "ts_gae_flat")
+
+    g = [d(v_s), d(v_n), d(z.view(np.uint8))]
+    for rounds in range(3):
+        rew = rng.standard_normal(N)
+        call(d(rew), N)
+        assert _close(adv.cpu().numpy(), orc.gae_return(v_s, v_n, rew, z, 1.0, 1.0), 1e-9), rounds
+        rew_s = rng.standard_normal(n_small)
+        call(d(rew_s), n_small)
+        want = orc.gae_return(v_s[:n_small], v_n[:n_small], rew_s, z[:n_small], 1.0, 1.0)
+        assert _close(adv[:n_small].cpu().numpy(), want, 1e-9), rounds
+
+
+@pytest.mark.parametrize("kinds", ["pageable", "pinned", "device_batch", "f64_values"])
+def test_host_call_numpy_in_numpy_out(kinds, monkeypatch):
+    """The drop-in with the reference's calling convention (NumPy critic values in, float64
+    NumPy out) on a canonical rollout goes through pipeline.GaeHostCall: pageable arrays, NumPy
+    views of pinned memory, a batch that is already on the device, f64 values; several chunks."""
+    import tianshou_fork_b200 as ts
+    from tianshou_fork_b200 import pipeline
+    from tianshou_fork_b200.policy import base as policy_base
+    monkeypatch.setattr(policy_base, "HOST_CALL_MIN_N", 1 << 10)
+    monkeypatch.setattr(pipeline.GaeHostCall, "CHUNK_BYTES", 1 << 20)  # ~10 chunks at this size
+    E, T = 640, 512
+    rew, v_s, v_next, term, trunc = c2_rollout(E, T, seed=21, p_term=1 / 70)
+    buf = ts.VectorReplayBuffer(E * T, E, rew_dtype=torch.float32)
+    z = np.zeros(E, np.uint8)
+    for t in range(T):
+        buf.add(ts.Batch(obs=z, act=z, rew=rew[:, t], terminated=term[:, t],
+                         truncated=trunc[:, t], obs_next=z, info={}))
+    batch, indices = buf.sample(0)
+    ref_ret, ref_adv = orc.episodic_return_rows(rew, v_s, v_next, term, trunc, 0.99, 0.95)
+    pin = lambda a: torch.from_numpy(a).pin_memory().numpy()  # noqa: E731
+    vs, vn = v_s.ravel(), v_next.ravel()
+    if kinds == "pinned":
+        vs, vn = pin(vs), pin(vn)
+        batch = ts.Batch(rew=pin(rew.ravel()), terminated=pin(term.ravel()),
+                         truncated=pin(trunc.ravel()))
+    elif kinds == "pageable":
+        batch = ts.Batch(rew=rew.ravel().astype(np.float64), terminated=term.ravel(),
+                         truncated=trunc.ravel())
+    elif kinds == "f64_values":
+        vs, vn = vs.astype(np.float64), vn.astype(np.float64)
+    hc = pipeline.gae_host_call(buf.device)
+    n0 = hc.launches
+    for _ in range(2):
+        ret, adv = ts.BasePolicy.compute_episodic_return(batch, buf, indices, vn, vs, 0.99, 0.95)
+        assert isinstance(ret, np.ndarray) and ret.dtype == np.float64 and ret.shape == (E * T,)
+        assert _close(adv, ref_adv.ravel(), 1e-9) and _close(ret, ref_ret.ravel(), 1e-9)
+    assert hc.launches - n0 >= 4  # chunked
+    # our extension: float32 out for NumPy callers halves the device-to-host bytes
+    ret32, adv32 = ts.BasePolicy.compute_episodic_return(batch, buf, indices, vn, vs, 0.99, 0.95,
+                                                         out_dtype=torch.float32)
+    assert ret32.dtype == np.float32 and _close(adv32, ref_adv.ravel())

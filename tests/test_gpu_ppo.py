@@ -331,3 +331,60 @@ def test_ppo_learns_the_point_task(graph):
     first, last = np.mean(hist[:3]), np.mean(hist[-3:])
     assert last > first + 0.25, (first, last)  # a random policy drifts around -0.95
     assert last > -0.6, hist[-3:]
+
+
+@pytest.mark.parametrize("graph", [False, True], ids=["eager", "cuda_graph"])
+def test_ppo_ant_shaped_update_vs_reference_update(graph):
+    """BASELINE.json configs[2] at full size: the reference's ``PPOPolicy.update`` (run on CPU by
+    make_golden.gen_ppo_ant) on an Ant-shaped rollout -- obs 27, act 8, 64 envs x 2048 steps =
+    131 072 transitions, Gaussian actor, minibatch 1024, one repeat (128 minibatches) -- against
+    this package's, same initial weights and numpy seed.  Tolerances: f32 networks on two
+    devices; GAE over 2048-step streams in f64 on both sides."""
+    import tianshou_fork_b200 as ts
+    import helpers as H
+    case = load_golden("ppo_ant")["ant"]
+    A = H.ANT
+    obs, act, rew, term, trunc = H.ant_rollout()
+    buf = ts.VectorReplayBuffer(A["E"] * A["T"], A["E"])
+    for t in range(A["T"]):
+        buf.add(ts.Batch(obs=obs[t], act=act[t], rew=rew[t], terminated=term[t],
+                         truncated=trunc[t], obs_next=obs[t + 1], info={}))
+    Actor, Critic = H.ant_nets(torch)
+    actor, critic = Actor(), Critic()
+    for net, tag in ((actor, "actor"), (critic, "critic")):
+        net.load_state_dict({k[len(f"init/{tag}/"):]: torch.from_numpy(v)
+                             for k, v in case.items() if k.startswith(f"init/{tag}/")})
+    actor, critic = actor.cuda(), critic.cuda()
+    optim = torch.optim.Adam(list(actor.parameters()) + list(critic.parameters()), lr=3e-4)
+    policy = ts.PPOPolicy(actor, critic, optim, H.ant_dist(torch), action_scaling=False,
+                          cuda_graph=graph, **H.ANT_KW)
+    seen = {}
+    inner = policy.process_fn
+
+    def spy(batch, buffer, indices):
+        assert buffer.is_canonical(indices) == (A["E"], A["T"])  # the rows kernel's layout
+        batch = inner(batch, buffer, indices)
+        for k in ("returns", "adv", "v_s", "logp_old"):
+            seen[k] = batch[k].detach().double().cpu().numpy().copy()
+        return batch
+
+    policy.process_fn = spy
+    np.random.seed(13)
+    res = policy.update(0, buf, batch_size=A["batch_size"], repeat=A["repeat"])
+    for k in ("returns", "adv", "v_s", "logp_old"):
+        v = seen[k]
+        assert v.shape == (A["E"] * A["T"],)
+        assert np.allclose(v[::37], case[f"{k}_sample"], rtol=1e-4, atol=1e-4), k
+        stats = np.array([v.sum(), np.abs(v).sum(), (v * v).sum()])
+        # sums of 131 072 terms: tolerance tied to the sum of magnitudes, not to the (cancelling) sum
+        assert np.allclose(stats, case[f"{k}_stats"], rtol=1e-4,
+                           atol=1e-5 * case[f"{k}_stats"][1]), k
+    n_mb = A["E"] * A["T"] // A["batch_size"]
+    for k in ("loss", "loss/clip", "loss/vf", "loss/ent"):
+        got, want = np.asarray(res[k]), case[k]
+        assert got.shape == want.shape == (n_mb * A["repeat"],)
+        assert np.allclose(got[:4], want[:4], rtol=1e-4, atol=1e-5), k
+        assert np.allclose(got, want, rtol=5e-3, atol=5e-4), k
+    for net, tag in ((actor, "actor"), (critic, "critic")):
+        for k, v in net.state_dict().items():
+            assert np.allclose(v.cpu().numpy(), case[f"final/{tag}/{k}"], rtol=3e-3, atol=3e-4), k

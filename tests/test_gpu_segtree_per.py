@@ -212,8 +212,17 @@ def test_per_full_size_step_vs_oracle(update_kernel):
         keys = np.fromiter(lastpos.keys(), np.int64)
         tdl = td[np.fromiter(lastpos.values(), np.int64)]
         p32 = np.abs(tdl) + np.finfo(np.float32).eps
-        exact = (p32.astype(np.float64) ** 0.6).astype(np.float32).astype(np.float64)
-        assert np.count_nonzero(got_tree[size + keys] != exact) <= 1
+        p64 = p32.astype(np.float64) ** 0.6
+        exact = p64.astype(np.float32).astype(np.float64)
+        bad = np.flatnonzero(got_tree[size + keys] != exact)
+        # Both sides round an f64 power to f32; the two f64 powers (CUDA's pow, the host libm's)
+        # may differ by an ulp or two, which flips the f32 rounding only when the f64 value sits
+        # on an f32 rounding boundary.  Any mismatch must be exactly that case: adjacent f32
+        # values, with the f64 power within 4 f64-ulp of their midpoint.
+        for j in bad:
+            lo, hi = sorted((got_tree[size + keys[j]], exact[j]))
+            assert np.nextafter(np.float32(lo), np.float32(np.inf)) == np.float32(hi)
+            assert abs(p64[j] - 0.5 * (lo + hi)) <= 4 * np.spacing(p64[j])
         # re-anchor on the oracle's leaves (f32 pow is not bit-reproducible across libms)
         touched = np.unique(idx)
         buf.weight[torch.from_numpy(touched).cuda()] = torch.from_numpy(

@@ -275,3 +275,101 @@ def test_golden_stack_gather():
         assert np.array_equal(orc.stack_gather(c["frames"], c["query"], k, *args, from_next=True),
                               c["obs_next"]), name
         assert np.array_equal(orc.stack_gather(c["frames"], c["query"], 2, *args), c["get2"]), name
+
+
+# ---- BASELINE.json configs[3] at full size: oracle vs the reference's own outputs -----------------
+def test_oracle_c4_full_size_vs_reference_golden():
+    """tests/golden/c4.npz (make_golden.gen_c4: the reference's PrioritizedVectorReplayBuffer of
+    2^20 slots in 16 wrapped rings): prev / next, the PER sampled indices, importance weights and
+    the n-step targets (n = 3, D = 1 and 51) of batches 32 / 256 / 4096 from the oracle."""
+    import hashlib
+    import helpers as H
+    g = load_golden("c4")["c4"]
+    rew, term, trunc = H.c4_stream()
+    s_rew, s_term, s_trunc, ring_index, last = H.c4_final_storage(rew, term, trunc)
+    sha = lambda a: np.frombuffer(hashlib.sha256(np.ascontiguousarray(a).tobytes()).digest(),  # noqa: E731
+                                  np.uint8)
+    assert np.array_equal(sha(s_rew), g["rew_sha"])
+    assert np.array_equal(sha(s_term | s_trunc), g["done_sha"])
+    E, sub = H.C4_E, H.C4_SUB
+    st = orc.RingState(E * sub, E)
+    st.rew, st.terminated, st.truncated, st.done = s_rew, s_term, s_trunc, s_term | s_trunc
+    st.index[:], st.size[:], st.lengths[:] = ring_index, sub, sub
+    st.last_index = last
+    assert np.array_equal(last, g["last_index"]) and np.array_equal(st.lengths, g["lengths"])
+    assert np.array_equal(st.unfinished_index(), g["unfinished"])
+    assert np.array_equal(st.prev(g["q"]), g["prev"]) and np.array_equal(st.next(g["q"]), g["next"])
+    per = orc.PER(E * sub, 0.6, 0.4)
+    per.weight[np.arange(E * sub)] = H.c4_leaves()
+    assert per.weight.reduce() == float(g["root0"])
+    rng = np.random.default_rng(4002)
+    rng.integers(0, E * sub, 4096)  # the generator drew q first
+    for bsz in H.C4_BATCHES:
+        np.random.seed(2000 + bsz)
+        idx = per.sample_indices(np.random.rand(bsz))
+        assert np.array_equal(idx, g[f"b{bsz}/idx"]), bsz  # bit-exact
+        assert np.allclose(per.batch_weight(idx), g[f"b{bsz}/weight"], rtol=1e-12)
+        for D in H.C4_DIMS:
+            r = orc.compute_nstep_return(st, idx, lambda t: H.c4_target_q(t, D), 0.99, 3)
+            r = r.astype(np.float32) if D > 1 else r.astype(np.float32).reshape(bsz, 1)
+            assert np.array_equal(r[:64].reshape(g[f"b{bsz}/d{D}/returns_head"].shape),
+                                  g[f"b{bsz}/d{D}/returns_head"])
+            assert np.array_equal(sha(r), g[f"b{bsz}/d{D}/returns_sha"]), (bsz, D)
+        td = rng.standard_normal(bsz).astype(np.float32)
+        idx_u = idx.copy()
+        k = bsz // 20
+        idx_u[:k] = idx_u[k:2 * k]
+        per.update_weight(idx_u, td)
+        uniq = np.unique(idx_u)
+        # NumPy computed these very leaves (same library): bit-equal here, 6e-7 on the GPU
+        assert np.array_equal(per.weight[uniq], g[f"b{bsz}/leaves"])
+        assert per.weight.reduce() == float(g[f"b{bsz}/root"])
+        assert np.array_equal([per._max_prio, per._min_prio], g[f"b{bsz}/prio"])
+
+
+def test_numba_port_matches_c_oracle_and_goldens():
+    """oracle/oracle_nb.py (the timed CPU baseline of bench.py: the reference's hot path restated
+    in numba + NumPy) returns what the C oracle and the reference's goldens hold."""
+    from oracle import oracle_nb as nb
+    import helpers as H
+    nb.warm()
+    rng = np.random.default_rng(5)
+    # GAE over a flattened rotated batch with unfinished tails
+    B, cap = 7, 50
+    idx = np.concatenate([k * cap + (np.arange(cap) + 3 * k) % cap for k in range(B)])
+    n = idx.size
+    buf_term = rng.random(B * cap) < 0.05
+    term, trunc = buf_term[idx], (rng.random(n) < 0.02) & ~buf_term[idx]
+    unfinished = np.array([k * cap + (3 * k - 1) % cap for k in range(0, B, 2)])
+    rew, v_s, v_n = rng.standard_normal(n), rng.standard_normal(n), rng.standard_normal(n)
+    want = orc.compute_episodic_return(rew, term, trunc, buf_term[idx], idx, unfinished,
+                                       v_s_=v_n, v_s=v_s, gamma=0.99, gae_lambda=0.95)
+    got = nb.compute_episodic_return(rew, term, trunc, buf_term, idx, unfinished, v_n, v_s,
+                                     0.99, 0.95)
+    assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+    # PER + n-step on the C4 golden, batch 256
+    g = load_golden("c4")["c4"]
+    r, t, tr = H.c4_stream()
+    s_rew, s_term, s_trunc, ring_index, last = H.c4_final_storage(r, t, tr)
+    size = H.C4_E * H.C4_SUB
+    per = nb.PER(size, 0.6, 0.4)
+    per.set_leaves(np.arange(size), H.c4_leaves())
+    for bsz in (32, 256):
+        np.random.seed(2000 + bsz)
+        idx = per.sample_indices(bsz)
+        assert np.array_equal(idx, g[f"b{bsz}/idx"])
+        assert np.allclose(per.batch_weight(idx), g[f"b{bsz}/weight"], rtol=1e-12)
+        off = np.arange(H.C4_E + 1) * H.C4_SUB
+        lens = np.full(H.C4_E, H.C4_SUB)
+        ret = nb.compute_nstep_return(
+            s_rew, s_term | s_trunc, s_term, off, last, lens, g["unfinished"], idx,
+            lambda tt: H.c4_target_q(tt, 51), 0.99, 3).astype(np.float32)
+        assert np.array_equal(ret[:64], g[f"b{bsz}/d51/returns_head"])
+        if bsz == 32:  # keep the tree in the golden's state for the next batch
+            rng2 = np.random.default_rng(4002)
+            rng2.integers(0, size, 4096)
+            td = rng2.standard_normal(bsz).astype(np.float32)
+            idx_u = idx.copy()
+            idx_u[:1] = idx_u[1:2]
+            per.update_weight(idx_u, td)
+            assert per._value[1] == float(g["b32/root"])

@@ -161,3 +161,174 @@ class GaeHostPipeline:
     def synchronize(self) -> None:
         self.join()
         torch.cuda.current_stream(self.device).synchronize()
+
+
+# ---------------------------------------------------------------------------------------------
+# The drop-in call with host arrays: BasePolicy.compute_episodic_return(NumPy in) -> NumPy out
+# ---------------------------------------------------------------------------------------------
+def _np_dtype(t: torch.dtype):
+    import numpy as np
+    return {torch.float32: np.float32, torch.float64: np.float64, torch.uint8: np.uint8}[t]
+
+
+class _Source:
+    """One ``[E, T]`` input of the rows kernel: already on the device (no copy), pinned host
+    memory (DMA straight from it), or pageable host memory (bounced through a pinned buffer by
+    a host copy that overlaps the previous chunk's DMA)."""
+
+    def __init__(self, arr, E: int, T: int, dtype: torch.dtype, device: torch.device) -> None:
+        import numpy as np
+        self.dtype = dtype
+        if isinstance(arr, torch.Tensor) and arr.is_cuda:
+            t = arr.detach()
+            if t.dtype == torch.bool:
+                t = t.view(torch.uint8)
+            if t.dtype != dtype:
+                t = t.to(dtype)
+            self.kind, self.t = "device", t.reshape(E, T).contiguous()
+            return
+        if isinstance(arr, torch.Tensor):
+            t = arr.detach()
+        else:
+            a = np.ascontiguousarray(arr)
+            if a.dtype == np.bool_:
+                a = a.view(np.uint8)
+            t = torch.from_numpy(a)
+        if t.dtype == torch.bool:
+            t = t.view(torch.uint8)
+        if t.dtype != dtype:
+            t = t.to(dtype)  # host-side widening (e.g. f64 rewards with f32 values stay f64 upstream)
+        self.t = t.reshape(E, T)
+        self.kind = "pinned" if self.t.is_pinned() else "pageable"
+
+    @property
+    def host_bytes_per_row(self) -> int:
+        return 0 if self.kind == "device" else self.t.shape[1] * self.t.element_size()
+
+
+class GaeHostCall:
+    """``compute_episodic_return`` for callers that hold the critic values (and possibly the
+    rollout) as host arrays and want NumPy back, as the reference's callers do
+    (tianshou/policy/base.py:337-346, a2c.py:91-116).  The [E, T] rows are cut into chunks; the
+    host-to-device copies of chunk c+1, the kernel of chunk c and the device-to-host copies of
+    chunk c-1 run on three streams (one per engine), so a call costs about the longer of the two
+    PCIe directions.  Outputs land in pinned host memory taken from torch's caching host
+    allocator and are returned as NumPy views of it (no extra host copy; the block goes back to
+    the allocator when the arrays are dropped)."""
+
+    CHUNK_BYTES = 24 << 20  # host bytes per chunk and direction: deep enough to hide latencies
+
+    def __init__(self, device: torch.device) -> None:
+        L.lib()
+        self.device = device
+        self.s_h2d, self.s_comp, self.s_d2h = (torch.cuda.Stream(device) for _ in range(3))
+        self._dev: dict = {}      # staging on the device, by (name, slot)
+        self._bounce: dict = {}   # pinned bounce buffers for pageable inputs, by (name, slot)
+        self.h2d_bytes = self.d2h_bytes = self.launches = 0
+
+    def _dev_buf(self, name: str, slot: int, rows: int, T: int, dtype: torch.dtype) -> torch.Tensor:
+        key = (name, slot)
+        t = self._dev.get(key)
+        if t is None or t.dtype != dtype or t.numel() < rows * T:
+            t = torch.empty(rows * T, dtype=dtype, device=self.device)
+            self._dev[key] = t
+        return t[: rows * T].view(rows, T)
+
+    def _bounce_buf(self, name: str, slot: int, rows: int, T: int, dtype: torch.dtype):
+        key = (name, slot)
+        t = self._bounce.get(key)
+        if t is None or t.dtype != dtype or t.numel() < rows * T:
+            t = torch.empty(rows * T, dtype=dtype).pin_memory()
+            self._bounce[key] = t
+        return t[: rows * T].view(rows, T)
+
+    def run(self, E: int, T: int, rew, v_s, v_next, terminated, truncated, gamma: float,
+            gae_lambda: float, rew_dtype: torch.dtype, val_dtype: torch.dtype,
+            out_dtype: torch.dtype):
+        """Returns ``(returns, advantage)`` as NumPy ``[E * T]`` arrays of ``out_dtype``."""
+        dev = self.device
+        src = {"rew": _Source(rew, E, T, rew_dtype, dev), "vs": _Source(v_s, E, T, val_dtype, dev),
+               "vn": _Source(v_next, E, T, val_dtype, dev),
+               "term": _Source(terminated, E, T, torch.uint8, dev),
+               "trunc": _Source(truncated, E, T, torch.uint8, dev)}
+        osz = 8 if out_dtype == torch.float64 else 4
+        in_row = sum(s.host_bytes_per_row for s in src.values())
+        out_row = 2 * T * osz
+        rows = max(1, min(E, self.CHUNK_BYTES // max(in_row, out_row, 1)))
+        chunks = (E + rows - 1) // rows
+        rows = (E + chunks - 1) // chunks  # even chunks
+        nb = 3
+        h_ret = torch.empty(E, T, dtype=out_dtype, pin_memory=True)
+        h_adv = torch.empty(E, T, dtype=out_dtype, pin_memory=True)
+        cur = torch.cuda.current_stream(dev)
+        for st in (self.s_h2d, self.s_comp, self.s_d2h):
+            st.wait_stream(cur)  # device-resident inputs may still be in flight on the caller's stream
+        ev_loaded = [torch.cuda.Event() for _ in range(nb)]
+        ev_kernel = [torch.cuda.Event() for _ in range(nb)]
+        ev_stored = [torch.cuda.Event() for _ in range(nb)]
+        ev_bounced: dict = {}
+        lib = L.lib()
+        code = lambda d: L.TS_F64 if d == torch.float64 else L.TS_F32  # noqa: E731
+        for c in range(chunks):
+            lo, hi = c * rows, min(E, (c + 1) * rows)
+            n, b = hi - lo, c % nb
+            ptrs = {}
+            with torch.cuda.stream(self.s_h2d):
+                if c >= nb:
+                    self.s_h2d.wait_event(ev_kernel[b])  # chunk c - nb has consumed this slot
+                for name, s in src.items():
+                    if s.kind == "device":
+                        ptrs[name] = s.t[lo:hi].data_ptr()
+                        continue
+                    d = self._dev_buf(name, b, rows, T, s.dtype)[:n]
+                    if s.kind == "pinned":
+                        d.copy_(s.t[lo:hi], non_blocking=True)
+                    else:
+                        # pageable: host copy into a pinned bounce buffer (multi-threaded for
+                        # chunks this size), then DMA; the bounce buffer of slot b is free once
+                        # the DMA that last read it has finished
+                        hb = self._bounce_buf(name, b, rows, T, s.dtype)[:n]
+                        ev = ev_bounced.get((name, b))
+                        if ev is not None:
+                            ev.synchronize()
+                        hb.copy_(s.t[lo:hi])
+                        d.copy_(hb, non_blocking=True)
+                        ev = torch.cuda.Event()
+                        ev.record(self.s_h2d)
+                        ev_bounced[(name, b)] = ev
+                    ptrs[name] = d.data_ptr()
+                    self.h2d_bytes += n * s.host_bytes_per_row
+                ev_loaded[b].record(self.s_h2d)
+            d_adv = self._dev_buf("adv", b, rows, T, out_dtype)[:n]
+            d_ret = self._dev_buf("ret", b, rows, T, out_dtype)[:n]
+            with torch.cuda.stream(self.s_comp):
+                self.s_comp.wait_event(ev_loaded[b])
+                if c >= nb:
+                    self.s_comp.wait_event(ev_stored[b])  # outputs of chunk c - nb copied out
+                L.check(lib.ts_gae_rows(
+                    ptrs["rew"], ptrs["vs"], ptrs["vn"], ptrs["term"], ptrs["trunc"], n, T, T, T,
+                    float(gamma), float(gae_lambda), code(rew_dtype), code(val_dtype),
+                    code(out_dtype), d_adv.data_ptr(), d_ret.data_ptr(),
+                    self.s_comp.cuda_stream), "ts_gae_rows")
+                self.launches += 1
+                ev_kernel[b].record(self.s_comp)
+            with torch.cuda.stream(self.s_d2h):
+                self.s_d2h.wait_event(ev_kernel[b])
+                h_adv[lo:hi].copy_(d_adv, non_blocking=True)
+                h_ret[lo:hi].copy_(d_ret, non_blocking=True)
+                ev_stored[b].record(self.s_d2h)
+            self.d2h_bytes += n * out_row
+        self.s_d2h.synchronize()  # the caller reads host memory next
+        cur.wait_stream(self.s_comp)
+        return h_ret.view(-1).numpy(), h_adv.view(-1).numpy()
+
+
+_host_calls: dict = {}
+
+
+def gae_host_call(device: torch.device) -> GaeHostCall:
+    key = device.index or 0
+    hc = _host_calls.get(key)
+    if hc is None:
+        hc = _host_calls[key] = GaeHostCall(device)
+    return hc

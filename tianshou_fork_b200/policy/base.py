@@ -33,6 +33,11 @@ _ws_cache: Dict[Tuple[int, int], torch.Tensor] = {}
 # transitions 48 vs 29 us, 8.4 M transitions 47.6 vs 66.0 us).
 LISTING_MIN_N = 1 << 21
 
+# NumPy callers of compute_episodic_return on a canonical rollout of at least this many
+# transitions go through the chunked host pipeline (pipeline.GaeHostCall): copies of successive
+# row chunks overlap with the kernel and with each other instead of running back to back.
+HOST_CALL_MIN_N = 1 << 18
+
 
 def _device_of(buffer: Any) -> torch.device:
     dev = getattr(buffer, "device", None)
@@ -97,6 +102,37 @@ def _buffer_layout(buffer: Any, device: torch.device):
     return (_dev(off, device), _dev(last, device), _dev(lens, device), last.size, sub,
             L.as_u8(_dev(buffer.done, device, torch.bool)),
             L.as_u8(_dev(buffer.terminated, device, torch.bool)))
+
+
+def _episodic_return_host_call(batch: Batch, dev: torch.device, canon: Tuple[int, int], v_s_: Any,
+                               v_s: Any, gamma: float, gae_lambda: float,
+                               out_dtype: Optional[torch.dtype]):
+    """The reference's calling convention at rollout scale: critic values (and possibly the
+    batch fields) as host arrays in, NumPy out (policy/base.py:337-346).  Canonical [E, T]
+    batches only; returns None when a dtype falls outside what the rows kernel takes."""
+    from ..pipeline import gae_host_call
+    E, T = canon
+    n = E * T
+
+    def float_dtype(x):
+        d = x.dtype
+        if isinstance(x, torch.Tensor):
+            return d if d in (torch.float32, torch.float64) else None
+        return {np.dtype(np.float32): torch.float32,
+                np.dtype(np.float64): torch.float64}.get(np.dtype(d))
+
+    rew = batch.rew
+    vs, vn = np.asarray(v_s) if not isinstance(v_s, torch.Tensor) else v_s, \
+        np.asarray(v_s_) if not isinstance(v_s_, torch.Tensor) else v_s_
+    rd, vd, nd = float_dtype(rew), float_dtype(vs), float_dtype(vn)
+    if rd is None or vd is None or nd is None or any(
+            int(np.prod(x.shape)) != n for x in (rew, vs, vn, batch.terminated, batch.truncated)):
+        return None
+    val_dtype = vd if vd == nd else torch.float64  # one value dtype per launch: widen
+    ret, adv = gae_host_call(dev).run(
+        E, T, rew, vs, vn, batch.terminated, batch.truncated, gamma, gae_lambda, rd, val_dtype,
+        out_dtype if out_dtype is not None else torch.float64)
+    return ret, adv
 
 
 def allreduce_mean_grads(params: Any, group: Any = None) -> None:
@@ -240,9 +276,15 @@ class BasePolicy(nn.Module):
         dev = _device_of(buffer)
         tensor_io = isinstance(v_s_, torch.Tensor) or isinstance(v_s, torch.Tensor) or (
             v_s_ is None and v_s is None and isinstance(batch.rew, torch.Tensor))
+        canon = buffer.is_canonical(indices) if hasattr(buffer, "is_canonical") else None
+        if (not tensor_io and canon is not None and v_s_ is not None and v_s is not None
+                and canon[0] * canon[1] >= HOST_CALL_MIN_N):
+            out = _episodic_return_host_call(batch, dev, canon, v_s_, v_s, gamma, gae_lambda,
+                                             out_dtype)
+            if out is not None:
+                return out
         rew = _float_dev(batch.rew, dev)
         n = rew.numel()
-        canon = buffer.is_canonical(indices) if hasattr(buffer, "is_canonical") else None
         off, last, lens, B, sub, buf_done, buf_term = _buffer_layout(buffer, dev)
         idx = _dev(indices, dev, torch.int64)
         if idx.ndim != 1:
