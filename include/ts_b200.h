@@ -40,6 +40,7 @@ extern "C" {
 #define TS_ERR_WORKSPACE (-2) /* workspace_bytes smaller than ts_*_workspace_bytes() */
 #define TS_ERR_CUDA (-3)      /* launch failed; see ts_last_cuda_error() */
 #define TS_ERR_ALIGN (-4)     /* pointer not aligned to its element size */
+#define TS_ERR_TOO_LARGE (-5) /* size beyond the fixed capacity of a *_static entry point */
 
 /* dtype codes for the float-typed arguments */
 #define TS_F32 0
@@ -133,6 +134,30 @@ int32_t ts_gae_flat(const void* rew, const void* v_s, const void* v_s_next,
                     double gae_lambda, int32_t rew_dtype, int32_t val_dtype, int32_t out_dtype,
                     void* adv, void* ret, void* workspace, size_t workspace_bytes,
                     ts_stream_t stream);
+
+/*
+ * ts_gae_flat without a caller workspace and without any allocation.
+ * NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments and results as ts_gae_flat minus `workspace`; the scratch
+ * is a file-scope `static __device__` array of 229 392 bytes inside the library (resident on
+ * every GPU that loads it until the process exits), which bounds the call at
+ * N <= TS_GAE_FLAT_STATIC_MAX_N transitions: larger N returns TS_ERR_TOO_LARGE before any
+ * launch.  The call performs no cudaMalloc / cudaFree / allocating library call.
+ * Every call shares that array and it keeps the last call's contents (the kernels clear or
+ * re-tag what must start fresh), so calls issued back to back on ONE stream are safe, while
+ * calls that overlap on the GPU -- other streams, other host threads -- race on it: use
+ * ts_gae_flat with one workspace per stream for those.
+ */
+#define TS_GAE_FLAT_STATIC_MAX_N (1 << 24)
+int64_t ts_gae_flat_static_max_n(void);
+int32_t ts_gae_flat_static(const void* rew, const void* v_s, const void* v_s_next,
+                           const uint8_t* terminated, const uint8_t* truncated,
+                           const int64_t* indices, const uint8_t* buf_terminated,
+                           const int64_t* unfinished, const int64_t* offset, int64_t B,
+                           int64_t sub_size, int64_t N, double gamma, double gae_lambda,
+                           int32_t rew_dtype, int32_t val_dtype, int32_t out_dtype, void* adv,
+                           void* ret, ts_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * Episode-aware index arithmetic.

@@ -40,6 +40,9 @@ SIGNATURES = {
     "ts_gae_flat_workspace_bytes": (_sz, [_i64]),
     "ts_gae_flat": (_i32, [_vp] * 9 + [_i64] * 3 + [_f64, _f64, _i32, _i32, _i32, _vp, _vp, _vp,
                                                    _sz, _vp]),
+    "ts_gae_flat_static_max_n": (_i64, []),
+    "ts_gae_flat_static": (_i32, [_vp] * 9 + [_i64] * 3 + [_f64, _f64, _i32, _i32, _i32, _vp, _vp,
+                                                          _vp]),
     "ts_prev_index": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     "ts_next_index": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     "ts_unfinished_index": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp]),

@@ -29,6 +29,8 @@ extern "C" const char* ts_error_string(int32_t code) {
         case TS_ERR_WORKSPACE: return "workspace too small";
         case TS_ERR_CUDA: return cudaGetErrorString((cudaError_t)ts::g_last_cuda_error);
         case TS_ERR_ALIGN: return "pointer not aligned to its element size";
+        case TS_ERR_TOO_LARGE:
+            return "size exceeds the fixed scratch capacity of this *_static entry point";
         default: return "unknown error code";
     }
 }

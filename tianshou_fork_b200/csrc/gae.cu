@@ -1437,3 +1437,77 @@ extern "C" int32_t ts_gae_flat(const void* rew, const void* v_s, const void* v_s
     TS_DISPATCH3(rew_dtype, val_dtype, out_dtype, TS_GO);
 #undef TS_GO
 }
+
+
+// ---------------------------------------------------------------------------------------------
+// ts_gae_flat_static: ts_gae_flat for callers that cannot provide (or allocate) a workspace.
+// No counterpart in the reference.
+//
+// The scratch of the flat kernels (call counter, inter-CTA flags, tile aggregates) lives in a
+// file-scope device array of fixed size, held by every GPU that loads this library until the
+// process exits.  Zero at module load, which is the "zero-initialised once" the kernels need;
+// afterwards it keeps the last call's contents like any caller-owned workspace (the look-back
+// kernel clears its own ticket and status words per call, the pipelined kernel tags its flags
+// with a call count), so back-to-back calls on ONE stream are safe.  Every call shares the
+// array: calls that overlap on the GPU (two streams, two host threads) race on it.
+// ---------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace ts {
+namespace {
+constexpr int64_t kStaticGaeMaxN = TS_GAE_FLAT_STATIC_MAX_N;
+constexpr size_t kStaticGaeTiles = (size_t)((kStaticGaeMaxN + FLAT_TILE - 1) / FLAT_TILE);
+constexpr size_t kStaticGaeBytes =
+    16 + ((kStaticGaeTiles * 4 + 15) / 16) * 16 + 3 * kStaticGaeTiles * 8;  // 229 392 B
+}  // namespace
+}  // namespace ts
+
+static __device__ __align__(256) unsigned char g_gae_flat_scratch[ts::kStaticGaeBytes];
+
+// In host code `g_gae_flat_scratch` is a host-side stand-in, not a device address: the address
+// the kernels get comes from cudaGetSymbolAddress, once per device, with that device current.
+static int32_t gae_static_scratch(void** out) {
+    constexpr int kMaxDevices = 64;
+    static void* ptrs[kMaxDevices] = {};
+    static std::mutex mu;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+        g_last_cuda_error = (int32_t)(e != cudaSuccess ? e : cudaErrorInvalidDevice);
+        return TS_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (ptrs[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_gae_flat_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            g_last_cuda_error = (int32_t)e;
+            (void)cudaGetLastError();
+            return TS_ERR_CUDA;
+        }
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return TS_OK;
+}
+
+extern "C" int64_t ts_gae_flat_static_max_n(void) { return ts::kStaticGaeMaxN; }
+
+extern "C" int32_t ts_gae_flat_static(const void* rew, const void* v_s, const void* v_s_next,
+                                      const uint8_t* terminated, const uint8_t* truncated,
+                                      const int64_t* indices, const uint8_t* buf_terminated,
+                                      const int64_t* unfinished, const int64_t* offset, int64_t B,
+                                      int64_t sub_size, int64_t N, double gamma,
+                                      double gae_lambda, int32_t rew_dtype, int32_t val_dtype,
+                                      int32_t out_dtype, void* adv, void* ret,
+                                      ts_stream_t stream) {
+    if (N > ts::kStaticGaeMaxN) return TS_ERR_TOO_LARGE;
+    if (N <= 0) return N == 0 ? TS_OK : TS_ERR_BAD_ARG;
+    static_assert(ts::kStaticGaeBytes <= sizeof(g_gae_flat_scratch), "scratch covers the maximum");
+    void* scratch = nullptr;
+    const int32_t rc = gae_static_scratch(&scratch);
+    if (rc != TS_OK) return rc;
+    return ts_gae_flat(rew, v_s, v_s_next, terminated, truncated, indices, buf_terminated,
+                       unfinished, offset, B, sub_size, N, gamma, gae_lambda, rew_dtype,
+                       val_dtype, out_dtype, adv, ret, scratch, ts::kStaticGaeBytes, stream);
+}
