@@ -308,6 +308,32 @@ int32_t ts_per_update(double* tree, int64_t size, int64_t bound, const int64_t* 
                       const void* td, int32_t td_dtype, int64_t M, double alpha, double* prio,
                       uint32_t* stamp, uint32_t* counter, int32_t* err_flag,
                       ts_stream_t stream);
+/*
+ * The replay step with a LAZILY finished tree (same reference lines as ts_per_update /
+ * ts_per_sample: prio.py:78-89, :59-64, :66-76, :101 over segtree.py:98-104, :122-137).
+ * ts_per_update_lazy writes the new leaves and every ancestor up to the roots of its per-CTA
+ * leaf ranges and stops: the levels above them -- heap indices below
+ * ts_segtree_lazy_top_nodes(bound), at most 128 nodes -- stay stale.  ts_per_sample_lazy stages
+ * the top of the tree in shared memory anyway; it rebuilds those levels there from the range
+ * roots in the tree's pairwise order (node = left + right, the bits the reference holds), samples
+ * from them and writes them back, so after it the tree in memory is complete again.  This takes
+ * the update's last-CTA ticket (fence + atomic), its serial top rebuild and their latency off the
+ * step.  Any OTHER reader of the inner nodes between the two calls (ts_segtree_reduce,
+ * ts_segtree_prefix_idx, ts_per_sample, a host copy) must call ts_segtree_finish_top first;
+ * leaves are always current.  Trees outside the ranged-update regime (<= 4096 or > 2^20 leaves,
+ * batches > 16383) are updated completely by ts_per_update_lazy; ts_segtree_lazy_top_nodes
+ * returns 0 for them and the other two calls then behave like their eager counterparts.
+ */
+int32_t ts_segtree_lazy_top_nodes(int64_t bound);
+int32_t ts_per_update_lazy(double* tree, int64_t size, int64_t bound, const int64_t* idx,
+                           const void* td, int32_t td_dtype, int64_t M, double alpha,
+                           double* prio, uint32_t* stamp, uint32_t* counter, int32_t* err_flag,
+                           ts_stream_t stream);
+int32_t ts_per_sample_lazy(double* tree, int64_t bound, const double* u, int64_t M,
+                           const double* prio, double beta, int32_t weight_norm, int64_t* idx,
+                           double* weight, int32_t* err_flag, ts_stream_t stream);
+int32_t ts_segtree_finish_top(double* tree, int64_t bound, ts_stream_t stream);
+
 /* init_weight (prio.py:42-43): tree[idx] = max_prio^alpha, max_prio read from the device
  * scalar; leaf_dtype TS_F32 rounds the power to f32 (the reference's result type once
  * _max_prio has become an np.float32, prio.py:88). */

@@ -48,6 +48,17 @@ def main():
                                   stamp.data_ptr(), counter.data_ptr(), err.data_ptr(), s),
                 "update")
 
+    def sample_lazy(r, s):
+        L.check(lib.ts_per_sample_lazy(tree.data_ptr(), bound, u[r].data_ptr(), B, prio.data_ptr(),
+                                       0.4, 1, idx[r].data_ptr(), w[r].data_ptr(), err.data_ptr(),
+                                       s), "sample_lazy")
+
+    def update_lazy(r, s):
+        L.check(lib.ts_per_update_lazy(tree.data_ptr(), size, bound, idx[r].data_ptr(),
+                                       td[r].data_ptr(), L.TS_F32, B, 0.6, prio.data_ptr(),
+                                       stamp.data_ptr(), counter.data_ptr(), err.data_ptr(), s),
+                "update_lazy")
+
     def prefix_on(buf, r, s):
         L.check(lib.ts_segtree_prefix_idx(tree.data_ptr(), bound, buf[r].data_ptr(), L.TS_F64, B, 1,
                                           idx[r].data_ptr(), err.data_ptr(), s), "prefix")
@@ -77,6 +88,14 @@ def main():
         print(json.dumps({"what": name, "lg": lg, "batch": B, "us_per_call": best}), flush=True)
 
     import ctypes
+    timed("sample+update", lambda r, s: (sample(r, s), update(r, s)))
+    timed("sample_lazy+update_lazy", lambda r, s: (sample_lazy(r, s), update_lazy(r, s)))
+    timed("update_lazy", update_lazy)
+    timed("sample_lazy", sample_lazy)
+    if os.environ.get("TS_PER_BENCH_SHORT"):
+        L.check(lib.ts_segtree_finish_top(tree.data_ptr(), bound, st0), "finish")
+        assert int(err.item()) == 0, int(err.item())
+        return
     for group in (1, 0):
         L.check(lib.ts_tune_set(b"segtree_ranged", group), "tune")
         timed(f"update(ranged={group})", update)

@@ -230,3 +230,114 @@ def test_per_full_size_step_vs_oracle(update_kernel):
         assert np.array_equal(buf.weight._value.cpu().numpy(), ref.weight._value), step
         assert buf._max_prio == ref._max_prio and buf._min_prio == ref._min_prio
     buf.check_errors()
+
+
+@pytest.mark.parametrize("lg,bsz", [(20, 4096), (20, 32), (17, 1000), (13, 300), (14, 9000),
+                                    (12, 64), (21, 512)])
+def test_lazy_top_update_then_sample(lg, bsz):
+    """ts_per_update_lazy stops at its range roots; ts_per_sample_lazy rebuilds the levels above
+    them in shared memory (pairwise order, the reference's bits) and writes them back.  Through
+    the raw C-ABI, chained steps: sampled indices and weights bit-equal to the eager pair
+    (ts_per_update + ts_per_sample) and to the oracle; the heap in memory is complete after every
+    sample and after ts_segtree_finish_top; sizes inside (2^13..2^20) and outside the regime."""
+    from tianshou_fork_b200 import _lib as L
+    lib = L.lib()
+    size = bound = 1 << lg
+    rng = np.random.default_rng(lg * 7 + bsz)
+    leaves = (np.abs(rng.standard_normal(size)) + 1e-7) ** 0.6
+    ref = orc.PER(size, 0.6, 0.4)
+    ref.weight[np.arange(size)] = leaves
+    trees = []
+    for _ in range(2):
+        t = {"tree": torch.from_numpy(ref.weight._value.copy()).cuda(),
+             "stamp": torch.zeros(size, dtype=torch.int32, device="cuda"),
+             "counter": torch.zeros(4, dtype=torch.int32, device="cuda"),
+             "err": torch.zeros(1, dtype=torch.int32, device="cuda"),
+             "prio": torch.ones(2, dtype=torch.float64, device="cuda")}
+        trees.append(t)
+    lazy, eager = trees
+    n_top = lib.ts_segtree_lazy_top_nodes(bound)
+    assert (n_top > 0) == (12 < lg <= 20)
+    st = L.stream()
+    for step in range(5):
+        idx = rng.integers(0, size, bsz)
+        idx[: bsz // 20] = idx[bsz // 20: 2 * (bsz // 20)]
+        td = rng.standard_normal(bsz).astype(np.float32)
+        u = rng.random(bsz)
+        g_idx, g_td, g_u = (torch.from_numpy(a).cuda() for a in (idx, td, u))
+        outs = []
+        for t, upd, smp in ((lazy, lib.ts_per_update_lazy, None), (eager, lib.ts_per_update, None)):
+            L.check(upd(t["tree"].data_ptr(), size, bound, g_idx.data_ptr(), g_td.data_ptr(),
+                        L.TS_F32, bsz, 0.6, t["prio"].data_ptr(), t["stamp"].data_ptr(),
+                        t["counter"].data_ptr(), t["err"].data_ptr(), st), "update")
+        if n_top and step == 0:
+            # everything from the range roots down is final, the levels above are not touched
+            assert torch.equal(lazy["tree"][n_top:], eager["tree"][n_top:])
+            assert not torch.equal(lazy["tree"][1:n_top], eager["tree"][1:n_top])
+        if step == 2:  # another reader between the calls: finish explicitly
+            L.check(lib.ts_segtree_finish_top(lazy["tree"].data_ptr(), bound, st), "finish")
+            assert torch.equal(lazy["tree"][1:], eager["tree"][1:])
+        for t, lazy_call in ((lazy, True), (eager, False)):
+            o_idx = torch.empty(bsz, dtype=torch.int64, device="cuda")
+            o_w = torch.empty(bsz, dtype=torch.float64, device="cuda")
+            if lazy_call:
+                L.check(lib.ts_per_sample_lazy(t["tree"].data_ptr(), bound, g_u.data_ptr(), bsz,
+                                               t["prio"].data_ptr(), 0.4, 1, o_idx.data_ptr(),
+                                               o_w.data_ptr(), t["err"].data_ptr(), st), "sample")
+            else:
+                L.check(lib.ts_per_sample(t["tree"].data_ptr(), bound, g_u.data_ptr(), bsz,
+                                          t["prio"].data_ptr(), 0.4, 1, o_idx.data_ptr(),
+                                          o_w.data_ptr(), None, t["err"].data_ptr(), st), "sample")
+            outs.append((o_idx, o_w))
+        assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1]), step
+        assert torch.equal(lazy["tree"][1:], eager["tree"][1:]), step  # written back: complete
+        assert torch.equal(lazy["prio"], eager["prio"])
+        # the oracle on the same leaves (re-anchored: the f32 power differs across libms)
+        ref.update_weight(idx, td)
+        touched = np.unique(idx)
+        ref.weight[touched] = eager["tree"][bound + torch.from_numpy(touched).cuda()].cpu().numpy()
+        assert np.array_equal(eager["tree"].cpu().numpy()[1:], ref.weight._value[1:]), step
+        assert np.array_equal(outs[0][0].cpu().numpy(), ref.sample_indices(u)), step
+    assert int(lazy["err"].item()) == 0
+
+
+def test_lazy_top_is_invisible_through_the_classes():
+    """PrioritizedVectorReplayBuffer.update_weight leaves the top to the next reader: reduce(),
+    tree[...], get_prefix_sum_idx and `weight._value` all see a complete tree."""
+    import tianshou_fork_b200 as ts
+    size = 1 << 15
+    rng = np.random.default_rng(4)
+    leaves = (np.abs(rng.standard_normal(size)) + 1e-7) ** 0.6
+    ref = orc.PER(size, 0.6, 0.4)
+    ref.weight[np.arange(size)] = leaves
+    buf = ts.PrioritizedVectorReplayBuffer(size, 8, alpha=0.6, beta=0.4)
+    buf.weight[torch.arange(size, device="cuda")] = torch.from_numpy(leaves).cuda()
+    buf._lengths[:] = size // 8
+    for reader in ("reduce", "value", "prefix", "setitem", "sample"):
+        idx = rng.integers(0, size, 500)
+        td = rng.standard_normal(500)  # f64 td: leaves bit-equal to NumPy's f64 power
+        buf.update_weight(idx, td)
+        assert buf.weight._top_stale
+        ref.update_weight(idx, td)
+        touched = torch.from_numpy(np.unique(idx)).cuda()
+        ref.weight[touched.cpu().numpy()] = buf.weight._heap[buf.weight._bound + touched].cpu().numpy()
+        assert buf.weight._top_stale  # reading leaves from the raw heap finishes nothing
+        if reader == "reduce":
+            assert buf.weight.reduce() == ref.weight.reduce()
+            assert buf.weight.reduce(3, size - 5) == ref.weight.reduce(3, size - 5)
+        elif reader == "value":
+            assert np.array_equal(buf.weight._value.cpu().numpy()[1:], ref.weight._value[1:])
+        elif reader == "prefix":
+            v = rng.random(64) * ref.weight.reduce()
+            assert np.array_equal(buf.weight.get_prefix_sum_idx(v.copy()),
+                                  ref.weight.get_prefix_sum_idx(v.copy()))
+        elif reader == "setitem":
+            buf.weight[np.array([5, 9])] = np.array([0.25, 4.0])
+            ref.weight[np.array([5, 9])] = np.array([0.25, 4.0])
+            assert np.array_equal(buf.weight._value.cpu().numpy()[1:], ref.weight._value[1:])
+        else:
+            u = rng.random(256)
+            got = buf.sample_with_uniforms(torch.from_numpy(u).cuda())
+            assert np.array_equal(got.cpu().numpy(), ref.sample_indices(u))
+            assert not buf.weight._top_stale
+            assert np.array_equal(buf.weight._heap.cpu().numpy()[1:], ref.weight._value[1:])

@@ -66,6 +66,11 @@ SIGNATURES = {
     "ts_per_weight": (_i32, [_vp, _i64, _vp, _i64, _vp, _f64, _i32, _vp, _vp, _vp]),
     "ts_per_update": (_i32, [_vp, _i64, _i64, _vp, _vp, _i32, _i64, _f64, _vp, _vp, _vp, _vp,
                              _vp]),
+    "ts_segtree_lazy_top_nodes": (_i32, [_i64]),
+    "ts_per_update_lazy": (_i32, [_vp, _i64, _i64, _vp, _vp, _i32, _i64, _f64, _vp, _vp, _vp, _vp,
+                                  _vp]),
+    "ts_per_sample_lazy": (_i32, [_vp, _i64, _vp, _i64, _vp, _f64, _i32, _vp, _vp, _vp, _vp]),
+    "ts_segtree_finish_top": (_i32, [_vp, _i64, _vp]),
     "ts_per_init_weight": (_i32, [_vp, _i64, _i64, _vp, _i64, _f64, _vp, _i32, _vp, _vp, _vp,
                                   _vp]),
     "ts_ppo_loss_workspace_bytes": (_sz, [_i64]),

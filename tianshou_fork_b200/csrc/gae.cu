@@ -274,11 +274,22 @@ gae_rows_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
 // local advantages independently through gl^1..gl^8.
 struct GlPow { double p[VEC + 1]; };  // p[j] = (gamma*lambda)^j, kernel parameter
 
+// A thread's eight consecutive f32 values are two 16-byte chunks, 32 bytes apart from the next
+// thread's: issued in program order, the eight threads of a quarter warp would hit every bank
+// group twice (a 2-way conflict on every 128-bit access: 2.07 M conflicts per C2 launch in
+// profiles/r01k_gae_ncu.md).  Threads 4..7 of every eight therefore take their SECOND chunk
+// first: the quarter warp then covers chunks {0, 2, 4, 6, 9, 11, 13, 15} -- all eight bank
+// groups once -- and the two halves are swapped back in registers.
+#ifndef TS_SMEM_SWZ
+#define TS_SMEM_SWZ 1  // 0: both chunks in program order (A/B switch, profiles/r02_gae.md)
+#endif
 template <typename T>
 __device__ __forceinline__ void smem_ld8(const T* p, T (&v)[VEC]) {
     if constexpr (sizeof(T) == 4) {
-        const float4 a = *reinterpret_cast<const float4*>(p);
-        const float4 b = *reinterpret_cast<const float4*>(p + 4);
+        const int sel = TS_SMEM_SWZ ? (threadIdx.x >> 2) & 1 : 0;
+        const float4* q = reinterpret_cast<const float4*>(p);
+        const float4 x = q[sel], y = q[sel ^ 1];
+        const float4 a = sel ? y : x, b = sel ? x : y;
         v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
         v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
     } else {
@@ -292,10 +303,12 @@ __device__ __forceinline__ void smem_ld8(const T* p, T (&v)[VEC]) {
 template <typename T>
 __device__ __forceinline__ void smem_st8(T* p, const double (&v)[VEC]) {
     if constexpr (sizeof(T) == 4) {
-        *reinterpret_cast<float4*>(p) =
-            make_float4((float)v[0], (float)v[1], (float)v[2], (float)v[3]);
-        *reinterpret_cast<float4*>(p + 4) =
-            make_float4((float)v[4], (float)v[5], (float)v[6], (float)v[7]);
+        const int sel = TS_SMEM_SWZ ? (threadIdx.x >> 2) & 1 : 0;
+        const float4 a = make_float4((float)v[0], (float)v[1], (float)v[2], (float)v[3]);
+        const float4 b = make_float4((float)v[4], (float)v[5], (float)v[6], (float)v[7]);
+        float4* q = reinterpret_cast<float4*>(p);
+        q[sel] = sel ? b : a;
+        q[sel ^ 1] = sel ? a : b;
     } else {
 #pragma unroll
         for (int k = 0; k < VEC / 2; ++k)

@@ -582,7 +582,10 @@ __device__ __noinline__ double per_priority_cold(const ValueSrc& vs, int64_t j) 
 
 // PERF32: vs.mode == VM_PER_F32, the replay step's update_weight (prio.py:78-89 on a f32 td_error);
 // every mode test folds away.  The other modes share the generic instantiation.
-template <bool PERF32>
+// DEFER: stop at the range roots.  The levels above them (heap indices < gridDim.x) are left
+// stale for the consumer to rebuild (per_weight_cluster_kernel<.., REBUILD> in shared memory,
+// or segtree_finish_top_kernel): no last-CTA ticket, no fence, no serial tail.
+template <bool PERF32, bool DEFER = false>
 __global__ void __launch_bounds__(RANGE_NT)
 segtree_update_ranged(double* __restrict__ tree, int64_t size, int lg_bound, int lg_range,
                       const int64_t* __restrict__ index, ValueSrc vs, int64_t M,
@@ -787,6 +790,7 @@ segtree_update_ranged(double* __restrict__ tree, int64_t size, int lg_bound, int
         }
         __syncwarp();
     }
+    if (DEFER) return;  // kernel completion publishes the range roots; the top is the reader's job
 
     // ---- warp 0 of every CTA: the one that arrives last rebuilds the levels above the ranges -------
     int last = 0;
@@ -916,7 +920,7 @@ int32_t publish_launch(const double* tree, const double* prio, const PublishInfo
 int32_t update_impl(double* tree, int64_t size, int64_t bound, const int64_t* index,
                     ValueSrc vs, int64_t M, uint32_t* stamp, uint32_t* counter,
                     int32_t* err_flag, cudaStream_t st,
-                    PublishInfo pub = PublishInfo{nullptr, nullptr, 1, 0}) {
+                    PublishInfo pub = PublishInfo{nullptr, nullptr, 1, 0}, bool defer_top = false) {
     if (M < 0 || size <= 0 || bound < size || (bound & (bound - 1)) != 0) return TS_ERR_BAD_ARG;
     if (M >= 0x7fffffffLL || bound > (1LL << 30)) return TS_ERR_BAD_ARG;
     if (M == 0) return pub.state != nullptr && tree ? publish_launch(tree, vs.prio, pub, st) : TS_OK;
@@ -939,6 +943,12 @@ int32_t update_impl(double* tree, int64_t size, int64_t bound, const int64_t* in
             if (e == cudaSuccess)
                 e = cudaFuncSetAttribute(segtree_update_ranged<false>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+            if (e == cudaSuccess)
+                e = cudaFuncSetAttribute(segtree_update_ranged<true, true>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+            if (e == cudaSuccess)
+                e = cudaFuncSetAttribute(segtree_update_ranged<false, true>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
             if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; return TS_ERR_CUDA; }
             attr_done = true;
         }
@@ -954,6 +964,9 @@ int32_t update_impl(double* tree, int64_t size, int64_t bound, const int64_t* in
         cfg.attrs = attr;
         cfg.numAttrs = g_tune_pdl ? 1 : 0;
         auto kern = vs.mode == VM_PER_F32 ? segtree_update_ranged<true> : segtree_update_ranged<false>;
+        if (defer_top && pub.state == nullptr)
+            kern = vs.mode == VM_PER_F32 ? segtree_update_ranged<true, true>
+                                         : segtree_update_ranged<false, true>;
         cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tree, size, lg, lg_range, index, vs, M,
                                            counter, err_flag, pub, prio_c);
         if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; (void)cudaGetLastError(); return TS_ERR_CUDA; }
@@ -1019,6 +1032,64 @@ __global__ void segtree_reduce_kernel(const double* __restrict__ tree, int64_t s
 // bit-exactly instead of being fetched -- 20 dependent loads become 11 shared + 3 global.
 // ============================================================================================
 constexpr int kTopCached = 4096;  // heap indices [0, 4096) = depths 0..11, 32 KB per CTA
+
+// warp 0: the levels above the n <= 128 nodes s_top[n .. 2n), rebuilt in shared memory in the
+// tree's own pairwise order (node = left + right, segtree.py:104) and, with `tree_out`, written
+// back to the heap in global memory.
+__device__ __forceinline__ void warp_top_smem(double* s_top, int n, int lane, double* tree_out) {
+    const int c = n >= 32 ? n / 32 : 1;  // nodes per lane: 1, 2 or 4
+    double v[4];
+    const bool mine = lane * c < n;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] = (k < c && mine) ? s_top[n + lane * c + k] : 0.0;
+    int node = n + lane * c;
+#pragma unroll
+    for (int w = 4; w > 1; w >>= 1) {
+        if (w > c) continue;
+        node >>= 1;
+#pragma unroll
+        for (int k = 0; k < w / 2; ++k) {
+            v[k] = __dadd_rn(v[2 * k], v[2 * k + 1]);
+            if (mine) {
+                s_top[node + k] = v[k];
+                if (tree_out != nullptr) tree_out[node + k] = v[k];
+            }
+        }
+    }
+    const int live = n < 32 ? n : 32;
+    double x = v[0];
+    for (int d = 1; d < live; d <<= 1) {
+        const double r = __shfl_down_sync(0xffffffffu, x, d);
+        x = __dadd_rn(x, r);
+        node >>= 1;
+        if ((lane & (2 * d - 1)) == 0 && lane < live) {
+            s_top[node] = x;
+            if (tree_out != nullptr) tree_out[node] = x;
+        }
+    }
+}
+
+// Levels above the `n` range roots, for readers of a lazily updated tree other than the sampling
+// kernel (reduce, pickling, tests): one warp.
+__global__ void __launch_bounds__(32)
+segtree_finish_top_kernel(double* __restrict__ tree, int n) {
+    __shared__ double s_top[256];
+    const int lane = threadIdx.x;
+    for (int i = lane; i < n; i += 32) s_top[n + i] = __ldcg(tree + n + i);
+    __syncwarp();
+    warp_top_smem(s_top, n, lane, tree);
+}
+
+// number of range roots of the ranged update for a tree of 2^lg leaves (0: not in that regime)
+inline int lazy_top_nodes(int64_t bound) {
+    if (bound <= kDenseBound || bound > (1LL << (kRangeLgMax + 7))) return 0;
+    int lg = 0;
+    while ((1LL << lg) < bound) ++lg;
+    int lg_range = lg - 7;
+    if (lg_range > kRangeLgMax) lg_range = kRangeLgMax;
+    if (lg_range < kRangeLgMin) lg_range = kRangeLgMin;
+    return (int)(bound >> lg_range);
+}
 
 template <int NT>
 __device__ __forceinline__ int stage_top(const double* __restrict__ tree, int64_t bound,
@@ -1178,7 +1249,7 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
                           const double* __restrict__ u, int64_t M,
                           const double* __restrict__ prio, double beta, int weight_norm,
                           int64_t* __restrict__ idx, double* __restrict__ weight,
-                          int32_t* __restrict__ err_flag, ShardInfo sh) {
+                          int32_t* __restrict__ err_flag, ShardInfo sh, int rebuild_n) {
     __shared__ double s_top[SAMPLE ? kTopCached : 2];
     __shared__ double s_gtop[2 * kMaxShards];  // heap of the levels above the shard roots
     __shared__ double s_warp[NT / 32];
@@ -1224,7 +1295,35 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
     // the first query's draw is fetched while the top of the tree is being staged
     const double u_first = SAMPLE && j0 < M ? __ldg(u + j0) : 0.0;
     if (SAMPLE) {
-        cached = stage_top<NT>(tree, bound, s_top, tid);
+        if (rebuild_n > 0) {
+            // lazily updated tree (ts_per_update_lazy): the levels above the rebuild_n range roots
+            // are stale in memory.  Warp 0 fetches the roots itself and rebuilds those levels in
+            // shared memory (bit-identical to what the eager update writes; cluster rank 0
+            // writes them back) WHILE the other warps stage the levels below: one barrier.
+            const int n = rebuild_n;
+            cached = (int)(2 * bound < kTopCached ? 2 * bound : kTopCached);
+            if (tid < 32) {
+                double r[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    r[q] = tid + 32 * q < n ? __ldcg(tree + n + tid + 32 * q) : 0.0;
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (tid + 32 * q < n) s_top[n + tid + 32 * q] = r[q];
+                __syncwarp();
+                warp_top_smem(s_top, n, tid,
+                              cluster_ctarank() == 0 ? const_cast<double*>(tree) : nullptr);
+            } else {
+                for (int i = 2 * n + (tid - 32) * 2; i < cached; i += (NT - 32) * 2) {
+                    const double2 t = __ldcg(reinterpret_cast<const double2*>(tree + i));
+                    s_top[i] = t.x;
+                    s_top[i + 1] = t.y;
+                }
+            }
+            __syncthreads();
+        } else {
+            cached = stage_top<NT>(tree, bound, s_top, tid);
+        }
         total = sharded ? s_gtop[1] : s_top[1];
     }
     double wmax = 0.0, w_first = 0.0;
@@ -1327,7 +1426,8 @@ template <bool SAMPLE, int SHARD>
 static int32_t launch_per_cluster_mode(const double* tree, int64_t bound, int lg, const double* u,
                                        int64_t M, const double* prio, double beta,
                                        int weight_norm, int64_t* idx, double* weight,
-                                       int32_t* err_flag, ShardInfo sh, cudaStream_t st) {
+                                       int32_t* err_flag, ShardInfo sh, cudaStream_t st,
+                                       int rebuild_n = 0) {
     // 16 CTAs x 256 threads spreads a large batch over twice the SMs (7.4 vs 8.7 us at 4096
     // queries); it is an opt-in cluster size, so it is used only where the device can place it.
     static int wide_ok = -1;  // per instantiation
@@ -1367,7 +1467,7 @@ static int32_t launch_per_cluster_mode(const double* tree, int64_t bound, int lg
     cfg.attrs = attr;
     cfg.numAttrs = g_tune_pdl ? 2 : 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tree, bound, lg, u, M, prio, beta, weight_norm,
-                                       idx, weight, err_flag, sh);
+                                       idx, weight, err_flag, sh, rebuild_n);
     if (e != cudaSuccess) { g_last_cuda_error = (int32_t)e; (void)cudaGetLastError(); return TS_ERR_CUDA; }
     return check_launch();
 }
@@ -1376,7 +1476,7 @@ template <bool SAMPLE>
 static int32_t launch_per_cluster(const double* tree, int64_t bound, int lg, const double* u,
                                   int64_t M, const double* prio, double beta, int weight_norm,
                                   int64_t* idx, double* weight, int32_t* err_flag,
-                                  ShardInfo sh, cudaStream_t st) {
+                                  ShardInfo sh, cudaStream_t st, int rebuild_n = 0) {
     if (sh.slots != nullptr)
         return launch_per_cluster_mode<SAMPLE, 2>(tree, bound, lg, u, M, prio, beta, weight_norm,
                                                   idx, weight, err_flag, sh, st);
@@ -1384,7 +1484,7 @@ static int32_t launch_per_cluster(const double* tree, int64_t bound, int lg, con
         return launch_per_cluster_mode<SAMPLE, 1>(tree, bound, lg, u, M, prio, beta, weight_norm,
                                                   idx, weight, err_flag, sh, st);
     return launch_per_cluster_mode<SAMPLE, 0>(tree, bound, lg, u, M, prio, beta, weight_norm, idx,
-                                              weight, err_flag, sh, st);
+                                              weight, err_flag, sh, st, rebuild_n);
 }
 
 extern "C" int32_t ts_segtree_update(double* tree, int64_t size, int64_t bound,
@@ -1465,6 +1565,49 @@ extern "C" int32_t ts_per_update(double* tree, int64_t size, int64_t bound, cons
     ValueSrc vs{td, 1, alpha, prio, td_dtype == TS_F64 ? VM_PER_F64 : VM_PER_F32};
     return update_impl(tree, size, bound, idx, vs, M, stamp, counter, err_flag,
                        (cudaStream_t)stream);
+}
+
+// ---- lazily finished tree: update stops at the range roots, the sampler rebuilds the top -------
+extern "C" int32_t ts_segtree_lazy_top_nodes(int64_t bound) {
+    if (bound <= 0 || (bound & (bound - 1)) != 0) return 0;
+    return g_tune_segtree_ranged != 0 ? lazy_top_nodes(bound) : 0;
+}
+
+extern "C" int32_t ts_per_update_lazy(double* tree, int64_t size, int64_t bound,
+                                      const int64_t* idx, const void* td, int32_t td_dtype,
+                                      int64_t M, double alpha, double* prio, uint32_t* stamp,
+                                      uint32_t* counter, int32_t* err_flag, ts_stream_t stream) {
+    if (!td || !prio) return TS_ERR_BAD_ARG;
+    if (td_dtype != TS_F32 && td_dtype != TS_F64) return TS_ERR_BAD_ARG;
+    ValueSrc vs{td, 1, alpha, prio, td_dtype == TS_F64 ? VM_PER_F64 : VM_PER_F32};
+    return update_impl(tree, size, bound, idx, vs, M, stamp, counter, err_flag,
+                       (cudaStream_t)stream, PublishInfo{nullptr, nullptr, 1, 0}, true);
+}
+
+extern "C" int32_t ts_per_sample_lazy(double* tree, int64_t bound, const double* u, int64_t M,
+                                      const double* prio, double beta, int32_t weight_norm,
+                                      int64_t* idx, double* weight, int32_t* err_flag,
+                                      ts_stream_t stream) {
+    if (M < 0 || bound <= 0) return TS_ERR_BAD_ARG;
+    if (!tree || !prio || (bound & (bound - 1)) != 0) return TS_ERR_BAD_ARG;
+    if (!aligned(tree, 16)) return TS_ERR_ALIGN;
+    const int n = ts_segtree_lazy_top_nodes(bound);
+    if (M == 0) {  // nothing to draw: still leave a finished tree behind
+        if (n > 0) segtree_finish_top_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(tree, n);
+        return check_launch();
+    }
+    if (!u || !idx || !weight || !err_flag) return TS_ERR_BAD_ARG;
+    return launch_per_cluster<true>(tree, bound, ilog2(bound), u, M, prio, beta, weight_norm, idx,
+                                    weight, err_flag,
+                                    ShardInfo{nullptr, 1, 0, nullptr, nullptr, nullptr, nullptr},
+                                    (cudaStream_t)stream, n);
+}
+
+extern "C" int32_t ts_segtree_finish_top(double* tree, int64_t bound, ts_stream_t stream) {
+    if (!tree || bound <= 0 || (bound & (bound - 1)) != 0) return TS_ERR_BAD_ARG;
+    const int n = ts_segtree_lazy_top_nodes(bound);
+    if (n > 0) segtree_finish_top_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(tree, n);
+    return check_launch();
 }
 
 extern "C" int32_t ts_per_init_weight(double* tree, int64_t size, int64_t bound,

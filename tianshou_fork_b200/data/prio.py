@@ -112,10 +112,12 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         idx = torch.empty(m, dtype=torch.int64, device=self.device)
         w = torch.empty(m, dtype=torch.float64, device=self.device)
         t = self.weight
-        L.check(L.lib().ts_per_sample(
-            L.ptr(t._value), t._bound, L.ptr(u), m, L.ptr(self._prio), float(self._beta),
-            int(self._weight_norm), L.ptr(idx), L.ptr(w), L.ptr(self._per_scratch),
-            L.ptr(t._err), L.stream()), "ts_per_sample")
+        # rebuilds the levels update_weight left stale, in shared memory, and writes them back
+        L.check(L.lib().ts_per_sample_lazy(
+            t._heap.data_ptr(), t._bound, L.ptr(u), m, L.ptr(self._prio), float(self._beta),
+            int(self._weight_norm), L.ptr(idx), L.ptr(w), L.ptr(t._err), L.stream()),
+            "ts_per_sample_lazy")
+        t._top_stale = False
         self._cached_weight = (idx, w)
         return idx
 
@@ -154,10 +156,14 @@ class PrioritizedReplayBuffer(ReplayBuffer):
             return
         self._cached_weight = None
         t = self.weight
-        L.check(L.lib().ts_per_update(
-            L.ptr(t._value), t._size, t._bound, L.ptr(idx), L.ptr(td), L.dtype_code(td),
+        # stops at the update kernel's range roots; the next sampling launch (or any reader of
+        # `weight._value`) finishes the levels above them
+        heap = t._value  # (a top left stale by a graph replay is finished before it is built on)
+        L.check(L.lib().ts_per_update_lazy(
+            heap.data_ptr(), t._size, t._bound, L.ptr(idx), L.ptr(td), L.dtype_code(td),
             idx.numel(), float(self._alpha), L.ptr(self._prio), L.ptr(t._stamp),
-            L.ptr(t._counter), L.ptr(t._err), L.stream()), "ts_per_update")
+            L.ptr(t._counter), L.ptr(t._err), L.stream()), "ts_per_update_lazy")
+        t._top_stale = True
         self._prio_f32 = td.dtype == torch.float32
 
     def __getitem__(self, index: Union[slice, IndexLike]) -> Batch:

@@ -40,7 +40,11 @@ class SegmentTree:
         self._bound = bound
         self.device = torch.device(device if device is not None else
                                    f"cuda:{torch.cuda.current_device()}")
-        self._value = torch.zeros(bound * 2, dtype=torch.float64, device=self.device)
+        self._heap = torch.zeros(bound * 2, dtype=torch.float64, device=self.device)
+        # Prioritized buffers update this tree lazily (ts_per_update_lazy): the levels above the
+        # update kernel's range roots may be stale until the next sampling launch rebuilds them.
+        # Every other reader goes through the `_value` property, which finishes the top first.
+        self._top_stale = False
         # scratch of the update kernel (see include/ts_b200.h): all-zero between calls
         self._stamp = torch.zeros(max(size, 1), dtype=torch.int32, device=self.device)
         self._counter = torch.zeros(4, dtype=torch.int32, device=self.device)
@@ -50,6 +54,15 @@ class SegmentTree:
 
     def __len__(self) -> int:
         return self._size
+
+    @property
+    def _value(self) -> torch.Tensor:
+        """The f64 heap of ``2 * bound`` nodes (segtree.py:27), complete."""
+        if self._top_stale:
+            self._top_stale = False
+            L.check(L.lib().ts_segtree_finish_top(self._heap.data_ptr(), self._bound,
+                                                  L.stream()), "ts_segtree_finish_top")
+        return self._heap
 
     # ---- helpers ---------------------------------------------------------------------------
     def _dev_index(self, index: Index) -> torch.Tensor:

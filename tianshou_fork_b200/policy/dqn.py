@@ -228,6 +228,8 @@ class _GraphedUpdate:
                                                  p.optim, self.dev)
         self._draw()
         graph.replay()
+        if self.per:  # the replayed update_weight left the top of the sum tree to the next reader
+            buf.weight._top_stale = True
         p._iter += 1
         if p.lr_scheduler is not None:
             p.lr_scheduler.step()
