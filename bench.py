@@ -476,6 +476,11 @@ def run_b200(args):
     updates = None
     if rank == 0 and world == 1 and not args.skip_updates and not args.skip_e2e:
         updates = run_updates()
+    elif world > 1 and not args.skip_updates:
+        # the data-parallel learner (all ranks take part: one NCCL all-reduce per minibatch)
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        import bench_dp
+        updates = bench_dp.run_dp_updates(torch, dist, dev, rank, world, max_over_ranks)
 
     if rank == 0:
         line = {
@@ -687,240 +692,12 @@ def run_updates():
 
 
 def run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
-    """BASELINE.json configs[3] (1 GPU) / configs[4] (N GPUs): one 2^20-leaf shard per GPU.
-
-    N == 1: step = ts_per_sample + ts_per_update, 8 steps per CUDA graph.
-    N  > 1: the reference's ONE global tree of N * 2^20 leaves, sharded; a
-    step samples the GLOBAL batch of 4096 from identical uniforms on every rank
-    (ts_per_sample_sharded: each rank descends only the queries it owns), MAX-all-reduces the
-    weight maximum, normalises, updates its own leaves and all-gathers the 24-byte
-    {root, max, min} records.  The batch is global, so this leg is strong scaling."""
-    rng = np.random.default_rng(100 + rank)
-    size = bound = PER_LEAVES
-    tree = torch.zeros(2 * bound, dtype=torch.float64, device=dev)
-    stamp = torch.zeros(size, dtype=torch.int32, device=dev)
-    counter = torch.zeros(4, dtype=torch.int32, device=dev)
-    err = torch.zeros(1, dtype=torch.int32, device=dev)
-    prio = torch.ones(2, dtype=torch.float64, device=dev)
-    leaves = torch.from_numpy((np.abs(rng.standard_normal(size)) + 1e-7) ** PER_ALPHA).to(dev)
-    all_idx = torch.arange(size, device=dev)
-    st = torch.cuda.current_stream().cuda_stream
-    L.check(lib.ts_segtree_update(tree.data_ptr(), size, bound, all_idx.data_ptr(),
-                                  leaves.data_ptr(), L.TS_F64, 1, size, stamp.data_ptr(),
-                                  counter.data_ptr(), err.data_ptr(), st), "ts_segtree_update")
-    R = 8  # distinct (uniforms, td) sets
-    shared = np.random.default_rng(2)  # the same draws on every rank
-    u = torch.from_numpy(shared.random((R, PER_BATCH))).to(dev)
-    td = torch.from_numpy(shared.standard_normal((R, PER_BATCH)).astype(np.float32)).to(dev)
-    idx = torch.empty(R, PER_BATCH, dtype=torch.int64, device=dev)
-    w = torch.empty(R, PER_BATCH, dtype=torch.float64, device=dev)
-    peak, _ = measured_peaks()
-
-    if world == 1:
-        def step(r, s):
-            L.check(lib.ts_per_sample(tree.data_ptr(), bound, u[r].data_ptr(), PER_BATCH,
-                                      prio.data_ptr(), PER_BETA, 1, idx[r].data_ptr(),
-                                      w[r].data_ptr(), None, err.data_ptr(), s), "ts_per_sample")
-            L.check(lib.ts_per_update(tree.data_ptr(), size, bound, idx[r].data_ptr(),
-                                      td[r].data_ptr(), L.TS_F32, PER_BATCH, PER_ALPHA,
-                                      prio.data_ptr(), stamp.data_ptr(), counter.data_ptr(),
-                                      err.data_ptr(), s), "ts_per_update")
-
-        side = torch.cuda.Stream(dev)
-        with torch.cuda.stream(side):
-            for r in range(R):
-                step(r, side.cuda_stream)
-        side.synchronize()
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph, stream=side):
-            for r in range(R):
-                step(r, side.cuda_stream)
-        replays = 50
-        for _ in range(5):
-            graph.replay()
-        barrier()
-        stream = torch.cuda.current_stream()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for _ in range(replays):
-            graph.replay()
-        e1.record(stream)
-        barrier()
-        ms = e0.elapsed_time(e1)
-        steps = replays * R
-        launches_per_step, scaling = 2, "n/a (1 GPU)"
-        how = "8 steps per CUDA graph"
-    else:
-        # preferred: the exchange inside the kernels over NVLink peer memory (CUDA-graph replay)
-        exchange = "p2p"
-        try:
-            import torch.distributed._symmetric_memory as symm_mem
-            slots = symm_mem.empty(12 * world, dtype=torch.float64, device=dev)
-            slots.zero_()
-            hdl = symm_mem.rendezvous(slots, dist.group.WORLD)
-            peers = int(hdl.buffer_ptrs_dev)
-            state = torch.zeros(2, dtype=torch.int64, device=dev)
-            torch.cuda.synchronize()
-            dist.barrier()
-        except Exception as e:  # no peer access: NCCL collectives between the kernels
-            exchange = f"nccl ({type(e).__name__})"
-        if exchange == "p2p":
-            def step(r, s):
-                L.check(lib.ts_per_sample_p2p(
-                    tree.data_ptr(), bound, u[r].data_ptr(), PER_BATCH, slots.data_ptr(), peers,
-                    state.data_ptr(), world, rank, prio.data_ptr(), PER_BETA, 1,
-                    idx[r].data_ptr(), w[r].data_ptr(), err.data_ptr(), s), "ts_per_sample_p2p")
-                L.check(lib.ts_per_update_publish(
-                    tree.data_ptr(), size, bound, idx[r].data_ptr(), td[r].data_ptr(), L.TS_F32,
-                    PER_BATCH, PER_ALPHA, prio.data_ptr(), stamp.data_ptr(), counter.data_ptr(),
-                    err.data_ptr(), state.data_ptr(), peers, world, rank, s),
-                    "ts_per_update_publish")
-
-            side = torch.cuda.Stream(dev)
-            with torch.cuda.stream(side):
-                L.check(lib.ts_per_publish(tree.data_ptr(), prio.data_ptr(), state.data_ptr(),
-                                           peers, world, rank, side.cuda_stream), "publish")
-                for r in range(R):
-                    step(r, side.cuda_stream)
-            side.synchronize()
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph, stream=side):
-                for r in range(R):
-                    step(r, side.cuda_stream)
-            replays = 50
-            for _ in range(5):
-                graph.replay()
-            barrier()
-            stream = torch.cuda.current_stream()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(stream)
-            for _ in range(replays):
-                graph.replay()
-            e1.record(stream)
-            barrier()
-            ms = e0.elapsed_time(e1)
-            steps = replays * R
-            launches_per_step = 2
-            how = ("8 steps per CUDA graph; shard records and the weight maximum are exchanged "
-                   "INSIDE the kernels over NVLink peer memory (no NCCL call on the step)")
-        else:
-            mine3 = torch.zeros(3, dtype=torch.float64, device=dev)
-            roots3 = torch.zeros(world, 3, dtype=torch.float64, device=dev)
-            wmax = torch.zeros(1, dtype=torch.float64, device=dev)
-
-            def sync_roots():
-                mine3[0:1].copy_(tree[1:2])
-                mine3[1:3].copy_(prio)
-                dist.all_gather_into_tensor(roots3.view(-1), mine3)
-                prio[0:1].copy_(roots3[:, 1].amax(0, keepdim=True))
-                prio[1:2].copy_(roots3[:, 2].amin(0, keepdim=True))
-
-            def step(r):
-                s = torch.cuda.current_stream().cuda_stream
-                L.check(lib.ts_per_sample_sharded(
-                    tree.data_ptr(), bound, u[r].data_ptr(), PER_BATCH, roots3.data_ptr(), world,
-                    rank, prio.data_ptr(), PER_BETA, 1, idx[r].data_ptr(), w[r].data_ptr(),
-                    wmax.data_ptr(), err.data_ptr(), s), "ts_per_sample_sharded")
-                dist.all_reduce(wmax, op=dist.ReduceOp.MAX)
-                L.check(lib.ts_per_normalize(w[r].data_ptr(), PER_BATCH, wmax.data_ptr(), s),
-                        "ts_per_normalize")
-                L.check(lib.ts_per_update(tree.data_ptr(), size, bound, idx[r].data_ptr(),
-                                          td[r].data_ptr(), L.TS_F32, PER_BATCH, PER_ALPHA,
-                                          prio.data_ptr(), stamp.data_ptr(), counter.data_ptr(),
-                                          err.data_ptr(), s), "ts_per_update")
-                sync_roots()
-
-            sync_roots()
-            for i in range(16):
-                step(i % R)
-            barrier()
-            stream = torch.cuda.current_stream()
-            steps = 400
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(stream)
-            for i in range(steps):
-                step(i % R)
-            e1.record(stream)
-            barrier()
-            ms = e0.elapsed_time(e1)
-            launches_per_step = 3
-            how = (f"exchange {exchange}: eager launches; 2 NCCL collectives per step (MAX "
-                   "all-reduce 8 B, all-gather 24 B)")
-        owned = (idx >= 0).sum().to(torch.float64)
-        dist.all_reduce(owned)
-        assert int(owned.item()) == R * PER_BATCH, "every query must be owned by exactly one rank"
-        scaling = "strong (global batch 4096 over all shards)"
-    ms = max_over_ranks(ms)
-    assert int(err.item()) == 0, "PER range flag raised"
-    us = ms * 1e3 / steps
-    value = PER_BATCH * steps / (ms * 1e-3)  # global samples/s (the batch is global for N > 1)
-    achieved = PER_BATCH * PER_ALG_BYTES_PER_SAMPLE / (us * 1e-6) / 1e9
-    e2e = per_e2e(torch, dev) if world == 1 else None
-    return {"metric": "PER samples/s", "value": value, "unit": "samples/s", "us_per_step": us,
-            "e2e": e2e, "scaling": scaling,
-            "workload": f"{world} shard(s) x 2^20-leaf f64 sum tree, global batch 4096, alpha 0.6 "
-                        "beta 0.4; step = sample (descent + IS weights + batch-max norm) + "
-                        "update_weight (|td|+eps, pow, last-writer table in shared memory, "
-                        "per-range rebuild, one launch; programmatic dependent launch on both "
-                        "kernels); " + how,
-            "gpu_launches_per_step": launches_per_step,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak,
-                         "note": "latency-bound: ~10 dependent L2 round trips of ~0.5 us per "
-                                 "step plus launch and barrier latency, not bytes; the tree is "
-                                 "L2-resident"}}
-
-
-def per_e2e(torch, dev):
-    """The PER step through the reference-facing class with HOST buffers: uniforms drawn by
-    np.random on the host (prio.py:61) and copied in, sampled indices and importance weights
-    read back to the host, host td-errors copied in for update_weight -- every step, inside the
-    timed region (wall clock around the loop, one sync at the end: every step already ends in a
-    blocking device-to-host read)."""
-    try:
-        import tianshou_fork_b200 as ts
-        buf = ts.PrioritizedVectorReplayBuffer(PER_LEAVES, 16, alpha=PER_ALPHA, beta=PER_BETA)
-        E = 16
-        for _ in range(2):  # allocate storage; the ring bookkeeping is then declared full
-            buf.add(ts.Batch(obs=np.zeros((E, 1), np.float32), act=np.zeros(E, np.int64),
-                             rew=np.zeros(E), terminated=np.zeros(E, bool),
-                             truncated=np.zeros(E, bool),
-                             obs_next=np.zeros((E, 1), np.float32), info={}))
-        T = PER_LEAVES // E
-        buf._rings[:, 0], buf._rings[:, 1] = 0, T
-        buf._lengths[:] = T
-        buf.last_index[:] = np.arange(E) * T + T - 1
-        buf._version += 1
-        rng = np.random.default_rng(3)
-        buf.update_weight(torch.arange(PER_LEAVES, device=dev),
-                          torch.from_numpy(rng.standard_normal(PER_LEAVES).astype(np.float32)
-                                           ).to(dev))
-        tds = [rng.standard_normal(PER_BATCH).astype(np.float32) for _ in range(8)]
-
-        def step(i):
-            idx = buf.sample_indices(PER_BATCH)            # host uniforms -> device descent
-            w = buf._cached_weight[1]                      # IS weights of the same launch
-            idx_h, w_h = idx.cpu().numpy(), w.cpu().numpy()  # the learner's host copies
-            buf.update_weight(idx_h, tds[i % 8])           # host td-errors -> device tree
-            return idx_h, w_h
-
-        for i in range(20):
-            step(i)
-        torch.cuda.synchronize()
-        steps = 300
-        t0 = time.perf_counter()
-        for i in range(steps):
-            step(i)
-        torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        return {"value": PER_BATCH * steps / dt, "unit": "samples/s",
-                "us_per_step": dt / steps * 1e6,
-                "h2d_bytes_per_step": PER_BATCH * (8 + 8 + 4),
-                "d2h_bytes_per_step": PER_BATCH * (8 + 8),
-                "api": "PrioritizedVectorReplayBuffer.sample_indices + importance weights + "
-                       "update_weight with NumPy arrays in and out"}
-    except Exception as e:  # reported, not fatal
-        return {"error": f"{type(e).__name__}: {e}"}
+    """PER samples/s, the metric's second half: scripts/bench_per.py (strong + weak scaling at
+    N > 1, parity against the oracle's single global tree, e2e through the buffer classes)."""
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import bench_per
+    return bench_per.run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks,
+                             measured_peaks()[0])
 
 
 _RESULT_FD = None

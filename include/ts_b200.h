@@ -321,7 +321,7 @@ int32_t ts_per_update(double* tree, int64_t size, int64_t bound, const int64_t* 
  * step.  Any OTHER reader of the inner nodes between the two calls (ts_segtree_reduce,
  * ts_segtree_prefix_idx, ts_per_sample, a host copy) must call ts_segtree_finish_top first;
  * leaves are always current.  Trees outside the ranged-update regime (<= 4096 or > 2^20 leaves,
- * batches > 16383) are updated completely by ts_per_update_lazy; ts_segtree_lazy_top_nodes
+ * batches > 262144) are updated completely by ts_per_update_lazy; ts_segtree_lazy_top_nodes
  * returns 0 for them and the other two calls then behave like their eager counterparts.
  */
 int32_t ts_segtree_lazy_top_nodes(int64_t bound);

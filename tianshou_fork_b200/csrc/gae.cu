@@ -275,13 +275,15 @@ gae_rows_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
 struct GlPow { double p[VEC + 1]; };  // p[j] = (gamma*lambda)^j, kernel parameter
 
 // A thread's eight consecutive f32 values are two 16-byte chunks, 32 bytes apart from the next
-// thread's: issued in program order, the eight threads of a quarter warp would hit every bank
-// group twice (a 2-way conflict on every 128-bit access: 2.07 M conflicts per C2 launch in
-// profiles/r01k_gae_ncu.md).  Threads 4..7 of every eight therefore take their SECOND chunk
-// first: the quarter warp then covers chunks {0, 2, 4, 6, 9, 11, 13, 15} -- all eight bank
-// groups once -- and the two halves are swapped back in registers.
+// thread's: in program order the eight threads of a quarter warp hit every bank group twice (a
+// 2-way conflict on every 128-bit access: 2.07 M conflicts per C2 launch, profiles/r01k_gae_ncu.md).
+// TS_SMEM_SWZ=1 lets threads 4..7 of every eight take their SECOND chunk first (the quarter warp
+// then covers all eight bank groups once) and swaps the halves back in registers: conflicts drop
+// to 0.80 M, but the selects cost 8 registers (64 -> 72) and 8 % more instructions, and the
+// kernel gets SLOWER -- A/B on one box, twice: 31.82 vs 30.80 us per C2 launch
+// (profiles/r02_gae.md).  The conflicts were never the bound; the switch stays off.
 #ifndef TS_SMEM_SWZ
-#define TS_SMEM_SWZ 1  // 0: both chunks in program order (A/B switch, profiles/r02_gae.md)
+#define TS_SMEM_SWZ 0
 #endif
 template <typename T>
 __device__ __forceinline__ void smem_ld8(const T* p, T (&v)[VEC]) {

@@ -539,6 +539,7 @@ constexpr int RANGE_NT = 1024;
 constexpr int kRangeLgMax = 13;       // 8192 leaves per CTA: 64 KB table
 constexpr int kRangeLgMin = 10;       // at least 8 groups per CTA
 constexpr int kRangeUnroll = 4;       // items per thread whose loads are in flight together
+constexpr int64_t kRangedMaxM = 1 << 18;  // every CTA scans the whole batch: beyond this the bulk path wins
 constexpr int kRangeList = 2048;      // compacted in-range items per pass (more: handled in place)
 
 __device__ __forceinline__ bool carries_f32(int mode) {
@@ -927,7 +928,8 @@ int32_t update_impl(double* tree, int64_t size, int64_t bound, const int64_t* in
     if (!tree || !index || !stamp || !counter || !err_flag) return TS_ERR_BAD_ARG;
 
     if (!aligned(tree, 16) || !aligned(stamp, 16)) return TS_ERR_ALIGN;
-    if (M <= kSmallM && bound > kDenseBound && bound <= (1LL << (kRangeLgMax + 7)) &&
+    // (the ranged kernel's table carries the batch position in 32 bits: no 14-bit limit)
+    if (M <= kRangedMaxM && bound > kDenseBound && bound <= (1LL << (kRangeLgMax + 7)) &&
         g_tune_segtree_ranged != 0) {
         const int lg = ilog2(bound);
         int lg_range = lg - 7;  // 128 CTAs when the range stays within [2^10, 2^13] leaves
