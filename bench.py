@@ -79,6 +79,12 @@ def rollout(E, T, seed):
     return rew, v_s, v_next, term.view(np.uint8), trunc.view(np.uint8)
 
 
+def note(msg: str) -> None:
+    """Progress on stderr (rank-tagged): tells where a multi-rank run stopped."""
+    print(f"[bench r{os.environ.get('RANK', '0')} {time.strftime('%H:%M:%S')}] {msg}",
+          file=sys.stderr, flush=True)
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -404,6 +410,7 @@ def run_b200(args):
             barrier()
         return e0.elapsed_time(e1)  # ms on the launching stream
 
+    note("gae device-resident leg")
     ms = timed_gae()
     if sampler.bad():  # thermal / hw slowdown seen: re-measure once
         sampler.samples.clear()
@@ -431,12 +438,14 @@ def run_b200(args):
     # ---- e2e: the drop-in call with host arrays in and out ------------------------------------------
     e2e = None
     if not args.skip_e2e:
+        note("e2e leg")
         e2e = run_e2e(torch, dist, L, args, dev, rank, world, host, sets, barrier, max_over_ranks,
                       sampler, K)
 
     # ---- PER: sample + importance weights + update_weight, CUDA-graph replay ------------------
     per = None
     if not args.skip_per:
+        note("per leg")
         per = run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks)
 
     # ---- CPU baseline (rank 0, N == 1 only): the oracle on the box's host cores -----------------
@@ -480,6 +489,7 @@ def run_b200(args):
         # the data-parallel learner (all ranks take part: one NCCL all-reduce per minibatch)
         sys.path.insert(0, os.path.join(ROOT, "scripts"))
         import bench_dp
+        note("data-parallel updates leg")
         updates = bench_dp.run_dp_updates(torch, dist, dev, rank, world, max_over_ranks)
 
     if rank == 0:
@@ -503,7 +513,14 @@ def run_b200(args):
         }
         emit_result(line)
     if world > 1:
-        dist.destroy_process_group()
+        # Every leg is done and the line is out.  Tearing NCCL down with captured graphs that
+        # hold collectives and symmetric-memory mappings still alive blocked for minutes in
+        # destroy_process_group() (r02o: all results printed, then a 20-minute wait for the
+        # watchdog); the ranks leave together instead.
+        note("done")
+        barrier()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def run_e2e(torch, dist, L, args, dev, rank, world, host, sets, barrier, max_over_ranks, sampler,

@@ -11,6 +11,7 @@ replicas end bit-identical.
 """
 from __future__ import annotations
 
+import sys
 import time
 
 import numpy as np
@@ -102,6 +103,7 @@ def run_dp_updates(torch, dist, dev, rank, world, max_over_ranks):
             rows = {}
             for mode in ("eager", "cuda_graph"):
                 for dp in (True, False):
+                    print(f"[bench_dp r{rank}] mb {bs} {mode} dp={dp}", file=sys.stderr, flush=True)
                     actor, critic, optim = _nets(torch, dev)
                     pol = ts.PPOPolicy(actor, critic, optim, dist_fn, eps_clip=0.2,
                                        value_clip=True, vf_coef=0.25, ent_coef=0.0,
@@ -132,6 +134,5 @@ def run_dp_updates(torch, dist, dev, rank, world, max_over_ranks):
             out[f"c3_ppo_learn_mb{bs}"] = rows
         out["allreduce"] = allreduce_latency(torch, dist, dev, numel, max_over_ranks)
         return out
-    except Exception as e:  # reported, not fatal
-        import traceback
-        return {"error": f"{type(e).__name__}: {e}", "trace": traceback.format_exc()[-600:]}
+    except Exception:
+        raise  # every rank is inside a collective sequence: a rank that drops out must fail the run

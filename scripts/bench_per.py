@@ -24,6 +24,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+
+def note(msg):
+    print(f"[bench_per r{os.environ.get('RANK', '0')} {time.strftime('%H:%M:%S')}] {msg}",
+          file=sys.stderr, flush=True)
+
 PER_LEAVES, PER_BATCH, PER_ALPHA, PER_BETA = 1 << 20, 4096, 0.6, 0.4
 PER_ALG_BYTES_PER_SAMPLE = 664
 R = 8  # distinct (uniforms, td) sets per graph
@@ -207,8 +212,10 @@ def run_sharded(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
                     sh.err.data_ptr(), state.data_ptr(), peers, world, rank, s),
                     "ts_per_update_publish")
 
+        note(f"sharded leg {leg}, global batch {M}")
         if leg == "strong":
             parity = _parity_check(torch, dist, L, lib, dev, rank, world, sh, step, u, td, idx)
+        note("parity done, timing" if leg == "strong" else "timing")
         ms, steps = time_graph(torch, dev, step, barrier)
         ms = max_over_ranks(ms)
         owned = (idx >= 0).sum().to(torch.float64)
@@ -287,7 +294,9 @@ def per_e2e(torch, dist, dev, rank, world, max_over_ranks):
                 "d2h_bytes_per_step": PER_BATCH * (8 + 8),
                 "api": api + ".sample_indices + importance weights + update_weight with NumPy "
                              "arrays in and out"}
-    except Exception as e:  # reported, not fatal
+    except Exception as e:  # reported, not fatal -- on ONE GPU.  With peers, a rank that drops out
+        if world > 1:       # of a collective sequence would leave them waiting: fail the run
+            raise
         return {"error": f"{type(e).__name__}: {e}"}
 
 
@@ -310,5 +319,6 @@ def run_per(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks, peak
                         "note": "latency-bound: ~9 dependent L2 round trips of ~0.5 us per step "
                                 "plus two launch boundaries, not bytes; the tree is L2-resident "
                                 "(ncu: ~0 B DRAM read per launch, profiles/r01c_per.md)"}}
+    note("per e2e through the buffer class")
     out["e2e"] = per_e2e(torch, dist, dev, rank, world, max_over_ranks)
     return out

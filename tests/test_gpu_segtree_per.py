@@ -341,3 +341,33 @@ def test_lazy_top_is_invisible_through_the_classes():
             assert np.array_equal(got.cpu().numpy(), ref.sample_indices(u))
             assert not buf.weight._top_stale
             assert np.array_equal(buf.weight._heap.cpu().numpy()[1:], ref.weight._value[1:])
+
+
+def test_host_array_step_matches_device_step_and_pickles():
+    """sample_indices_numpy (one upload, one packed download) + update_weight with NumPy arrays
+    (one packed pinned upload): same draws, indices, weights and tree as the tensor path."""
+    import pickle
+    import tianshou_fork_b200 as ts
+    size, bsz = 1 << 16, 512
+    rng = np.random.default_rng(9)
+    leaves = torch.from_numpy((np.abs(rng.standard_normal(size)) + 1e-7) ** 0.6).cuda()
+    bufs = [ts.PrioritizedVectorReplayBuffer(size, 8, alpha=0.6, beta=0.4) for _ in range(2)]
+    for b in bufs:
+        b.weight[torch.arange(size, device="cuda")] = leaves
+        b._lengths[:] = size // 8
+    host, devb = bufs
+    for step in range(4):
+        td = rng.standard_normal(bsz).astype(np.float32 if step % 2 == 0 else np.float64)
+        np.random.seed(40 + step)
+        idx_h, w_h = host.sample_indices_numpy(bsz)
+        np.random.seed(40 + step)
+        idx_d = devb.sample_indices(bsz)
+        assert isinstance(idx_h, np.ndarray) and idx_h.dtype == np.int64
+        assert np.array_equal(idx_h, idx_d.cpu().numpy())
+        assert np.array_equal(w_h, devb._cached_weight[1].cpu().numpy())
+        host.update_weight(idx_h, td)
+        devb.update_weight(idx_d, torch.from_numpy(td).cuda())
+        assert torch.equal(host.weight._value, devb.weight._value), step
+        assert torch.equal(host._prio, devb._prio)
+    clone = pickle.loads(pickle.dumps(host))
+    assert torch.equal(clone.weight._value, host.weight._value)

@@ -100,6 +100,51 @@ def build(verbose: bool = False) -> str:
     return LIB_PATH
 
 
+SHIM_DIR = os.path.join(CSRC, "shim_build")
+SHIM_NAME = "ts_b200_shim"
+_shim = None
+_shim_tried = False
+
+
+def build_shim(verbose: bool = False) -> str:
+    """Compile csrc/shim.cpp (the C++ host shim over the C-ABI: tensors in, tensors out, the PPO
+    loss as a C++ autograd function) in-tree with torch's extension builder.  Host code only --
+    no kernels -- linked against libts_b200.so next to it."""
+    from torch.utils import cpp_extension
+    os.makedirs(SHIM_DIR, exist_ok=True)
+    cpp_extension.load(
+        name=SHIM_NAME, sources=[os.path.join(CSRC, "shim.cpp")], build_directory=SHIM_DIR,
+        extra_cflags=["-O2", "-std=c++17"], extra_include_paths=["/usr/local/cuda/include"],
+        # $$ORIGIN: ninja's escape for a literal `$`; the quotes keep it from the shell
+        extra_ldflags=[f"-L{CSRC}", "-lts_b200", "-Wl,-rpath,'$$ORIGIN/..'", "-lc10_cuda",
+                       "-L/usr/local/cuda/lib64", "-lcudart"],
+        with_cuda=False, is_python_module=False, verbose=verbose)
+    return os.path.join(SHIM_DIR, SHIM_NAME + ".so")
+
+
+def shim():
+    """The compiled shim module, or None when it has not been built (the Python layer then makes
+    the same C-ABI calls through ctypes).  Never compiles anything at run time."""
+    global _shim, _shim_tried
+    if not _shim_tried:
+        _shim_tried = True
+        path = os.path.join(SHIM_DIR, SHIM_NAME + ".so")
+        if os.path.exists(path) and os.environ.get("TS_NO_SHIM") != "1":
+            import importlib.machinery
+            import importlib.util
+            load()  # libts_b200.so first (the shim links against it)
+            try:
+                loader = importlib.machinery.ExtensionFileLoader(SHIM_NAME, path)
+                spec = importlib.util.spec_from_loader(SHIM_NAME, loader)
+                mod = importlib.util.module_from_spec(spec)
+                loader.exec_module(mod)
+                _shim = mod
+            except Exception as e:  # pragma: no cover - reported once, ctypes path is used
+                import warnings
+                warnings.warn(f"ts_b200 shim failed to load ({e}); using the ctypes binding")
+    return _shim
+
+
 def load() -> ctypes.CDLL:
     """Load the library (does not need a GPU) and bind every declared symbol."""
     global _lib
@@ -108,7 +153,7 @@ def load() -> ctypes.CDLL:
             raise ImportError(
                 f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; "
                 "g.build()'` (there is no CPU or PyTorch fallback for this path)")
-        lib = ctypes.CDLL(LIB_PATH)
+        lib = ctypes.CDLL(LIB_PATH, mode=ctypes.RTLD_GLOBAL)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(lib, name)  # AttributeError if the .so lacks a declared symbol
             fn.restype, fn.argtypes = res, args

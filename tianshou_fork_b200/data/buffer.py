@@ -135,6 +135,8 @@ class ReplayBuffer:
                     "_cached_weight"):
             if key in state:
                 state[key] = None
+        for key in ("_pin", "_host_io", "_host_io_upd", "_upd_ev"):  # staging of host-array calls
+            state.pop(key, None)
         state["_dev_state_version"] = -1
         if "_dev_add_version" in state:
             state["_dev_add_version"] = -1
@@ -232,6 +234,10 @@ class ReplayBuffer:
         if (isinstance(index, torch.Tensor) and index.is_cuda and index.dtype == torch.int64
                 and index.is_contiguous()):
             # device tensor in -> device tensor out: nothing but the launch
+            sh = L.shim()
+            if sh is not None:
+                return sh.neighbour(index, st["packed"], st["B"], st["sub_size"],
+                                    self._meta.__dict__["done"], fn_name == "ts_next_index")
             out = torch.empty_like(index)
             n = index.numel()
             if n:

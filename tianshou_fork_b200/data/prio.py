@@ -121,6 +121,71 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         self._cached_weight = (idx, w)
         return idx
 
+    # ---- host-array callers (the reference's calling convention: NumPy in, NumPy out) ----------
+    def _pinned(self, name: str, nbytes: int) -> torch.Tensor:
+        """Reusable pinned staging buffers (one per direction and purpose)."""
+        cache = self.__dict__.setdefault("_pin", {})
+        t = cache.get(name)
+        if t is None or t.numel() < nbytes:
+            t = cache[name] = torch.empty(max(nbytes, 1 << 16), dtype=torch.uint8).pin_memory()
+        return t
+
+    def sample_indices_numpy(self, batch_size: int) -> Tuple[np.ndarray, np.ndarray]:
+        """``sample_indices(batch_size)`` and the importance weights of the draw as NumPy arrays
+        (what the reference's ``buffer.sample`` hands a host-side learner: indices + ``weight``,
+        prio.py:59-64, 91-102) with ONE upload (the ``np.random.rand`` draws, prio.py:61) and ONE
+        download (indices and weights share a device buffer) instead of a copy per array."""
+        m = int(batch_size)
+        assert m > 0 and len(self) > 0
+        stage = self._pinned("u", 8 * m)[: 8 * m].view(torch.float64)
+        stage.numpy()[:] = np.random.rand(m)  # prio.py:61
+        dev = self.__dict__.setdefault("_host_io", {})
+        if dev.get("m") != m:
+            dev.clear()
+            dev.update(m=m, u=torch.empty(m, dtype=torch.float64, device=self.device),
+                       out=torch.empty(2 * m, dtype=torch.int64, device=self.device))
+        u, out = dev["u"], dev["out"]
+        u.copy_(stage, non_blocking=True)
+        t = self.weight
+        idx, w = out[:m], out[m:].view(torch.float64)
+        L.check(L.lib().ts_per_sample_lazy(
+            t._heap.data_ptr(), t._bound, u.data_ptr(), m, self._prio.data_ptr(),
+            float(self._beta), int(self._weight_norm), idx.data_ptr(), w.data_ptr(),
+            t._err.data_ptr(), L.stream()), "ts_per_sample_lazy")
+        t._top_stale = False
+        self._cached_weight = None
+        host = self._pinned("out", 16 * m)[: 16 * m].view(torch.int64)
+        host.copy_(out, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        h = host.numpy()
+        return h[:m].copy(), h[m:].view(np.float64).copy()
+
+    def _upload_update(self, index: np.ndarray, new_weight: np.ndarray):
+        """Host indices + host td-errors -> device, as one pinned buffer and one copy."""
+        idx = np.ascontiguousarray(index, dtype=np.int64).reshape(-1)
+        td = np.ascontiguousarray(new_weight).reshape(-1)
+        if td.dtype not in (np.float32, np.float64):
+            td = td.astype(np.float64)
+        m = idx.size
+        assert td.size == m
+        nb = 8 * m + td.itemsize * m
+        stage = self._pinned("upd", nb)
+        stage[: 8 * m].view(torch.int64).numpy()[:] = idx
+        tdt = torch.float32 if td.dtype == np.float32 else torch.float64
+        stage[8 * m: nb].view(tdt).numpy()[:] = td
+        ev = self.__dict__.get("_upd_ev")
+        key = ("upd_dev", nb)
+        dev = self.__dict__.setdefault("_host_io_upd", {})
+        buf = dev.get(key)
+        if buf is None:
+            dev.clear()
+            buf = dev[key] = torch.empty(nb, dtype=torch.uint8, device=self.device)
+        buf.copy_(stage[:nb], non_blocking=True)
+        if ev is None:
+            ev = self.__dict__["_upd_ev"] = torch.cuda.Event()
+        ev.record()  # the staging buffer may be rewritten once this copy has been issued AND run
+        return buf[: 8 * m].view(torch.int64), buf[8 * m:].view(tdt), ev
+
     def get_weight(self, index: IndexLike):
         """Importance weight ``(p_j / p_min) ** (-beta)`` (prio.py:66-76), un-normalised."""
         return self._weights(index, normalise=False)
@@ -143,14 +208,22 @@ class PrioritizedReplayBuffer(ReplayBuffer):
                       ) -> None:
         """``weight[index] = (|new_weight| + eps) ** alpha`` plus max/min tracking
         (prio.py:78-89), one launch, no host sync when given CUDA tensors."""
-        idx = self.weight._dev_index(index)
-        if isinstance(new_weight, torch.Tensor):
-            td = new_weight.detach().to(self.device)
+        if (isinstance(index, np.ndarray) and isinstance(new_weight, np.ndarray) and index.size
+                and type(self).update_weight is PrioritizedReplayBuffer.update_weight):
+            # host arrays in: one packed pinned upload instead of two pageable ones
+            ev = self.__dict__.get("_upd_ev")
+            if ev is not None:
+                ev.synchronize()  # the previous call's copy has left the staging buffer
+            idx, td, _ = self._upload_update(index, new_weight)
         else:
-            td = torch.as_tensor(np.asarray(new_weight), device=self.device)
-        if td.dtype not in (torch.float32, torch.float64):
-            td = td.to(torch.float64)
-        td = td.reshape(-1).contiguous()
+            idx = self.weight._dev_index(index)
+            if isinstance(new_weight, torch.Tensor):
+                td = new_weight.detach().to(self.device)
+            else:
+                td = torch.as_tensor(np.asarray(new_weight), device=self.device)
+            if td.dtype not in (torch.float32, torch.float64):
+                td = td.to(torch.float64)
+            td = td.reshape(-1).contiguous()
         assert td.numel() == idx.numel()
         if idx.numel() == 0:
             return

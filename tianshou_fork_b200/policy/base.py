@@ -392,6 +392,26 @@ class BasePolicy(nn.Module):
             rew = rew.to(torch.float64)
         idx = _flat(_dev(indice, dev, torch.int64))
         bsz = idx.numel()
+        sh = L.shim()
+        if sh is not None and isinstance(buffer, ReplayBuffer) and bsz > 0:
+            # the same two C-ABI calls from C++ (csrc/shim.cpp)
+            st = buffer._state()
+            terminal, fl = sh.nstep_chain(idx, rew.contiguous(), buf_done, buf_term, st["packed"],
+                                          B, sub, float(gamma), int(n_step))
+            terminal_arg = terminal if isinstance(indice, torch.Tensor) else terminal.cpu().numpy()
+            with torch.no_grad():
+                target_q_torch = target_q_fn(buffer, terminal_arg)  # (bsz, ?)  :430
+            tq_dev = target_q_torch.reshape(bsz, -1).to(dev)
+            if tq_dev.dtype not in (torch.float32, torch.float64):
+                tq_dev = tq_dev.to(torch.float32)
+            out = sh.nstep_combine(tq_dev.contiguous(), fl)
+            batch.returns = out.to(device=target_q_torch.device, dtype=target_q_torch.dtype)
+            if hasattr(batch, "weight"):  # prio buffer update  :438-439
+                w = batch.weight
+                if not isinstance(w, torch.Tensor):
+                    w = torch.from_numpy(np.asarray(w))
+                batch.weight = w.to(device=target_q_torch.device, dtype=target_q_torch.dtype)
+            return batch
         terminal = torch.empty(bsz, dtype=torch.int64, device=dev)
         ret_sum = torch.empty(bsz, dtype=torch.float64, device=dev)
         coef = torch.empty(bsz, dtype=torch.float64, device=dev)

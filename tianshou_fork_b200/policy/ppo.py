@@ -94,6 +94,11 @@ def ppo_loss(logp: torch.Tensor, value: torch.Tensor, logp_old: torch.Tensor,
         assert mb_index.dtype == torch.int64 and mb_index.is_contiguous()
         assert mb_index.numel() == logp.numel()
     assert not value_clip or v_s is not None
+    sh = L.shim()
+    if sh is not None:  # the same C-ABI call from C++ (csrc/shim.cpp): no ctypes, C++ autograd node
+        return tuple(sh.ppo_loss(logp, value, logp_old, adv, returns, v_s, mb_index,
+                                 _ws(logp.device), float(eps_clip), float(dual_clip or 0.0),
+                                 bool(value_clip), bool(norm_adv), float(eps)))
     return _PPOLoss.apply(logp, value, logp_old, adv, returns, v_s, mb_index, eps_clip,
                           dual_clip, value_clip, norm_adv, eps)
 
