@@ -270,9 +270,13 @@ def per_e2e(torch, dist, dev, rank, world, max_over_ranks):
         np.random.seed(12345)  # the same host draws on every rank
 
         def step(i):
-            idx = buf.sample_indices(PER_BATCH)            # host uniforms -> device descent
-            w = buf._cached_weight[1]                      # IS weights of the same launch
-            idx_h, w_h = idx.cpu().numpy(), w.cpu().numpy()  # the learner's host copies
+            if world == 1:
+                # host draws up, indices + IS weights down as one packed copy (prio.py:59-64, 91-102)
+                idx_h, w_h = buf.sample_indices_numpy(PER_BATCH)
+            else:
+                idx = buf.sample_indices(PER_BATCH)        # host uniforms -> device descent
+                w = buf._cached_weight[1]                  # IS weights of the same launch
+                idx_h, w_h = idx.cpu().numpy(), w.cpu().numpy()  # the learner's host copies
             buf.update_weight(idx_h, tds[i % 8])           # host td-errors -> device tree
             return idx_h, w_h
 
@@ -292,8 +296,11 @@ def per_e2e(torch, dist, dev, rank, world, max_over_ranks):
                 "us_per_step": dt / steps * 1e6,
                 "h2d_bytes_per_step": PER_BATCH * (8 + 8 + 4),
                 "d2h_bytes_per_step": PER_BATCH * (8 + 8),
-                "api": api + ".sample_indices + importance weights + update_weight with NumPy "
-                             "arrays in and out"}
+                "api": api + (".sample_indices_numpy (host draws up, indices + importance weights "
+                              "down in one packed copy) + update_weight(NumPy, NumPy) (one packed "
+                              "pinned upload)" if world == 1 else
+                              ".sample_indices + importance weights + update_weight with NumPy "
+                              "arrays in and out")}
     except Exception as e:  # reported, not fatal -- on ONE GPU.  With peers, a rank that drops out
         if world > 1:       # of a collective sequence would leave them waiting: fail the run
             raise

@@ -430,12 +430,16 @@ def row_ppo():
             vl = torch.max((ret[mb] - val).pow(2), (ret[mb] - vclip).pow(2)).mean()
             (cl + 0.5 * vl).backward()
 
+        lpd, vald = lp.detach(), val.detach()
+        fwd_us = gpu_us(lambda: ts.ppo_loss(lpd, vald, lo, adv, ret, vs, mb, 0.2, None, True, True),
+                        iters=100)  # the call alone: no autograd graph, no backward
         us, eus = gpu_us(fused, iters=100), gpu_us(eager, iters=100)
         lpn, lon = lp.detach().cpu().numpy(), lo[mb].cpu().numpy()
         an, rn = adv[mb].cpu().numpy(), ret[mb].cpu().numpy()
         vn_, valn = vs[mb].cpu().numpy(), val.detach().cpu().numpy()
         cus = cpu_us(lambda: orc.ppo_loss(lpn, lon, an, rn, vn_, valn, 0.2, None, True, True), 1.0)
-        emit("a11 ppo_loss fwd+bwd", m=m, fused_gpu_us=us, torch_eager_gpu_us=eus,
+        emit("a11 ppo_loss fwd+bwd", m=m, fused_gpu_us=us, fused_forward_only_us=fwd_us,
+             shim=L.shim() is not None, torch_eager_gpu_us=eus,
              cpu_port_fwd_us=cus, speedup_vs_eager=eus / us)
 
 

@@ -9,6 +9,7 @@ streams.  Env streams are independent, so chunking along E needs no carry.
 """
 from __future__ import annotations
 
+import os
 from typing import List, Tuple
 
 import torch
@@ -216,7 +217,12 @@ class GaeHostCall:
     allocator and are returned as NumPy views of it (no extra host copy; the block goes back to
     the allocator when the arrays are dropped)."""
 
-    CHUNK_BYTES = 24 << 20  # host bytes per chunk and direction: deep enough to hide latencies
+    # Host bytes per chunk and direction.  Measured on the B200 box (profiles/r02_e2e.md): 8 / 12 /
+    # 24 / 32 / 48 / 96 MB -> 4.13 / 3.82 / 3.60 / 3.63 / 3.76 / 3.99 ms per C2 call; smaller chunks
+    # lose to the per-copy cost of the DMA engines (issuing the same pipeline from C++ did not help:
+    # 2 / 4 / 8 / 16 MB -> 5.3 / 4.4 / 4.3 / 3.8 ms), larger ones to the un-overlapped first upload
+    # and last download of a synchronous call.
+    CHUNK_BYTES = int(os.environ.get("TS_HOST_CALL_CHUNK_MB", "24")) << 20
 
     def __init__(self, device: torch.device) -> None:
         L.lib()
@@ -257,6 +263,23 @@ class GaeHostCall:
         rows = max(1, min(E, self.CHUNK_BYTES // max(in_row, out_row, 1)))
         chunks = (E + rows - 1) // rows
         rows = (E + chunks - 1) // chunks  # even chunks
+        # The call is synchronous: the first chunk's upload and the last chunk's download overlap
+        # with nothing, so both ends taper (1/4, 1/4, 1/2 of a chunk) to keep them short.
+        taper = os.environ.get("TS_HOST_CALL_TAPER", "0") == "1"
+        bounds, lo = [], 0
+        for c in range(chunks):
+            hi = min(E, lo + rows)
+            n = hi - lo
+            if taper and chunks >= 2 and n >= 8 and c in (0, chunks - 1):
+                parts = [n // 4, n // 4, n - 2 * (n // 4)]
+                if c == chunks - 1:
+                    parts.reverse()
+                for p_ in parts:
+                    bounds.append((lo, lo + p_))
+                    lo += p_
+            else:
+                bounds.append((lo, hi))
+                lo = hi
         nb = 3
         h_ret = torch.empty(E, T, dtype=out_dtype, pin_memory=True)
         h_adv = torch.empty(E, T, dtype=out_dtype, pin_memory=True)
@@ -269,8 +292,7 @@ class GaeHostCall:
         ev_bounced: dict = {}
         lib = L.lib()
         code = lambda d: L.TS_F64 if d == torch.float64 else L.TS_F32  # noqa: E731
-        for c in range(chunks):
-            lo, hi = c * rows, min(E, (c + 1) * rows)
+        for c, (lo, hi) in enumerate(bounds):
             n, b = hi - lo, c % nb
             ptrs = {}
             with torch.cuda.stream(self.s_h2d):
