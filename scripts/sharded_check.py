@@ -72,6 +72,18 @@ def main():
             buf.weight[torch.from_numpy(ch).to(dev)] = torch.from_numpy(ref_l[ch]).to(dev)
         buf.sync_roots()
         buf.check_errors()
+    # prev / next / n-step on the sharded buffer in this exchange mode (ReplayBuffer._state must
+    # stay callable next to the exchange's own state words)
+    buf._meta = ts.Batch(rew=torch.zeros(cap, dtype=torch.float64, device=dev),
+                         done=torch.zeros(cap, dtype=torch.bool, device=dev),
+                         terminated=torch.zeros(cap, dtype=torch.bool, device=dev))
+    q = torch.arange(0, cap, 37, device=dev)
+    nxt = buf.next(q).cpu().numpy()
+    qn, sub = q.cpu().numpy(), cap // nbuf
+    assert np.array_equal(nxt, np.where((qn + 1) % sub == 0, qn - sub + 1, qn + 1)), "next"
+    r = ts.BasePolicy.compute_nstep_return(ts.Batch(), buf, q,
+                                           lambda b, i: torch.ones(i.numel(), device=dev), 0.5, 2)
+    assert bool((r.returns.flatten() == 0.25).all()), "n-step on a sharded buffer"
     # ---- timing: eager steps (host launches included), identical draws on every rank ----------
     R = 8
     us = torch.from_numpy(rng.random((R, bsz))).to(dev)

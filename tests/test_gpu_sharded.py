@@ -137,6 +137,16 @@ def test_world_size_one_class_equals_unsharded():
         assert torch.equal(a.weight._value, b.weight._value)
         assert a._max_prio == b._max_prio and a._min_prio == b._min_prio
     assert torch.equal(a.to_global(ia), ia)
+    # The p2p exchange keeps its own sequence words (`_p2p_state`); it must never shadow
+    # ReplayBuffer._state(), which prev / next / n-step / GAE read (round-1 advisor finding).
+    a._p2p_state = torch.zeros(2, dtype=torch.int64, device="cuda")  # what _setup_p2p creates
+    assert callable(a._state) and callable(type(a)._state)
+    q = torch.from_numpy(rng.integers(0, 1 << 12, 64)).cuda()
+    assert torch.equal(a.next(q), b.next(q)) and torch.equal(a.prev(q), b.prev(q))
+    tq = lambda buf, idx: torch.ones(idx.numel(), device="cuda")  # noqa: E731
+    ra = ts.BasePolicy.compute_nstep_return(ts.Batch(), a, ia, tq, 0.9, 3).returns
+    rb = ts.BasePolicy.compute_nstep_return(ts.Batch(), b, ib, tq, 0.9, 3).returns
+    assert torch.equal(ra, rb)
 
 
 @pytest.mark.parametrize("G,cap,bsz", [(2, 1 << 13, 700), (8, 1 << 15, 4096)])

@@ -1236,6 +1236,7 @@ __device__ __forceinline__ double is_weight(double leaf, double min_prio, double
 // kernel spins (bounded) until the G records of its epoch have landed, and the weight maximum
 // is exchanged the same way before the normalising division -- no collective library call,
 // no extra launch, capturable in a CUDA graph (epochs live on the device).
+constexpr int kOwnedList = 768;  // owned draws a CTA keeps for its dense descent pass (12 KB)
 struct ShardInfo {
     const double* roots3;  // NCCL mode: G x {root, max_prio, min_prio}; nullptr otherwise
     int G, rank;
@@ -1258,6 +1259,8 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
     __shared__ double s_cta;
     const int tid = threadIdx.x;
     __shared__ double s_gext[2 * kMaxShards];  // max_prio | min_prio of every rank
+    __shared__ ulonglong2 s_list[SAMPLE && SHARD != 0 ? kOwnedList : 1];  // {position, routed v}
+    __shared__ unsigned int s_nlist;
     constexpr bool p2p = SHARD == 2;
     constexpr bool sharded = SHARD != 0;
     pdl_launch_dependents();
@@ -1329,22 +1332,61 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
         total = sharded ? s_gtop[1] : s_top[1];
     }
     double wmax = 0.0, w_first = 0.0;
-    for (int64_t j = j0; j < M; j += sweep) {
+    // Sharded sampling: a rank owns ~1/G of the draws, scattered over the batch.  Descending "if
+    // mine" inside the sweep loop makes every warp walk a full dependent chain per sweep for the
+    // one or two lanes that own something (G = 8, batch 4096 per rank: 8 chains per thread instead
+    // of 1).  So the sweeps only ROUTE (shared-memory top of the global tree) and append the owned
+    // draws to a CTA-wide list; the descents then run densely, one per thread.
+    constexpr bool compact = SAMPLE && sharded;
+    if (compact) {
+        if (tid == 0) s_nlist = 0u;
+        __syncthreads();
+        for (int64_t j = j0; j < M; j += sweep) {
+            double v = __dmul_rn(j == j0 ? u_first : u[j], total);  // prio.py:61
+            if (!(v >= 0.0 && v < total)) atomicOr(err_flag, TS_FLAG_PREFIX_RANGE);
+            int node = 1;
+            while (node < G) {                                   // the global tree's top levels
+                node <<= 1;
+                node += step_down(s_gtop[node], v);
+            }
+            if (node - G != sh.rank) {
+                idx[j] = -1;
+                weight[j] = 0.0;
+                continue;
+            }
+            const unsigned int pos = atomicAdd(&s_nlist, 1u);
+            if (pos < (unsigned)kOwnedList) {
+                s_list[pos] = make_ulonglong2((unsigned long long)j,
+                                              (unsigned long long)__double_as_longlong(v));
+            } else {  // far more than this CTA's share lands in this shard: finish it here
+                double leaf_val = 0.0;
+                idx[j] = descend<double>(tree, bound, lg_bound, s_top, cached, v, &leaf_val);
+                const double w = is_weight(leaf_val, min_prio, beta);
+                weight[j] = w;
+                wmax = fmax(wmax, w);
+            }
+        }
+        __syncthreads();
+        const unsigned int n = min(s_nlist, (unsigned)kOwnedList);
+        for (unsigned int i = tid; i < n; i += NT) {
+            const ulonglong2 it = s_list[i];
+            double v = __longlong_as_double((long long)it.y), leaf_val = 0.0;
+            const int64_t j = (int64_t)it.x;
+            idx[j] = descend<double>(tree, bound, lg_bound, s_top, cached, v, &leaf_val);
+            const double w = is_weight(leaf_val, min_prio, beta);
+            weight[j] = w;  // raw; normalised below by the thread whose sweep owns position j
+            wmax = fmax(wmax, w);
+        }
+        __syncthreads();  // the raw weights of this CTA's positions are all in place
+    }
+    for (int64_t j = j0; !compact && j < M; j += sweep) {
         int64_t leaf;
         double leaf_val = 0.0;
         bool mine = true;
         if (SAMPLE) {
             double v = __dmul_rn(j == j0 ? u_first : u[j], total);  // prio.py:61
             if (!(v >= 0.0 && v < total)) atomicOr(err_flag, TS_FLAG_PREFIX_RANGE);
-            if (sharded) {
-                int node = 1;
-                while (node < G) {                               // the global tree's top levels
-                    node <<= 1;
-                    node += step_down(s_gtop[node], v);
-                }
-                mine = node - G == sh.rank;
-            }
-            leaf = mine ? descend<double>(tree, bound, lg_bound, s_top, cached, v, &leaf_val) : -1;
+            leaf = descend<double>(tree, bound, lg_bound, s_top, cached, v, &leaf_val);
             idx[j] = leaf;
         } else {
             leaf = idx[j];
@@ -1389,7 +1431,7 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
         }
     }
     for (int64_t j = j0; j < M; j += sweep) {
-        const double w = j == j0 ? w_first : weight[j];
+        const double w = (!compact && j == j0) ? w_first : weight[j];
         weight[j] = scale ? __ddiv_rn(w, wmax) : w;              // prio.py:101
     }
     if (weight_norm) cluster_wait();  // second half of cluster_max's closing barrier
