@@ -121,10 +121,11 @@ int32_t ts_gae_rows(const void* rew, const void* v_s, const void* v_s_next,
  *   the caller and opaque afterwards (one stream at a time): the pipelined kernel keeps a call
  *   count in it that tags its inter-CTA flags, so no call has to clear anything (calls of any
  *   size may alternate on one workspace: the short-sequence kernel clears only its own words).
- * Approximation (documented, bounded): when a CTA of the pipelined kernel reads ahead for the
- *   carry into its range, it treats an accumulated discount (gamma*lambda)^n < 1e-60 as zero
- *   (csrc/gae.cu:kCarryNegligible) -- a relative error below 1e-60 of the carried advantage, far
- *   under one f64 ulp; every other operation is the reference's f64 recurrence.
+ * Approximation (documented, bounded): a CTA of the pipelined kernel obtains the carry into its
+ *   range from a "ghost" pass over the next 2048 steps; when no episode ends there it treats a
+ *   discount product (gamma*lambda)^2048 < 1e-30 as zero (csrc/gae.cu:kCarryNegligible) -- a
+ *   relative error below 1e-30 of the carried advantage, fourteen orders under one f64 ulp; every
+ *   other operation is the reference's f64 recurrence.
  */
 size_t ts_gae_flat_workspace_bytes(int64_t N);
 int32_t ts_gae_flat(const void* rew, const void* v_s, const void* v_s_next,

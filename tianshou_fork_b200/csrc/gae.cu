@@ -496,11 +496,11 @@ gae_rows_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
 // a CONTIGUOUS range of tiles and walks it from its end with the same stage ring, scan and
 // staged stores as gae_rows_tma_kernel, so the carry between tiles stays in registers.  What
 // a CTA needs from outside is ONE number: the advantage of the first step after its range.
-// It does not wait for the CTA that owns that step; one warp reads AHEAD from the range
-// boundary in windows of 256 steps and composes their maps until an episode boundary (P == 0)
-// or until the accumulated discount is below 1e-60 of the carry -- on real rollouts one or two
-// windows of redundant reads.  Only if neither happens within 4096 steps (no episode end AND
-// gamma*lambda ~ 1) does the CTA fall back to waiting for its neighbour's published head value;
+// It does not wait for the CTA that owns that step: it runs that CTA's bottom tile as a GHOST
+// tile through its own pipeline first (scanned with zero carry-in, nothing stored).  An episode
+// boundary anywhere in those 2048 steps, or a discount product below 1e-30 over them, makes the
+// ghost tile's head advantage exact -- on real rollouts always.  Only with no episode end AND
+// gamma*lambda ~ 1 does the CTA fall back to waiting for its neighbour's published head value;
 // the chain starts at the CTA that owns the end of the sequence, which never waits.
 // ============================================================================================
 struct FlatGather {               // how value mask and unfinished tails are found (nullable)
@@ -534,109 +534,9 @@ __device__ __forceinline__ void flat_flags(const FlatGather& g, int64_t idx, uin
     }
 }
 
-// One warp: the map (P, X) of the 256 steps starting at i_first, read straight from global
-// memory.  Steps at or beyond N act as "episode over, value 0".  Split in two so that the caller
-// can put other work (the first bulk loads) between issuing the reads and needing them.
-template <typename T>
-__device__ __forceinline__ void gmem_ld8(const T* __restrict__ p, int nvalid, T (&v)[VEC]) {
-    if (nvalid == VEC) {
-        constexpr int PER = 16 / sizeof(T);
-        using V = typename std::conditional<sizeof(T) == 4, float4, double2>::type;
-#pragma unroll
-        for (int q = 0; q < VEC / PER; ++q) {
-            const V x = __ldcs(reinterpret_cast<const V*>(p) + q);
-            const T* e = reinterpret_cast<const T*>(&x);
-#pragma unroll
-            for (int j = 0; j < PER; ++j) v[q * PER + j] = e[j];
-        }
-    } else {
-#pragma unroll
-        for (int k = 0; k < VEC; ++k) v[k] = k < nvalid ? __ldcs(p + k) : T(0);
-    }
-}
-__device__ __forceinline__ uint2 gmem_ld8_flags(const uint8_t* __restrict__ p, int nvalid) {
-    if (nvalid == VEC) return __ldcs(reinterpret_cast<const uint2*>(p));
-    uint2 w = make_uint2(0u, 0u);
-#pragma unroll
-    for (int k = 0; k < VEC; ++k) {
-        const uint32_t byte = k < nvalid ? (uint32_t)__ldcs(p + k) : 0u;
-        if (k < 4) w.x |= byte << (8 * k);
-        else w.y |= byte << (8 * (k - 4));
-    }
-    return w;
-}
-
-template <typename RewT, typename InT>
-struct FlatWindow {
-    RewT rw[VEC];
-    InT vs[VEC], vn[VEC];
-    uint2 wt, wc;
-    int64_t idx[VEC];
-    int64_t first;  // sequence position of this lane's first step
-    int nvalid;
-
-    // issue the reads of this lane's 8 steps (all arrays are 16-byte aligned, i_first % 8 == 0)
-    __device__ __forceinline__ void load(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
-                                         const InT* __restrict__ v_next,
-                                         const uint8_t* __restrict__ term,
-                                         const uint8_t* __restrict__ trunc, const FlatGather& g,
-                                         int64_t i_first, int64_t N, int lane) {
-        const int64_t i0 = i_first + lane * VEC;
-        first = i0;
-        const int64_t left = N - i0;
-        nvalid = left >= VEC ? VEC : (left > 0 ? (int)left : 0);
-        const int64_t at = nvalid > 0 ? i0 : 0;  // keep the address in range when nothing is read
-        gmem_ld8(rew + at, nvalid, rw);
-        gmem_ld8(v_s + at, nvalid, vs);
-        gmem_ld8(v_next + at, nvalid, vn);
-        wt = gmem_ld8_flags(term + at, nvalid);
-        wc = gmem_ld8_flags(trunc + at, nvalid);
-        if (g.indices != nullptr) {
-#pragma unroll
-            for (int k = 0; k < VEC; ++k) idx[k] = k < nvalid ? __ldg(g.indices + at + k) : 0;
-        }
-    }
-    // the window's map, valid in every lane
-    __device__ __forceinline__ void reduce(const FlatGather& g, double gamma, const GlPow& glp,
-                                           int lane, double& Pw, double& Xw) {
-        wc.x |= wt.x;
-        wc.y |= wt.y;
-        if (g.seg > 0) seg_cut((uint32_t)(first % g.seg), (uint32_t)g.seg, wc);
-        if (g.indices != nullptr) {  // value mask / unfinished tails live in the buffer
-            uint2 bt = make_uint2(0u, 0u), un = make_uint2(0u, 0u);
-#pragma unroll
-            for (int k = 0; k < VEC; ++k) {
-                const uint32_t bit = 1u << (8 * (k & 3));
-                if (g.buf_term != nullptr && __ldg(g.buf_term + idx[k]) != 0)
-                    (k < 4 ? bt.x : bt.y) |= bit;
-                if (g.unfinished != nullptr &&
-                    __ldg(g.unfinished + sub_of(idx[k], g.offset, g.B, g.sub_size)) == idx[k])
-                    (k < 4 ? un.x : un.y) |= bit;
-            }
-            if (g.buf_term != nullptr) wt = bt;
-            wc.x |= un.x;
-            wc.y |= un.y;
-        }
-        double P = 1.0, X = 0.0;
-#pragma unroll
-        for (int k = VEC - 1; k >= 0; --k) {  // last step first
-            if (k >= nvalid) { P = 0.0; X = 0.0; continue; }
-            const double v1 = flag_byte(wt, k) ? 0.0 : (double)vn[k];
-            const double d = fma(v1, gamma, (double)rw[k]) - (double)vs[k];
-            const bool cut = flag_byte(wc, k);
-            X = cut ? d : fma(glp.p[1], X, d);
-            P = cut ? 0.0 : P * glp.p[1];
-        }
-#pragma unroll
-        for (int dlt = 1; dlt < 32; dlt <<= 1) {
-            const double P2 = shfl_down_f64(P, dlt), X2 = shfl_down_f64(X, dlt);
-            if (lane + dlt < 32) { X = fma(P, X2, X); P *= P2; }
-        }
-        Pw = shfl_idx_f64(P, 0);
-        Xw = shfl_idx_f64(X, 0);
-    }
-};
-constexpr double kCarryNegligible = 1e-60;  // accumulated discount below which the rest is 0
+// Discount product over a ghost tile below which the carry from beyond it is taken as 0: a
+// relative error of 1e-30 of the carried advantage, fourteen orders below one f64 ulp.
+constexpr double kCarryNegligible = 1e-30;
 
 template <typename RewT, typename InT, typename OutT, int NT, bool HAS_IDX>
 struct FlatTmaLayout {
@@ -687,9 +587,23 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     const int64_t k_hi = ntiles_all - before;
     const int n_last = (int)(N16 - (ntiles_all - 1) * TILE);  // steps in the sequence's last tile
 
+    // The carry INTO the range (the advantage of step k_hi * TILE) comes from a GHOST tile: every
+    // CTA but the one that owns the end of the sequence runs its neighbour's bottom tile k_hi
+    // through the same ring and the same scan first, with zero carry-in and without storing
+    // anything.  If an episode ends anywhere in those 2048 steps (or the discount product over them
+    // is negligible) the ghost tile's head advantage IS the carry; only otherwise (no episode end
+    // and gamma * lambda ~ 1) does the CTA wait for its neighbour's published head value.  The
+    // earlier design read ahead with plain loads BEFORE the first tile: two to six dependent DRAM
+    // round trips queued behind the bulk loads of all CTAs, 4 us of every launch without indices
+    // and 10 us with them (profiles/r02_gae.md); the ghost tile costs 1 / 14 more input reads.
+    // (rows of `seg` steps packed back to back: a range that starts on a row boundary needs no
+    // carry at all -- always the case when seg divides the tile)
+    const bool ghost = blockIdx.x > 0 && ntiles > 0 &&
+                       !(g.seg > 0 && (k_hi * (int64_t)TILE) % g.seg == 0);
+    const int nit = ntiles + (ghost ? 1 : 0);
     // producer cursor (elected thread): tile p_k, descending
     int p_it = 0, p_stage = 0;
-    int64_t p_k = k_hi - 1;
+    int64_t p_k = k_hi - (ghost ? 0 : 1);
     auto issue = [&]() {
         const int n = p_k == ntiles_all - 1 ? n_last : TILE;
         const int64_t t0 = p_k * TILE;
@@ -707,12 +621,7 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
         if (++p_stage == stages) p_stage = 0;
     };
 
-    // ---- carry into the range: the advantage of step k_hi * TILE -----------------------------
-    // CTA 0: the ragged end [N16, N), at most 15 steps, one per lane, outputs included.
-    // Others: read ahead -- first 256 steps by one warp (resolves ~3 ranges in 4 on rollouts with
-    // an episode end every ~200 steps), then 2048 more by the whole CTA, then the neighbour.
-    // (Issuing the first window's reads ahead of the first bulk loads was tried: the registers it
-    // pins cost more than the queueing it avoids, 41.2 vs 38.7 us at 8.4 M steps.)
+    // ---- CTA 0: the ragged end [N16, N), at most 15 steps, one per lane, outputs included ------
     __shared__ int s_state;  // 0 unresolved, 1 resolved
     double carry = 0.0;
     const bool working = ntiles > 0 || blockIdx.x == 0;
@@ -728,7 +637,7 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     }
     pdl_wait();  // inputs and the workspace may come from the kernel before
     if (tid == 0) {
-        while (p_it < stages && p_it < ntiles) issue();
+        while (p_it < stages && p_it < nit) issue();
         if (sync != nullptr) tag = (__ldcg(sync + 1) + 1u) | 0x80000000u;
     }
     __syncthreads();
@@ -742,80 +651,35 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
             }
         }
     };
-    FlatWindow<RewT, InT> W;
-    if (working) {
-        if (blockIdx.x == 0) {
-            if (warp == 0) {  // one step per lane: loads in parallel, the recurrence by shuffles
-                const int nr = (int)(N - N16);
-                const int64_t i = N16 + lane;
-                double dl = 0.0, vsl = 0.0, mine = 0.0;
-                bool cutl = true;
-                if (lane < nr) {
-                    const int64_t idx = g.indices != nullptr ? g.indices[i] : i;
-                    bool masked;
-                    flat_flags(g, idx, term[i], trunc[i], masked, cutl);
-                    if (g.seg > 0 && (i + 1) % g.seg == 0) cutl = true;
-                    const double v1 = masked ? 0.0 : (double)v_next[i];
-                    vsl = (double)v_s[i];
-                    dl = fma(v1, gamma, (double)rew[i]) - vsl;
-                }
-                double A = 0.0;
-                for (int j = nr - 1; j >= 0; --j) {
-                    const double dj = shfl_idx_f64(dl, j);
-                    const bool cj = __shfl_sync(0xffffffffu, (int)cutl, j) != 0;
-                    A = cj ? dj : fma(glp.p[1], A, dj);
-                    if (lane == j) mine = A;
-                }
-                if (lane < nr) {
-                    adv[i] = (OutT)mine;
-                    ret[i] = (OutT)(mine + vsl);
-                }
-                if (lane == 0) { s_carry = A; s_state = 1; }
+    if (working && blockIdx.x == 0) {
+        if (warp == 0) {  // one step per lane: loads in parallel, the recurrence by shuffles
+            const int nr = (int)(N - N16);
+            const int64_t i = N16 + lane;
+            double dl = 0.0, vsl = 0.0, mine = 0.0;
+            bool cutl = true;
+            if (lane < nr) {
+                const int64_t idx = g.indices != nullptr ? g.indices[i] : i;
+                bool masked;
+                flat_flags(g, idx, term[i], trunc[i], masked, cutl);
+                if (g.seg > 0 && (i + 1) % g.seg == 0) cutl = true;
+                const double v1 = masked ? 0.0 : (double)v_next[i];
+                vsl = (double)v_s[i];
+                dl = fma(v1, gamma, (double)rew[i]) - vsl;
             }
-            __syncthreads();
-        } else {
-            double Pc = 1.0, Xc = 0.0;
-            if (warp == 0) {
-                W.load(rew, v_s, v_next, term, trunc, g, p_ahead, N, lane);
-                W.reduce(g, gamma, glp, lane, Pc, Xc);
-                if (lane == 0) {
-                    s_state = fabs(Pc) < kCarryNegligible ? 1 : 0;
-                    s_carry = Xc;
-                    sP[0] = Pc;
-                }
+            double A = 0.0;
+            for (int j = nr - 1; j >= 0; --j) {
+                const double dj = shfl_idx_f64(dl, j);
+                const bool cj = __shfl_sync(0xffffffffu, (int)cutl, j) != 0;
+                A = cj ? dj : fma(glp.p[1], A, dj);
+                if (lane == j) mine = A;
             }
-            __syncthreads();
-            if (s_state == 0) {  // CTA-uniform: the next NW * 256 steps, one window per warp
-                double Pw, Xw;
-                W.load(rew, v_s, v_next, term, trunc, g, p_ahead + 256 + (int64_t)warp * 256, N,
-                       lane);
-                W.reduce(g, gamma, glp, lane, Pw, Xw);
-                __syncthreads();  // sP[0] has been read by nobody else yet; keep it in a register
-                Pc = sP[0];
-                Xc = s_carry;
-                __syncthreads();
-                if (lane == 0) { sP[warp] = Pw; sX[warp] = Xw; }
-                __syncthreads();
-                if (tid == 0) {
-                    for (int w = 0; w < NW && fabs(Pc) >= kCarryNegligible; ++w) {
-                        Xc = fma(Pc, sX[w], Xc);
-                        Pc *= sP[w];
-                    }
-                    if (fabs(Pc) >= kCarryNegligible && head_flags != nullptr) {
-                        // no boundary within reach: the neighbour's published head value
-                        // (never with row segments: a row end lies within the 2304 steps read)
-                        unsigned int f;
-                        do {
-                            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];"
-                                         : "=r"(f) : "l"(head_flags + blockIdx.x - 1) : "memory");
-                        } while (f != tag);
-                        Xc = __ldcg(heads + blockIdx.x - 1);
-                    }
-                    s_carry = Xc;
-                }
-                __syncthreads();
+            if (lane < nr) {
+                adv[i] = (OutT)mine;
+                ret[i] = (OutT)(mine + vsl);
             }
+            if (lane == 0) { s_carry = A; s_state = 1; }
         }
+        __syncthreads();
         carry = s_carry;
     }
     __syncthreads();
@@ -831,12 +695,13 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
 
     int stage = 0;
     uint32_t parity = 0;
-    int64_t k = k_hi - 1;
+    int64_t k = k_hi - (ghost ? 0 : 1);
     // row position of the current tile's first step, kept incrementally (tiles go down by TILE)
     const uint32_t seg = (uint32_t)g.seg;
     uint32_t r_tile = seg ? (uint32_t)((k * TILE) % g.seg) : 0u;
     const uint32_t r_back = seg ? seg - (uint32_t)(TILE % g.seg) : 0u;
-    for (int it = 0; it < ntiles; ++it, --k) {
+    for (int it = 0; it < nit; ++it, --k) {
+        const bool is_ghost = ghost && it == 0;  // the neighbour's tile: scanned, not stored
         const int n = k == ntiles_all - 1 ? n_last : TILE;
         mbar_wait(bar0 + 8u * stage, parity);
 
@@ -944,7 +809,7 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
         if (lane == 0) { sP[warp] = P; sX[warp] = X; }
         if (tid == 0) bulk_wait_read0();
         __syncthreads();
-        if (tid == 0 && p_it < ntiles) issue();
+        if (tid == 0 && p_it < nit) issue();
 
         double cin = carry;
 #pragma unroll
@@ -957,14 +822,34 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
             if (no_flag_from(wc, q)) d[q] = fma(glp.p[VEC - q], cin, d[q]);
             r_out[q] = d[q] + (double)vs[q];
         }
-        if (live) {
+        if (live && !is_ghost) {
             smem_st8(s_adv + e0, d);
             smem_st8(s_ret + e0, r_out);
         }
         fence_proxy_async_smem();
-        if (tid == 0) s_carry = d[0];
-        __syncthreads();
         if (tid == 0) {
+            double head = d[0];  // the advantage of the tile's first step
+            if (is_ghost) {
+                // exact iff the carry from beyond the ghost tile cannot reach its first step
+                double Pt = 1.0;
+#pragma unroll
+                for (int w = 0; w < NW; ++w) Pt *= sP[w];
+                if (fabs(Pt) >= kCarryNegligible && head_flags != nullptr) {
+                    // no episode end in 2048 steps and no discount to speak of: the neighbour's
+                    // published head value (the chain starts at CTA 0, which never waits; all
+                    // CTAs of the launch are co-resident).  Never with row segments.
+                    unsigned int f;
+                    do {
+                        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];"
+                                     : "=r"(f) : "l"(head_flags + blockIdx.x - 1) : "memory");
+                    } while (f != tag);
+                    head = __ldcg(heads + blockIdx.x - 1);
+                }
+            }
+            s_carry = head;
+        }
+        __syncthreads();
+        if (tid == 0 && !is_ghost) {
             const int64_t t0 = k * TILE;
             bulk_s2g(adv + t0, smem_u32(s_adv), (uint32_t)n * sizeof(OutT));
             bulk_s2g(ret + t0, smem_u32(s_ret), (uint32_t)n * sizeof(OutT));
