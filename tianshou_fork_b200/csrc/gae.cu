@@ -353,8 +353,10 @@ gae_rows_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     constexpr int NW = NT / 32;
     static_assert(NW > 1 && NW <= 8, "cross-warp step assumes 2..8 warps");
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ double sP[NW], sX[NW];
-    __shared__ double s_carry;
+    // double-buffered by tile parity: only the storing warp waits at a tile's end (see below)
+    __shared__ double sP[2][NW], sX[2][NW];
+    __shared__ double s_carry[2];
+    constexpr int STORER = NT - 32;  // lane 0 of the last warp issues the bulk stores
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int e0 = tid * VEC;
@@ -400,11 +402,10 @@ gae_rows_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     // consumer cursor (all threads)
     int row = blockIdx.x, c = nchunks - 1, stage = 0;
     uint32_t parity = 0;
-    double carry = 0.0;
     for (int it = 0; it < ntiles; ++it) {
+        const int b = it & 1;
         const bool row_end = c == nchunks - 1;  // this tile holds the stream's last step
         const int n = row_end ? n_first : TILE;
-        if (row_end) carry = 0.0;               // nothing beyond the end of the stream
         mbar_wait(bar0 + 8u * stage, parity);
 
         const unsigned char* in = smem + (size_t)stage * L::IN_BYTES;
@@ -449,17 +450,18 @@ gae_rows_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
         // map of the lanes after this one
         double eP = shfl_down_f64(P, 1), eX = shfl_down_f64(X, 1);
         if (lane == 31) { eP = 1.0; eX = 0.0; }
-        if (lane == 0) { sP[warp] = P; sX[warp] = X; }
-        if (tid == 0) bulk_wait_read0();  // previous tile's stores have left the out buffer
+        if (lane == 0) { sP[b][warp] = P; sX[b][warp] = X; }
+        if (tid == STORER) bulk_wait_read0();  // previous tile's stores have left the out buffer
         __syncthreads();
         // every thread holds its strip in registers: the stage can be refilled
         if (tid == 0 && p_it < ntiles) issue();
 
-        // carry into this thread's strip: through the later warps, then the later lanes
-        double cin = carry;
+        // carry into this thread's strip: the advantage at the previous tile's first step (nothing
+        // beyond the end of a stream), through the later warps, then the later lanes
+        double cin = row_end ? 0.0 : s_carry[b ^ 1];
 #pragma unroll
         for (int w = NW - 1; w >= 1; --w)
-            if (w > warp) cin = fma(sP[w], cin, sX[w]);
+            if (w > warp) cin = fma(sP[b][w], cin, sX[b][w]);
         cin = fma(eP, cin, eX);
         // A_k = d[k] + gl^(8-k) * cin while no episode ends in k..7
         double r_out[VEC];
@@ -473,19 +475,25 @@ gae_rows_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
             smem_st8(s_ret + e0, r_out);
         }
         fence_proxy_async_smem();
-        if (tid == 0) s_carry = d[0];  // advantage at the tile's first step
-        __syncthreads();
-        if (tid == 0) {
-            const int64_t v = (int64_t)row * val_stride + (int64_t)c * TILE;
-            bulk_s2g(adv + v, smem_u32(s_adv), (uint32_t)n * sizeof(OutT));
-            bulk_s2g(ret + v, smem_u32(s_ret), (uint32_t)n * sizeof(OutT));
-            bulk_commit();
+        if (tid == 0) s_carry[b] = d[0];  // advantage at the tile's first step
+        // End of tile: only the storing warp waits for the staged outputs (named barrier 1); the
+        // others arrive and go on to the next tile's loads and strip arithmetic.  The next tile's
+        // __syncthreads orders s_carry / sP / sX (other parity) and the reuse of the out buffer.
+        if (warp == NW - 1) {
+            named_bar_sync(1, NT);
+            if (lane == 0) {
+                const int64_t v = (int64_t)row * val_stride + (int64_t)c * TILE;
+                bulk_s2g(adv + v, smem_u32(s_adv), (uint32_t)n * sizeof(OutT));
+                bulk_s2g(ret + v, smem_u32(s_ret), (uint32_t)n * sizeof(OutT));
+                bulk_commit();
+            }
+        } else {
+            named_bar_arrive(1, NT);
         }
-        carry = s_carry;
         if (--c < 0) { c = nchunks - 1; row += gridDim.x; }
         if (++stage == stages) { stage = 0; parity ^= 1u; }
     }
-    if (tid == 0) bulk_wait0();
+    if (tid == STORER) bulk_wait0();
 }
 
 // ============================================================================================
@@ -567,8 +575,10 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     constexpr int NW = NT / 32;
     static_assert(NW > 1 && NW <= 8, "cross-warp step assumes 2..8 warps");
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ double sP[NW], sX[NW];
-    __shared__ double s_carry;
+    // double-buffered by tile parity: only the storing warp waits at a tile's end (gae_rows_tma_kernel)
+    __shared__ double sP[2][NW], sX[2][NW];
+    __shared__ double s_carry[2];
+    constexpr int STORER = NT - 32;  // lane 0 of the last warp issues the bulk stores
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int e0 = tid * VEC;
@@ -622,8 +632,7 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     };
 
     // ---- CTA 0: the ragged end [N16, N), at most 15 steps, one per lane, outputs included ------
-    __shared__ int s_state;  // 0 unresolved, 1 resolved
-    double carry = 0.0;
+    if (tid == 0) s_carry[1] = 0.0;  // slot of the tile "before" the first one
     const bool working = ntiles > 0 || blockIdx.x == 0;
     const int64_t p_ahead = k_hi * TILE;
     pdl_launch_dependents();
@@ -677,15 +686,13 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
                 adv[i] = (OutT)mine;
                 ret[i] = (OutT)(mine + vsl);
             }
-            if (lane == 0) { s_carry = A; s_state = 1; }
+            if (lane == 0) s_carry[1] = A;
         }
-        __syncthreads();
-        carry = s_carry;
     }
     __syncthreads();
     if (ntiles == 0) {  // nothing but (for CTA 0) the ragged end: pass the value on
         if (blockIdx.x == 0 && tid == 0 && heads != nullptr) {
-            heads[0] = carry;
+            heads[0] = s_carry[1];
             __threadfence();
             *(volatile unsigned int*)head_flags = tag;
         }
@@ -701,6 +708,7 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     uint32_t r_tile = seg ? (uint32_t)((k * TILE) % g.seg) : 0u;
     const uint32_t r_back = seg ? seg - (uint32_t)(TILE % g.seg) : 0u;
     for (int it = 0; it < nit; ++it, --k) {
+        const int b = it & 1;
         const bool is_ghost = ghost && it == 0;  // the neighbour's tile: scanned, not stored
         const int n = k == ntiles_all - 1 ? n_last : TILE;
         mbar_wait(bar0 + 8u * stage, parity);
@@ -806,15 +814,15 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
         }
         double eP = shfl_down_f64(P, 1), eX = shfl_down_f64(X, 1);
         if (lane == 31) { eP = 1.0; eX = 0.0; }
-        if (lane == 0) { sP[warp] = P; sX[warp] = X; }
-        if (tid == 0) bulk_wait_read0();
+        if (lane == 0) { sP[b][warp] = P; sX[b][warp] = X; }
+        if (tid == STORER) bulk_wait_read0();
         __syncthreads();
         if (tid == 0 && p_it < nit) issue();
 
-        double cin = carry;
+        double cin = s_carry[b ^ 1];  // the advantage at the previous tile's first step
 #pragma unroll
         for (int w = NW - 1; w >= 1; --w)
-            if (w > warp) cin = fma(sP[w], cin, sX[w]);
+            if (w > warp) cin = fma(sP[b][w], cin, sX[b][w]);
         cin = fma(eP, cin, eX);
         double r_out[VEC];
 #pragma unroll
@@ -833,7 +841,7 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
                 // exact iff the carry from beyond the ghost tile cannot reach its first step
                 double Pt = 1.0;
 #pragma unroll
-                for (int w = 0; w < NW; ++w) Pt *= sP[w];
+                for (int w = 0; w < NW; ++w) Pt *= sP[b][w];
                 if (fabs(Pt) >= kCarryNegligible && head_flags != nullptr) {
                     // no episode end in 2048 steps and no discount to speak of: the neighbour's
                     // published head value (the chain starts at CTA 0, which never waits; all
@@ -846,26 +854,32 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
                     head = __ldcg(heads + blockIdx.x - 1);
                 }
             }
-            s_carry = head;
+            s_carry[b] = head;
         }
-        __syncthreads();
-        if (tid == 0 && !is_ghost) {
-            const int64_t t0 = k * TILE;
-            bulk_s2g(adv + t0, smem_u32(s_adv), (uint32_t)n * sizeof(OutT));
-            bulk_s2g(ret + t0, smem_u32(s_ret), (uint32_t)n * sizeof(OutT));
-            bulk_commit();
+        // only the storing warp waits for the staged outputs; the next tile's __syncthreads orders
+        // s_carry / sP / sX (other parity) and the reuse of the out buffer
+        if (!is_ghost) {
+            if (warp == NW - 1) {
+                named_bar_sync(1, NT);
+                if (lane == 0) {
+                    const int64_t t0 = k * TILE;
+                    bulk_s2g(adv + t0, smem_u32(s_adv), (uint32_t)n * sizeof(OutT));
+                    bulk_s2g(ret + t0, smem_u32(s_ret), (uint32_t)n * sizeof(OutT));
+                    bulk_commit();
+                }
+            } else {
+                named_bar_arrive(1, NT);
+            }
         }
-        carry = s_carry;
         if (++stage == stages) { stage = 0; parity ^= 1u; }
     }
-    if (tid == 0) {
-        if (heads != nullptr) {
-            heads[blockIdx.x] = carry;  // this range's first advantage, for a waiting neighbour
-            __threadfence();
-            *(volatile unsigned int*)(head_flags + blockIdx.x) = tag;
-        }
-        bulk_wait0();
+    if (tid == 0 && heads != nullptr) {
+        // this range's first advantage (written by this thread), for a waiting neighbour
+        heads[blockIdx.x] = s_carry[(nit - 1) & 1];
+        __threadfence();
+        *(volatile unsigned int*)(head_flags + blockIdx.x) = tag;
     }
+    if (tid == STORER) bulk_wait0();
     leave();
 }
 

@@ -172,6 +172,14 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+// named barriers (1..15; 0 is __syncthreads): `threads` = arrivals that complete it, a multiple of 32
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void named_bar_arrive(int id, int threads) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
 // Tuning knobs (ts_tune_set): 0 = automatic choice.
 extern int g_tune_gae_rows_variant;
 extern int g_tune_gae_flat_variant;  // 0 auto, 1 decoupled look-back, 2 pipelined ranges
