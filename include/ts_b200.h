@@ -295,6 +295,23 @@ int32_t ts_per_sample_p2p(const double* tree, int64_t bound, const double* u, in
                           double* slots, double* const* peer_slots, uint64_t* state, int32_t G,
                           int32_t rank, double* prio, double beta, int32_t weight_norm,
                           int64_t* idx, double* weight, int32_t* err_flag, ts_stream_t stream);
+/* The same pair with a hand-over for batches larger than one update pass (4096 entries): with G
+ * shards a rank owns ~M / G of the M draws, but ts_per_update_publish has to scan all M entries
+ * of `idx` (in every CTA) to find them.  `owned` is int32[4 + M] on the device, zero-initialised
+ * once: the sampling kernel appends the batch positions it owns and leaves their count in
+ * owned[2]; the update of the SAME, unmodified `idx` then visits only those.  owned == NULL gives
+ * the plain entry points.  (No reference counterpart: prio.py:78-89 is one NumPy assignment.) */
+int32_t ts_per_sample_p2p_owned(const double* tree, int64_t bound, const double* u, int64_t M,
+                                double* slots, double* const* peer_slots, uint64_t* state,
+                                int32_t G, int32_t rank, double* prio, double beta,
+                                int32_t weight_norm, int64_t* idx, double* weight, int32_t* owned,
+                                int32_t* err_flag, ts_stream_t stream);
+int32_t ts_per_update_publish_owned(double* tree, int64_t size, int64_t bound, const int64_t* idx,
+                                    const void* td, int32_t td_dtype, int64_t M, double alpha,
+                                    double* prio, uint32_t* stamp, uint32_t* counter,
+                                    int32_t* err_flag, uint64_t* state,
+                                    double* const* peer_slots, int32_t G, int32_t rank,
+                                    const int32_t* owned, ts_stream_t stream);
 /* weight[j] /= *wmax  (prio.py:101) */
 int32_t ts_per_normalize(double* weight, int64_t M, const double* wmax, ts_stream_t stream);
 /* get_weight on given indices (prio.py:66-76), optional batch-max normalisation (:101);

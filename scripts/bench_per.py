@@ -124,7 +124,8 @@ def run_single(torch, L, lib, dev, barrier, max_over_ranks):
     }
 
 
-def _parity_check(torch, dist, L, lib, dev, rank, world, sh, step_one, u_all, td_all, idx, steps=3):
+def _parity_check(torch, dist, L, lib, dev, rank, world, sh, step_one, u_all, td_all, idx, steps=3,
+                  reread=False):
     """Rank 0 compares the first `steps` draws of the sharded path with the oracle's SINGLE global
     tree of world * 2^20 leaves (manager.py:209-214) on identical uniforms.  After every
     update_weight the oracle's touched leaves are re-anchored on the GPU's (NumPy's f32 `power`
@@ -133,9 +134,16 @@ def _parity_check(torch, dist, L, lib, dev, rank, world, sh, step_one, u_all, td
     from oracle import oracle as orc  # checker only (task statement 4: bench N > 1 parity)
     M = u_all.shape[1]
     ref = None
+    if reread:  # the shards have been updated since they were filled: gather their leaves as they are
+        mine_l = sh.tree[PER_LEAVES:].clone()
+        all_l = [torch.empty_like(mine_l) for _ in range(world)]
+        dist.all_gather(all_l, mine_l)
+        start = torch.cat(all_l).cpu().numpy() if rank == 0 else None
+    elif rank == 0:
+        start = np.concatenate([shard_leaves(r) for r in range(world)])
     if rank == 0:
         ref = orc.SegTree(world * PER_LEAVES)
-        ref[np.arange(world * PER_LEAVES)] = np.concatenate([shard_leaves(r) for r in range(world)])
+        ref[np.arange(world * PER_LEAVES)] = start
     st = torch.cuda.current_stream().cuda_stream
     mism = 0
     for k in range(steps):
@@ -184,6 +192,7 @@ def run_sharded(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
     hdl = symm_mem.rendezvous(slots, dist.group.WORLD)
     peers = int(hdl.buffer_ptrs_dev)
     state = torch.zeros(2, dtype=torch.int64, device=dev)
+    own_list = torch.zeros(4 + PER_BATCH * world, dtype=torch.int32, device=dev)  # weak leg's owner list
     torch.cuda.synchronize()
     dist.barrier()
     t = sh.tree.data_ptr()
@@ -191,7 +200,7 @@ def run_sharded(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
     L.check(lib.ts_per_publish(t, sh.prio.data_ptr(), state.data_ptr(), peers, world, rank, st0),
             "ts_per_publish")
     legs = {}
-    parity = None
+    parity = weak_parity = None
     for leg, M in (("strong", PER_BATCH), ("weak", PER_BATCH * world)):
         shared = np.random.default_rng(2 + M)  # the same draws on every rank
         u = torch.from_numpy(shared.random((R, M))).to(dev)
@@ -200,22 +209,31 @@ def run_sharded(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
         w = torch.empty(R, M, dtype=torch.float64, device=dev)
 
         def step(r, s, sample=True, update=True, M=M, u=u, td=td, idx=idx, w=w):
+            # batches of more than one update pass hand the owned positions from the sampler to
+            # the update (what ShardedPrioritizedVectorReplayBuffer does for them)
+            own = own_list.data_ptr() if M > PER_BATCH and os.environ.get("TS_PER_NO_OWNED") != "1" else None
             if sample:
-                L.check(lib.ts_per_sample_p2p(
+                L.check(lib.ts_per_sample_p2p_owned(
                     t, bound, u[r].data_ptr(), M, slots.data_ptr(), peers, state.data_ptr(), world,
-                    rank, sh.prio.data_ptr(), PER_BETA, 1, idx[r].data_ptr(), w[r].data_ptr(),
-                    sh.err.data_ptr(), s), "ts_per_sample_p2p")
+                    rank, sh.prio.data_ptr(), PER_BETA, 1, idx[r].data_ptr(), w[r].data_ptr(), own,
+                    sh.err.data_ptr(), s), "ts_per_sample_p2p_owned")
             if update:
-                L.check(lib.ts_per_update_publish(
+                L.check(lib.ts_per_update_publish_owned(
                     t, size, bound, idx[r].data_ptr(), td[r].data_ptr(), L.TS_F32, M, PER_ALPHA,
                     sh.prio.data_ptr(), sh.stamp.data_ptr(), sh.counter.data_ptr(),
-                    sh.err.data_ptr(), state.data_ptr(), peers, world, rank, s),
-                    "ts_per_update_publish")
+                    sh.err.data_ptr(), state.data_ptr(), peers, world, rank, own, s),
+                    "ts_per_update_publish_owned")
 
         note(f"sharded leg {leg}, global batch {M}")
+        # both legs start from the leaves the oracle is built from only in the strong leg; the
+        # weak leg's check re-reads this rank's leaves first
+        check = _parity_check(torch, dist, L, lib, dev, rank, world, sh, step, u, td, idx,
+                              steps=3 if leg == "strong" else 2, reread=leg != "strong")
         if leg == "strong":
-            parity = _parity_check(torch, dist, L, lib, dev, rank, world, sh, step, u, td, idx)
-        note("parity done, timing" if leg == "strong" else "timing")
+            parity = check
+        else:
+            weak_parity = check["parity"]
+        note("parity done, timing")
         ms, steps = time_graph(torch, dev, step, barrier)
         ms = max_over_ranks(ms)
         owned = (idx >= 0).sum().to(torch.float64)
@@ -226,7 +244,9 @@ def run_sharded(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
     assert int(sh.err.item()) == 0, "PER range / peer-timeout flag raised"
     return {
         "value": legs["strong"]["value"], "us_per_step": legs["strong"]["us_per_step"],
-        "strong": legs["strong"], "weak": legs["weak"], **parity, "gpu_launches_per_step": 2,
+        "strong": legs["strong"], "weak": {**legs["weak"], "parity": weak_parity,
+                                            "owner_list": os.environ.get("TS_PER_NO_OWNED") != "1"},
+        **parity, "gpu_launches_per_step": 2,
         "scaling": "strong (global batch 4096 over all shards) in `value`; weak (4096 per rank) "
                    "in `weak`",
         "how": "8 steps per CUDA graph; ts_per_sample_p2p + ts_per_update_publish: shard records "

@@ -72,6 +72,29 @@ def main():
             buf.weight[torch.from_numpy(ch).to(dev)] = torch.from_numpy(ref_l[ch]).to(dev)
         buf.sync_roots()
         buf.check_errors()
+    # ---- a batch of several update passes (4096 * world draws): the sampler's owner list ---------
+    big = 4096 * world + 123
+    for step in range(3):
+        u = rng.random(big)
+        want = glob.sample_indices(u)
+        idx = buf.sample_with_uniforms(torch.from_numpy(u).to(dev))
+        own = idx >= 0
+        gi = buf.to_global(idx).cpu().numpy()
+        m = own.cpu().numpy()
+        assert np.array_equal(gi[m], want[m]), (rank, "big", step)
+        if mode == "p2p":
+            assert buf._owned_src is not None and int(buf._owned[2]) == int(own.sum()), "owner list"
+        td = rng.standard_normal(big).astype(np.float32)
+        glob.update_weight(want, td)
+        buf.update_weight(idx, torch.from_numpy(td).to(dev))  # the sampler's own tensor: listed scan
+        got_l = buf.weight._value[cap:].cpu().numpy()
+        ref_l = glob.weight._value[total + rank * cap: total + (rank + 1) * cap]
+        assert np.allclose(got_l, ref_l, rtol=6e-7, atol=0), (rank, "big", step)
+        ch = np.nonzero(got_l != ref_l)[0]
+        if ch.size:
+            buf.weight[torch.from_numpy(ch).to(dev)] = torch.from_numpy(ref_l[ch]).to(dev)
+        buf.sync_roots()
+        buf.check_errors()
     # prev / next / n-step on the sharded buffer in this exchange mode (ReplayBuffer._state must
     # stay callable next to the exchange's own state words)
     buf._meta = ts.Batch(rew=torch.zeros(cap, dtype=torch.float64, device=dev),
@@ -116,7 +139,9 @@ def main():
     if rank == 0:
         print(f"sharded PER check ok: world={world} exchange={mode} "
               f"step={float(t):.1f} us (device, max over ranks) wall={wall:.1f} us", flush=True)
-    dist.destroy_process_group()
+    dist.barrier()
+    sys.stdout.flush()
+    os._exit(0)  # destroy_process_group() has hung after symmetric-memory use (profiles/r02_per.md)
 
 
 if __name__ == "__main__":

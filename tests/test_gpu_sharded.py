@@ -221,3 +221,83 @@ def test_p2p_protocol_emulated_on_one_gpu(G, cap, bsz):
                                               L.ptr(d["counter"]), L.ptr(d["err"]), L.stream()),
                         "anchor")
         publish_all()
+
+
+@pytest.mark.parametrize("G,cap,bsz", [(8, 1 << 15, 3 * 4096 + 37), (2, 1 << 13, 28800)])
+def test_p2p_owned_list_emulated_on_one_gpu(G, cap, bsz):
+    """Batches larger than one update pass: ts_per_sample_p2p_owned lists the batch positions a
+    rank owns (second case: more per CTA than its shared-memory list holds), and
+    ts_per_update_publish_owned, scanning only those, leaves exactly the tree that the plain
+    ts_per_update leaves after scanning the whole batch."""
+    from tianshou_fork_b200 import _lib as L
+    lib = L.lib()
+    rng = np.random.default_rng(G * 17 + 5)
+    total = G * cap
+    leaves = (np.abs(rng.standard_normal(total)) + 1e-7) ** 0.6
+    glob = orc.PER(total, 0.6, 0.4)
+    glob.weight[np.arange(total)] = leaves
+    ranks = []
+    for r in range(G):
+        d = dict(tree=torch.zeros(2 * cap, dtype=torch.float64, device="cuda"),
+                 stamp=torch.zeros(cap, dtype=torch.int32, device="cuda"),
+                 counter=torch.zeros(4, dtype=torch.int32, device="cuda"),
+                 err=torch.zeros(1, dtype=torch.int32, device="cuda"),
+                 prio=torch.ones(2, dtype=torch.float64, device="cuda"),
+                 slots=torch.zeros(12 * G, dtype=torch.float64, device="cuda"),
+                 state=torch.zeros(2, dtype=torch.int64, device="cuda"),
+                 owned=torch.zeros(4 + bsz, dtype=torch.int32, device="cuda"))
+        _fill(d["tree"], d["stamp"], d["counter"], d["err"], leaves[r * cap:(r + 1) * cap], L)
+        ranks.append(d)
+    peers = torch.tensor([d["slots"].data_ptr() for d in ranks], dtype=torch.int64, device="cuda")
+    for r, d in enumerate(ranks):
+        L.check(lib.ts_per_publish(L.ptr(d["tree"]), L.ptr(d["prio"]), L.ptr(d["state"]),
+                                   L.ptr(peers), G, r, L.stream()), "publish")
+    for step in range(3):
+        u = rng.random(bsz)
+        want = glob.sample_indices(u)
+        ud = torch.from_numpy(u).cuda()
+        td = rng.standard_normal(bsz).astype(np.float32)
+        tdd = torch.from_numpy(td).cuda()
+        idxs = []
+        for r, d in enumerate(ranks):
+            idx = torch.empty(bsz, dtype=torch.int64, device="cuda")
+            w = torch.empty(bsz, dtype=torch.float64, device="cuda")
+            L.check(lib.ts_per_sample_p2p_owned(
+                L.ptr(d["tree"]), cap, L.ptr(ud), bsz, L.ptr(d["slots"]), L.ptr(peers),
+                L.ptr(d["state"]), G, r, L.ptr(d["prio"]), 0.4, 0, L.ptr(idx), L.ptr(w),
+                L.ptr(d["owned"]), L.ptr(d["err"]), L.stream()), "sample_p2p_owned")
+            idxs.append(idx)
+            mine = torch.nonzero(idx >= 0).reshape(-1)
+            n = int(d["owned"][2])
+            assert n == mine.numel(), (r, step, n, mine.numel())
+            listed = d["owned"][4:4 + n].to(torch.int64).sort().values
+            assert torch.equal(listed, mine), (r, step)
+        got = sum(torch.where(i >= 0, i + r * cap, torch.zeros_like(i))
+                  for r, i in enumerate(idxs)).cpu().numpy()
+        assert np.array_equal(got, want), (G, step)
+        glob.update_weight(want, td)
+        for r, d in enumerate(ranks):
+            # the plain update on a copy of the shard: scans all bsz entries
+            ref_tree, ref_prio = d["tree"].clone(), d["prio"].clone()
+            L.check(lib.ts_per_update(L.ptr(ref_tree), cap, cap, L.ptr(idxs[r]), L.ptr(tdd),
+                                      L.TS_F32, bsz, 0.6, L.ptr(ref_prio), L.ptr(d["stamp"]),
+                                      L.ptr(d["counter"]), L.ptr(d["err"]), L.stream()), "update")
+            L.check(lib.ts_per_update_publish_owned(
+                L.ptr(d["tree"]), cap, cap, L.ptr(idxs[r]), L.ptr(tdd), L.TS_F32, bsz, 0.6,
+                L.ptr(d["prio"]), L.ptr(d["stamp"]), L.ptr(d["counter"]), L.ptr(d["err"]),
+                L.ptr(d["state"]), L.ptr(peers), G, r, L.ptr(d["owned"]), L.stream()),
+                "update_publish_owned")
+            assert torch.equal(d["tree"], ref_tree), (r, step)
+            assert torch.equal(d["prio"], ref_prio), (r, step)
+            assert int(d["err"].item()) == 0
+            # re-anchor the touched leaves on the oracle's f32 powers, then publish again
+            loc = idxs[r][idxs[r] >= 0].unique()
+            if loc.numel():
+                vals = torch.from_numpy(glob.weight[loc.cpu().numpy() + r * cap]).cuda()
+                L.check(lib.ts_segtree_update(L.ptr(d["tree"]), cap, cap, L.ptr(loc), L.ptr(vals),
+                                              L.TS_F64, 1, loc.numel(), L.ptr(d["stamp"]),
+                                              L.ptr(d["counter"]), L.ptr(d["err"]), L.stream()),
+                        "anchor")
+        for r, d in enumerate(ranks):
+            L.check(lib.ts_per_publish(L.ptr(d["tree"]), L.ptr(d["prio"]), L.ptr(d["state"]),
+                                       L.ptr(peers), G, r, L.stream()), "publish")

@@ -155,6 +155,10 @@ struct PublishInfo {
     unsigned long long* state;
     double* const* peer_slots;
     int G, rank;
+    // Optional hand-over from ts_per_sample_p2p_owned (nullptr: none): int32[4 + capacity] =
+    // {accumulator of even draws, of odd draws, count of the latest draw, -, batch positions this
+    // rank owns ...}.  With it the update scans count ~ M / G positions instead of all M.
+    const int32_t* owned = nullptr;
 };
 // G threads: store {root, max_prio, min_prio, epoch} into every peer's slot buffer
 __device__ __forceinline__ void publish_record(const double* tree, const double* prio,
@@ -631,14 +635,31 @@ segtree_update_ranged(double* __restrict__ tree, int64_t size, int lg_bound, int
     double pmax = 0.0, pmin = INFINITY;                 // VM_PER_F64
     uint32_t fmax_bits = 0u, fmin_bits = 0x7f800000u;   // VM_PER_F32: positive floats order like bits
     int pass = 0;
-    for (int64_t j0 = 0; j0 < M; j0 += kPass, pass ^= 1) {
+    // A batch of several passes whose owner list came with it (sharded sampling: most entries are
+    // "not in this shard"): scan the listed positions only.  The first pass's list entries are
+    // fetched together with the count (the list's capacity is >= M > kPass: always in bounds).
+    const bool listed = pub.owned != nullptr && M > kPass;
+    int64_t Mscan = M;
+    int first_j[kRangeUnroll];
+    if (listed) {
+#pragma unroll
+        for (int q = 0; q < kRangeUnroll; ++q) first_j[q] = __ldcg(pub.owned + 4 + q * RANGE_NT + tid);
+        Mscan = (int64_t)__ldcg(pub.owned + 2);
+        if (Mscan > M) Mscan = M;
+    }
+    for (int64_t j0 = 0; j0 < Mscan; j0 += kPass, pass ^= 1) {
         int64_t id[kRangeUnroll];
         float tdf[kRangeUnroll];
+        int jj[kRangeUnroll];  // batch position (M < 2^31 checked by the host)
 #pragma unroll
         for (int q = 0; q < kRangeUnroll; ++q) {
-            const int64_t j = j0 + (int64_t)q * RANGE_NT + tid;
-            id[q] = j < M ? __ldg(index + j) : kSkipIndex;
-            tdf[q] = PERF32 && j < M ? __ldg((const float*)vs.ptr + j) : 0.f;
+            const int64_t i = j0 + (int64_t)q * RANGE_NT + tid;
+            int j = i < Mscan ? (int)i : -1;
+            if (listed && j >= 0) j = j0 == 0 ? first_j[q] : __ldcg(pub.owned + 4 + i);
+            if (listed && (j < 0 || j >= M)) j = -1;  // a corrupt list must not read out of bounds
+            jj[q] = j;
+            id[q] = j >= 0 ? __ldg(index + j) : kSkipIndex;
+            tdf[q] = PERF32 && j >= 0 ? __ldg((const float*)vs.ptr + j) : 0.f;
         }
         if (audits) {
 #pragma unroll
@@ -650,7 +671,7 @@ segtree_update_ranged(double* __restrict__ tree, int64_t size, int lg_bound, int
                     fmax_bits = max(fmax_bits, pb);
                     fmin_bits = min(fmin_bits, pb);
                 } else if (tracks_prio) {
-                    const double p = per_priority_cold(vs, j0 + (int64_t)q * RANGE_NT + tid);
+                    const double p = per_priority_cold(vs, (int64_t)jj[q]);
                     pmax = fmax(pmax, p);
                     pmin = fmin(pmin, p);
                 }
@@ -659,7 +680,7 @@ segtree_update_ranged(double* __restrict__ tree, int64_t size, int lg_bound, int
         }
 #pragma unroll
         for (int q = 0; q < kRangeUnroll; ++q) {
-            const int64_t j = j0 + (int64_t)q * RANGE_NT + tid;
+            const int64_t j = jj[q];
             const int64_t rel = id[q] - lo;
             if (id[q] == kSkipIndex || rel < 0 || rel >= L || id[q] >= size) continue;
             s_touched[rel >> 7] = 1u;
@@ -1244,6 +1265,7 @@ struct ShardInfo {
     double* slots;                       // P2P mode: this rank's slot buffer, 12 * G doubles
     double* const* peer_slots;           // P2P mode: device array of the G ranks' slot buffers
     unsigned long long* state;           // P2P mode: {records published, samples drawn} by this rank
+    int32_t* owned = nullptr;            // P2P mode, optional: see PublishInfo::owned
 };
 // SHARD: 0 = one GPU (no exchange code in the instantiation at all), 1 = NCCL mode, 2 = P2P mode
 template <bool SAMPLE, int NT, int SHARD>
@@ -1338,8 +1360,17 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
     // of 1).  So the sweeps only ROUTE (shared-memory top of the global tree) and append the owned
     // draws to a CTA-wide list; the descents then run densely, one per thread.
     constexpr bool compact = SAMPLE && sharded;
+    __shared__ unsigned int s_obase;
+    // owned-position list for the update that follows (accumulator slot = parity of the draw number;
+    // the lead CTA clears the other slot for the next draw: nobody touches it during this launch)
+    unsigned int* const o_acc = p2p && sh.owned != nullptr
+        ? reinterpret_cast<unsigned int*>(sh.owned) + (draw & 1ull) : nullptr;
     if (compact) {
-        if (tid == 0) s_nlist = 0u;
+        if (tid == 0) {
+            s_nlist = 0u;
+            if (o_acc != nullptr && cluster_ctarank() == 0)
+                reinterpret_cast<unsigned int*>(sh.owned)[(draw & 1ull) ^ 1ull] = 0u;
+        }
         __syncthreads();
         for (int64_t j = j0; j < M; j += sweep) {
             double v = __dmul_rn(j == j0 ? u_first : u[j], total);  // prio.py:61
@@ -1360,6 +1391,7 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
                                               (unsigned long long)__double_as_longlong(v));
             } else {  // far more than this CTA's share lands in this shard: finish it here
                 double leaf_val = 0.0;
+                if (o_acc != nullptr) sh.owned[4 + atomicAdd(o_acc, 1u)] = (int32_t)j;
                 idx[j] = descend<double>(tree, bound, lg_bound, s_top, cached, v, &leaf_val);
                 const double w = is_weight(leaf_val, min_prio, beta);
                 weight[j] = w;
@@ -1368,6 +1400,7 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
         }
         __syncthreads();
         const unsigned int n = min(s_nlist, (unsigned)kOwnedList);
+        if (o_acc != nullptr && tid == 0 && n > 0) s_obase = atomicAdd(o_acc, n);
         for (unsigned int i = tid; i < n; i += NT) {
             const ulonglong2 it = s_list[i];
             double v = __longlong_as_double((long long)it.y), leaf_val = 0.0;
@@ -1378,6 +1411,8 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
             wmax = fmax(wmax, w);
         }
         __syncthreads();  // the raw weights of this CTA's positions are all in place
+        if (o_acc != nullptr)
+            for (unsigned int i = tid; i < n; i += NT) sh.owned[4 + s_obase + i] = (int32_t)s_list[i].x;
     }
     for (int64_t j = j0; !compact && j < M; j += sweep) {
         int64_t leaf;
@@ -1422,6 +1457,8 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
         }
         if (!weight_norm) cluster_sync_all();  // every CTA has read `state` before it moves
         if (lead && tid == 0) {
+            // (a cluster barrier lies behind us: every CTA's additions to the accumulator are done)
+            if (o_acc != nullptr) sh.owned[2] = (int32_t)__ldcg(o_acc);
             sh.state[1] = draw;
             // the reference has ONE _max_prio / _min_prio (prio.py:35): adopt the global extrema
             double gmax = 0.0;
@@ -1711,11 +1748,12 @@ extern "C" int32_t ts_per_normalize(double* weight, int64_t M, const double* wma
     return check_launch();
 }
 
-extern "C" int32_t ts_per_sample_p2p(const double* tree, int64_t bound, const double* u, int64_t M,
-                                     double* slots, double* const* peer_slots, uint64_t* state,
-                                     int32_t G, int32_t rank, double* prio, double beta,
-                                     int32_t weight_norm, int64_t* idx, double* weight,
-                                     int32_t* err_flag, ts_stream_t stream) {
+extern "C" int32_t ts_per_sample_p2p_owned(const double* tree, int64_t bound, const double* u,
+                                           int64_t M, double* slots, double* const* peer_slots,
+                                           uint64_t* state, int32_t G, int32_t rank, double* prio,
+                                           double beta, int32_t weight_norm, int64_t* idx,
+                                           double* weight, int32_t* owned, int32_t* err_flag,
+                                           ts_stream_t stream) {
     if (M < 0 || bound <= 0 || G < 1 || G > kMaxShards || (G & (G - 1)) != 0 || rank < 0 ||
         rank >= G)
         return TS_ERR_BAD_ARG;
@@ -1726,8 +1764,17 @@ extern "C" int32_t ts_per_sample_p2p(const double* tree, int64_t bound, const do
     if (!aligned(tree, 16) || !aligned(slots, 8)) return TS_ERR_ALIGN;
     return launch_per_cluster<true>(
         tree, bound, ilog2(bound), u, M, prio, beta, weight_norm, idx, weight, err_flag,
-        ShardInfo{nullptr, G, rank, nullptr, slots, peer_slots, (unsigned long long*)state},
+        ShardInfo{nullptr, G, rank, nullptr, slots, peer_slots, (unsigned long long*)state, owned},
         (cudaStream_t)stream);
+}
+
+extern "C" int32_t ts_per_sample_p2p(const double* tree, int64_t bound, const double* u, int64_t M,
+                                     double* slots, double* const* peer_slots, uint64_t* state,
+                                     int32_t G, int32_t rank, double* prio, double beta,
+                                     int32_t weight_norm, int64_t* idx, double* weight,
+                                     int32_t* err_flag, ts_stream_t stream) {
+    return ts_per_sample_p2p_owned(tree, bound, u, M, slots, peer_slots, state, G, rank, prio, beta,
+                                   weight_norm, idx, weight, nullptr, err_flag, stream);
 }
 
 extern "C" int32_t ts_per_publish(const double* tree, const double* prio, uint64_t* state,
@@ -1740,17 +1787,29 @@ extern "C" int32_t ts_per_publish(const double* tree, const double* prio, uint64
                           (cudaStream_t)stream);
 }
 
-extern "C" int32_t ts_per_update_publish(double* tree, int64_t size, int64_t bound,
-                                         const int64_t* idx, const void* td, int32_t td_dtype,
-                                         int64_t M, double alpha, double* prio, uint32_t* stamp,
-                                         uint32_t* counter, int32_t* err_flag, uint64_t* state,
-                                         double* const* peer_slots, int32_t G, int32_t rank,
-                                         ts_stream_t stream) {
+extern "C" int32_t ts_per_update_publish_owned(double* tree, int64_t size, int64_t bound,
+                                               const int64_t* idx, const void* td,
+                                               int32_t td_dtype, int64_t M, double alpha,
+                                               double* prio, uint32_t* stamp, uint32_t* counter,
+                                               int32_t* err_flag, uint64_t* state,
+                                               double* const* peer_slots, int32_t G, int32_t rank,
+                                               const int32_t* owned, ts_stream_t stream) {
     if (!td || !prio || !state || !peer_slots || G < 1 || G > kMaxShards || rank < 0 || rank >= G)
         return TS_ERR_BAD_ARG;
     if (td_dtype != TS_F32 && td_dtype != TS_F64) return TS_ERR_BAD_ARG;
     ValueSrc vs{td, 1, alpha, prio, td_dtype == TS_F64 ? VM_PER_F64 : VM_PER_F32};
     return update_impl(tree, size, bound, idx, vs, M, stamp, counter, err_flag,
                        (cudaStream_t)stream,
-                       PublishInfo{(unsigned long long*)state, peer_slots, G, rank});
+                       PublishInfo{(unsigned long long*)state, peer_slots, G, rank, owned});
+}
+
+extern "C" int32_t ts_per_update_publish(double* tree, int64_t size, int64_t bound,
+                                         const int64_t* idx, const void* td, int32_t td_dtype,
+                                         int64_t M, double alpha, double* prio, uint32_t* stamp,
+                                         uint32_t* counter, int32_t* err_flag, uint64_t* state,
+                                         double* const* peer_slots, int32_t G, int32_t rank,
+                                         ts_stream_t stream) {
+    return ts_per_update_publish_owned(tree, size, bound, idx, td, td_dtype, M, alpha, prio, stamp,
+                                       counter, err_flag, state, peer_slots, G, rank, nullptr,
+                                       stream);
 }

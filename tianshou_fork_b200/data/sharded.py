@@ -25,6 +25,10 @@ import torch.distributed as dist
 from .. import _lib as L
 from .prio import PrioritizedVectorReplayBuffer
 
+# the ranged update kernel takes 4096 batch entries per pass (csrc/segtree.cu: kRangeUnroll *
+# RANGE_NT); only larger batches gain from the sampler's owner list
+OWNED_LIST_MIN_BATCH = 4096
+
 
 def shard_layout(total_size: int, buffer_num: int, world_size: int, rank: int):
     """(sub-buffer size, sub-buffers per rank, leaves per rank, first global leaf of ``rank``)
@@ -102,6 +106,10 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
         self._symm = symm_mem.rendezvous(self._slots, grp)
         self._peer_ptrs = int(self._symm.buffer_ptrs_dev)
         self._p2p_state = torch.zeros(2, dtype=torch.int64, device=self.device)
+        # batch positions this rank owns, handed from the sampling kernel to the update of the
+        # same batch (int32[4 + capacity], see ts_per_sample_p2p_owned); grown on demand
+        self._owned: Optional[torch.Tensor] = None
+        self._owned_src: Optional[tuple] = None  # (index tensor handed out, its version)
         torch.cuda.synchronize(self.device)
         dist.barrier(group=self.group)
 
@@ -143,11 +151,20 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
         w = torch.empty(m, dtype=torch.float64, device=self.device)
         t = self.weight
         if self.exchange == "p2p":
-            L.check(L.lib().ts_per_sample_p2p(
+            # a batch the update kernel would scan in several passes: let the sampler list the
+            # positions this rank owns (~ m / world_size of them) for it
+            owned = 0
+            self._owned_src = None
+            if m > OWNED_LIST_MIN_BATCH:
+                if self._owned is None or self._owned.numel() < 4 + m:
+                    self._owned = torch.zeros(4 + m, dtype=torch.int32, device=self.device)
+                owned = L.ptr(self._owned)
+                self._owned_src = (idx, idx._version)
+            L.check(L.lib().ts_per_sample_p2p_owned(
                 L.ptr(t._value), t._bound, L.ptr(u), m, L.ptr(self._slots), self._peer_ptrs,
                 L.ptr(self._p2p_state), self.world_size, self.rank, L.ptr(self._prio),
-                float(self._beta), int(self._weight_norm), L.ptr(idx), L.ptr(w), L.ptr(t._err),
-                L.stream()), "ts_per_sample_p2p")
+                float(self._beta), int(self._weight_norm), L.ptr(idx), L.ptr(w), owned,
+                L.ptr(t._err), L.stream()), "ts_per_sample_p2p_owned")
             self._cached_weight = (idx, w)
             return idx
         L.check(L.lib().ts_per_sample_sharded(
@@ -177,10 +194,15 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
         assert td.numel() == idx.numel()
         self._cached_weight = None
         t = self.weight
+        # the sampler's owner list is valid only for the very tensor it filled, unmodified
+        src = self._owned_src
+        owned = L.ptr(self._owned) if (src is not None and index is src[0]
+                                       and index._version == src[1]
+                                       and idx.data_ptr() == index.data_ptr()) else 0
         # update + publish in one launch (the record must go out even for an empty batch)
-        L.check(L.lib().ts_per_update_publish(
+        L.check(L.lib().ts_per_update_publish_owned(
             L.ptr(t._value), t._size, t._bound, L.ptr(idx), L.ptr(td), L.dtype_code(td),
             idx.numel(), float(self._alpha), L.ptr(self._prio), L.ptr(t._stamp),
             L.ptr(t._counter), L.ptr(t._err), L.ptr(self._p2p_state), self._peer_ptrs,
-            self.world_size, self.rank, L.stream()), "ts_per_update_publish")
+            self.world_size, self.rank, owned, L.stream()), "ts_per_update_publish_owned")
         self._prio_f32 = td.dtype == torch.float32
