@@ -312,6 +312,12 @@ int32_t ts_per_update_publish_owned(double* tree, int64_t size, int64_t bound, c
                                     int32_t* err_flag, uint64_t* state,
                                     double* const* peer_slots, int32_t G, int32_t rank,
                                     const int32_t* owned, ts_stream_t stream);
+/* Measurement only (scripts/nvlink_pingpong.py): `iters` flag round trips between this GPU and rank
+ * `peer` through 4-double slots in peer-writable memory, with the primitives of the exchange above
+ * (mode 0: release flag / acquire poll; 1: a full shard record + system fence; 2: tight poll).
+ * out_ns[0] = nanoseconds for all round trips (0: timed out).  No reference counterpart. */
+int32_t ts_debug_pingpong(double* mine, double* const* peers, int32_t peer, int32_t iters,
+                          int32_t initiator, int32_t mode, uint64_t* out_ns, ts_stream_t stream);
 /* weight[j] /= *wmax  (prio.py:101) */
 int32_t ts_per_normalize(double* weight, int64_t M, const double* wmax, ts_stream_t stream);
 /* get_weight on given indices (prio.py:66-76), optional batch-max normalisation (:101);

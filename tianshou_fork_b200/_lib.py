@@ -66,6 +66,7 @@ SIGNATURES = {
                                            _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp]),
     "ts_per_sample_p2p_owned": (_i32, [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i32, _i32, _vp, _f64,
                                        _i32, _vp, _vp, _vp, _vp, _vp]),
+    "ts_debug_pingpong": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp]),
     "ts_per_normalize": (_i32, [_vp, _i64, _vp, _vp]),
     "ts_per_weight": (_i32, [_vp, _i64, _vp, _i64, _vp, _f64, _i32, _vp, _vp, _vp]),
     "ts_per_update": (_i32, [_vp, _i64, _i64, _vp, _vp, _i32, _i64, _f64, _vp, _vp, _vp, _vp,

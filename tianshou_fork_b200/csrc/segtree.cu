@@ -169,7 +169,8 @@ __device__ __forceinline__ void publish_record(const double* tree, const double*
         st_relaxed_sys_f64(dst, __ldcg(tree + 1));
         st_relaxed_sys_f64(dst + 1, __ldcg(prio));
         st_relaxed_sys_f64(dst + 2, __ldcg(prio + 1));
-        __threadfence_system();
+        // the release store orders this thread's three stores above before the flag: no separate
+        // system fence (it cost 1.9 us per hop, scripts/nvlink_pingpong.py)
         st_release_sys_u64(dst + 3, e);
     }
     __syncthreads();
@@ -566,7 +567,8 @@ __device__ __forceinline__ void publish_record_warp(const double* tree, const do
         st_relaxed_sys_f64(dst, __ldcg(tree + 1));
         st_relaxed_sys_f64(dst + 1, __ldcg(prio));
         st_relaxed_sys_f64(dst + 2, __ldcg(prio + 1));
-        __threadfence_system();
+        // the release store orders this thread's three stores above before the flag: no separate
+        // system fence (it cost 1.9 us per hop, scripts/nvlink_pingpong.py)
         st_release_sys_u64(dst + 3, e);
     }
     __syncwarp();
@@ -1442,8 +1444,7 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
             if (lead && tid < G) {
                 double* dst = sh.peer_slots[tid] + slot_wmax(G, draw, sh.rank);
                 st_relaxed_sys_f64(dst, wmax);
-                __threadfence_system();
-                st_release_sys_u64(dst + 1, draw);
+                st_release_sys_u64(dst + 1, draw);  // release: orders the store above, no fence
             }
             if (tid < G) {
                 const double* src = sh.slots + slot_wmax(G, draw, tid);
@@ -1775,6 +1776,55 @@ extern "C" int32_t ts_per_sample_p2p(const double* tree, int64_t bound, const do
                                      int32_t* err_flag, ts_stream_t stream) {
     return ts_per_sample_p2p_owned(tree, bound, u, M, slots, peer_slots, state, G, rank, prio, beta,
                                    weight_norm, idx, weight, nullptr, err_flag, stream);
+}
+
+// ---- measurement only: flag round trip between two GPUs over peer memory ------------------------
+namespace ts { namespace {
+// One thread per GPU.  Rank 0 sends i, waits for the echo; rank 1 waits for i, echoes it.  mode 0:
+// the exchange's own primitives (st.release.sys flag, ld.acquire.sys poll with the 64 ns back-off of
+// wait_epoch); mode 1: a full shard record as publish_record writes it (three relaxed stores, a
+// system fence, the release flag); mode 2: mode 0 with a tight poll; mode 3: the record WITHOUT the
+// fence (the release store alone orders this thread's earlier stores).
+__global__ void pingpong_kernel(double* mine, double* const* peers, int peer, int iters,
+                                int initiator, int mode, unsigned long long* out_ns) {
+    double* remote = peers[peer];
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    bool ok = true;
+    for (int i = 1; i <= iters && ok; ++i) {
+        const unsigned long long tag = (unsigned long long)i;
+        auto send = [&]() {
+            if (mode == 1 || mode == 3) {
+                st_relaxed_sys_f64(remote, (double)i);
+                st_relaxed_sys_f64(remote + 1, 1.0);
+                st_relaxed_sys_f64(remote + 2, 2.0);
+                if (mode == 1) __threadfence_system();
+            }
+            st_release_sys_u64(remote + 3, tag);
+        };
+        auto recv = [&]() {
+            if (mode == 2) {
+                int spin = 0;
+                while (ld_acquire_sys_u64(mine + 3) != tag)
+                    if (++spin > (1 << 26)) return false;
+                return true;
+            }
+            return wait_epoch(mine + 3, tag);
+        };
+        if (initiator) { send(); ok = recv(); } else { ok = recv(); if (ok) send(); }
+    }
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    out_ns[0] = ok ? t1 - t0 : 0ull;
+}
+} }  // namespace ts::
+
+extern "C" int32_t ts_debug_pingpong(double* mine, double* const* peers, int32_t peer,
+                                     int32_t iters, int32_t initiator, int32_t mode,
+                                     uint64_t* out_ns, ts_stream_t stream) {
+    if (!mine || !peers || !out_ns || iters < 1 || mode < 0 || mode > 3) return TS_ERR_BAD_ARG;
+    pingpong_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(mine, peers, peer, iters, initiator, mode,
+                                                       (unsigned long long*)out_ns);
+    return check_launch();
 }
 
 extern "C" int32_t ts_per_publish(const double* tree, const double* prio, uint64_t* state,
