@@ -272,7 +272,7 @@ int32_t ts_per_sample_sharded(const double* tree, int64_t bound, const double* u
                               double* wmax_out, int32_t* err_flag, ts_stream_t stream);
 /* The same step with the exchange INSIDE the kernels, over NVLink peer memory (no collective
  * library call, CUDA-graph capturable).  Every rank owns `slots`, a zero-initialised buffer of
- * 12 * G doubles that all peers can write (symmetric memory / cudaIpc); `peer_slots` is a DEVICE
+ * 16 * G doubles that all peers can write (symmetric memory / cudaIpc); `peer_slots` is a DEVICE
  * array of the G ranks' buffer addresses as mapped in this process; `state` is uint64[2] on the
  * device, zero-initialised: {records published, samples drawn}.
  *   ts_per_publish    after every tree change (fill, add, update_weight): stores this rank's

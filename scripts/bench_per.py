@@ -187,7 +187,7 @@ def run_sharded(torch, dist, L, lib, dev, rank, world, barrier, max_over_ranks):
     import torch.distributed._symmetric_memory as symm_mem
     sh = Shard(torch, L, lib, dev, rank)
     size = bound = PER_LEAVES
-    slots = symm_mem.empty(12 * world, dtype=torch.float64, device=dev)
+    slots = symm_mem.empty(16 * world, dtype=torch.float64, device=dev)
     slots.zero_()
     hdl = symm_mem.rendezvous(slots, dist.group.WORLD)
     peers = int(hdl.buffer_ptrs_dev)

@@ -170,7 +170,7 @@ def test_p2p_protocol_emulated_on_one_gpu(G, cap, bsz):
                  counter=torch.zeros(4, dtype=torch.int32, device="cuda"),
                  err=torch.zeros(1, dtype=torch.int32, device="cuda"),
                  prio=torch.ones(2, dtype=torch.float64, device="cuda"),
-                 slots=torch.zeros(12 * G, dtype=torch.float64, device="cuda"),
+                 slots=torch.zeros(16 * G, dtype=torch.float64, device="cuda"),
                  state=torch.zeros(2, dtype=torch.int64, device="cuda"))
         _fill(d["tree"], d["stamp"], d["counter"], d["err"], leaves[r * cap:(r + 1) * cap], L)
         ranks.append(d)
@@ -243,7 +243,7 @@ def test_p2p_owned_list_emulated_on_one_gpu(G, cap, bsz):
                  counter=torch.zeros(4, dtype=torch.int32, device="cuda"),
                  err=torch.zeros(1, dtype=torch.int32, device="cuda"),
                  prio=torch.ones(2, dtype=torch.float64, device="cuda"),
-                 slots=torch.zeros(12 * G, dtype=torch.float64, device="cuda"),
+                 slots=torch.zeros(16 * G, dtype=torch.float64, device="cuda"),
                  state=torch.zeros(2, dtype=torch.int64, device="cuda"),
                  owned=torch.zeros(4 + bsz, dtype=torch.int32, device="cuda"))
         _fill(d["tree"], d["stamp"], d["counter"], d["err"], leaves[r * cap:(r + 1) * cap], L)

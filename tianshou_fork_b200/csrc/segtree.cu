@@ -115,12 +115,19 @@ __device__ __forceinline__ double dsmem_ld_f64(const double* local, uint32_t ran
 
 // ---- sharded PER: peer-memory exchange helpers --------------------------------------------
 constexpr int kMaxShards = 64;
-// slot buffer: records [2][G][4] = {root, max, min, epoch bits}; maxima [2][G][2] = {wmax, epoch}
+// Slot buffer, 16 * G 64-bit words: records [2][G][6] (root, max, min as three doubles), weight
+// maxima [2][G][2] (one double), both indexed by the parity of their sequence number.  Every
+// 64-bit word is SELF-VALIDATING: low half = 32 bits of payload, high half = the low 32 bits of
+// the sequence number it belongs to (the "LL" scheme of NCCL: an aligned 8-byte store arrives
+// whole).  A record therefore needs no flag behind it and no ordering between its stores: one
+// NVLink hop instead of payload -> release -> flag (6.7 us vs 5.0 us per round trip,
+// scripts/nvlink_pingpong.py).  Zero-initialised words carry sequence 0; sequences start at 1
+// and a parity slot is reused two sequence numbers later, so a stale word never matches.
 __host__ __device__ inline int slot_record(int G, unsigned long long e, int r) {
-    return ((int)(e & 1ull) * G + r) * 4;
+    return ((int)(e & 1ull) * G + r) * 6;
 }
 __host__ __device__ inline int slot_wmax(int G, unsigned long long e, int r) {
-    return 8 * G + ((int)(e & 1ull) * G + r) * 2;
+    return 12 * G + ((int)(e & 1ull) * G + r) * 2;
 }
 constexpr int kPeerSpin = 1 << 22;  // bounded wait (~ seconds), then TS_FLAG_PEER_TIMEOUT
 
@@ -140,7 +147,33 @@ __device__ __forceinline__ double ld_relaxed_sys_f64(const double* p) {
 __device__ __forceinline__ void st_relaxed_sys_f64(double* p, double v) {
     asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
 }
-// spin until the epoch word at `flag` equals `want`; false on timeout
+// one double as two self-validating words at dst[0..1], tagged with sequence number `seq`
+__device__ __forceinline__ void ll_store_f64(double* dst, double v, unsigned long long seq) {
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+    const unsigned long long tag = (seq & 0xffffffffull) << 32;
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(tag | (bits & 0xffffffffull))
+                 : "memory");
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(dst + 1), "l"(tag | (bits >> 32))
+                 : "memory");
+}
+// spin until both words at src[0..1] carry sequence number `seq`; false on timeout
+__device__ __forceinline__ bool ll_load_f64(const double* src, unsigned long long seq, double& v) {
+    const unsigned long long want = seq & 0xffffffffull;
+    unsigned long long w[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        int it = 0;
+        for (;;) {
+            asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w[h]) : "l"(src + h) : "memory");
+            if ((w[h] >> 32) == want) break;
+            if (++it >= kPeerSpin) return false;
+            __nanosleep(64);
+        }
+    }
+    v = __longlong_as_double((long long)((w[0] & 0xffffffffull) | (w[1] << 32)));
+    return true;
+}
+// spin until the epoch word at `flag` equals `want`; false on timeout (ts_debug_pingpong only)
 __device__ __forceinline__ bool wait_epoch(const double* flag, unsigned long long want) {
     for (int it = 0; it < kPeerSpin; ++it) {
         if (ld_acquire_sys_u64(flag) == want) return true;
@@ -166,12 +199,9 @@ __device__ __forceinline__ void publish_record(const double* tree, const double*
     const unsigned long long e = __ldcg(pub.state) + 1;
     if (tid < pub.G) {
         double* dst = pub.peer_slots[tid] + slot_record(pub.G, e, pub.rank);
-        st_relaxed_sys_f64(dst, __ldcg(tree + 1));
-        st_relaxed_sys_f64(dst + 1, __ldcg(prio));
-        st_relaxed_sys_f64(dst + 2, __ldcg(prio + 1));
-        // the release store orders this thread's three stores above before the flag: no separate
-        // system fence (it cost 1.9 us per hop, scripts/nvlink_pingpong.py)
-        st_release_sys_u64(dst + 3, e);
+        ll_store_f64(dst, __ldcg(tree + 1), e);
+        ll_store_f64(dst + 2, __ldcg(prio), e);
+        ll_store_f64(dst + 4, __ldcg(prio + 1), e);
     }
     __syncthreads();
     if (tid == 0) pub.state[0] = e;
@@ -564,12 +594,9 @@ __device__ __forceinline__ void publish_record_warp(const double* tree, const do
     const unsigned long long e = __ldcg(pub.state) + 1;
     for (int t = lane; t < pub.G; t += 32) {
         double* dst = pub.peer_slots[t] + slot_record(pub.G, e, pub.rank);
-        st_relaxed_sys_f64(dst, __ldcg(tree + 1));
-        st_relaxed_sys_f64(dst + 1, __ldcg(prio));
-        st_relaxed_sys_f64(dst + 2, __ldcg(prio + 1));
-        // the release store orders this thread's three stores above before the flag: no separate
-        // system fence (it cost 1.9 us per hop, scripts/nvlink_pingpong.py)
-        st_release_sys_u64(dst + 3, e);
+        ll_store_f64(dst, __ldcg(tree + 1), e);
+        ll_store_f64(dst + 2, __ldcg(prio), e);
+        ll_store_f64(dst + 4, __ldcg(prio + 1), e);
     }
     __syncwarp();
     if (lane == 0) pub.state[0] = e;
@@ -1264,7 +1291,7 @@ struct ShardInfo {
     const double* roots3;  // NCCL mode: G x {root, max_prio, min_prio}; nullptr otherwise
     int G, rank;
     double* wmax_out;      // NCCL mode
-    double* slots;                       // P2P mode: this rank's slot buffer, 12 * G doubles
+    double* slots;                       // P2P mode: this rank's slot buffer, 16 * G doubles
     double* const* peer_slots;           // P2P mode: device array of the G ranks' slot buffers
     unsigned long long* state;           // P2P mode: {records published, samples drawn} by this rank
     int32_t* owned = nullptr;            // P2P mode, optional: see PublishInfo::owned
@@ -1302,10 +1329,13 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
         if (tid < G) {
             if (p2p) {
                 const double* rec = sh.slots + slot_record(G, epoch, tid);
-                if (!wait_epoch(rec + 3, epoch)) atomicOr(err_flag, TS_FLAG_PEER_TIMEOUT);
-                s_gtop[G + tid] = ld_relaxed_sys_f64(rec);
-                s_gext[tid] = ld_relaxed_sys_f64(rec + 1);
-                s_gext[G + tid] = ld_relaxed_sys_f64(rec + 2);
+                double r0 = 0.0, r1 = 0.0, r2 = 0.0;
+                if (!(ll_load_f64(rec, epoch, r0) && ll_load_f64(rec + 2, epoch, r1) &&
+                      ll_load_f64(rec + 4, epoch, r2)))
+                    atomicOr(err_flag, TS_FLAG_PEER_TIMEOUT);
+                s_gtop[G + tid] = r0;
+                s_gext[tid] = r1;
+                s_gext[G + tid] = r2;
             } else {
                 s_gtop[G + tid] = __ldcg(sh.roots3 + 3 * tid);
                 s_gext[tid] = __ldcg(sh.roots3 + 3 * tid + 1);
@@ -1442,14 +1472,13 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
         if (weight_norm) {
             // maximum over ALL ranks: store ours into every peer's buffer, wait for theirs
             if (lead && tid < G) {
-                double* dst = sh.peer_slots[tid] + slot_wmax(G, draw, sh.rank);
-                st_relaxed_sys_f64(dst, wmax);
-                st_release_sys_u64(dst + 1, draw);  // release: orders the store above, no fence
+                ll_store_f64(sh.peer_slots[tid] + slot_wmax(G, draw, sh.rank), wmax, draw);
             }
             if (tid < G) {
-                const double* src = sh.slots + slot_wmax(G, draw, tid);
-                if (!wait_epoch(src + 1, draw)) atomicOr(err_flag, TS_FLAG_PEER_TIMEOUT);
-                s_gtop[tid] = ld_relaxed_sys_f64(src);
+                double m = 0.0;
+                if (!ll_load_f64(sh.slots + slot_wmax(G, draw, tid), draw, m))
+                    atomicOr(err_flag, TS_FLAG_PEER_TIMEOUT);
+                s_gtop[tid] = m;
             }
             __syncthreads();
             wmax = 0.0;

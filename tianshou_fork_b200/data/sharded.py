@@ -100,7 +100,7 @@ class ShardedPrioritizedVectorReplayBuffer(PrioritizedVectorReplayBuffer):
         exchanged through the process group's store), zeroed before anyone publishes."""
         import torch.distributed._symmetric_memory as symm_mem
         grp = self.group if self.group is not None else dist.group.WORLD
-        self._slots = symm_mem.empty(12 * self.world_size, dtype=torch.float64,
+        self._slots = symm_mem.empty(16 * self.world_size, dtype=torch.float64,
                                      device=self.device)
         self._slots.zero_()
         self._symm = symm_mem.rendezvous(self._slots, grp)
