@@ -342,7 +342,9 @@ struct RowsTmaLayout {
 };
 
 template <typename RewT, typename InT, typename OutT, int NT>
-__global__ void __launch_bounds__(NT)
+// (768 / NT: ptxas allots the same 80 registers with or without the second argument, but
+// schedules better with it -- 16384 x 2048 rows: 120 vs 128 us on one box, profiles/r02_gae.md)
+__global__ void __launch_bounds__(NT, 768 / NT)
 gae_rows_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
                     const InT* __restrict__ v_next, const uint8_t* __restrict__ term,
                     const uint8_t* __restrict__ trunc, int E, int64_t T, int64_t buf_stride,
