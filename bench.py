@@ -45,7 +45,7 @@ GAMMA, LAMBDA = 0.99, 0.95
 ALG_BYTES_PER_TRANSITION = 21  # rew 4 + v_s 4 + v_s_ 4 + end flag 1 + adv 4 + ret 4
 MOVED_BYTES_PER_TRANSITION = 22  # terminated and truncated are two separate bytes
 E2E_CHUNKS = int(os.environ.get("TS_E2E_CHUNKS", "2"))
-NCU_DRAM_BYTES_PER_LAUNCH = 145744384  # profiles/r02_gae_ncu.md: 117.46 MB read + 28.28 MB write
+NCU_DRAM_BYTES_PER_LAUNCH = 145051904  # profiles/r02_gae_ncu.md: 117.49 MB read + 27.57 MB write
 PER_LEAVES, PER_BATCH, PER_ALPHA, PER_BETA = 1 << 20, 4096, 0.6, 0.4
 PER_ALG_BYTES_PER_SAMPLE = 664
 
@@ -427,7 +427,7 @@ def run_b200(args):
                 "frac": achieved / peak, "traffic": NCU_DRAM_BYTES_PER_LAUNCH if (E, T) == (
                     E_PER_GPU, T_STEPS) else None,
                 "traffic_source": "ncu --set full, profiles/r02_gae_ncu.md (r02_gae_top): dram read "
-                                  "117.46 MB + write 28.28 MB; the rest of the 67.1 MB output is "
+                                  "117.49 MB + write 27.57 MB; the rest of the 67.1 MB output is "
                                   "still dirty in L2 at kernel end",
                 "peak_source": peak_src,
                 "kernel": "gae_rows_tma_kernel<float,float,float,256> (persistent, cp.async.bulk pipelined, 3 stages x 2 CTAs/SM)",
