@@ -1148,7 +1148,8 @@ int32_t launch_rows(const void* rew, const void* v_s, const void* v_next, const 
     // Short rows stored back to back (T < one 2048-step tile): the row-per-tile kernel would run
     // its tiles mostly empty (T = 512: a quarter full).  The whole [E, T] block is instead walked
     // as ONE sequence of E * T steps by the pipelined-ranges kernel, with a cut at every row end;
-    // a row end always lies within its 2304-step read-ahead, so it needs no workspace.
+    // a row end always lies inside a CTA's 2048-step ghost tile, so the carry into its range is
+    // always exact and it needs no workspace (no neighbour flags).
     if (variant == 0 && g_tune_gae_rows_packed && bs == T && vs == T && T >= VEC && T < 2048 &&
         E * T >= (1 << 20) && vec_ok && aligned(term, 16) && aligned(trunc, 16) &&
         E * T < (1LL << 40)) {
@@ -1236,7 +1237,7 @@ int32_t launch_flat(const void* rew, const void* v_s, const void* v_next, const 
     const bool tma_ok = vec_ok && aligned(term, 16) && aligned(trunc, 16) &&
                         (indices == nullptr || aligned(indices, 16)) && N < (1LL << 40);
     int variant = g_tune_gae_flat_variant;  // 0 auto, 1 decoupled look-back, 2 pipelined ranges
-    // short sequences have too few tiles per CTA to amortise the read-ahead: look-back kernel
+    // short sequences have too few tiles per CTA to amortise the ghost tile: look-back kernel
     if (variant == 0) variant = N >= (1 << 20) ? 2 : 1;
     if (variant == 2 && tma_ok) {
         const FlatGather g{indices, buf_term, unfinished, offset, B, sub_size, 0};
