@@ -301,3 +301,58 @@ def test_p2p_owned_list_emulated_on_one_gpu(G, cap, bsz):
         for r, d in enumerate(ranks):
             L.check(lib.ts_per_publish(L.ptr(d["tree"]), L.ptr(d["prio"]), L.ptr(d["state"]),
                                        L.ptr(peers), G, r, L.stream()), "publish")
+
+
+@pytest.mark.parametrize("G,cap,bsz", [(2, 1 << 13, 700), (4, 1 << 14, 4096)])
+def test_p2p_weight_maximum_exchange_on_concurrent_streams(G, cap, bsz):
+    """The MUTUAL half of the in-kernel exchange (every rank stores its weight maximum into every
+    peer's slot buffer and waits for theirs) on one GPU: the G ranks' sampling kernels run
+    CONCURRENTLY on G streams (G clusters of 16 CTAs are co-resident on a B200), so each one's
+    bounded wait is answered by the others.  Normalised weights must equal the oracle's
+    w / max(w) over the whole batch (prio.py:101); a peer timeout would raise the error flag."""
+    from tianshou_fork_b200 import _lib as L
+    lib = L.lib()
+    rng = np.random.default_rng(G * 13 + 2)
+    total = G * cap
+    leaves = (np.abs(rng.standard_normal(total)) + 1e-7) ** 0.6
+    glob = orc.PER(total, 0.6, 0.4)
+    glob.weight[np.arange(total)] = leaves
+    ranks = []
+    for r in range(G):
+        d = dict(tree=torch.zeros(2 * cap, dtype=torch.float64, device="cuda"),
+                 stamp=torch.zeros(cap, dtype=torch.int32, device="cuda"),
+                 counter=torch.zeros(4, dtype=torch.int32, device="cuda"),
+                 err=torch.zeros(1, dtype=torch.int32, device="cuda"),
+                 prio=torch.ones(2, dtype=torch.float64, device="cuda"),
+                 slots=torch.zeros(16 * G, dtype=torch.float64, device="cuda"),
+                 state=torch.zeros(2, dtype=torch.int64, device="cuda"),
+                 idx=torch.empty(bsz, dtype=torch.int64, device="cuda"),
+                 w=torch.empty(bsz, dtype=torch.float64, device="cuda"),
+                 stream=torch.cuda.Stream())
+        _fill(d["tree"], d["stamp"], d["counter"], d["err"], leaves[r * cap:(r + 1) * cap], L)
+        ranks.append(d)
+    peers = torch.tensor([d["slots"].data_ptr() for d in ranks], dtype=torch.int64, device="cuda")
+    for r, d in enumerate(ranks):
+        L.check(lib.ts_per_publish(L.ptr(d["tree"]), L.ptr(d["prio"]), L.ptr(d["state"]),
+                                   L.ptr(peers), G, r, L.stream()), "publish")
+    torch.cuda.synchronize()
+    for step in range(3):
+        u = rng.random(bsz)
+        want = glob.sample_indices(u)
+        want_w = glob.batch_weight(want)
+        ud = torch.from_numpy(u).cuda()
+        torch.cuda.synchronize()
+        for r, d in enumerate(ranks):  # no dependencies between the streams: the kernels overlap
+            L.check(lib.ts_per_sample_p2p(
+                L.ptr(d["tree"]), cap, L.ptr(ud), bsz, L.ptr(d["slots"]), L.ptr(peers),
+                L.ptr(d["state"]), G, r, L.ptr(d["prio"]), 0.4, 1, L.ptr(d["idx"]), L.ptr(d["w"]),
+                L.ptr(d["err"]), d["stream"].cuda_stream), "sample_p2p")
+        torch.cuda.synchronize()
+        for r, d in enumerate(ranks):
+            assert int(d["err"].item()) == 0, (r, step, "peer timeout or range flag")
+        got = sum(torch.where(d["idx"] >= 0, d["idx"] + r * cap, torch.zeros_like(d["idx"]))
+                  for r, d in enumerate(ranks)).cpu().numpy()
+        assert np.array_equal(got, want), (G, step)
+        got_w = sum(d["w"] for d in ranks).cpu().numpy()  # non-owners hold 0
+        assert np.allclose(got_w, want_w, rtol=1e-12, atol=0), (G, step)
+        assert float(got_w.max()) == 1.0
