@@ -1298,7 +1298,7 @@ struct ShardInfo {
 };
 // SHARD: 0 = one GPU (no exchange code in the instantiation at all), 1 = NCCL mode, 2 = P2P mode
 template <bool SAMPLE, int NT, int SHARD>
-__global__ void __launch_bounds__(NT)
+__global__ void __launch_bounds__(NT, 1)
 per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg_bound,
                           const double* __restrict__ u, int64_t M,
                           const double* __restrict__ prio, double beta, int weight_norm,
@@ -1404,8 +1404,12 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
                 reinterpret_cast<unsigned int*>(sh.owned)[(draw & 1ull) ^ 1ull] = 0u;
         }
         __syncthreads();
+        double u_next = u_first;
         for (int64_t j = j0; j < M; j += sweep) {
-            double v = __dmul_rn(j == j0 ? u_first : u[j], total);  // prio.py:61
+            const double uj = u_next;
+            // the next sweep's draw is fetched under this one's routing (weak scaling: G sweeps)
+            if (j + sweep < M) u_next = __ldg(u + j + sweep);
+            double v = __dmul_rn(uj, total);  // prio.py:61
             if (!(v >= 0.0 && v < total)) atomicOr(err_flag, TS_FLAG_PREFIX_RANGE);
             int node = 1;
             while (node < G) {                                   // the global tree's top levels
@@ -1497,9 +1501,21 @@ per_weight_cluster_kernel(const double* __restrict__ tree, int64_t bound, int lg
             const_cast<double*>(prio)[1] = min_prio;
         }
     }
-    for (int64_t j = j0; j < M; j += sweep) {
-        const double w = (!compact && j == j0) ? w_first : weight[j];
-        weight[j] = scale ? __ddiv_rn(w, wmax) : w;              // prio.py:101
+    if (compact && s_nlist <= (unsigned)kOwnedList) {
+        // only the owned positions carry a weight (the others were written as 0 while routing):
+        // normalise those from the CTA's list instead of sweeping the whole batch again
+        if (scale) {
+            const unsigned int n = s_nlist;
+            for (unsigned int i = tid; i < n; i += NT) {
+                const int64_t j = (int64_t)s_list[i].x;
+                weight[j] = __ddiv_rn(weight[j], wmax);          // prio.py:101
+            }
+        }
+    } else {
+        for (int64_t j = j0; j < M; j += sweep) {
+            const double w = (!compact && j == j0) ? w_first : weight[j];
+            weight[j] = scale ? __ddiv_rn(w, wmax) : w;          // prio.py:101
+        }
     }
     if (weight_norm) cluster_wait();  // second half of cluster_max's closing barrier
 }
