@@ -12,6 +12,7 @@
 
 #include <c10/cuda/CUDAGuard.h>
 #include <c10/cuda/CUDAStream.h>
+#include <cuda_runtime.h>
 
 #include "../../include/ts_b200.h"
 
@@ -134,9 +135,62 @@ std::vector<at::Tensor> ppo_loss(const at::Tensor& logp, const at::Tensor& value
                             value_clip, norm_adv, eps);
 }
 
+// ---- prioritized replay step with HOST arrays (prio.py:59-64, 78-102) ----------------------------
+// The learner of the reference holds indices, importance weights and td-errors as NumPy arrays.
+// These two calls are the copies and the launch of data/prio.py's host path issued from C++
+// (one call instead of ~8 torch calls): pinned staging in, pinned staging out.
+inline void cuda_ok(cudaError_t e, const char* what) {
+    TORCH_CHECK(e == cudaSuccess, what, ": ", cudaGetErrorString(e));
+}
+
+// stage_u: pinned f64[m] holding the np.random.rand draws; dev_u f64[m]; dev_out / host_out:
+// i64[2m] (device / pinned) = indices | importance weights (f64 bits).  Returns when host_out is valid.
+void per_sample_host(const at::Tensor& heap, int64_t bound, const at::Tensor& prio,
+                     const at::Tensor& err, const at::Tensor& stage_u, const at::Tensor& dev_u,
+                     const at::Tensor& dev_out, const at::Tensor& host_out, int64_t m, double beta,
+                     bool weight_norm) {
+    TORCH_CHECK(stage_u.is_pinned() && host_out.is_pinned(), "staging buffers must be pinned");
+    TORCH_CHECK(dev_u.numel() >= m && dev_out.numel() >= 2 * m && host_out.numel() >= 2 * m);
+    c10::cuda::CUDAGuard guard(heap.device());
+    cudaStream_t st = c10::cuda::getCurrentCUDAStream(heap.get_device()).stream();
+    cuda_ok(cudaMemcpyAsync(dev_u.data_ptr(), stage_u.data_ptr(), 8 * (size_t)m,
+                            cudaMemcpyHostToDevice, st), "upload of the draws");
+    int64_t* out = dev_out.data_ptr<int64_t>();
+    check(ts_per_sample_lazy(heap.data_ptr<double>(), bound, dev_u.data_ptr<double>(), m,
+                             prio.data_ptr<double>(), beta, weight_norm ? 1 : 0, out,
+                             reinterpret_cast<double*>(out + m), err.data_ptr<int32_t>(), (void*)st),
+          "ts_per_sample_lazy");
+    cuda_ok(cudaMemcpyAsync(host_out.data_ptr(), out, 16 * (size_t)m, cudaMemcpyDeviceToHost, st),
+            "download of indices and weights");
+    pybind11::gil_scoped_release nogil;
+    cuda_ok(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+}
+
+// stage: pinned bytes = idx (i64[m]) | td (f32[m] or f64[m]); dev_buf: device bytes of the same size
+void per_update_host(const at::Tensor& heap, int64_t size, int64_t bound, const at::Tensor& prio,
+                     const at::Tensor& stamp, const at::Tensor& counter, const at::Tensor& err,
+                     const at::Tensor& stage, const at::Tensor& dev_buf, int64_t m, bool td_f32,
+                     double alpha) {
+    const size_t nb = (size_t)m * (8 + (td_f32 ? 4 : 8));
+    TORCH_CHECK(stage.is_pinned() && (size_t)stage.numel() >= nb && (size_t)dev_buf.numel() >= nb);
+    c10::cuda::CUDAGuard guard(heap.device());
+    cudaStream_t st = c10::cuda::getCurrentCUDAStream(heap.get_device()).stream();
+    uint8_t* d = static_cast<uint8_t*>(dev_buf.data_ptr());
+    cuda_ok(cudaMemcpyAsync(d, stage.data_ptr(), nb, cudaMemcpyHostToDevice, st),
+            "upload of indices and td-errors");
+    check(ts_per_update_lazy(heap.data_ptr<double>(), size, bound, reinterpret_cast<int64_t*>(d),
+                             d + 8 * (size_t)m, td_f32 ? TS_F32 : TS_F64, m, alpha,
+                             prio.data_ptr<double>(), reinterpret_cast<uint32_t*>(stamp.data_ptr()),
+                             reinterpret_cast<uint32_t*>(counter.data_ptr()),
+                             err.data_ptr<int32_t>(), (void*)st),
+          "ts_per_update_lazy");
+}
+
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+    m.def("per_sample_host", &per_sample_host, "draws up, ts_per_sample_lazy, indices + weights down");
+    m.def("per_update_host", &per_update_host, "indices + td up, ts_per_update_lazy");
     m.def("neighbour", &neighbour, "ts_prev_index / ts_next_index");
     m.def("nstep_chain", &nstep_chain, "ts_nstep_chain");
     m.def("nstep_combine", &nstep_combine, "ts_nstep_combine");

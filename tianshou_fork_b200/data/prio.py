@@ -145,8 +145,17 @@ class PrioritizedReplayBuffer(ReplayBuffer):
             dev.update(m=m, u=torch.empty(m, dtype=torch.float64, device=self.device),
                        out=torch.empty(2 * m, dtype=torch.int64, device=self.device))
         u, out = dev["u"], dev["out"]
-        u.copy_(stage, non_blocking=True)
         t = self.weight
+        sh = L.shim()
+        if sh is not None:  # the same copies and launch issued from C++ (csrc/shim.cpp)
+            host = self._pinned("out", 16 * m)[: 16 * m].view(torch.int64)
+            sh.per_sample_host(t._heap, t._bound, self._prio, t._err, stage, u, out, host, m,
+                               float(self._beta), bool(self._weight_norm))
+            t._top_stale = False
+            self._cached_weight = None
+            h = host.numpy()
+            return h[:m].copy(), h[m:].view(np.float64).copy()
+        u.copy_(stage, non_blocking=True)
         idx, w = out[:m], out[m:].view(torch.float64)
         L.check(L.lib().ts_per_sample_lazy(
             t._heap.data_ptr(), t._bound, u.data_ptr(), m, self._prio.data_ptr(),
@@ -159,6 +168,42 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         torch.cuda.current_stream(self.device).synchronize()
         h = host.numpy()
         return h[:m].copy(), h[m:].view(np.float64).copy()
+
+    def _update_host_shim(self, index: np.ndarray, new_weight: np.ndarray) -> bool:
+        """``update_weight`` on host arrays through csrc/shim.cpp: pack into the pinned staging
+        buffer, then ONE C++ call (upload + ts_per_update_lazy).  False: shim absent."""
+        sh = L.shim()
+        if sh is None:
+            return False
+        idx = np.ascontiguousarray(index, dtype=np.int64).reshape(-1)
+        td = np.ascontiguousarray(new_weight).reshape(-1)
+        if td.dtype not in (np.float32, np.float64):
+            td = td.astype(np.float64)
+        m = idx.size
+        assert td.size == m
+        f32 = td.dtype == np.float32
+        nb = 8 * m + td.itemsize * m
+        stage = self._pinned("upd", nb)
+        stage[: 8 * m].view(torch.int64).numpy()[:] = idx
+        stage[8 * m: nb].view(torch.float32 if f32 else torch.float64).numpy()[:] = td
+        dev = self.__dict__.setdefault("_host_io_upd", {})
+        key = ("upd_dev", nb)
+        buf = dev.get(key)
+        if buf is None:
+            dev.clear()
+            buf = dev[key] = torch.empty(nb, dtype=torch.uint8, device=self.device)
+        t = self.weight
+        heap = t._value  # (a top left stale by a graph replay is finished before it is built on)
+        sh.per_update_host(heap, t._size, t._bound, self._prio, t._stamp, t._counter, t._err,
+                           stage, buf, m, f32, float(self._alpha))
+        ev = self.__dict__.get("_upd_ev")
+        if ev is None:
+            ev = self.__dict__["_upd_ev"] = torch.cuda.Event()
+        ev.record()  # the staging buffer may be rewritten once this copy has run
+        self._cached_weight = None
+        t._top_stale = True
+        self._prio_f32 = f32
+        return True
 
     def _upload_update(self, index: np.ndarray, new_weight: np.ndarray):
         """Host indices + host td-errors -> device, as one pinned buffer and one copy."""
@@ -214,6 +259,8 @@ class PrioritizedReplayBuffer(ReplayBuffer):
             ev = self.__dict__.get("_upd_ev")
             if ev is not None:
                 ev.synchronize()  # the previous call's copy has left the staging buffer
+            if self._update_host_shim(index, new_weight):
+                return
             idx, td, _ = self._upload_update(index, new_weight)
         else:
             idx = self.weight._dev_index(index)
