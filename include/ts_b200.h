@@ -276,7 +276,9 @@ int32_t ts_per_sample_sharded(const double* tree, int64_t bound, const double* u
  * array of the G ranks' buffer addresses as mapped in this process; `state` is uint64[2] on the
  * device, zero-initialised: {records published, samples drawn}.
  *   ts_per_publish    after every tree change (fill, add, update_weight): stores this rank's
- *                     {root, max_prio, min_prio, epoch} into every peer's buffer.
+ *                     {root, max_prio, min_prio} into every peer's buffer as six self-validating
+ *                     64-bit words (32 bits of payload + the low 32 bits of the epoch each: no
+ *                     flag word and no ordering between the stores, one NVLink hop).
  *   ts_per_sample_p2p waits (bounded; TS_FLAG_PEER_TIMEOUT) for the G records of the current
  *                     epoch, routes and descends as ts_per_sample_sharded, exchanges the weight
  *                     maximum the same way and writes NORMALISED weights; adopts the global

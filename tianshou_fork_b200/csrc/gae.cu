@@ -636,7 +636,6 @@ gae_flat_tma_kernel(const RewT* __restrict__ rew, const InT* __restrict__ v_s,
     // ---- CTA 0: the ragged end [N16, N), at most 15 steps, one per lane, outputs included ------
     if (tid == 0) s_carry[1] = 0.0;  // slot of the tile "before" the first one
     const bool working = ntiles > 0 || blockIdx.x == 0;
-    const int64_t p_ahead = k_hi * TILE;
     pdl_launch_dependents();
     // sync[1] = calls completed on this workspace, sync[2] = CTAs of this call that are done.
     // Head flags carry the call's tag, so nothing has to be cleared between calls (and CUDA-graph

@@ -139,11 +139,6 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const void* p) 
 __device__ __forceinline__ void st_release_sys_u64(void* p, unsigned long long v) {
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ double ld_relaxed_sys_f64(const double* p) {
-    double v;
-    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
-    return v;
-}
 __device__ __forceinline__ void st_relaxed_sys_f64(double* p, double v) {
     asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
 }
@@ -1027,7 +1022,7 @@ int32_t update_impl(double* tree, int64_t size, int64_t bound, const int64_t* in
     if (M <= kSmallM && bound > kDenseBound) {
         const int lg = ilog2(bound);
         // level handed to the top phase: strip LG levels per tier until <= kTopMax nodes
-        const int K = g_tune_segtree_group == 256 ? 8 : 4, LG = K == 8 ? 8 : 7;
+        const int K = g_tune_segtree_group == 256 ? 8 : 4;
         auto kern = K == 8 ? segtree_update_tiered<8> : segtree_update_tiered<4>;
         int64_t ctas = (M * 32 + TIER_NT - 1) / TIER_NT;  // one warp per item
         if (ctas > g_tune_segtree_max_ctas) ctas = g_tune_segtree_max_ctas;  // co-resident
